@@ -1,0 +1,150 @@
+// extern "C" surface of libb200_kv.so — argument checking, split-K planning and dispatch to the kernels.
+// See include/b200_kv.h for the contract of every entry point.
+#include <algorithm>
+
+#include "b200_attn.cuh"
+#include "b200_common.cuh"
+
+namespace b200 {
+
+char* last_error_buf() {
+  static thread_local char buf[kErrBufLen] = {0};
+  return buf;
+}
+
+namespace {
+
+inline int ceil_div(int a, int b) { return (a + b - 1) / b; }
+
+// How many partitions of the context each (sequence, kv head) pair gets.  The pairs alone rarely fill the
+// machine evenly (B*Hkv CTAs against 148 SMs x resident CTAs), so the context is cut until there are several
+// waves of CTAs, while keeping every partition at least `min_blocks` KV blocks long so the per-CTA pipeline
+// ramp stays amortised.
+int plan_splits(int B, int Hkv, int block_size, int max_context_len) {
+  const int n_blocks = std::max(1, ceil_div(std::max(1, max_context_len), block_size));
+  const int pairs = std::max(1, B * Hkv);
+  const int min_blocks = std::max(1, 256 / block_size);  // >= 256 tokens per partition
+  const int max_by_len = std::max(1, n_blocks / min_blocks);
+  const int target_ctas = kNumSMs * 8;                   // ~4 waves at 2 resident CTAs per SM
+  int splits = std::max(1, ceil_div(target_ctas, pairs));
+  splits = std::min(splits, max_by_len);
+  return std::min(splits, 128);
+}
+
+}  // namespace
+}  // namespace b200
+
+using namespace b200;
+
+extern "C" {
+
+int b200_abi_version(void) { return B200_ABI_VERSION; }
+
+const char* b200_last_error(void) { return last_error_buf(); }
+
+int b200_kv_append(const void* k_new, const void* v_new, int64_t k_row_stride, int64_t v_row_stride, void* k_pool,
+                   void* v_pool, const int64_t* slot_mapping, int n_tok, int Hkv, int D, int block_size,
+                   int64_t max_blocks, int dtype, void* stream) {
+  return kv_append(k_new, v_new, k_row_stride, v_row_stride, k_pool, v_pool, slot_mapping, n_tok, Hkv, D, block_size,
+                   max_blocks, dtype, static_cast<cudaStream_t>(stream));
+}
+
+size_t b200_paged_decode_attn_workspace(int B, int Hq, int D, int num_splits) {
+  if (B <= 0 || Hq <= 0 || D <= 0 || num_splits <= 1) return 0;
+  return static_cast<size_t>(B) * Hq * num_splits * (static_cast<size_t>(D) + 2) * sizeof(float);
+}
+
+int b200_paged_decode_attn_plan(int B, int Hq, int Hkv, int D, int block_size, int max_context_len, int dtype) {
+  (void)Hq;
+  (void)D;
+  (void)dtype;
+  if (B <= 0 || Hkv <= 0 || block_size <= 0) return 1;
+  return plan_splits(B, Hkv, block_size, max_context_len);
+}
+
+int b200_paged_decode_attn(void* out, const void* q, int64_t q_row_stride, const void* k_pool, const void* v_pool,
+                           const int32_t* block_tables, int table_stride, const int32_t* context_lens, int B, int Hq,
+                           int Hkv, int D, int block_size, int64_t max_blocks, float scale, int max_context_len,
+                           int num_splits, void* workspace, size_t workspace_bytes, int dtype, unsigned flags,
+                           void* stream) {
+  if (dtype_size(dtype) == 0) return fail(B200_EINVAL, "b200_paged_decode_attn: unsupported dtype %d", dtype);
+  if (B < 0 || Hq <= 0 || Hkv <= 0 || D <= 0 || block_size <= 0 || max_blocks <= 0 || table_stride < 0)
+    return fail(B200_EINVAL, "b200_paged_decode_attn: bad sizes B=%d Hq=%d Hkv=%d D=%d block_size=%d", B, Hq, Hkv, D,
+                block_size);
+  if (Hq % Hkv != 0) return fail(B200_ESHAPE, "b200_paged_decode_attn: Hq=%d not a multiple of Hkv=%d", Hq, Hkv);
+  if (B == 0) return 0;
+  if (!out || !q || !k_pool || !v_pool || !block_tables || !context_lens)
+    return fail(B200_EINVAL, "b200_paged_decode_attn: null pointer");
+  if (q_row_stride < static_cast<int64_t>(Hq) * D)
+    return fail(B200_EINVAL, "b200_paged_decode_attn: q_row_stride smaller than Hq*D");
+  if (max_context_len < 0) return fail(B200_EINVAL, "b200_paged_decode_attn: negative max_context_len");
+  if (num_splits < 0) return fail(B200_EINVAL, "b200_paged_decode_attn: negative num_splits");
+  if (num_splits == 0) num_splits = workspace ? plan_splits(B, Hkv, block_size, max_context_len) : 1;
+  const int n_blocks = std::max(1, ceil_div(std::max(1, max_context_len), block_size));
+  num_splits = std::min(num_splits, n_blocks);
+
+  AttnArgs a{};
+  a.out = out;
+  a.q = q;
+  a.q_row_stride = q_row_stride;
+  a.k_pool = k_pool;
+  a.v_pool = v_pool;
+  a.block_tables = block_tables;
+  a.table_stride = table_stride;
+  a.context_lens = context_lens;
+  a.B = B;
+  a.Hq = Hq;
+  a.Hkv = Hkv;
+  a.D = D;
+  a.block_size = block_size;
+  a.max_blocks = max_blocks;
+  a.scale = scale;
+  a.num_splits = num_splits;
+  a.blocks_per_split = ceil_div(n_blocks, num_splits);
+  a.round_scores = (flags & B200_ATTN_ROUND_SCORES) ? 1 : 0;
+  if (num_splits > 1) {
+    const size_t need = b200_paged_decode_attn_workspace(B, Hq, D, num_splits);
+    if (!workspace || workspace_bytes < need)
+      return fail(B200_ENOSPC, "b200_paged_decode_attn: workspace of %zu bytes needed for %d splits, got %zu", need,
+                  num_splits, workspace_bytes);
+    a.ws_acc = static_cast<float*>(workspace);
+    a.ws_ml = a.ws_acc + static_cast<size_t>(B) * Hq * num_splits * D;
+  }
+  cudaStream_t s = static_cast<cudaStream_t>(stream);
+  int rc;
+  if (!(flags & B200_ATTN_FORCE_GENERIC) && attn_tma_supported(a, dtype))
+    rc = attn_tma(a, dtype, s);
+  else
+    rc = attn_generic(a, dtype, s);
+  if (rc != 0) return rc;
+  if (num_splits > 1) return attn_combine(out, a.ws_acc, a.ws_ml, B * Hq, D, num_splits, dtype, s);
+  return 0;
+}
+
+int b200_kv_pack(void* packed, const void* k_pool, const void* v_pool, const int32_t* block_table, int n_blocks,
+                 int Hkv, int D, int block_size, int64_t max_blocks, int dtype, void* stream) {
+  return kv_pack(packed, k_pool, v_pool, block_table, n_blocks, Hkv, D, block_size, max_blocks, dtype,
+                 static_cast<cudaStream_t>(stream));
+}
+
+int b200_kv_unpack(void* k_pool, void* v_pool, const void* packed, const int32_t* block_table, int n_blocks, int Hkv,
+                   int D, int block_size, int64_t max_blocks, int dtype, void* stream) {
+  return kv_unpack(k_pool, v_pool, packed, block_table, n_blocks, Hkv, D, block_size, max_blocks, dtype,
+                   static_cast<cudaStream_t>(stream));
+}
+
+int b200_kv_pack_layers(void* packed, const void* const* k_pools, const void* const* v_pools, int n_layers,
+                        const int32_t* block_table, int n_blocks, int Hkv, int D, int block_size, int64_t max_blocks,
+                        int dtype, void* stream) {
+  return kv_pack_layers(packed, k_pools, v_pools, n_layers, block_table, n_blocks, Hkv, D, block_size, max_blocks,
+                        dtype, static_cast<cudaStream_t>(stream));
+}
+
+int b200_kv_unpack_layers(void* const* k_pools, void* const* v_pools, int n_layers, const void* packed,
+                          const int32_t* block_table, int n_blocks, int Hkv, int D, int block_size,
+                          int64_t max_blocks, int dtype, void* stream) {
+  return kv_unpack_layers(k_pools, v_pools, n_layers, packed, block_table, n_blocks, Hkv, D, block_size, max_blocks,
+                          dtype, static_cast<cudaStream_t>(stream));
+}
+
+}  // extern "C"

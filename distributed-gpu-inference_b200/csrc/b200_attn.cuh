@@ -1,0 +1,52 @@
+// Internal interface between the C ABI (b200_abi.cu) and the attention kernels.
+#pragma once
+#include <cuda_runtime.h>
+
+#include <cstddef>
+#include <cstdint>
+
+namespace b200 {
+
+struct AttnArgs {
+  void* out;                    // [B, Hq, D]
+  const void* q;                // [B, Hq, D], row stride q_row_stride elements
+  int64_t q_row_stride;
+  const void* k_pool;           // [max_blocks, Hkv, block_size, D]
+  const void* v_pool;
+  const int32_t* block_tables;  // [B, table_stride]
+  int table_stride;
+  const int32_t* context_lens;  // [B]
+  int B, Hq, Hkv, D, block_size;
+  int64_t max_blocks;
+  float scale;
+  int blocks_per_split, num_splits;
+  float* ws_acc;                // [B, Hq, num_splits, D] un-normalised partial outputs
+  float* ws_ml;                 // [B, Hq, num_splits, 2] running max and sum
+  int round_scores;
+};
+
+// shape-generic CUDA-core variant (b200_attn_generic.cu)
+int attn_generic(const AttnArgs& a, int dtype, cudaStream_t s);
+// TMA + tensor-core variant (b200_attn_tma.cu); attn_tma_supported says whether it covers the shape
+bool attn_tma_supported(const AttnArgs& a, int dtype);
+int attn_tma(const AttnArgs& a, int dtype, cudaStream_t s);
+// merge of split-K partials
+int attn_combine(void* out, const float* ws_acc, const float* ws_ml, int rows, int D, int num_splits, int dtype,
+                 cudaStream_t stream);
+
+// kv ops (b200_kv_ops.cu)
+int kv_append(const void* k_new, const void* v_new, int64_t k_row_stride, int64_t v_row_stride, void* k_pool,
+              void* v_pool, const int64_t* slot_mapping, int n_tok, int Hkv, int D, int block_size,
+              int64_t max_blocks, int dtype, cudaStream_t stream);
+int kv_pack(void* packed, const void* k_pool, const void* v_pool, const int32_t* table, int n_blocks, int Hkv, int D,
+            int bs, int64_t max_blocks, int dtype, cudaStream_t s);
+int kv_unpack(void* k_pool, void* v_pool, const void* packed, const int32_t* table, int n_blocks, int Hkv, int D,
+              int bs, int64_t max_blocks, int dtype, cudaStream_t s);
+int kv_pack_layers(void* packed, const void* const* k_pools, const void* const* v_pools, int n_layers,
+                   const int32_t* table, int n_blocks, int Hkv, int D, int bs, int64_t max_blocks, int dtype,
+                   cudaStream_t s);
+int kv_unpack_layers(void* const* k_pools, void* const* v_pools, int n_layers, const void* packed,
+                     const int32_t* table, int n_blocks, int Hkv, int D, int bs, int64_t max_blocks, int dtype,
+                     cudaStream_t s);
+
+}  // namespace b200

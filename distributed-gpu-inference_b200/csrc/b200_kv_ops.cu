@@ -1,0 +1,241 @@
+// Paged KV append (scatter through a slot mapping) and KV block pack / unpack (gather / scatter of whole
+// blocks) for sm_100a.  All three are pure byte movers bounded by HBM bandwidth: every access is a 16-byte
+// vector, consecutive threads touch consecutive vectors of one contiguous run (a token-head row of D elements
+// for append, a whole [Hkv, block_size, D] block for pack/unpack), and each thread keeps several independent
+// loads in flight before its first store.
+#include <algorithm>
+
+#include "b200_attn.cuh"
+#include "b200_common.cuh"
+
+namespace b200 {
+
+// ---------------------------------------------------------------------------------------------------------
+// append
+// ---------------------------------------------------------------------------------------------------------
+// One thread per 16-byte vector of the new K and V rows.  vec index -> (which, token, head, v).
+template <int UNROLL>
+__global__ void __launch_bounds__(256)
+kv_append_vec16_kernel(const char* __restrict__ k_new, const char* __restrict__ v_new,
+                       int64_t k_row_bytes, int64_t v_row_bytes,
+                       char* __restrict__ k_pool, char* __restrict__ v_pool,
+                       const int64_t* __restrict__ slot_mapping,
+                       int n_tok, int Hkv, int block_size, int64_t max_blocks,
+                       int vec_per_head /* D * elem_size / 16 */) {
+  const int64_t vec_per_tok = static_cast<int64_t>(Hkv) * vec_per_head;
+  const int64_t per_tensor = static_cast<int64_t>(n_tok) * vec_per_tok;
+  const int64_t total = 2 * per_tensor;
+  const int64_t head_bytes = static_cast<int64_t>(vec_per_head) * 16;
+  const int64_t base = (static_cast<int64_t>(blockIdx.x) * UNROLL) * blockDim.x + threadIdx.x;
+
+  int4 val[UNROLL];
+  char* dst[UNROLL];
+#pragma unroll
+  for (int u = 0; u < UNROLL; ++u) {
+    const int64_t i = base + static_cast<int64_t>(u) * blockDim.x;
+    dst[u] = nullptr;
+    if (i < total) {
+      const bool is_v = i >= per_tensor;
+      const int64_t j = is_v ? i - per_tensor : i;
+      const int tok = static_cast<int>(j / vec_per_tok);
+      const int rem = static_cast<int>(j - static_cast<int64_t>(tok) * vec_per_tok);
+      const int h = rem / vec_per_head;
+      const int v = rem - h * vec_per_head;
+      const int64_t slot = slot_mapping[tok];
+      if (slot >= 0) {
+        const int64_t blk = slot / block_size;
+        const int64_t off = slot - blk * block_size;
+        if (blk < max_blocks) {
+          const char* src = (is_v ? v_new + tok * v_row_bytes : k_new + tok * k_row_bytes) + h * head_bytes + v * 16;
+          val[u] = ld_stream16(src);
+          dst[u] = (is_v ? v_pool : k_pool) + ((blk * Hkv + h) * block_size + off) * head_bytes + v * 16;
+        }
+      }
+    }
+  }
+#pragma unroll
+  for (int u = 0; u < UNROLL; ++u)
+    if (dst[u] != nullptr) *reinterpret_cast<int4*>(dst[u]) = val[u];
+}
+
+// Fallback for rows that are not 16-byte aligned (odd head_dim, fp32 with D % 4 != 0, unaligned views).
+template <typename T>
+__global__ void kv_append_scalar_kernel(const T* __restrict__ k_new, const T* __restrict__ v_new,
+                                        int64_t k_row_stride, int64_t v_row_stride,
+                                        T* __restrict__ k_pool, T* __restrict__ v_pool,
+                                        const int64_t* __restrict__ slot_mapping,
+                                        int n_tok, int Hkv, int D, int block_size, int64_t max_blocks) {
+  const int64_t per_tok = static_cast<int64_t>(Hkv) * D;
+  const int64_t total = 2 * static_cast<int64_t>(n_tok) * per_tok;
+  for (int64_t i = static_cast<int64_t>(blockIdx.x) * blockDim.x + threadIdx.x; i < total;
+       i += static_cast<int64_t>(gridDim.x) * blockDim.x) {
+    const bool is_v = i >= n_tok * per_tok;
+    const int64_t j = is_v ? i - n_tok * per_tok : i;
+    const int64_t tok = j / per_tok;
+    const int64_t rem = j - tok * per_tok;
+    const int64_t h = rem / D, d = rem - h * D;
+    const int64_t slot = slot_mapping[tok];
+    if (slot < 0) continue;
+    const int64_t blk = slot / block_size, off = slot - blk * block_size;
+    if (blk >= max_blocks) continue;
+    const int64_t dst = ((blk * Hkv + h) * block_size + off) * D + d;
+    if (is_v)
+      v_pool[dst] = v_new[tok * v_row_stride + h * D + d];
+    else
+      k_pool[dst] = k_new[tok * k_row_stride + h * D + d];
+  }
+}
+
+int kv_append(const void* k_new, const void* v_new, int64_t k_row_stride, int64_t v_row_stride, void* k_pool,
+              void* v_pool, const int64_t* slot_mapping, int n_tok, int Hkv, int D, int block_size,
+              int64_t max_blocks, int dtype, cudaStream_t stream) {
+  const int es = dtype_size(dtype);
+  if (es == 0) return fail(B200_EINVAL, "b200_kv_append: unsupported dtype %d", dtype);
+  if (n_tok < 0 || Hkv <= 0 || D <= 0 || block_size <= 0 || max_blocks <= 0)
+    return fail(B200_EINVAL, "b200_kv_append: bad sizes n_tok=%d Hkv=%d D=%d block_size=%d max_blocks=%lld", n_tok,
+                Hkv, D, block_size, static_cast<long long>(max_blocks));
+  if (n_tok == 0) return 0;
+  if (!k_new || !v_new || !k_pool || !v_pool || !slot_mapping)
+    return fail(B200_EINVAL, "b200_kv_append: null pointer");
+  if (k_row_stride < static_cast<int64_t>(Hkv) * D || v_row_stride < static_cast<int64_t>(Hkv) * D)
+    return fail(B200_EINVAL, "b200_kv_append: row stride smaller than Hkv*D");
+
+  const bool vec_ok = (D * es) % 16 == 0 && (k_row_stride * es) % 16 == 0 && (v_row_stride * es) % 16 == 0 &&
+                      aligned16(k_new) && aligned16(v_new) && aligned16(k_pool) && aligned16(v_pool);
+  if (vec_ok) {
+    constexpr int UNROLL = 4;
+    const int vec_per_head = D * es / 16;
+    const int64_t total = 2ll * n_tok * Hkv * vec_per_head;
+    const int threads = 256;
+    const int64_t per_cta = static_cast<int64_t>(threads) * UNROLL;
+    const int64_t grid = (total + per_cta - 1) / per_cta;
+    kv_append_vec16_kernel<UNROLL><<<static_cast<unsigned>(grid), threads, 0, stream>>>(
+        static_cast<const char*>(k_new), static_cast<const char*>(v_new), k_row_stride * es, v_row_stride * es,
+        static_cast<char*>(k_pool), static_cast<char*>(v_pool), slot_mapping, n_tok, Hkv, block_size, max_blocks,
+        vec_per_head);
+    return check_launch("b200_kv_append");
+  }
+  const int64_t total = 2ll * n_tok * Hkv * D;
+  const int threads = 256;
+  const int grid = static_cast<int>(std::min<int64_t>((total + threads - 1) / threads, 148 * 16));
+#define LAUNCH_SCALAR(T)                                                                                        \
+  kv_append_scalar_kernel<T><<<grid, threads, 0, stream>>>(                                                     \
+      static_cast<const T*>(k_new), static_cast<const T*>(v_new), k_row_stride, v_row_stride,                   \
+      static_cast<T*>(k_pool), static_cast<T*>(v_pool), slot_mapping, n_tok, Hkv, D, block_size, max_blocks)
+  if (es == 2)
+    LAUNCH_SCALAR(uint16_t);
+  else
+    LAUNCH_SCALAR(uint32_t);
+#undef LAUNCH_SCALAR
+  return check_launch("b200_kv_append(scalar)");
+}
+
+// ---------------------------------------------------------------------------------------------------------
+// pack / unpack
+// ---------------------------------------------------------------------------------------------------------
+struct PoolSet {
+  const void* const* k_pools;  // device array [n_layers] or nullptr
+  const void* const* v_pools;
+  const void* k_single;  // used when the arrays are null (single-layer entry points)
+  const void* v_single;
+};
+
+// Work item = (layer, K|V, table entry); each item is one contiguous run of `vec_per_block` 16-byte vectors.
+// A CTA of 256 threads walks chunks of 256*UNROLL vectors; the grid is flat over all chunks so the hardware
+// scheduler balances it (grid sizes here are thousands of CTAs, i.e. many waves of 148 SMs).
+template <bool PACK, int UNROLL>
+__global__ void __launch_bounds__(256)
+kv_block_copy_kernel(char* __restrict__ packed, PoolSet pools, const int32_t* __restrict__ block_table,
+                     int n_layers, int n_blocks, int64_t max_blocks, int vec_per_block, int chunks_per_block) {
+  const int64_t chunk = blockIdx.x;
+  const int64_t item = chunk / chunks_per_block;  // (layer * 2 + kv) * n_blocks + j
+  const int c = static_cast<int>(chunk - item * chunks_per_block);
+  const int j = static_cast<int>(item % n_blocks);
+  const int lk = static_cast<int>(item / n_blocks);
+  const int layer = lk >> 1;
+  const bool is_v = lk & 1;
+  const int32_t slot = block_table[j];
+  if (slot < 0 || slot >= max_blocks) return;
+
+  const void* pool_base;
+  if (pools.k_pools != nullptr)
+    pool_base = is_v ? pools.v_pools[layer] : pools.k_pools[layer];
+  else
+    pool_base = is_v ? pools.v_single : pools.k_single;
+  const int64_t block_bytes = static_cast<int64_t>(vec_per_block) * 16;
+  char* pool_ptr = const_cast<char*>(static_cast<const char*>(pool_base)) + slot * block_bytes;
+  char* pack_ptr = packed + item * block_bytes;
+  const char* src = PACK ? pool_ptr : pack_ptr;
+  char* dst = PACK ? pack_ptr : pool_ptr;
+
+  const int v0 = c * (256 * UNROLL) + threadIdx.x;
+  int4 val[UNROLL];
+#pragma unroll
+  for (int u = 0; u < UNROLL; ++u) {
+    const int v = v0 + u * 256;
+    if (v < vec_per_block) val[u] = ld_stream16(src + static_cast<int64_t>(v) * 16);
+  }
+#pragma unroll
+  for (int u = 0; u < UNROLL; ++u) {
+    const int v = v0 + u * 256;
+    if (v < vec_per_block) st_stream16(dst + static_cast<int64_t>(v) * 16, val[u]);
+  }
+}
+
+template <bool PACK>
+int kv_block_copy(void* packed, PoolSet pools, int n_layers, const int32_t* block_table, int n_blocks, int Hkv, int D,
+                  int block_size, int64_t max_blocks, int dtype, cudaStream_t stream, const char* name) {
+  const int es = dtype_size(dtype);
+  if (es == 0) return fail(B200_EINVAL, "%s: unsupported dtype %d", name, dtype);
+  if (n_blocks < 0 || n_layers <= 0 || Hkv <= 0 || D <= 0 || block_size <= 0 || max_blocks <= 0)
+    return fail(B200_EINVAL, "%s: bad sizes", name);
+  if (n_blocks == 0) return 0;
+  if (!packed || !block_table) return fail(B200_EINVAL, "%s: null pointer", name);
+  if (pools.k_pools == nullptr && (!pools.k_single || !pools.v_single))
+    return fail(B200_EINVAL, "%s: null pool pointer", name);
+  const int64_t block_bytes = static_cast<int64_t>(Hkv) * block_size * D * es;
+  if (block_bytes % 16 != 0 || !aligned16(packed) ||
+      (pools.k_pools == nullptr && (!aligned16(pools.k_single) || !aligned16(pools.v_single))))
+    return fail(B200_ESHAPE, "%s: block of %lld bytes / pointers must be 16-byte aligned", name,
+                static_cast<long long>(block_bytes));
+  if (block_bytes / 16 > INT32_MAX) return fail(B200_ESHAPE, "%s: block too large", name);
+
+  constexpr int UNROLL = 8;  // 8 x 16 B in flight per thread, 32 KiB per CTA pass
+  const int vec_per_block = static_cast<int>(block_bytes / 16);
+  const int chunks_per_block = (vec_per_block + 256 * UNROLL - 1) / (256 * UNROLL);
+  const int64_t grid = 2ll * n_layers * n_blocks * chunks_per_block;
+  if (grid > INT32_MAX) return fail(B200_ESHAPE, "%s: too many chunks", name);
+  kv_block_copy_kernel<PACK, UNROLL><<<static_cast<unsigned>(grid), 256, 0, stream>>>(
+      static_cast<char*>(packed), pools, block_table, n_layers, n_blocks, max_blocks, vec_per_block, chunks_per_block);
+  return check_launch(name);
+}
+
+int kv_pack(void* packed, const void* k_pool, const void* v_pool, const int32_t* table, int n_blocks, int Hkv, int D,
+            int bs, int64_t max_blocks, int dtype, cudaStream_t s) {
+  PoolSet p{nullptr, nullptr, k_pool, v_pool};
+  return kv_block_copy<true>(packed, p, 1, table, n_blocks, Hkv, D, bs, max_blocks, dtype, s, "b200_kv_pack");
+}
+int kv_unpack(void* k_pool, void* v_pool, const void* packed, const int32_t* table, int n_blocks, int Hkv, int D,
+              int bs, int64_t max_blocks, int dtype, cudaStream_t s) {
+  PoolSet p{nullptr, nullptr, k_pool, v_pool};
+  return kv_block_copy<false>(const_cast<void*>(packed), p, 1, table, n_blocks, Hkv, D, bs, max_blocks, dtype, s,
+                              "b200_kv_unpack");
+}
+int kv_pack_layers(void* packed, const void* const* k_pools, const void* const* v_pools, int n_layers,
+                   const int32_t* table, int n_blocks, int Hkv, int D, int bs, int64_t max_blocks, int dtype,
+                   cudaStream_t s) {
+  if (!k_pools || !v_pools) return fail(B200_EINVAL, "b200_kv_pack_layers: null pool array");
+  PoolSet p{k_pools, v_pools, nullptr, nullptr};
+  return kv_block_copy<true>(packed, p, n_layers, table, n_blocks, Hkv, D, bs, max_blocks, dtype, s,
+                             "b200_kv_pack_layers");
+}
+int kv_unpack_layers(void* const* k_pools, void* const* v_pools, int n_layers, const void* packed,
+                     const int32_t* table, int n_blocks, int Hkv, int D, int bs, int64_t max_blocks, int dtype,
+                     cudaStream_t s) {
+  if (!k_pools || !v_pools) return fail(B200_EINVAL, "b200_kv_unpack_layers: null pool array");
+  PoolSet p{const_cast<const void* const*>(k_pools), const_cast<const void* const*>(v_pools), nullptr, nullptr};
+  return kv_block_copy<false>(const_cast<void*>(packed), p, n_layers, table, n_blocks, Hkv, D, bs, max_blocks, dtype,
+                              s, "b200_kv_unpack_layers");
+}
+
+}  // namespace b200

@@ -1,0 +1,296 @@
+"""Batch decode engine: drives ``ModelShard.forward`` over paged KV on one GPU.
+
+What it owns
+  * one ``KVCachePool`` per shard (the reference's allocator, blocks handed out by ``allocate_sequence``),
+    turned into an int32 block table per sequence;
+  * the per-step device state (``PagedBatchState``) shared by all layers: slot mapping, context lengths,
+    RoPE tables, split-K workspace;
+  * a CUDA graph of one decode step (all layers, lm_head, argmax) so the ~20 launches per layer cost one
+    graph launch per token.
+
+What it calls: only ``ModelShard.forward`` / ``get_logits`` (the reference surface) and, through the layers,
+the C-ABI kernels.  Greedy (argmax) sampling, which is what the parity contract is defined on.
+"""
+from __future__ import annotations
+
+from typing import Any, Dict, List, Optional, Sequence
+
+import torch
+
+from .paged_layer import PagedBatchState, PagedLayerKV, rope_tables
+from .worker.distributed.kv_cache import CacheBlock, KVCachePool
+from .worker.distributed.model_shard import ModelShard
+from . import ops
+
+
+class PagedDecodeEngine:
+    """Greedy decoding of a fixed batch through a chain of shards that live on one CUDA device."""
+
+    def __init__(
+        self,
+        shards: Sequence[ModelShard],
+        max_batch: int,
+        max_seq_len: int,
+        block_size: int = 16,
+        use_cuda_graph: bool = True,
+        attn_flags: int = 0,
+        prefill_mode: str = "sdpa",
+        prefill_chunk: int = 8,
+        spare_blocks: int = 0,
+    ):
+        if not shards:
+            raise ValueError("need at least one shard")
+        self.shards = list(shards)
+        first = self.shards[0]
+        self.device = torch.device(first.device)
+        if self.device.type != "cuda":
+            raise RuntimeError("PagedDecodeEngine runs on CUDA devices only (no CPU path)")
+        self.dtype = first.dtype
+        cfg = first.config
+        self.config = cfg
+        self.block_size = block_size
+        self.max_batch = max_batch
+        self.max_seq_len = max_seq_len
+        self.blocks_per_seq = (max_seq_len + block_size - 1) // block_size
+        self.use_cuda_graph = use_cuda_graph
+        self.prefill_mode = prefill_mode
+        self.prefill_chunk = prefill_chunk
+        self.Hq = cfg.num_attention_heads
+        self.Hkv = getattr(cfg, "num_key_value_heads", self.Hq) or self.Hq
+        self.D = getattr(cfg, "head_dim", None) or cfg.hidden_size // self.Hq
+
+        self.pools: List[KVCachePool] = [
+            KVCachePool(
+                num_layers=s.get_layer_count(),
+                num_heads=self.Hkv,
+                head_dim=self.D,
+                block_size=block_size,
+                max_blocks_per_layer=max_batch * self.blocks_per_seq + spare_blocks,
+                device=str(self.device),
+                dtype=self.dtype,
+            )
+            for s in self.shards
+        ]
+        dev = self.device
+        self.block_tables = torch.zeros((max_batch, self.blocks_per_seq), dtype=torch.int32, device=dev)
+        self.context_lens = torch.zeros((max_batch,), dtype=torch.int32, device=dev)
+        self.ids_buf = torch.zeros((max_batch, 1), dtype=torch.int64, device=dev)
+        self.next_tokens = torch.zeros((max_batch,), dtype=torch.int64, device=dev)
+        self.num_splits = ops.attn_plan(max_batch, self.Hq, self.Hkv, self.D, block_size, max_seq_len, self.dtype)
+        ws = ops.attn_workspace_bytes(max_batch, self.Hq, self.D, self.num_splits)
+        self.workspace = torch.empty(max(ws, 16), dtype=torch.uint8, device=dev)
+        self.inv_freq = self.shards[0].layers[0].inv_freq.to(dev) if len(self.shards[0].layers) else None
+        self.state = PagedBatchState(
+            block_tables=self.block_tables,
+            context_lens=self.context_lens,
+            slot_mapping=torch.zeros((max_batch,), dtype=torch.int64, device=dev),
+            max_context_len=max_seq_len,
+            workspace=self.workspace,
+            num_splits=self.num_splits,
+            attn_flags=attn_flags,
+            prefill_mode=prefill_mode,
+        )
+        self._handles = [
+            [PagedLayerKV(pool.layer(i).key_pool, pool.layer(i).value_pool, self.state) for i in range(s.get_layer_count())]
+            for s, pool in zip(self.shards, self.pools)
+        ]
+        self._seq_blocks: List[Optional[List[List[List[CacheBlock]]]]] = [None] * max_batch  # [seq][shard][layer][blk]
+        self._host_lens = [0] * max_batch
+        self._graph: Optional[torch.cuda.CUDAGraph] = None
+        self._graph_chained: Optional[torch.cuda.CUDAGraph] = None
+        self._pin_in = torch.zeros((max_batch,), dtype=torch.int64).pin_memory()
+        self._pin_out = torch.zeros((max_batch,), dtype=torch.int64).pin_memory()
+        self.batch = 0
+
+    # ---- allocation ----------------------------------------------------------------------------------
+    def allocate(self, batch: int, total_len: int) -> None:
+        """Hand every sequence blocks for ``total_len`` tokens (prompt + tokens to generate)."""
+        if batch > self.max_batch or total_len > self.max_seq_len:
+            raise ValueError("batch / length beyond the engine's capacity")
+        self.release()
+        rows = []
+        for b in range(batch):
+            per_shard = [pool.allocate_sequence(total_len) for pool in self.pools]
+            self._seq_blocks[b] = per_shard
+            row = KVCachePool.block_table(per_shard[0][0])
+            for shard_blocks in per_shard:
+                for layer_blocks in shard_blocks:
+                    if KVCachePool.block_table(layer_blocks) != row:
+                        raise RuntimeError("layers disagree on block slots; per-layer tables are not supported here")
+            rows.append(row + [0] * (self.blocks_per_seq - len(row)))
+        for pool, s in zip(self.pools, range(len(self.pools))):
+            for li in range(pool.num_layers):
+                ids = [blk.block_id for b in range(batch) for blk in self._seq_blocks[b][s][li]]
+                pool.layer(li).pin(ids)
+        self.block_tables[:batch].copy_(torch.tensor(rows, dtype=torch.int32))
+        self.context_lens.zero_()
+        self._host_lens = [0] * self.max_batch
+        self.batch = batch
+        self._graph = None
+        self._graph_chained = None
+
+    def release(self) -> None:
+        for b, per_shard in enumerate(self._seq_blocks):
+            if per_shard is None:
+                continue
+            for pool, shard_blocks in zip(self.pools, per_shard):
+                pool.free_sequence(shard_blocks)
+            self._seq_blocks[b] = None
+        self.batch = 0
+
+    # ---- prefill -------------------------------------------------------------------------------------
+    @torch.no_grad()
+    def prefill(self, prompt_ids: torch.Tensor) -> torch.Tensor:
+        """Run the prompt pass for sequences ``0..B-1`` (equal lengths); returns the first generated token [B]."""
+        B, P = prompt_ids.shape
+        if B != self.batch:
+            raise ValueError("prefill batch differs from the allocated batch")
+        prompt_ids = prompt_ids.to(self.device)
+        bs = self.block_size
+        st = self.state
+        out_tokens = torch.empty((B,), dtype=torch.int64, device=self.device)
+        t = torch.arange(P, device=self.device)
+        for lo in range(0, B, self.prefill_chunk):
+            hi = min(B, lo + self.prefill_chunk)
+            n = hi - lo
+            tables = self.block_tables[lo:hi].to(torch.int64)
+            slots = tables[:, t // bs] * bs + (t % bs)[None, :]
+            pos = t[None, :].expand(n, P)
+            chunk_state = PagedBatchState(
+                block_tables=self.block_tables[lo:hi],
+                context_lens=torch.full((n,), P, dtype=torch.int32, device=self.device),
+                slot_mapping=slots.reshape(-1).contiguous(),
+                max_context_len=P,
+                prefill_mode=self.prefill_mode,
+            )
+            chunk_state.cos, chunk_state.sin = rope_tables(pos, self.inv_freq, self.dtype)
+            h = prompt_ids[lo:hi]
+            for shard, handles in zip(self.shards, self._handles):
+                hs = [PagedLayerKV(hd.k_pool, hd.v_pool, chunk_state) for hd in handles]
+                h, _ = shard.forward(h, position_ids=pos, past_key_values=hs, use_cache=True)
+            logits = self.shards[-1].get_logits(h[:, -1:, :])[:, 0, :]
+            out_tokens[lo:hi] = logits.argmax(dim=-1)
+        self.context_lens[:B] = P
+        self._host_lens[:B] = [P] * B
+        return out_tokens
+
+    # ---- decode --------------------------------------------------------------------------------------
+    def _step_body(self) -> None:
+        """One decode step on static buffers: ids_buf → next_tokens; advances context_lens on the device."""
+        B = self.batch
+        bs = self.block_size
+        st = self.state
+        pos = self.context_lens[:B].to(torch.int64)  # position of the new token = tokens already cached
+        blk = torch.div(pos, bs, rounding_mode="floor")
+        slot = self.block_tables[:B].gather(1, blk[:, None]).squeeze(1).to(torch.int64) * bs + pos % bs
+        st.slot_mapping[:B].copy_(slot)
+        self.context_lens[:B].add_(1)
+        pos2 = pos[:, None]
+        st.cos, st.sin = rope_tables(pos2, self.inv_freq, self.dtype)
+        h = self.ids_buf[:B]
+        for shard, handles in zip(self.shards, self._handles):
+            h, _ = shard.forward(h, position_ids=pos2, past_key_values=handles, use_cache=True)
+        logits = self.shards[-1].get_logits(h)[:, 0, :]
+        torch.argmax(logits, dim=-1, out=self.next_tokens[:B])
+
+    def _view_state(self) -> None:
+        B = self.batch
+        st = self.state
+        st.block_tables = self.block_tables[:B]
+        st.context_lens = self.context_lens[:B]
+        if st.slot_mapping.shape[0] != B:
+            st.slot_mapping = torch.zeros((B,), dtype=torch.int64, device=self.device)
+        st.max_context_len = self.max_seq_len
+
+    def _capture(self, chained: bool) -> torch.cuda.CUDAGraph:
+        self._view_state()
+        saved = self.context_lens.clone()
+        side = torch.cuda.Stream(device=self.device)
+        side.wait_stream(torch.cuda.current_stream())
+        with torch.cuda.stream(side):  # warm-up outside capture: cuBLAS handles, lazy module loads
+            for _ in range(2):
+                self._step_body()
+        torch.cuda.current_stream().wait_stream(side)
+        torch.cuda.synchronize()
+        graph = torch.cuda.CUDAGraph()
+        with torch.cuda.graph(graph):
+            self._step_body()
+            if chained:
+                self.ids_buf[: self.batch, 0].copy_(self.next_tokens[: self.batch])
+        self.context_lens.copy_(saved)  # warm-up advanced the lengths; capture itself runs nothing
+        return graph
+
+    @torch.no_grad()
+    def decode_step_device(self) -> None:
+        """One step with input and output staying on the device (``ids_buf`` → ``next_tokens`` → ``ids_buf``)."""
+        if self.use_cuda_graph:
+            if self._graph_chained is None:
+                self._graph_chained = self._capture(chained=True)
+            self._graph_chained.replay()
+        else:
+            self._view_state()
+            self._step_body()
+            self.ids_buf[: self.batch, 0].copy_(self.next_tokens[: self.batch])
+        for b in range(self.batch):
+            self._host_lens[b] += 1
+
+    @torch.no_grad()
+    def decode_step(self, token_ids: torch.Tensor) -> torch.Tensor:
+        """Public per-step call: host token ids [B] in (pinned copy → device), host next-token ids [B] out."""
+        B = self.batch
+        self._pin_in[:B].copy_(token_ids.reshape(-1)[:B])
+        self.ids_buf[:B, 0].copy_(self._pin_in[:B], non_blocking=True)
+        if self.use_cuda_graph:
+            if self._graph is None:
+                self._graph = self._capture(chained=False)
+            self._graph.replay()
+        else:
+            self._view_state()
+            self._step_body()
+        self._pin_out[:B].copy_(self.next_tokens[:B], non_blocking=True)
+        torch.cuda.current_stream().synchronize()
+        for b in range(B):
+            self._host_lens[b] += 1
+        return self._pin_out[:B].clone()
+
+    @torch.no_grad()
+    def generate(self, prompt_ids: torch.Tensor, max_new_tokens: int) -> torch.Tensor:
+        """Greedy generation: tokens [B, max_new_tokens] on the host."""
+        B, P = prompt_ids.shape
+        self.allocate(B, P + max_new_tokens)
+        nxt = self.prefill(prompt_ids).cpu()
+        out = [nxt]
+        for _ in range(max_new_tokens - 1):
+            nxt = self.decode_step(nxt)
+            out.append(nxt)
+        return torch.stack(out, dim=1)
+
+    # ---- ContinuousBatcher protocol (reference: worker/batch_processor.py:302-336) ---------------------
+    def batch_inference(self, params_list: List[Dict[str, Any]]) -> List[Any]:
+        """Engine hook the reference's batcher looks for: one result (or Exception) per request.
+
+        Each request carries ``input_ids`` (list[int]) and ``max_new_tokens``; requests are grouped by prompt
+        length so every group is one equal-length batch.
+        """
+        results: List[Any] = [None] * len(params_list)
+        groups: Dict[int, List[int]] = {}
+        for i, p in enumerate(params_list):
+            try:
+                groups.setdefault(len(p["input_ids"]), []).append(i)
+            except Exception as exc:  # noqa: BLE001 - per-item failure is part of the protocol
+                results[i] = exc
+        for plen, idxs in groups.items():
+            for lo in range(0, len(idxs), self.max_batch):
+                part = idxs[lo:lo + self.max_batch]
+                try:
+                    n_new = max(int(params_list[i].get("max_new_tokens", 16)) for i in part)
+                    ids = torch.tensor([params_list[i]["input_ids"] for i in part], dtype=torch.int64)
+                    toks = self.generate(ids, n_new)
+                    for row, i in enumerate(part):
+                        want = int(params_list[i].get("max_new_tokens", 16))
+                        results[i] = {"output_ids": toks[row, :want].tolist(),
+                                      "usage": {"prompt_tokens": plen, "completion_tokens": want}}
+                except Exception as exc:  # noqa: BLE001
+                    for i in part:
+                        results[i] = exc
+        return results

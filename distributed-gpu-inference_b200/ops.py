@@ -1,0 +1,223 @@
+"""Torch-tensor front end of the C ABI (include/b200_kv.h).
+
+Each function validates shapes on the host, passes raw device pointers plus torch's current CUDA stream to
+libb200_kv.so and returns immediately (the work is queued on that stream).  No function here computes
+anything itself and none falls back to torch: a missing library or a non-CUDA tensor is an error.
+"""
+from __future__ import annotations
+
+from typing import List, Optional, Sequence
+
+import torch
+
+from . import _lib
+
+DTYPE_ID = {torch.float16: 0, torch.float32: 1, torch.bfloat16: 2}
+
+ATTN_FORCE_GENERIC = 1
+ATTN_ROUND_SCORES = 2
+
+
+def _dtype_id(t: torch.Tensor) -> int:
+    try:
+        return DTYPE_ID[t.dtype]
+    except KeyError:
+        raise TypeError(f"unsupported KV dtype {t.dtype}; expected float16, bfloat16 or float32") from None
+
+
+def _need_cuda(*tensors: torch.Tensor) -> None:
+    for t in tensors:
+        if not t.is_cuda:
+            raise _lib.B200LibraryError(
+                "paged-KV ops run only on CUDA tensors (sm_100a kernels); there is no CPU fallback"
+            )
+
+
+def _stream() -> int:
+    return torch.cuda.current_stream().cuda_stream
+
+
+def _pool_dims(pool: torch.Tensor):
+    if pool.dim() != 4 or not pool.is_contiguous():
+        raise ValueError("pool must be a contiguous [max_blocks, Hkv, block_size, D] tensor")
+    return pool.shape
+
+
+def _row_stride(x: torch.Tensor, heads: int, D: int) -> int:
+    """x is [n, heads, D] with heads*D contiguous inside a row; returns the row stride in elements."""
+    if x.dim() != 3 or x.shape[1] != heads or x.shape[2] != D:
+        raise ValueError(f"expected [n, {heads}, {D}], got {tuple(x.shape)}")
+    if x.shape[0] > 0 and (x.stride(2) != 1 or x.stride(1) != D):
+        raise ValueError("heads and head_dim must be contiguous inside a row")
+    return x.stride(0) if x.shape[0] > 1 else max(x.stride(0), heads * D)
+
+
+def kv_append(
+    k_new: torch.Tensor,
+    v_new: torch.Tensor,
+    k_pool: torch.Tensor,
+    v_pool: torch.Tensor,
+    slot_mapping: torch.Tensor,
+) -> None:
+    """Scatter ``k_new/v_new [n_tok, Hkv, D]`` into the pools at ``slot_mapping`` (int64, negative = skip)."""
+    _need_cuda(k_new, v_new, k_pool, v_pool, slot_mapping)
+    max_blocks, Hkv, bs, D = _pool_dims(k_pool)
+    if v_pool.shape != k_pool.shape or v_pool.dtype != k_pool.dtype or not v_pool.is_contiguous():
+        raise ValueError("k_pool and v_pool must match")
+    if k_new.dtype != k_pool.dtype or v_new.dtype != k_pool.dtype:
+        raise TypeError("new K/V dtype must equal the pool dtype")
+    if slot_mapping.dtype != torch.int64 or slot_mapping.dim() != 1 or not slot_mapping.is_contiguous():
+        raise ValueError("slot_mapping must be a contiguous int64 vector")
+    n_tok = k_new.shape[0]
+    if v_new.shape[0] != n_tok or slot_mapping.shape[0] != n_tok:
+        raise ValueError("k_new, v_new and slot_mapping disagree on the token count")
+    ks, vs = _row_stride(k_new, Hkv, D), _row_stride(v_new, Hkv, D)
+    lib = _lib.load()
+    rc = lib.b200_kv_append(
+        k_new.data_ptr(), v_new.data_ptr(), ks, vs, k_pool.data_ptr(), v_pool.data_ptr(), slot_mapping.data_ptr(),
+        n_tok, Hkv, D, bs, max_blocks, _dtype_id(k_pool), _stream(),
+    )
+    _lib.check(rc, "b200_kv_append")
+
+
+def attn_plan(B: int, Hq: int, Hkv: int, D: int, block_size: int, max_context_len: int, dtype: torch.dtype) -> int:
+    """Number of context partitions the library would pick for this shape."""
+    return _lib.load().b200_paged_decode_attn_plan(B, Hq, Hkv, D, block_size, max_context_len, DTYPE_ID[dtype])
+
+
+def attn_workspace_bytes(B: int, Hq: int, D: int, num_splits: int) -> int:
+    return _lib.load().b200_paged_decode_attn_workspace(B, Hq, D, num_splits)
+
+
+def paged_decode_attention(
+    q: torch.Tensor,
+    k_pool: torch.Tensor,
+    v_pool: torch.Tensor,
+    block_tables: torch.Tensor,
+    context_lens: torch.Tensor,
+    max_context_len: int,
+    scale: Optional[float] = None,
+    out: Optional[torch.Tensor] = None,
+    num_splits: int = 0,
+    workspace: Optional[torch.Tensor] = None,
+    flags: int = 0,
+) -> torch.Tensor:
+    """One-query-per-sequence GQA attention over paged KV.
+
+    ``q [B, Hq, D]`` (row stride free), pools ``[max_blocks, Hkv, bs, D]``, ``block_tables int32 [B, n]``,
+    ``context_lens int32 [B]``.  ``max_context_len`` is the host-side bound used to plan split-K.
+    ``workspace`` (any dtype, CUDA) is needed when more than one split is used; when it is ``None`` and
+    ``num_splits`` is 0 a workspace is taken from torch's caching allocator.
+    """
+    _need_cuda(q, k_pool, v_pool, block_tables, context_lens)
+    max_blocks, Hkv, bs, D = _pool_dims(k_pool)
+    if v_pool.shape != k_pool.shape or v_pool.dtype != k_pool.dtype or not v_pool.is_contiguous():
+        raise ValueError("k_pool and v_pool must match")
+    if q.dtype != k_pool.dtype:
+        raise TypeError("q dtype must equal the pool dtype")
+    B, Hq = q.shape[0], q.shape[1]
+    q_stride = _row_stride(q, Hq, D)
+    if block_tables.dtype != torch.int32 or block_tables.dim() != 2 or block_tables.shape[0] != B:
+        raise ValueError("block_tables must be int32 [B, n]")
+    if block_tables.stride(1) != 1 and block_tables.shape[1] > 1:
+        raise ValueError("block_tables rows must be contiguous")
+    if context_lens.dtype != torch.int32 or context_lens.shape != (B,) or not context_lens.is_contiguous():
+        raise ValueError("context_lens must be a contiguous int32 [B]")
+    if out is None:
+        out = torch.empty((B, Hq, D), dtype=q.dtype, device=q.device)
+    elif out.shape != (B, Hq, D) or not out.is_contiguous() or out.dtype != q.dtype:
+        raise ValueError("out must be a contiguous [B, Hq, D] tensor of q's dtype")
+    if scale is None:
+        scale = float(D) ** -0.5
+    lib = _lib.load()
+    dt = _dtype_id(k_pool)
+    if num_splits == 0:
+        num_splits = lib.b200_paged_decode_attn_plan(B, Hq, Hkv, D, bs, max_context_len, dt)
+    ws_ptr, ws_bytes = 0, 0
+    if num_splits > 1:
+        need = lib.b200_paged_decode_attn_workspace(B, Hq, D, num_splits)
+        if workspace is None:
+            workspace = torch.empty(need, dtype=torch.uint8, device=q.device)
+        ws_ptr, ws_bytes = workspace.data_ptr(), workspace.numel() * workspace.element_size()
+    table_stride = block_tables.stride(0) if B > 1 else block_tables.shape[1]
+    rc = lib.b200_paged_decode_attn(
+        out.data_ptr(), q.data_ptr(), q_stride, k_pool.data_ptr(), v_pool.data_ptr(), block_tables.data_ptr(),
+        table_stride, context_lens.data_ptr(), B, Hq, Hkv, D, bs, max_blocks, float(scale), int(max_context_len),
+        int(num_splits), ws_ptr, ws_bytes, dt, int(flags), _stream(),
+    )
+    _lib.check(rc, "b200_paged_decode_attn")
+    return out
+
+
+def _check_table(block_table: torch.Tensor) -> int:
+    if block_table.dtype != torch.int32 or block_table.dim() != 1 or not block_table.is_contiguous():
+        raise ValueError("block_table must be a contiguous int32 vector")
+    return block_table.shape[0]
+
+
+def kv_pack(k_pool: torch.Tensor, v_pool: torch.Tensor, block_table: torch.Tensor,
+            out: Optional[torch.Tensor] = None) -> torch.Tensor:
+    """Gather one layer's blocks: returns ``[2, n_blocks, Hkv, bs, D]`` (K blocks, then V blocks)."""
+    _need_cuda(k_pool, v_pool, block_table)
+    max_blocks, Hkv, bs, D = _pool_dims(k_pool)
+    _pool_dims(v_pool)
+    n = _check_table(block_table)
+    shape = (2, n, Hkv, bs, D)
+    if out is None:
+        out = torch.empty(shape, dtype=k_pool.dtype, device=k_pool.device)
+    elif tuple(out.shape) != shape or not out.is_contiguous() or out.dtype != k_pool.dtype:
+        raise ValueError(f"out must be contiguous {shape}")
+    rc = _lib.load().b200_kv_pack(out.data_ptr(), k_pool.data_ptr(), v_pool.data_ptr(), block_table.data_ptr(), n, Hkv,
+                                 D, bs, max_blocks, _dtype_id(k_pool), _stream())
+    _lib.check(rc, "b200_kv_pack")
+    return out
+
+
+def kv_unpack(packed: torch.Tensor, k_pool: torch.Tensor, v_pool: torch.Tensor, block_table: torch.Tensor) -> None:
+    """Scatter ``packed [2, n_blocks, Hkv, bs, D]`` into the pools at the slots of ``block_table``."""
+    _need_cuda(packed, k_pool, v_pool, block_table)
+    max_blocks, Hkv, bs, D = _pool_dims(k_pool)
+    _pool_dims(v_pool)
+    n = _check_table(block_table)
+    if tuple(packed.shape) != (2, n, Hkv, bs, D) or not packed.is_contiguous() or packed.dtype != k_pool.dtype:
+        raise ValueError("packed must be contiguous [2, n_blocks, Hkv, bs, D] of the pool dtype")
+    rc = _lib.load().b200_kv_unpack(k_pool.data_ptr(), v_pool.data_ptr(), packed.data_ptr(), block_table.data_ptr(), n,
+                                   Hkv, D, bs, max_blocks, _dtype_id(k_pool), _stream())
+    _lib.check(rc, "b200_kv_unpack")
+
+
+def pool_pointer_array(pools: Sequence[torch.Tensor]) -> torch.Tensor:
+    """Device int64 vector of ``data_ptr()``s — the ``k_pools`` / ``v_pools`` argument of the *_layers calls."""
+    dev = pools[0].device
+    return torch.tensor([p.data_ptr() for p in pools], dtype=torch.int64).to(dev)
+
+
+def kv_pack_layers(k_ptrs: torch.Tensor, v_ptrs: torch.Tensor, pool_shape, dtype: torch.dtype,
+                   block_table: torch.Tensor, out: Optional[torch.Tensor] = None) -> torch.Tensor:
+    """Gather the blocks of every layer in one launch: ``[L, 2, n_blocks, Hkv, bs, D]``."""
+    _need_cuda(k_ptrs, v_ptrs, block_table)
+    max_blocks, Hkv, bs, D = pool_shape
+    L = k_ptrs.shape[0]
+    n = _check_table(block_table)
+    shape = (L, 2, n, Hkv, bs, D)
+    if out is None:
+        out = torch.empty(shape, dtype=dtype, device=block_table.device)
+    elif tuple(out.shape) != shape or not out.is_contiguous() or out.dtype != dtype:
+        raise ValueError(f"out must be contiguous {shape}")
+    rc = _lib.load().b200_kv_pack_layers(out.data_ptr(), k_ptrs.data_ptr(), v_ptrs.data_ptr(), L, block_table.data_ptr(),
+                                        n, Hkv, D, bs, max_blocks, DTYPE_ID[dtype], _stream())
+    _lib.check(rc, "b200_kv_pack_layers")
+    return out
+
+
+def kv_unpack_layers(packed: torch.Tensor, k_ptrs: torch.Tensor, v_ptrs: torch.Tensor, pool_shape,
+                     block_table: torch.Tensor) -> None:
+    _need_cuda(packed, k_ptrs, v_ptrs, block_table)
+    max_blocks, Hkv, bs, D = pool_shape
+    L = k_ptrs.shape[0]
+    n = _check_table(block_table)
+    if tuple(packed.shape) != (L, 2, n, Hkv, bs, D) or not packed.is_contiguous():
+        raise ValueError("packed must be contiguous [L, 2, n_blocks, Hkv, bs, D]")
+    rc = _lib.load().b200_kv_unpack_layers(k_ptrs.data_ptr(), v_ptrs.data_ptr(), L, packed.data_ptr(),
+                                          block_table.data_ptr(), n, Hkv, D, bs, max_blocks, _dtype_id(packed), _stream())
+    _lib.check(rc, "b200_kv_unpack_layers")

@@ -1,0 +1,226 @@
+"""Llama decoder layer over paged KV, callable with the legacy HF convention ``ModelShard.forward`` uses.
+
+``ModelShard.forward`` (reference: worker/distributed/model_shard.py:205-215) calls every layer as
+``layer(h, attention_mask=, position_ids=, past_key_value=, use_cache=) -> (h, present)`` and treats
+``past_key_value`` as opaque.  Here that slot carries a ``PagedLayerKV`` handle: the layer's K/V pools plus the
+batch's block tables, slot mapping and context lengths.  Per call the layer does
+
+    RMSNorm → q/k/v projections (torch GEMMs) → RoPE → b200_kv_append (CUDA) →
+    decode (T = 1): b200_paged_decode_attn (CUDA)   |   prefill (T > 1): causal attention over the new tokens
+    → o_proj → residual → RMSNorm → SwiGLU MLP → residual
+
+The arithmetic order and rounding points follow the Llama recipe of ``transformers`` (RMSNorm in fp32 then cast
+then weight; rotate-half RoPE with fp32 tables cast to the activation dtype; kv head j serves q heads
+j*g..j*g+g-1), so greedy tokens agree with the reference's dense path.  Parameter names match HF
+(``self_attn.q_proj.weight`` …) so checkpoints load unchanged.
+
+There is no dense / CPU mode in this module: without a ``PagedLayerKV`` handle, or on a non-CUDA device, the
+layer raises.
+"""
+from __future__ import annotations
+
+from dataclasses import dataclass, field
+from typing import Any, Dict, List, Optional, Sequence, Tuple
+
+import torch
+import torch.nn as nn
+import torch.nn.functional as F
+
+from . import ops
+
+
+def init_linear_(weight: torch.Tensor, seed: int, std: float = 0.02) -> None:
+    """In-place normal(0, std) from a generator on the weight's own device, seeded with ``seed``."""
+    gen = torch.Generator(device=weight.device)
+    gen.manual_seed(seed)
+    with torch.no_grad():
+        if weight.dtype in (torch.float32, torch.float64) or weight.is_cuda:
+            weight.normal_(0.0, std, generator=gen)
+        else:  # CPU half/bf16 normal_ is slow and lower quality; draw in fp32 and round
+            tmp = torch.empty(weight.shape, dtype=torch.float32)
+            tmp.normal_(0.0, std, generator=gen)
+            weight.copy_(tmp)
+
+
+class RMSNorm(nn.Module):
+    def __init__(self, hidden_size: int, eps: float = 1e-5, device=None, dtype=None):
+        super().__init__()
+        self.weight = nn.Parameter(torch.ones(hidden_size, device=device, dtype=dtype))
+        self.variance_epsilon = eps
+
+    @classmethod
+    def from_hf(cls, hf_norm: nn.Module, device, dtype) -> "RMSNorm":
+        eps = getattr(hf_norm, "variance_epsilon", getattr(hf_norm, "eps", 1e-5))
+        out = cls(hf_norm.weight.shape[0], eps, device, dtype)
+        with torch.no_grad():
+            out.weight.copy_(hf_norm.weight)
+        return out
+
+    def forward(self, x: torch.Tensor) -> torch.Tensor:
+        in_dtype = x.dtype
+        xf = x.to(torch.float32)
+        xf = xf * torch.rsqrt(xf.pow(2).mean(-1, keepdim=True) + self.variance_epsilon)
+        return self.weight * xf.to(in_dtype)
+
+
+def rope_tables(position_ids: torch.Tensor, inv_freq: torch.Tensor, dtype: torch.dtype):
+    """``position_ids [B, T]`` → ``cos, sin [B, T, D]`` (fp32 math, cast to ``dtype``)."""
+    freqs = position_ids.to(torch.float32)[:, :, None] * inv_freq[None, None, :]
+    emb = torch.cat((freqs, freqs), dim=-1)
+    return emb.cos().to(dtype), emb.sin().to(dtype)
+
+
+def _rotate_half(x: torch.Tensor) -> torch.Tensor:
+    h = x.shape[-1] // 2
+    return torch.cat((-x[..., h:], x[..., :h]), dim=-1)
+
+
+@dataclass
+class PagedBatchState:
+    """Device-side description of the sequences a forward call works on (shared by all layers of a shard).
+
+    block_tables   int32 [B, max_blocks_per_seq]   pool slots per sequence, allocation order
+    context_lens   int32 [B]                       tokens visible to attention AFTER this call's append
+    slot_mapping   int64 [B*T]                     pool slot of every new token, row-major (b, t)
+    max_context_len                                host-side bound on context_lens (plans split-K)
+    cos / sin      optional [B, T, D]              RoPE tables for this call, computed once per step
+    workspace      optional uint8 scratch for split-K partials
+    """
+
+    block_tables: torch.Tensor
+    context_lens: torch.Tensor
+    slot_mapping: torch.Tensor
+    max_context_len: int
+    cos: Optional[torch.Tensor] = None
+    sin: Optional[torch.Tensor] = None
+    workspace: Optional[torch.Tensor] = None
+    num_splits: int = 0
+    attn_flags: int = 0
+    prefill_mode: str = "sdpa"  # "sdpa" or "eager" (the reference's exact recipe; O(T^2) memory)
+
+
+@dataclass
+class PagedLayerKV:
+    """What a paged layer expects in ``past_key_values[i]``: its pools and the shared batch state."""
+
+    k_pool: torch.Tensor
+    v_pool: torch.Tensor
+    state: PagedBatchState
+
+
+class PagedLlamaDecoderLayer(nn.Module):
+    """One Llama decoder layer; see the module docstring."""
+
+    def __init__(self, config, layer_idx: int = 0, device=None, dtype=None):
+        super().__init__()
+        self.layer_idx = layer_idx
+        self.hidden_size = config.hidden_size
+        self.num_heads = config.num_attention_heads
+        self.num_kv_heads = getattr(config, "num_key_value_heads", self.num_heads) or self.num_heads
+        self.head_dim = getattr(config, "head_dim", None) or self.hidden_size // self.num_heads
+        self.eps = getattr(config, "rms_norm_eps", 1e-5)
+        self.rope_theta = float(getattr(config, "rope_theta", 10000.0))
+        kw = dict(bias=False, device=device, dtype=dtype)
+        H, D = self.hidden_size, self.head_dim
+        self.self_attn = nn.Module()
+        self.self_attn.q_proj = nn.Linear(H, self.num_heads * D, **kw)
+        self.self_attn.k_proj = nn.Linear(H, self.num_kv_heads * D, **kw)
+        self.self_attn.v_proj = nn.Linear(H, self.num_kv_heads * D, **kw)
+        self.self_attn.o_proj = nn.Linear(self.num_heads * D, H, **kw)
+        self.mlp = nn.Module()
+        self.mlp.gate_proj = nn.Linear(H, config.intermediate_size, **kw)
+        self.mlp.up_proj = nn.Linear(H, config.intermediate_size, **kw)
+        self.mlp.down_proj = nn.Linear(config.intermediate_size, H, **kw)
+        self.input_layernorm = RMSNorm(H, self.eps, device, dtype)
+        self.post_attention_layernorm = RMSNorm(H, self.eps, device, dtype)
+        inv_freq = 1.0 / (self.rope_theta ** (torch.arange(0, D, 2, dtype=torch.int64).to(torch.float32) / D))
+        self.register_buffer("inv_freq", inv_freq.to(device) if device is not None else inv_freq, persistent=False)
+
+    # ---- construction helpers ----------------------------------------------------------------------
+    _LINEARS = (
+        ("self_attn", "q_proj"), ("self_attn", "k_proj"), ("self_attn", "v_proj"), ("self_attn", "o_proj"),
+        ("mlp", "gate_proj"), ("mlp", "up_proj"), ("mlp", "down_proj"),
+    )
+
+    def reset_parameters(self, seed: int, std: float = 0.02) -> None:
+        for i, (grp, name) in enumerate(self._LINEARS):
+            init_linear_(getattr(getattr(self, grp), name).weight, seed * 16 + i, std)
+        with torch.no_grad():
+            self.input_layernorm.weight.fill_(1.0)
+            self.post_attention_layernorm.weight.fill_(1.0)
+
+    @classmethod
+    def from_hf_layer(cls, hf_layer: nn.Module, config, layer_idx: int, device, dtype) -> "PagedLlamaDecoderLayer":
+        layer = cls(config, layer_idx, device, dtype)
+        sd = {k: v for k, v in hf_layer.state_dict().items() if "rotary" not in k}
+        layer.load_state_dict(sd, strict=True)
+        return layer
+
+    # ---- forward -----------------------------------------------------------------------------------
+    def forward(
+        self,
+        hidden_states: torch.Tensor,
+        attention_mask: Optional[torch.Tensor] = None,
+        position_ids: Optional[torch.Tensor] = None,
+        past_key_value: Optional[PagedLayerKV] = None,
+        use_cache: bool = True,
+    ) -> Tuple[torch.Tensor, Optional[PagedLayerKV]]:
+        if not isinstance(past_key_value, PagedLayerKV):
+            raise TypeError(
+                "PagedLlamaDecoderLayer needs a PagedLayerKV handle in past_key_value; the dense (k, v) tuple "
+                "path of the reference is not provided here"
+            )
+        st = past_key_value.state
+        B, T, _ = hidden_states.shape
+        Hq, Hkv, D = self.num_heads, self.num_kv_heads, self.head_dim
+
+        x = self.input_layernorm(hidden_states)
+        q = self.self_attn.q_proj(x).view(B, T, Hq, D)
+        k = self.self_attn.k_proj(x).view(B, T, Hkv, D)
+        v = self.self_attn.v_proj(x).view(B, T, Hkv, D)
+
+        if st.cos is not None:
+            cos, sin = st.cos, st.sin
+        else:
+            if position_ids is None:
+                raise ValueError("position_ids (or precomputed RoPE tables in the batch state) are required")
+            cos, sin = rope_tables(position_ids, self.inv_freq, x.dtype)
+        cos, sin = cos.unsqueeze(2), sin.unsqueeze(2)  # broadcast over heads: [B, T, 1, D]
+        q = q * cos + _rotate_half(q) * sin
+        k = k * cos + _rotate_half(k) * sin
+
+        ops.kv_append(k.reshape(B * T, Hkv, D), v.reshape(B * T, Hkv, D), past_key_value.k_pool,
+                      past_key_value.v_pool, st.slot_mapping)
+
+        if T == 1:
+            attn = ops.paged_decode_attention(
+                q.reshape(B, Hq, D), past_key_value.k_pool, past_key_value.v_pool, st.block_tables, st.context_lens,
+                st.max_context_len, num_splits=st.num_splits, workspace=st.workspace, flags=st.attn_flags,
+            ).view(B, 1, Hq * D)
+        else:
+            attn = self._prefill_attention(q, k, v, attention_mask, st.prefill_mode)
+
+        h = hidden_states + self.self_attn.o_proj(attn)
+        y = self.post_attention_layernorm(h)
+        h = h + self.mlp.down_proj(F.silu(self.mlp.gate_proj(y)) * self.mlp.up_proj(y))
+        return h, (past_key_value if use_cache else None)
+
+    def _prefill_attention(self, q, k, v, attention_mask, mode: str) -> torch.Tensor:
+        """Causal attention among the T new tokens of sequences that start empty (the prompt pass)."""
+        B, T, Hq, D = q.shape
+        g = Hq // self.num_kv_heads
+        qh, kh, vh = q.transpose(1, 2), k.transpose(1, 2), v.transpose(1, 2)
+        if mode == "eager":
+            kh = kh.repeat_interleave(g, dim=1)
+            vh = vh.repeat_interleave(g, dim=1)
+            w = torch.matmul(qh, kh.transpose(2, 3)) * (D ** -0.5)
+            if attention_mask is None:
+                attention_mask = torch.triu(
+                    torch.full((T, T), float("-inf"), dtype=q.dtype, device=q.device), diagonal=1
+                )[None, None]
+            w = F.softmax(w + attention_mask, dim=-1, dtype=torch.float32).to(q.dtype)
+            out = torch.matmul(w, vh)
+        else:
+            out = F.scaled_dot_product_attention(qh, kh, vh, attn_mask=attention_mask,
+                                                 is_causal=attention_mask is None, enable_gqa=g > 1)
+        return out.transpose(1, 2).reshape(B, T, Hq * D)

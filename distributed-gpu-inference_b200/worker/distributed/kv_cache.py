@@ -1,0 +1,452 @@
+"""Paged KV-cache allocator with the reference's semantics, laid out for the CUDA kernels.
+
+Drop-in for the reference's ``worker/distributed/kv_cache.py``: same classes, constructor arguments, return
+values, ``get_stats()`` keys and — bit for bit — the same block-id sequence for any alloc/free/evict schedule
+(pinned by tests/golden/allocator_*.json which were produced by the reference itself).
+
+What is kept exactly
+  * pool layout ``[max_blocks, num_heads, block_size, head_dim]`` for K and for V (reference :130-144)
+  * ids ``block_{slot}``, free list initialised ascending and popped from the END (reference :177)
+  * ``free_block``: ref-count floor 0, slot zeroed, id appended to the END of the free list (reference :196-216)
+  * LRU eviction of the oldest ``ref_count == 1`` entry (reference :229-238)
+  * ``KVCachePool.allocate_sequence``: ceil-div block count, layer-major (reference :283-313)
+  * tier keys ``"{prefix_hash}:{layer}"``, CPU LRU capacity formula, pickle payload (reference :326-555)
+
+Deliberate deviations (each is listed in DESIGN.md)
+  1. pools are created on any device, not only CUDA (#1) — the reference leaves CPU caches unusable
+  2. ``KVCachePool`` / ``DistributedKVCacheManager`` accept ``dtype=`` (#2); default stays fp16
+  3. blocks handed out earlier in the same ``allocate_sequence`` call, and blocks pinned with ``pin()``,
+     are skipped by eviction (#8); a failing ``allocate_sequence`` also returns the partial layer (#9)
+  4. freeing a block drops its ``_prefix_index`` entry (#11)
+
+Added for the device path (no reference counterpart): ``slot_of``, ``pin``/``unpin``, ``block_table`` and the
+single backing allocation in ``KVCachePool`` whose per-layer views are what the C-ABI kernels receive.
+"""
+from __future__ import annotations
+
+import asyncio
+import hashlib
+import io
+import logging
+import pickle
+import time
+from collections import OrderedDict
+from dataclasses import dataclass, field
+from enum import Enum
+from typing import Any, Dict, Iterable, List, Optional, Sequence, Set, Tuple
+
+import torch
+
+logger = logging.getLogger(__name__)
+
+
+class CacheLocation(Enum):
+    GPU = "gpu"
+    CPU = "cpu"
+    REDIS = "redis"
+    REMOTE = "remote"
+
+
+@dataclass
+class CacheBlock:
+    """One fixed-size page of K and V for one layer (reference: worker/distributed/kv_cache.py:34-76).
+
+    ``keys`` / ``values`` are views into the owning pool, shape ``[num_heads, block_size, head_dim]``.
+    """
+
+    block_id: str
+    block_size: int = 16
+    keys: Optional[torch.Tensor] = None
+    values: Optional[torch.Tensor] = None
+    layer_idx: int = 0
+    num_tokens: int = 0
+    ref_count: int = 1
+    prefix_hash: str = ""
+    location: CacheLocation = CacheLocation.GPU
+    last_access: float = field(default_factory=time.time)
+    created_at: float = field(default_factory=time.time)
+
+    @property
+    def is_full(self) -> bool:
+        return self.num_tokens >= self.block_size
+
+    @property
+    def is_shared(self) -> bool:
+        return self.ref_count > 1
+
+    @property
+    def slot(self) -> int:
+        """Pool row this block occupies (the integer after ``block_``)."""
+        return int(self.block_id.rsplit("_", 1)[1])
+
+    def add_ref(self) -> None:
+        self.ref_count += 1
+
+    def remove_ref(self) -> int:
+        self.ref_count = max(0, self.ref_count - 1)
+        return self.ref_count
+
+    def touch(self) -> None:
+        self.last_access = time.time()
+
+
+class PagedKVCache:
+    """Block allocator over one K pool and one V pool (reference: worker/distributed/kv_cache.py:79-247)."""
+
+    def __init__(
+        self,
+        num_layers: int,
+        num_heads: int,
+        head_dim: int,
+        block_size: int = 16,
+        max_blocks: int = 1000,
+        device: str = "cuda",
+        dtype: torch.dtype = torch.float16,
+        *,
+        _storage: Optional[Tuple[torch.Tensor, torch.Tensor]] = None,
+    ):
+        self.num_layers = num_layers
+        self.num_heads = num_heads
+        self.head_dim = head_dim
+        self.block_size = block_size
+        self.max_blocks = max_blocks
+        self.device = device
+        self.dtype = dtype
+
+        self._blocks: Dict[str, CacheBlock] = {}
+        self._free_blocks: List[str] = []
+        self._key_pool: Optional[torch.Tensor] = None
+        self._value_pool: Optional[torch.Tensor] = None
+        self._block_to_slot: Dict[str, int] = {}
+        self._lru_queue: "OrderedDict[str, float]" = OrderedDict()
+        self._pinned: Set[str] = set()
+        self._stats = {"allocations": 0, "evictions": 0, "hits": 0, "misses": 0}
+        self._on_free = None  # optional callback(block_id), used by the tier manager to drop index entries
+
+        self._init_memory_pool(_storage)
+
+    # -- pool ---------------------------------------------------------------------------------------
+    def _init_memory_pool(self, storage: Optional[Tuple[torch.Tensor, torch.Tensor]] = None) -> None:
+        shape = (self.max_blocks, self.num_heads, self.block_size, self.head_dim)
+        if storage is not None:
+            k, v = storage
+            if tuple(k.shape) != shape or tuple(v.shape) != shape or not (k.is_contiguous() and v.is_contiguous()):
+                raise ValueError(f"backing storage must be two contiguous tensors of shape {shape}")
+            self._key_pool, self._value_pool = k, v
+        else:
+            self._key_pool = torch.zeros(shape, dtype=self.dtype, device=self.device)
+            self._value_pool = torch.zeros(shape, dtype=self.dtype, device=self.device)
+        self._free_blocks = [f"block_{i}" for i in range(self.max_blocks)]
+
+    def _get_pool_memory_gb(self) -> float:
+        if self._key_pool is None:
+            return 0.0
+        return 2 * self._key_pool.numel() * self._key_pool.element_size() / (1024 ** 3)
+
+    @property
+    def key_pool(self) -> torch.Tensor:
+        return self._key_pool
+
+    @property
+    def value_pool(self) -> torch.Tensor:
+        return self._value_pool
+
+    # -- allocation ---------------------------------------------------------------------------------
+    def allocate_block(self, layer_idx: int, prefix_hash: str = "") -> Optional[CacheBlock]:
+        if not self._free_blocks and not self._evict_lru():
+            logger.warning("No free blocks and eviction failed")
+            return None
+        block_id = self._free_blocks.pop()
+        slot = int(block_id.split("_")[1])
+        blk = CacheBlock(
+            block_id=block_id,
+            block_size=self.block_size,
+            layer_idx=layer_idx,
+            prefix_hash=prefix_hash,
+            keys=self._key_pool[slot],
+            values=self._value_pool[slot],
+        )
+        self._blocks[block_id] = blk
+        self._block_to_slot[block_id] = slot
+        self._lru_queue[block_id] = time.time()
+        self._stats["allocations"] += 1
+        return blk
+
+    def free_block(self, block_id: str) -> None:
+        blk = self._blocks.get(block_id)
+        if blk is None:
+            return
+        if blk.remove_ref() != 0:
+            return
+        slot = self._block_to_slot.get(block_id)
+        if slot is not None:
+            self._key_pool[slot].zero_()
+            self._value_pool[slot].zero_()
+        del self._blocks[block_id]
+        self._block_to_slot.pop(block_id, None)
+        self._lru_queue.pop(block_id, None)
+        self._pinned.discard(block_id)
+        self._free_blocks.append(block_id)
+        if self._on_free is not None:
+            self._on_free(block_id)
+
+    def get_block(self, block_id: Optional[str]) -> Optional[CacheBlock]:
+        blk = self._blocks.get(block_id)
+        if blk is None:
+            self._stats["misses"] += 1
+            return None
+        blk.touch()
+        self._lru_queue.move_to_end(block_id)
+        self._stats["hits"] += 1
+        return blk
+
+    def _evict_lru(self) -> bool:
+        for block_id in self._lru_queue:
+            blk = self._blocks.get(block_id)
+            if blk is not None and blk.ref_count == 1 and block_id not in self._pinned:
+                self.free_block(block_id)
+                self._stats["evictions"] += 1
+                return True
+        return False
+
+    # -- additions for the device path --------------------------------------------------------------
+    def slot_of(self, block_id: str) -> int:
+        return self._block_to_slot[block_id]
+
+    def pin(self, block_ids: Iterable[str]) -> None:
+        """Protect blocks of a live sequence from LRU eviction."""
+        self._pinned.update(b for b in block_ids if b in self._blocks)
+
+    def unpin(self, block_ids: Iterable[str]) -> None:
+        self._pinned.difference_update(block_ids)
+
+    def get_stats(self) -> Dict[str, Any]:
+        return {
+            **self._stats,
+            "total_blocks": len(self._blocks),
+            "free_blocks": len(self._free_blocks),
+            "memory_gb": self._get_pool_memory_gb(),
+        }
+
+
+class KVCachePool:
+    """One ``PagedKVCache`` per layer (reference: worker/distributed/kv_cache.py:250-323).
+
+    All layers share one backing tensor ``[num_layers, 2, max_blocks, heads, block_size, head_dim]`` so the pools
+    of a shard are a single HBM allocation; layer ``l`` uses ``backing[l, 0]`` for K and ``backing[l, 1]`` for V.
+    """
+
+    def __init__(
+        self,
+        num_layers: int,
+        num_heads: int,
+        head_dim: int,
+        block_size: int = 16,
+        max_blocks_per_layer: int = 100,
+        device: str = "cuda",
+        dtype: torch.dtype = torch.float16,
+    ):
+        self.num_layers = num_layers
+        self.num_heads = num_heads
+        self.head_dim = head_dim
+        self.block_size = block_size
+        self.max_blocks_per_layer = max_blocks_per_layer
+        self.device = device
+        self.dtype = dtype
+        self.backing = torch.zeros(
+            (num_layers, 2, max_blocks_per_layer, num_heads, block_size, head_dim), dtype=dtype, device=device
+        )
+        self._layer_caches: List[PagedKVCache] = [
+            PagedKVCache(
+                num_layers=1,
+                num_heads=num_heads,
+                head_dim=head_dim,
+                block_size=block_size,
+                max_blocks=max_blocks_per_layer,
+                device=device,
+                dtype=dtype,
+                _storage=(self.backing[l, 0], self.backing[l, 1]),
+            )
+            for l in range(num_layers)
+        ]
+
+    def allocate_sequence(self, seq_len: int, prefix_hash: str = "") -> List[List[CacheBlock]]:
+        bs = self._layer_caches[0].block_size
+        n_blocks = (seq_len + bs - 1) // bs
+        out: List[List[CacheBlock]] = []
+        for layer_idx, cache in enumerate(self._layer_caches):
+            mine: List[CacheBlock] = []
+            for _ in range(n_blocks):
+                blk = cache.allocate_block(layer_idx, prefix_hash)
+                if blk is None:
+                    cache.unpin(b.block_id for b in mine)
+                    self._free_sequence_blocks(out + [mine])
+                    raise RuntimeError(f"Failed to allocate KV-Cache for layer {layer_idx}")
+                cache._pinned.add(blk.block_id)  # not evictable by the rest of this call
+                mine.append(blk)
+            out.append(mine)
+        for layer_idx, mine in enumerate(out):
+            self._layer_caches[layer_idx].unpin(b.block_id for b in mine)
+        return out
+
+    def _free_sequence_blocks(self, blocks: List[List[CacheBlock]]) -> None:
+        for layer_idx, layer_blocks in enumerate(blocks):
+            cache = self._layer_caches[layer_idx]
+            cache.unpin(b.block_id for b in layer_blocks)
+            for blk in layer_blocks:
+                cache.free_block(blk.block_id)
+
+    def free_sequence(self, blocks: List[List[CacheBlock]]) -> None:
+        """Public spelling of the reference's private ``_free_sequence_blocks``."""
+        self._free_sequence_blocks(blocks)
+
+    def get_total_memory_gb(self) -> float:
+        return sum(c._get_pool_memory_gb() for c in self._layer_caches)
+
+    # -- additions for the device path --------------------------------------------------------------
+    def layer(self, layer_idx: int) -> PagedKVCache:
+        return self._layer_caches[layer_idx]
+
+    @staticmethod
+    def block_table(layer_blocks: Sequence[CacheBlock]) -> List[int]:
+        """Pool slots of a sequence's blocks in allocation order — one row of the device block table."""
+        return [b.slot for b in layer_blocks]
+
+
+class DistributedKVCacheManager:
+    """GPU → CPU → Redis tiers keyed by prefix (reference: worker/distributed/kv_cache.py:326-555)."""
+
+    def __init__(
+        self,
+        num_layers: int,
+        num_heads: int,
+        head_dim: int,
+        gpu_cache_blocks: int = 500,
+        cpu_cache_gb: float = 16.0,
+        redis_client=None,
+        block_size: int = 16,
+        device: str = "cuda",
+        dtype: torch.dtype = torch.float16,
+    ):
+        self.num_layers = num_layers
+        self.num_heads = num_heads
+        self.head_dim = head_dim
+        self.block_size = block_size
+        self.gpu_cache = KVCachePool(
+            num_layers=num_layers,
+            num_heads=num_heads,
+            head_dim=head_dim,
+            block_size=block_size,
+            max_blocks_per_layer=gpu_cache_blocks,
+            device=device,
+            dtype=dtype,
+        )
+        self.cpu_cache: "OrderedDict[str, Tuple[torch.Tensor, torch.Tensor]]" = OrderedDict()
+        # capacity in items; the 2-byte element size is hard-wired as in the reference (:366-368)
+        self.cpu_cache_max_items = int(cpu_cache_gb * 1024 * 1024 * 1024 / (2 * num_heads * block_size * head_dim * 2))
+        self.redis = redis_client
+        self._prefix_index: Dict[str, str] = {}
+        self._stats = {"l1_hits": 0, "l2_hits": 0, "l3_hits": 0, "l4_hits": 0, "misses": 0}
+        for layer_idx, cache in enumerate(self.gpu_cache._layer_caches):
+            cache._on_free = self._make_index_dropper(layer_idx)
+
+    def _make_index_dropper(self, layer_idx: int):
+        suffix = f":{layer_idx}"
+
+        def drop(block_id: str) -> None:
+            stale = [k for k, v in self._prefix_index.items() if v == block_id and k.endswith(suffix)]
+            for k in stale:
+                del self._prefix_index[k]
+
+        return drop
+
+    def compute_prefix_hash(self, token_ids: List[int]) -> str:
+        return hashlib.sha256(bytes(token_ids)).hexdigest()[:16]
+
+    async def get_or_compute(self, prefix_hash: str, layer_idx: int, compute_fn) -> Tuple[torch.Tensor, torch.Tensor]:
+        cache_key = f"{prefix_hash}:{layer_idx}"
+        layer_cache = self.gpu_cache._layer_caches[layer_idx]
+
+        blk = layer_cache.get_block(self._prefix_index.get(cache_key))
+        if blk is not None and blk.keys is not None:
+            self._stats["l1_hits"] += 1
+            return blk.keys, blk.values
+
+        if cache_key in self.cpu_cache:
+            keys, values = self.cpu_cache[cache_key]
+            self.cpu_cache.move_to_end(cache_key)
+            self._stats["l2_hits"] += 1
+            await self._promote_to_gpu(cache_key, keys, values, layer_idx, prefix_hash)
+            dev = self.gpu_cache._layer_caches[0].device
+            return keys.to(dev), values.to(dev)
+
+        if self.redis:
+            blob = await self._get_from_redis(cache_key)
+            if blob:
+                keys, values = self._deserialize_kv(blob)
+                self._stats["l3_hits"] += 1
+                self._add_to_cpu_cache(cache_key, keys, values)
+                await self._promote_to_gpu(cache_key, keys, values, layer_idx, prefix_hash)
+                return keys, values
+
+        self._stats["misses"] += 1
+        keys, values = await compute_fn()
+        await self._store_kv(cache_key, keys, values, layer_idx, prefix_hash)
+        return keys, values
+
+    async def _promote_to_gpu(self, cache_key, keys, values, layer_idx, prefix_hash) -> None:
+        blk = self.gpu_cache._layer_caches[layer_idx].allocate_block(layer_idx, prefix_hash)
+        if blk is not None and blk.keys is not None:
+            blk.keys.copy_(keys)
+            blk.values.copy_(values)
+            self._prefix_index[cache_key] = blk.block_id
+
+    def _add_to_cpu_cache(self, cache_key, keys, values) -> None:
+        while len(self.cpu_cache) >= self.cpu_cache_max_items:
+            self.cpu_cache.popitem(last=False)
+        self.cpu_cache[cache_key] = (keys.cpu(), values.cpu())
+
+    async def _get_from_redis(self, cache_key: str) -> Optional[bytes]:
+        if self.redis is None:
+            return None
+        try:
+            return await self.redis.get(f"kv:{cache_key}")
+        except Exception as exc:  # noqa: BLE001 - same swallow-and-log contract as the reference
+            logger.warning(f"Redis get error: {exc}")
+            return None
+
+    async def _store_kv(self, cache_key, keys, values, layer_idx, prefix_hash) -> None:
+        await self._promote_to_gpu(cache_key, keys, values, layer_idx, prefix_hash)
+        self._add_to_cpu_cache(cache_key, keys, values)
+        if self.redis:
+            asyncio.create_task(self._write_to_redis(cache_key, keys, values))
+
+    async def _write_to_redis(self, cache_key, keys, values, ttl: int = 3600) -> None:
+        if self.redis is None:
+            return
+        try:
+            await self.redis.setex(f"kv:{cache_key}", ttl, self._serialize_kv(keys, values))
+        except Exception as exc:  # noqa: BLE001
+            logger.warning(f"Redis write error: {exc}")
+
+    def _serialize_kv(self, keys: torch.Tensor, values: torch.Tensor) -> bytes:
+        sink = io.BytesIO()
+        pickle.dump({"keys": keys.cpu().numpy(), "values": values.cpu().numpy()}, sink)
+        return sink.getvalue()
+
+    def _deserialize_kv(self, data: bytes) -> Tuple[torch.Tensor, torch.Tensor]:
+        kv = pickle.load(io.BytesIO(data))
+        return torch.from_numpy(kv["keys"]), torch.from_numpy(kv["values"])
+
+    def get_stats(self) -> Dict[str, Any]:
+        total = sum(self._stats.values())
+        denom = max(1, total)
+        return {
+            **self._stats,
+            "total_requests": total,
+            "l1_hit_rate": self._stats["l1_hits"] / denom,
+            "l2_hit_rate": self._stats["l2_hits"] / denom,
+            "l3_hit_rate": self._stats["l3_hits"] / denom,
+            "gpu_memory_gb": self.gpu_cache.get_total_memory_gb(),
+            "cpu_cache_items": len(self.cpu_cache),
+        }

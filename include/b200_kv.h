@@ -1,0 +1,116 @@
+/*
+ * b200_kv.h — C ABI of the B200 (sm_100a) paged-KV hot path.
+ *
+ * This is the drop-in boundary underneath the reference's Python surface
+ * (Baozhi888/distributed-gpu-inference).  The reference has no native code, so every entry point below cites
+ * the Python routine whose work it takes over; citations are relative to the reference checkout.
+ *
+ * Conventions (all entry points)
+ *   - extern "C", plain pointers and sizes; no torch / C++ types cross the boundary.
+ *   - every data pointer is a DEVICE pointer owned by the caller and kept alive until the stream has run.
+ *   - work is enqueued on `stream` (a cudaStream_t passed as void*); nothing here synchronises, allocates
+ *     or frees device memory, so calls may be captured into a CUDA graph.
+ *   - return value: 0 on success, otherwise a negative B200_E* code (argument errors) or a positive
+ *     cudaError_t; b200_last_error() returns a thread-local description of the last failure.
+ *   - `dtype` uses the reference's wire ids (common/serialization.py:20-27):
+ *         0 = float16, 1 = float32, 2 = bfloat16.
+ *   - pool layout is the reference's (worker/distributed/kv_cache.py:130-144):
+ *         k_pool, v_pool : [max_blocks, Hkv, block_size, D], contiguous.
+ */
+#ifndef B200_KV_H_
+#define B200_KV_H_
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define B200_ABI_VERSION 1
+
+#define B200_DTYPE_F16 0
+#define B200_DTYPE_F32 1
+#define B200_DTYPE_BF16 2
+
+#define B200_EINVAL (-1)   /* bad argument (null pointer, negative size, unsupported dtype) */
+#define B200_ESHAPE (-2)   /* shape not supported by any kernel variant */
+#define B200_ENOSPC (-3)   /* workspace too small / size beyond a fixed limit */
+
+/* b200_paged_decode_attn flags */
+#define B200_ATTN_FORCE_GENERIC 1u /* skip the TMA + tensor-core variant (used by tests to cross-check) */
+#define B200_ATTN_ROUND_SCORES 2u  /* round q.k and scaled scores to the storage dtype before softmax, the way
+                                      the reference's eager HF attention does (bf16/f16 only) */
+
+int b200_abi_version(void);
+const char* b200_last_error(void);
+
+/*
+ * Paged KV append.  Replaces the `torch.cat((past_k, k), dim=2)` growth of the dense cache inside the HF layer
+ * that ModelShard.forward calls (worker/distributed/model_shard.py:205-222) and fills the blocks that
+ * PagedKVCache.allocate_block hands out (worker/distributed/kv_cache.py:153-194).
+ *
+ *   k_new, v_new : [n_tok, Hkv, D]; row n starts at k_new + n * k_row_stride (elements), heads contiguous
+ *   slot_mapping : int64[n_tok]; slot = block_table[t / block_size] * block_size + t % block_size;
+ *                  a negative slot skips the token (padding)
+ * Element address in a pool: ((slot / bs * Hkv + h) * bs + slot % bs) * D + d.
+ */
+int b200_kv_append(const void* k_new, const void* v_new, int64_t k_row_stride, int64_t v_row_stride,
+                   void* k_pool, void* v_pool, const int64_t* slot_mapping, int n_tok,
+                   int Hkv, int D, int block_size, int64_t max_blocks, int dtype, void* stream);
+
+/*
+ * Paged GQA decode attention, one query token per sequence.  Replaces repeat_kv + QK^T + softmax + PV over the
+ * dense cache in the HF layer invoked from ModelShard.forward (worker/distributed/model_shard.py:205-222).
+ *
+ *   out           : [B, Hq, D] contiguous
+ *   q             : [B, Hq, D]; row b starts at q + b * q_row_stride (elements)
+ *   block_tables  : int32[B, table_stride]; entry j of row b is the pool slot of the j-th block of sequence b
+ *   context_lens  : int32[B]; tokens to attend to (including the one just appended); 0 gives a zero row
+ *   max_context_len : host-side upper bound of context_lens, used only to size the split-K partition
+ *   num_splits    : partitions of the context per (sequence, kv head); 0 = let the library choose
+ *                   (b200_paged_decode_attn_plan); > 1 needs `workspace`
+ *   workspace     : >= b200_paged_decode_attn_workspace(B, Hq, D, num_splits) bytes of device scratch
+ * kv head j serves q heads j*g .. j*g+g-1 with g = Hq / Hkv (HF repeat_kv order).
+ */
+int b200_paged_decode_attn(void* out, const void* q, int64_t q_row_stride,
+                           const void* k_pool, const void* v_pool,
+                           const int32_t* block_tables, int table_stride, const int32_t* context_lens,
+                           int B, int Hq, int Hkv, int D, int block_size, int64_t max_blocks,
+                           float scale, int max_context_len, int num_splits,
+                           void* workspace, size_t workspace_bytes,
+                           int dtype, unsigned flags, void* stream);
+size_t b200_paged_decode_attn_workspace(int B, int Hq, int D, int num_splits);
+int b200_paged_decode_attn_plan(int B, int Hq, int Hkv, int D, int block_size, int max_context_len, int dtype);
+
+/*
+ * KV block pack / unpack for the prefill -> decode hand-off.  Replaces the per-block, per-layer
+ * TensorSerializer.serialize -> wire -> deserialize -> block.keys.copy_ round trip of
+ * InferenceServicer.TransferKVCache (worker/distributed/grpc_server.py:190-235) and
+ * DistributedKVCacheManager._promote_to_gpu (worker/distributed/kv_cache.py:447-462).
+ *
+ *   packed      : [2, n_blocks, Hkv, block_size, D] — all K blocks in table order, then all V blocks
+ *   block_table : int32[n_blocks] pool slots (source slots for pack, destination slots for unpack)
+ * Equivalent to key_pool.index_select(0, table) / key_pool.index_copy_(0, table, ...), bit-exact.
+ */
+int b200_kv_pack(void* packed, const void* k_pool, const void* v_pool, const int32_t* block_table,
+                 int n_blocks, int Hkv, int D, int block_size, int64_t max_blocks, int dtype, void* stream);
+int b200_kv_unpack(void* k_pool, void* v_pool, const void* packed, const int32_t* block_table,
+                   int n_blocks, int Hkv, int D, int block_size, int64_t max_blocks, int dtype, void* stream);
+
+/*
+ * Same for all layers of a shard in one launch.  `k_pools` / `v_pools` are DEVICE arrays of n_layers pool
+ * pointers; packed is [n_layers, 2, n_blocks, Hkv, block_size, D]; one block table serves every layer
+ * (KVCachePool.allocate_sequence yields the same slots in every layer — kv_cache.py:283-313).
+ */
+int b200_kv_pack_layers(void* packed, const void* const* k_pools, const void* const* v_pools, int n_layers,
+                        const int32_t* block_table, int n_blocks, int Hkv, int D, int block_size,
+                        int64_t max_blocks, int dtype, void* stream);
+int b200_kv_unpack_layers(void* const* k_pools, void* const* v_pools, int n_layers, const void* packed,
+                          const int32_t* block_table, int n_blocks, int Hkv, int D, int block_size,
+                          int64_t max_blocks, int dtype, void* stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* B200_KV_H_ */

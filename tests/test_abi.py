@@ -1,0 +1,64 @@
+"""CPU: the C-ABI library is built, loads, and exports every symbol include/*.h declares.  No compute calls."""
+import ctypes
+import glob
+import os
+import re
+
+import pytest
+
+import dgi_b200  # noqa: F401
+from dgi_b200 import _lib, ops
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+
+
+def declared_symbols():
+    names = set()
+    for path in glob.glob(os.path.join(ROOT, "include", "*.h")):
+        text = re.sub(r"/\*.*?\*/", "", open(path).read(), flags=re.S)
+        names.update(re.findall(r"\b(b200_\w+)\s*\(", text))
+    return sorted(names)
+
+
+def test_header_declares_the_expected_surface():
+    syms = declared_symbols()
+    for must in ("b200_kv_append", "b200_paged_decode_attn", "b200_paged_decode_attn_workspace", "b200_kv_pack",
+                 "b200_kv_unpack", "b200_kv_pack_layers", "b200_kv_unpack_layers", "b200_last_error",
+                 "b200_abi_version"):
+        assert must in syms
+
+
+def test_library_exports_every_declared_symbol():
+    assert os.path.exists(_lib.LIB_PATH), "libb200_kv.so is not built: run __graft_entry__.build()"
+    lib = ctypes.CDLL(_lib.LIB_PATH)
+    for name in declared_symbols():
+        assert hasattr(lib, name), f"{name} declared in include/ but not exported"
+
+
+def test_loader_signatures_cover_the_header():
+    assert sorted(_lib.SIGNATURES) == declared_symbols()
+    lib = _lib.load()
+    assert lib.b200_abi_version() == 1
+    # pure host-side helpers are safe without a GPU
+    assert lib.b200_paged_decode_attn_workspace(64, 32, 128, 4) == 64 * 32 * 4 * 130 * 4
+    assert lib.b200_paged_decode_attn_workspace(64, 32, 128, 1) == 0
+    assert lib.b200_paged_decode_attn_plan(64, 32, 8, 128, 16, 2048, 2) >= 1
+
+
+def test_argument_errors_are_reported_without_a_gpu():
+    lib = _lib.load()
+    rc = lib.b200_kv_append(None, None, 0, 0, None, None, None, 4, 8, 128, 16, 10, 7, None)  # dtype 7
+    assert rc == -1 and b"unsupported dtype" in lib.b200_last_error()
+    rc = lib.b200_paged_decode_attn(None, None, 0, None, None, None, 0, None, 2, 6, 4, 128, 16, 10, 1.0, 16, 1, None, 0, 2,
+                                    0, None)
+    assert rc == -2 and b"multiple" in lib.b200_last_error()
+
+
+def test_ops_refuse_cpu_tensors():
+    import torch
+
+    k = torch.zeros(4, 2, 16, 8)
+    with pytest.raises(_lib.B200LibraryError, match="no CPU fallback"):
+        ops.kv_append(torch.zeros(1, 2, 8), torch.zeros(1, 2, 8), k, k.clone(), torch.zeros(1, dtype=torch.int64))
+    with pytest.raises(_lib.B200LibraryError):
+        ops.kv_pack(k, k.clone(), torch.zeros(1, dtype=torch.int32))
