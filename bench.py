@@ -1,0 +1,396 @@
+#!/usr/bin/env python
+"""Headline benchmark: greedy decode tokens/s of the layer-range path over paged KV (BASELINE.json).
+
+    python bench.py --gpus N --steps K --warmup W            # this repo's CUDA path
+    python bench.py --impl reference --gpus N --steps K ...  # the reference's torch CPU path (oracle port)
+
+N = 1 : BASELINE config 2 — Llama-3-8B shape, random-init bf16, block 16, batch 64, context 2k, decode.
+N > 1 : BASELINE config 4 — Llama-3-70B shape layer-sharded over N ranks (torchrun, NCCL send/recv of
+        activations), batch 128, context 4k.
+A "step" is one decode step of the whole batch.  `value` times K chained CUDA-graph steps with inputs resident
+in HBM (CUDA events, max over ranks); `e2e` times the public per-step call with host token ids in and out.
+Prints ONE JSON line on rank 0.
+"""
+from __future__ import annotations
+
+import argparse
+import json
+import os
+import statistics
+import subprocess
+import sys
+import tempfile
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+if ROOT not in sys.path:
+    sys.path.insert(0, ROOT)
+
+import torch  # noqa: E402
+
+SHAPES = {
+    "tiny": dict(hidden_size=512, num_attention_heads=8, num_key_value_heads=2, intermediate_size=1408,
+                 vocab_size=1024, num_hidden_layers=4),
+    "8b": dict(hidden_size=4096, num_attention_heads=32, num_key_value_heads=8, intermediate_size=14336,
+               vocab_size=128256, num_hidden_layers=32),
+    "70b": dict(hidden_size=8192, num_attention_heads=64, num_key_value_heads=8, intermediate_size=28672,
+                vocab_size=128256, num_hidden_layers=80),
+}
+
+
+class ShapeConfig:
+    """Attribute bag with the HF config names the shards read."""
+
+    def __init__(self, **kw):
+        self.rms_norm_eps = 1e-5
+        self.rope_theta = 500000.0
+        self.initializer_range = 0.02
+        self.__dict__.update(kw)
+        self.head_dim = self.hidden_size // self.num_attention_heads
+
+
+def measured_peaks():
+    path = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(path):
+        with open(path) as f:
+            return json.load(f), "measured"
+    return {"hbm_gbs": 6650.0, "bf16_tflops": 1590.0}, "fallback"
+
+
+# ---------------------------------------------------------------------------------------------------------
+# clocks
+# ---------------------------------------------------------------------------------------------------------
+class ClockSampler:
+    FIELDS = ("index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.active,"
+              "clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
+              "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, gpu_index: int):
+        self.gpu_index = gpu_index
+        self.proc = None
+        self.path = None
+
+    def start(self):
+        try:
+            fd, self.path = tempfile.mkstemp(suffix=".csv")
+            os.close(fd)
+            self.proc = subprocess.Popen(
+                ["nvidia-smi", f"--id={self.gpu_index}", f"--query-gpu={self.FIELDS}", "--format=csv,noheader,nounits",
+                 "-lms", "100"], stdout=open(self.path, "w"), stderr=subprocess.DEVNULL)
+        except Exception:  # noqa: BLE001 - no nvidia-smi: report nulls
+            self.proc = None
+
+    def stop(self):
+        out = {"sm_mhz": None, "sm_max_mhz": None, "reasons": []}
+        if self.proc is None:
+            return out
+        self.proc.terminate()
+        try:
+            self.proc.wait(timeout=5)
+        except Exception:  # noqa: BLE001
+            self.proc.kill()
+        sm, mx, reasons = [], [], set()
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        try:
+            for line in open(self.path):
+                parts = [p.strip() for p in line.split(",")]
+                if len(parts) < 9:
+                    continue
+                try:
+                    sm.append(float(parts[1]))
+                    mx.append(float(parts[2]))
+                except ValueError:
+                    continue
+                for name, val in zip(names, parts[5:9]):
+                    if val.lower().startswith("active"):
+                        reasons.add(name)
+            os.unlink(self.path)
+        except Exception:  # noqa: BLE001
+            pass
+        if sm:
+            out.update(sm_mhz=statistics.median(sm), sm_max_mhz=max(mx), reasons=sorted(reasons), samples=len(sm))
+        return out
+
+
+# ---------------------------------------------------------------------------------------------------------
+# reference CPU path (oracle port) — bounded sample
+# ---------------------------------------------------------------------------------------------------------
+def cpu_reference_tokens_per_s(shape: str, batch: int, ctx: int, steps: int, warmup: int, sample_layers: int = 2):
+    """Time the reference's torch path (oracle.llama_ref: ModelShard.forward restatement + legacy HF layer with
+    dense (k, v) tuples, fp32) on the host cores for `sample_layers` layers of the named shape at the full batch
+    and context, plus the embedding / final norm / lm_head once per step, and extrapolate to the full depth."""
+    from oracle import llama_ref as L
+
+    cores = os.cpu_count() or 1
+    torch.set_num_threads(cores)
+    cfg = L.RefConfig(**SHAPES[shape])
+    total_layers = cfg.num_hidden_layers
+    g = torch.Generator().manual_seed(0)
+    layers = []
+    for _ in range(sample_layers):
+        layer = L.RefDecoderLayer(cfg)
+        for p in layer.parameters():
+            if p.dim() == 2:
+                p.data.normal_(0.0, 0.02, generator=g)
+        layers.append(layer)
+    head = torch.empty(cfg.vocab_size, cfg.hidden_size).normal_(0.0, 0.02, generator=g)
+    embed = torch.empty(cfg.vocab_size, cfg.hidden_size).normal_(0.0, 0.02, generator=g)
+    norm_w = torch.ones(cfg.hidden_size)
+    start_ctx = ctx - (steps + warmup)
+    pasts = [(torch.randn(batch, cfg.num_key_value_heads, start_ctx, cfg.head_dim, generator=g),
+              torch.randn(batch, cfg.num_key_value_heads, start_ctx, cfg.head_dim, generator=g)) for _ in layers]
+    ids = torch.randint(0, cfg.vocab_size, (batch, 1), generator=g)
+    t_layers, t_ends = [], []
+    with torch.no_grad():
+        for it in range(warmup + steps):
+            pos = torch.full((batch, 1), start_ctx + it, dtype=torch.long)
+            t0 = time.perf_counter()
+            h = torch.nn.functional.embedding(ids, embed)
+            t1 = time.perf_counter()
+            for li, layer in enumerate(layers):
+                h, pasts[li] = layer(h, position_ids=pos, past_key_value=pasts[li], use_cache=True)
+            t2 = time.perf_counter()
+            logits = torch.nn.functional.linear(L.rms_norm(h, norm_w, cfg.rms_norm_eps), head)
+            ids = logits[:, 0].argmax(-1, keepdim=True)
+            t3 = time.perf_counter()
+            if it >= warmup:
+                t_layers.append(t2 - t1)
+                t_ends.append((t1 - t0) + (t3 - t2))
+    per_layer = statistics.mean(t_layers) / sample_layers
+    step_s = per_layer * total_layers + statistics.mean(t_ends)
+    return {
+        "value": batch / step_s,
+        "unit": "tokens/s",
+        "cores": cores,
+        "kind": "port",
+        "sample": (f"{sample_layers} of {total_layers} layers of the {shape} shape at batch {batch}, context "
+                   f"{start_ctx + warmup}..{ctx}, fp32, dense (k,v) cache, {steps} decode steps after {warmup} "
+                   f"warm-up; per-layer time x {total_layers} + embed/norm/lm_head per step"),
+        "ms_per_step_extrapolated": step_s * 1e3,
+        "sample_seconds": sum(t_layers) + sum(t_ends),
+    }
+
+
+def run_reference(args, workload, rank, world):
+    if rank != 0:
+        return
+    shape, batch, ctx = workload["shape"], workload["batch"], workload["context"]
+    res = cpu_reference_tokens_per_s(shape, batch, ctx, args.steps, args.warmup)
+    line = {
+        "impl": "reference",
+        "metric": "decode_tokens_per_s",
+        "value": res["value"],
+        "unit": "tokens/s",
+        "n_gpus": args.gpus,
+        "steps": args.steps,
+        "warmup": args.warmup,
+        "ms_per_step": res["ms_per_step_extrapolated"],
+        "higher_is_better": True,
+        "scaling": workload["scaling"],
+        "vs_baseline": None,
+        "dtype": "f32",
+        "data": "synthetic",
+        "config": {"workload": workload["name"], "l2": "inputs larger than L2"},
+        "cpu_baseline": {k: res[k] for k in ("value", "unit", "cores", "kind", "sample")},
+        "e2e": {"value": res["value"], "unit": "tokens/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        "gpu_launches": 0,
+    }
+    print(json.dumps(line), flush=True)
+
+
+# ---------------------------------------------------------------------------------------------------------
+# this repo's path
+# ---------------------------------------------------------------------------------------------------------
+def workload_for(args):
+    if args.workload:
+        name = args.workload
+    else:
+        name = "cfg2" if args.gpus == 1 else "cfg4"
+    table = {
+        "cfg2": dict(shape="8b", batch=64, context=2048, scaling="weak",
+                     name="configs[1]: Llama-3-8B-shape random-init bf16, 1xB200, block 16, batch 64, context 2k, decode"),
+        "cfg4": dict(shape="70b", batch=128, context=4096, scaling="strong",
+                     name=f"configs[3]: Llama-3-70B-shape layer-sharded over {args.gpus} B200, batch 128, context 4k, decode"),
+        "cfg5": dict(shape="8b", batch=8, context=32768, scaling="weak",
+                     name="configs[4]: Llama-3-8B-shape long-context decode, batch 8, context 32k"),
+        "tiny": dict(shape="tiny", batch=4, context=192, scaling="weak",
+                     name="configs[0]: tiny 4-layer model, batch 4, prompt 128, 64 decode tokens"),
+    }
+    w = dict(table[name])
+    w["key"] = name
+    if args.batch:
+        w["batch"] = args.batch
+    if args.context:
+        w["context"] = args.context
+    return w
+
+
+def fill_pools_synthetic(engine, batch, ctx_len):
+    """Kernel-level fill: K/V ~ N(0, 1) in every allocated slot (used with --synthetic-kv; default is a real prefill)."""
+    for pool in engine.pools:
+        pool.backing.normal_(0.0, 1.0)
+    engine.context_lens[:batch] = ctx_len
+    engine._host_lens[:batch] = [ctx_len] * batch
+
+
+def run_single(args, workload):
+    import dgi_b200  # noqa: F401
+    from dgi_b200 import ops
+    from dgi_b200.engine import PagedDecodeEngine
+    from dgi_b200.worker.distributed.model_shard import ModelShard
+
+    dev = "cuda:0"
+    torch.cuda.set_device(0)
+    cfg = ShapeConfig(**SHAPES[workload["shape"]])
+    B, ctx = workload["batch"], workload["context"]
+    K, W = args.steps, args.warmup
+    total_steps = 2 * (K + W) + K + 2  # device loop + e2e loop + instrumented pass
+    P = ctx - total_steps
+    if P < 1:
+        raise SystemExit("context too short for the requested steps")
+    t_setup = time.time()
+    shard = ModelShard.from_config(cfg, 0, cfg.num_hidden_layers, device=dev, dtype=torch.bfloat16, seed=0)
+    eng = PagedDecodeEngine([shard], max_batch=B, max_seq_len=ctx, block_size=16, prefill_chunk=args.prefill_chunk)
+    eng.allocate(B, ctx)
+    prompts = torch.randint(0, cfg.vocab_size, (B, P), generator=torch.Generator().manual_seed(1234))
+    if args.synthetic_kv:
+        fill_pools_synthetic(eng, B, P)
+        first = prompts[:, -1].to(dev)
+    else:
+        first = eng.prefill(prompts)
+    torch.cuda.synchronize()
+    setup_s = time.time() - t_setup
+
+    sampler = ClockSampler(0)
+    # ---- device-resident loop: K chained graph replays --------------------------------------------------
+    eng.ids_buf[:B, 0].copy_(first)
+    for _ in range(W):
+        eng.decode_step_device()
+    torch.cuda.synchronize()
+    sampler.start()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for _ in range(K):
+        eng.decode_step_device()
+    e1.record()
+    torch.cuda.synchronize()
+    dev_ms = e0.elapsed_time(e1)
+
+    # ---- end to end: host ids in (pinned H2D) and out (D2H) every step through the public call ------------
+    nxt = eng.next_tokens[:B].cpu()
+    for _ in range(W):
+        nxt = eng.decode_step(nxt)
+    torch.cuda.synchronize()
+    t0 = time.perf_counter()
+    for _ in range(K):
+        nxt = eng.decode_step(nxt)
+    torch.cuda.synchronize()
+    e2e_s = time.perf_counter() - t0
+    clocks = sampler.stop()
+
+    # ---- instrumented pass: same steps launched eagerly with CUDA events around every attention launch ----
+    eng.use_cuda_graph = False
+    ops.ATTN_EVENTS = []
+    eng.ids_buf[:B, 0].copy_(nxt.to(dev))
+    n_inst = min(K, 4)
+    for _ in range(n_inst):
+        eng.decode_step_device()
+    torch.cuda.synchronize()
+    ev = ops.ATTN_EVENTS
+    ops.ATTN_EVENTS = None
+    attn_ms = [a.elapsed_time(b) for a, b in ev]
+    attn_ms_mean = statistics.mean(attn_ms) if attn_ms else float("nan")
+    ctx_now = P + 1 + 2 * (K + W) + n_inst // 2  # mean context during the instrumented pass
+    es = 2
+    algo_bytes = B * ctx_now * 2 * eng.Hkv * eng.D * es + 2 * B * eng.Hq * eng.D * es
+    peaks, peak_kind = measured_peaks()
+    achieved = algo_bytes / (attn_ms_mean * 1e-3) / 1e9
+    traffic = None
+    tpath = os.path.join(ROOT, "profiles", "attn_traffic.json")
+    if os.path.exists(tpath):
+        try:
+            traffic = json.load(open(tpath)).get(workload["key"])
+        except Exception:  # noqa: BLE001
+            traffic = None
+    launches_per_step = cfg.num_hidden_layers * (2 + (1 if eng.num_splits > 1 else 0))
+
+    line = {
+        "metric": "decode_tokens_per_s",
+        "value": B * K / (dev_ms * 1e-3),
+        "unit": "tokens/s",
+        "n_gpus": 1,
+        "steps": K,
+        "warmup": W,
+        "ms_per_step": dev_ms / K,
+        "higher_is_better": True,
+        "scaling": workload["scaling"],
+        "vs_baseline": None,
+        "dtype": "bf16",
+        "data": "synthetic",
+        "config": {
+            "workload": workload["name"],
+            "block_size": 16,
+            "batch": B,
+            "context": f"{P + 1 + W}..{P + W + K} during the timed steps",
+            "kv_fill": "synthetic normal(0,1)" if args.synthetic_kv else "real prefill of random prompts",
+            "l2": "inputs larger than L2 (weights 16 GB + KV 17 GB streamed per step)",
+            "attn_splits": eng.num_splits,
+            "setup_s": round(setup_s, 1),
+        },
+        "clocks": clocks,
+        "e2e": {"value": B * K / e2e_s, "unit": "tokens/s", "h2d_bytes_per_step": B * 8, "d2h_bytes_per_step": B * 8,
+                "ms_per_step": e2e_s / K * 1e3},
+        "gpu_launches": launches_per_step * K,
+        "roofline": {
+            "bound": "hbm",
+            "kernel": "paged_attn_tma_kernel (b200_paged_decode_attn)",
+            "achieved": achieved,
+            "peak": peaks["hbm_gbs"],
+            "peak_source": f"MEASURED_PEAKS.json ({peak_kind})",
+            "unit": "GB/s",
+            "frac": achieved / peaks["hbm_gbs"],
+            "frac_of_nominal_8TBs": achieved / 8000.0,
+            "traffic": traffic,
+            "algorithmic_bytes_per_launch": algo_bytes,
+            "launch_ms": attn_ms_mean,
+            "launches_timed": len(attn_ms),
+            "how": "CUDA events around each attention launch of eagerly launched decode steps (same state as the timed loop)",
+        },
+    }
+    if not args.no_cpu_baseline:
+        res = cpu_reference_tokens_per_s(workload["shape"], B, ctx, steps=2, warmup=1)
+        line["cpu_baseline"] = {k: res[k] for k in ("value", "unit", "cores", "kind", "sample")}
+    print(json.dumps(line), flush=True)
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=16)
+    ap.add_argument("--warmup", type=int, default=4)
+    ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
+    ap.add_argument("--workload", default="", help="cfg2 | cfg4 | cfg5 | tiny (default: by --gpus)")
+    ap.add_argument("--batch", type=int, default=0)
+    ap.add_argument("--context", type=int, default=0)
+    ap.add_argument("--synthetic-kv", action="store_true", help="fill KV pools with N(0,1) instead of a real prefill")
+    ap.add_argument("--prefill-chunk", type=int, default=8)
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    args = ap.parse_args()
+    if args.warmup < 3:
+        args.warmup = 3
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    workload = workload_for(args)
+    if args.impl == "reference":
+        run_reference(args, workload, rank, world)
+        return
+    if world == 1 and args.gpus == 1:
+        run_single(args, workload)
+    else:
+        from dgi_b200.bench_pipeline import run_pipeline  # multi-GPU layer-sharded decode
+
+        run_pipeline(args, workload, SHAPES, ShapeConfig, ClockSampler, measured_peaks, cpu_reference_tokens_per_s)
+
+
+if __name__ == "__main__":
+    main()

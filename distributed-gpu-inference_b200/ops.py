@@ -17,6 +17,10 @@ DTYPE_ID = {torch.float16: 0, torch.float32: 1, torch.bfloat16: 2}
 ATTN_FORCE_GENERIC = 1
 ATTN_ROUND_SCORES = 2
 
+# bench.py instrumentation: when set to a list, every attention call appends a (start, end) CUDA-event pair
+# recorded on the launching stream around the C-ABI call.
+ATTN_EVENTS = None
+
 
 def _dtype_id(t: torch.Tensor) -> int:
     try:
@@ -140,11 +144,18 @@ def paged_decode_attention(
             workspace = torch.empty(need, dtype=torch.uint8, device=q.device)
         ws_ptr, ws_bytes = workspace.data_ptr(), workspace.numel() * workspace.element_size()
     table_stride = block_tables.stride(0) if B > 1 else block_tables.shape[1]
+    events = ATTN_EVENTS
+    if events is not None:
+        ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        ev0.record()
     rc = lib.b200_paged_decode_attn(
         out.data_ptr(), q.data_ptr(), q_stride, k_pool.data_ptr(), v_pool.data_ptr(), block_tables.data_ptr(),
         table_stride, context_lens.data_ptr(), B, Hq, Hkv, D, bs, max_blocks, float(scale), int(max_context_len),
         int(num_splits), ws_ptr, ws_bytes, dt, int(flags), _stream(),
     )
+    if events is not None:
+        ev1.record()
+        events.append((ev0, ev1))
     _lib.check(rc, "b200_paged_decode_attn")
     return out
 
