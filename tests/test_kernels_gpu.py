@@ -196,7 +196,8 @@ def test_attention_vs_reference_eager_recipe_bf16():
         print(f"flags={flags}: vs eager relL2 {l2:.2e} per-row {_rel_err(out, eager):.2e}; "
               f"vs exact {_rel_err(out, exact):.2e}; eager vs exact {eager_vs_exact:.2e}")
         assert l2 <= 1e-2
-        assert _rel_err(out, exact) <= 1e-2
+        # with ROUND_SCORES the kernel takes over the eager recipe's bf16 rounding of the scores, and its error too
+        assert _rel_err(out, exact) <= (1.5e-2 if flags & ops.ATTN_ROUND_SCORES else 1e-2)
         assert _rel_err(out, eager) <= eager_vs_exact + _rel_err(out, exact)
 
 
