@@ -26,6 +26,11 @@ SIGNATURES = {
         [c_void_p, c_void_p, c_int64, c_void_p, c_void_p, c_void_p, c_int, c_void_p, c_int, c_int, c_int, c_int, c_int,
          c_int64, c_float, c_int, c_int, c_void_p, c_size_t, c_int, c_uint, c_void_p],
     ),
+    "b200_paged_decode_attn_static": (
+        c_int,
+        [c_void_p, c_void_p, c_int64, c_void_p, c_void_p, c_void_p, c_int, c_void_p, c_int, c_int, c_int, c_int, c_int,
+         c_int64, c_float, c_int, c_int, c_int, c_uint, c_void_p],
+    ),
     "b200_paged_decode_attn_workspace": (c_size_t, [c_int, c_int, c_int, c_int]),
     "b200_paged_decode_attn_plan": (c_int, [c_int, c_int, c_int, c_int, c_int, c_int, c_int]),
     "b200_kv_pack": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_int, c_int, c_int, c_int, c_int64, c_int, c_void_p]),

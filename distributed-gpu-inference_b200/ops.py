@@ -160,6 +160,48 @@ def paged_decode_attention(
     return out
 
 
+STATIC_SCRATCH_BYTES = 8 * 1024 * 1024
+
+
+def paged_decode_attention_static(
+    q: torch.Tensor,
+    k_pool: torch.Tensor,
+    v_pool: torch.Tensor,
+    block_tables: torch.Tensor,
+    context_lens: torch.Tensor,
+    max_context_len: int,
+    out: torch.Tensor,
+    scale: Optional[float] = None,
+    num_splits: int = 0,
+    flags: int = 0,
+) -> torch.Tensor:
+    """``paged_decode_attention`` for callers that may not allocate: nothing is allocated here or below.
+
+    Meant for code that only holds pointers it was given — an extension living inside another serving runtime that
+    bans allocation on its hot path, or a binding with no tensor library behind it.  ``out`` must be supplied; the
+    split-K partials go to the library's built-in 8 MiB scratch array instead of a workspace tensor.  Shapes whose
+    partials exceed that raise; the first call per device performs a one-time address look-up, so issue it before
+    any stream capture; calls that overlap on the GPU (different streams) race on the shared array.
+    """
+    _need_cuda(q, k_pool, v_pool, block_tables, context_lens, out)
+    max_blocks, Hkv, bs, D = _pool_dims(k_pool)
+    B, Hq = q.shape[0], q.shape[1]
+    if tuple(out.shape) != (B, Hq, D) or not out.is_contiguous() or out.dtype != q.dtype:
+        raise ValueError("out must be a contiguous [B, Hq, D] tensor of q's dtype")
+    if block_tables.dtype != torch.int32 or context_lens.dtype != torch.int32:
+        raise ValueError("block_tables and context_lens must be int32")
+    q_stride = _row_stride(q, Hq, D)
+    table_stride = block_tables.stride(0) if B > 1 else block_tables.shape[1]
+    rc = _lib.load().b200_paged_decode_attn_static(
+        out.data_ptr(), q.data_ptr(), q_stride, k_pool.data_ptr(), v_pool.data_ptr(), block_tables.data_ptr(),
+        table_stride, context_lens.data_ptr(), B, Hq, Hkv, D, bs, max_blocks,
+        float(D) ** -0.5 if scale is None else float(scale), int(max_context_len), int(num_splits), _dtype_id(k_pool),
+        int(flags), _stream(),
+    )
+    _lib.check(rc, "b200_paged_decode_attn_static")
+    return out
+
+
 def _check_table(block_table: torch.Tensor) -> int:
     if block_table.dtype != torch.int32 or block_table.dim() != 1 or not block_table.is_contiguous():
         raise ValueError("block_table must be a contiguous int32 vector")

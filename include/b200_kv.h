@@ -9,7 +9,8 @@
  *   - extern "C", plain pointers and sizes; no torch / C++ types cross the boundary.
  *   - every data pointer is a DEVICE pointer owned by the caller and kept alive until the stream has run.
  *   - work is enqueued on `stream` (a cudaStream_t passed as void*); nothing here synchronises, allocates
- *     or frees device memory, so calls may be captured into a CUDA graph.
+ *     or frees device memory, so calls may be captured into a CUDA graph (b200_paged_decode_attn_static has a
+ *     one-time set-up step of its own; see its comment).
  *   - return value: 0 on success, otherwise a negative B200_E* code (argument errors) or a positive
  *     cudaError_t; b200_last_error() returns a thread-local description of the last failure.
  *   - `dtype` uses the reference's wire ids (common/serialization.py:20-27):
@@ -82,6 +83,32 @@ int b200_paged_decode_attn(void* out, const void* q, int64_t q_row_stride,
                            int dtype, unsigned flags, void* stream);
 size_t b200_paged_decode_attn_workspace(int B, int Hq, int D, int num_splits);
 int b200_paged_decode_attn_plan(int B, int Hq, int Hkv, int D, int block_size, int max_context_len, int dtype);
+
+/*
+ * Paged decode attention for callers that cannot allocate device memory.  No counterpart in the reference: it
+ * exists for hosts that are handed pointers and nothing else — a plugin inside another runtime's serving loop
+ * where cudaMalloc is off limits because it stalls the whole device, or a binding without an allocator behind it
+ * (cgo / JNI / bare ctypes with no torch underneath).
+ *
+ * Same arguments and result as b200_paged_decode_attn, minus the workspace: the split-K partials go to an array
+ * of B200_STATIC_SCRATCH_BYTES that is part of the library image (each GPU that loads the library holds it until
+ * the process exits).  The call itself never calls cudaMalloc / cudaFree or any allocating routine.
+ *   - Sizes whose partials do not fit (b200_paged_decode_attn_workspace(B, Hq, D, num_splits) >
+ *     B200_STATIC_SCRATCH_BYTES) are rejected with B200_ENOSPC; pass a smaller num_splits (1 needs no scratch).
+ *   - The first call on each device looks up the array's device address (with that device current).  Make that
+ *     first call before starting any stream capture on the device.
+ *   - All calls on a device share the one array, which keeps the previous call's partials.  Nothing in it needs
+ *     to be zero beforehand (every call rewrites all it reads), but two calls that overlap on the GPU — different
+ *     streams, or different host threads feeding different streams — race on it.  Keep them on one stream, or
+ *     order them with events.
+ */
+#define B200_STATIC_SCRATCH_BYTES (8 * 1024 * 1024)
+int b200_paged_decode_attn_static(void* out, const void* q, int64_t q_row_stride,
+                                  const void* k_pool, const void* v_pool,
+                                  const int32_t* block_tables, int table_stride, const int32_t* context_lens,
+                                  int B, int Hq, int Hkv, int D, int block_size, int64_t max_blocks,
+                                  float scale, int max_context_len, int num_splits,
+                                  int dtype, unsigned flags, void* stream);
 
 /*
  * KV block pack / unpack for the prefill -> decode hand-off.  Replaces the per-block, per-layer
