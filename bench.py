@@ -175,7 +175,7 @@ def run_reference(args, workload, rank, world):
     if rank != 0:
         return
     shape, batch, ctx = workload["shape"], workload["batch"], workload["context"]
-    res = cpu_reference_tokens_per_s(shape, batch, ctx, args.steps, args.warmup)
+    res = cpu_reference_tokens_per_s(shape, batch, ctx, args.steps, args.warmup, sample_layers=2 if shape != "70b" else 1)
     line = {
         "impl": "reference",
         "metric": "decode_tokens_per_s",
@@ -375,6 +375,8 @@ def main():
     ap.add_argument("--synthetic-kv", action="store_true", help="fill KV pools with N(0,1) instead of a real prefill")
     ap.add_argument("--prefill-chunk", type=int, default=8)
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--micro-batches", type=int, default=0, help="pipeline micro-batches (default: one per rank)")
+    ap.add_argument("--real-prefill", action="store_true", help="multi-GPU: run a real prompt pass instead of synthetic KV")
     args = ap.parse_args()
     if args.warmup < 3:
         args.warmup = 3

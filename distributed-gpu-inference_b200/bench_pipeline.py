@@ -1,0 +1,152 @@
+"""bench.py's multi-GPU leg: layer-sharded decode over N ranks (BASELINE config 4 by default).
+
+Launched by torchrun, one rank per GPU.  Rank r builds layers ``get_layer_range_for_worker(L, N, r)`` of the
+named shape (random-init, same seed scheme on every partition), one ``PagedDecodeEngine`` per micro-batch, and
+joins a ``LayerPipeline``.  Timed region: K decode steps of all micro-batches, bracketed by barrier +
+synchronize, CUDA events on every rank, MAX over ranks.
+"""
+from __future__ import annotations
+
+import json
+import os
+import statistics
+import time
+
+import torch
+import torch.distributed as dist
+
+from . import ops
+from .engine import PagedDecodeEngine
+from .pipeline import LayerPipeline, make_pipeline_groups
+from .worker.distributed.model_shard import ModelShard, get_layer_range_for_worker
+
+
+def run_pipeline(args, workload, SHAPES, ShapeConfig, ClockSampler, measured_peaks, cpu_reference):
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local = int(os.environ.get("LOCAL_RANK", str(rank)))
+    torch.cuda.set_device(local)
+    dev = f"cuda:{local}"
+    dist.init_process_group("nccl", device_id=torch.device(dev))
+    try:
+        _run(args, workload, SHAPES, ShapeConfig, ClockSampler, measured_peaks, rank, world, local, dev)
+    finally:
+        dist.destroy_process_group()
+
+
+def _run(args, workload, SHAPES, ShapeConfig, ClockSampler, measured_peaks, rank, world, local, dev):
+    cfg = ShapeConfig(**SHAPES[workload["shape"]])
+    B, ctx = workload["batch"], workload["context"]
+    K, W = args.steps, args.warmup
+    M = getattr(args, "micro_batches", 0) or world
+    if B % M:
+        raise SystemExit(f"batch {B} not divisible into {M} micro-batches")
+    mb = B // M
+    total_steps = 2 * (K + W) + 4
+    P = ctx - total_steps
+    start, end = get_layer_range_for_worker(cfg.num_hidden_layers, world, rank)
+    t0 = time.time()
+    shard = ModelShard.from_config(cfg, start, end, device=dev, dtype=torch.bfloat16, seed=0)
+    engines = [PagedDecodeEngine([shard], max_batch=mb, max_seq_len=ctx, block_size=16, prefill_chunk=2) for _ in range(M)]
+    for e in engines:
+        e.allocate(mb, ctx)
+    groups = make_pipeline_groups(world, warm_up_device=torch.device(dev))
+    pipe = LayerPipeline(engines, rank, world, groups)
+    synthetic = not getattr(args, "real_prefill", False)
+    gen = torch.Generator().manual_seed(1234)
+    prompts = [torch.randint(0, cfg.vocab_size, (mb, P), generator=gen) for _ in range(M)]
+    if synthetic:
+        for e in engines:
+            for pool in e.pools:
+                pool.backing.normal_(0.0, 1.0)
+            e.context_lens[:mb] = P
+        firsts = [p[:, -1].to(dev) for p in prompts]
+    else:
+        firsts = pipe.prefill([p.to(dev) for p in prompts] if rank == 0 else None, P, chunk=2)
+    if rank == 0:
+        pipe.set_first_tokens(firsts)
+    torch.cuda.synchronize()
+    setup_s = time.time() - t0
+
+    def timed(steps, host_roundtrip):
+        dist.barrier()
+        torch.cuda.synchronize()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        pipe.decode(steps, host_roundtrip=host_roundtrip)
+        e1.record()
+        torch.cuda.synchronize()
+        dist.barrier()
+        ms = torch.tensor([e0.elapsed_time(e1)], device=dev)
+        dist.all_reduce(ms, op=dist.ReduceOp.MAX)
+        return float(ms.item())
+
+    pipe.decode(W)  # warm-up: graph capture, communicator bring-up
+    sampler = ClockSampler(local)
+    if rank == 0:
+        sampler.start()
+    dev_ms = timed(K, host_roundtrip=False)
+    pipe.decode(W, host_roundtrip=True)
+    e2e_ms = timed(K, host_roundtrip=True)
+    clocks = sampler.stop() if rank == 0 else None
+
+    # attention launch time on this rank's first micro-batch, eagerly launched (no comm; state advances locally)
+    eng = engines[0]
+    eng.use_cuda_graph = False
+    ops.ATTN_EVENTS = []
+    for _ in range(2):
+        eng.stage_step()
+    torch.cuda.synchronize()
+    ev, ops.ATTN_EVENTS = ops.ATTN_EVENTS, None
+    attn_ms = statistics.mean(a.elapsed_time(b) for a, b in ev)
+    ctx_now = P + 2 * (K + W) + 1
+    algo = mb * ctx_now * 2 * eng.Hkv * eng.D * 2 + 2 * mb * eng.Hq * eng.D * 2
+    if rank != 0:
+        return
+    peaks, kind = measured_peaks()
+    achieved = algo / (attn_ms * 1e-3) / 1e9
+    layers_here = end - start
+    per_step = M * layers_here * (2 + (1 if eng.num_splits > 1 else 0))
+    line = {
+        "metric": "decode_tokens_per_s",
+        "value": B * K / (dev_ms * 1e-3),
+        "unit": "tokens/s",
+        "n_gpus": world,
+        "steps": K,
+        "warmup": W,
+        "ms_per_step": dev_ms / K,
+        "higher_is_better": True,
+        "scaling": workload["scaling"],
+        "vs_baseline": None,
+        "dtype": "bf16",
+        "data": "synthetic",
+        "config": {
+            "workload": workload["name"],
+            "parallelism": f"layer ranges over {world} ranks (pp{world}), {M} micro-batches of {mb}",
+            "block_size": 16,
+            "batch": B,
+            "context": f"{P + W + 1}..{P + W + K} during the timed steps",
+            "kv_fill": "synthetic normal(0,1)" if synthetic else "real prefill of random prompts",
+            "l2": "inputs larger than L2 (each rank streams its weights once per micro-batch plus its KV per step)",
+            "attn_splits": eng.num_splits,
+            "setup_s": round(setup_s, 1),
+        },
+        "clocks": clocks,
+        "e2e": {"value": B * K / (e2e_ms * 1e-3), "unit": "tokens/s", "h2d_bytes_per_step": B * 8,
+                "d2h_bytes_per_step": B * 8, "ms_per_step": e2e_ms / K},
+        "gpu_launches": per_step * K,
+        "roofline": {
+            "bound": "hbm",
+            "kernel": "paged_attn_tma_kernel (b200_paged_decode_attn), one micro-batch on rank 0",
+            "achieved": achieved,
+            "peak": peaks["hbm_gbs"],
+            "peak_source": f"MEASURED_PEAKS.json ({kind})",
+            "unit": "GB/s",
+            "frac": achieved / peaks["hbm_gbs"],
+            "traffic": None,
+            "algorithmic_bytes_per_launch": algo,
+            "launch_ms": attn_ms,
+            "launches_timed": len(ev),
+        },
+    }
+    print(json.dumps(line), flush=True)

@@ -16,17 +16,20 @@ namespace {
 
 inline int ceil_div(int a, int b) { return (a + b - 1) / b; }
 
-// How many partitions of the context each (sequence, kv head) pair gets.  The pairs alone rarely fill the
-// machine evenly (B*Hkv CTAs against 148 SMs x resident CTAs), so the context is cut until there are several
-// waves of CTAs, while keeping every partition at least `min_blocks` KV blocks long so the per-CTA pipeline
-// ramp stays amortised.
+// How many partitions of the context each (sequence, kv head) pair gets.  Measured on B200 (tools/kbench.py,
+// profiles/r01_kbench.log): at config 2 (512 pairs) one partition streams at 98 % of the copy peak and every
+// extra split costs 4-20 % (partials + combine + ramp), so the context is only cut when the pairs alone cannot
+// give each of the 148 SMs its two resident CTAs; then it is cut to about `kTargetCtas` CTAs, keeping every
+// partition at least 256 tokens long so the per-CTA pipeline ramp stays amortised.
+constexpr int kTargetCtas = kNumSMs * 4;
+
 int plan_splits(int B, int Hkv, int block_size, int max_context_len) {
   const int n_blocks = std::max(1, ceil_div(std::max(1, max_context_len), block_size));
   const int pairs = std::max(1, B * Hkv);
-  const int min_blocks = std::max(1, 256 / block_size);  // >= 256 tokens per partition
+  if (pairs >= kNumSMs * 2) return 1;
+  const int min_blocks = std::max(1, 256 / block_size);
   const int max_by_len = std::max(1, n_blocks / min_blocks);
-  const int target_ctas = kNumSMs * 8;                   // ~4 waves at 2 resident CTAs per SM
-  int splits = std::max(1, ceil_div(target_ctas, pairs));
+  int splits = std::max(1, ceil_div(kTargetCtas, pairs));
   splits = std::min(splits, max_by_len);
   return std::min(splits, 128);
 }

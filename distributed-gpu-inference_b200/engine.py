@@ -54,7 +54,7 @@ class PagedDecodeEngine:
         self.blocks_per_seq = (max_seq_len + block_size - 1) // block_size
         self.use_cuda_graph = use_cuda_graph
         self.prefill_mode = prefill_mode
-        self.prefill_chunk = prefill_chunk
+        self.prefill_chunk_size = prefill_chunk
         self.Hq = cfg.num_attention_heads
         self.Hkv = getattr(cfg, "num_key_value_heads", self.Hq) or self.Hq
         self.D = getattr(cfg, "head_dim", None) or cfg.hidden_size // self.Hq
@@ -74,8 +74,13 @@ class PagedDecodeEngine:
         dev = self.device
         self.block_tables = torch.zeros((max_batch, self.blocks_per_seq), dtype=torch.int32, device=dev)
         self.context_lens = torch.zeros((max_batch,), dtype=torch.int32, device=dev)
+        self.is_first = bool(self.shards[0].is_first_shard)
+        self.is_last = bool(self.shards[-1].is_last_shard)
         self.ids_buf = torch.zeros((max_batch, 1), dtype=torch.int64, device=dev)
         self.next_tokens = torch.zeros((max_batch,), dtype=torch.int64, device=dev)
+        # a middle / last stage takes hidden states in, a first / middle stage hands hidden states out
+        self.h_in = None if self.is_first else torch.zeros((max_batch, 1, cfg.hidden_size), dtype=self.dtype, device=dev)
+        self.h_out = None if self.is_last else torch.zeros((max_batch, 1, cfg.hidden_size), dtype=self.dtype, device=dev)
         self.num_splits = ops.attn_plan(max_batch, self.Hq, self.Hkv, self.D, block_size, max_seq_len, self.dtype)
         ws = ops.attn_workspace_bytes(max_batch, self.Hq, self.D, self.num_splits)
         self.workspace = torch.empty(max(ws, 16), dtype=torch.uint8, device=dev)
@@ -140,38 +145,49 @@ class PagedDecodeEngine:
 
     # ---- prefill -------------------------------------------------------------------------------------
     @torch.no_grad()
+    def prefill_chunk(self, lo: int, hi: int, inputs: torch.Tensor) -> torch.Tensor:
+        """Prompt pass for sequences ``lo..hi-1`` through this engine's shards.
+
+        ``inputs`` is ``[n, P]`` token ids on a first stage, ``[n, P, hidden]`` hidden states otherwise.  Returns the
+        first generated token ``[n]`` on a last stage, the hidden states ``[n, P, hidden]`` otherwise.
+        """
+        n, P = inputs.shape[0], inputs.shape[1]
+        bs = self.block_size
+        t = torch.arange(P, device=self.device)
+        tables = self.block_tables[lo:hi].to(torch.int64)
+        slots = tables[:, t // bs] * bs + (t % bs)[None, :]
+        pos = t[None, :].expand(n, P)
+        chunk_state = PagedBatchState(
+            block_tables=self.block_tables[lo:hi],
+            context_lens=torch.full((n,), P, dtype=torch.int32, device=self.device),
+            slot_mapping=slots.reshape(-1).contiguous(),
+            max_context_len=P,
+            prefill_mode=self.prefill_mode,
+        )
+        chunk_state.cos, chunk_state.sin = rope_tables(pos, self.inv_freq, self.dtype)
+        h = inputs.to(self.device)
+        for shard, handles in zip(self.shards, self._handles):
+            hs = [PagedLayerKV(hd.k_pool, hd.v_pool, chunk_state) for hd in handles]
+            h, _ = shard.forward(h, position_ids=pos, past_key_values=hs, use_cache=True)
+        self.context_lens[lo:hi] = P
+        self._host_lens[lo:hi] = [P] * n
+        if self.is_last:
+            return self.shards[-1].get_logits(h[:, -1:, :])[:, 0, :].argmax(dim=-1)
+        return h
+
+    @torch.no_grad()
     def prefill(self, prompt_ids: torch.Tensor) -> torch.Tensor:
         """Run the prompt pass for sequences ``0..B-1`` (equal lengths); returns the first generated token [B]."""
         B, P = prompt_ids.shape
         if B != self.batch:
             raise ValueError("prefill batch differs from the allocated batch")
+        if not (self.is_first and self.is_last):
+            raise RuntimeError("prefill() drives a whole model; pipeline stages use prefill_chunk()")
         prompt_ids = prompt_ids.to(self.device)
-        bs = self.block_size
-        st = self.state
         out_tokens = torch.empty((B,), dtype=torch.int64, device=self.device)
-        t = torch.arange(P, device=self.device)
-        for lo in range(0, B, self.prefill_chunk):
-            hi = min(B, lo + self.prefill_chunk)
-            n = hi - lo
-            tables = self.block_tables[lo:hi].to(torch.int64)
-            slots = tables[:, t // bs] * bs + (t % bs)[None, :]
-            pos = t[None, :].expand(n, P)
-            chunk_state = PagedBatchState(
-                block_tables=self.block_tables[lo:hi],
-                context_lens=torch.full((n,), P, dtype=torch.int32, device=self.device),
-                slot_mapping=slots.reshape(-1).contiguous(),
-                max_context_len=P,
-                prefill_mode=self.prefill_mode,
-            )
-            chunk_state.cos, chunk_state.sin = rope_tables(pos, self.inv_freq, self.dtype)
-            h = prompt_ids[lo:hi]
-            for shard, handles in zip(self.shards, self._handles):
-                hs = [PagedLayerKV(hd.k_pool, hd.v_pool, chunk_state) for hd in handles]
-                h, _ = shard.forward(h, position_ids=pos, past_key_values=hs, use_cache=True)
-            logits = self.shards[-1].get_logits(h[:, -1:, :])[:, 0, :]
-            out_tokens[lo:hi] = logits.argmax(dim=-1)
-        self.context_lens[:B] = P
-        self._host_lens[:B] = [P] * B
+        for lo in range(0, B, self.prefill_chunk_size):
+            hi = min(B, lo + self.prefill_chunk_size)
+            out_tokens[lo:hi] = self.prefill_chunk(lo, hi, prompt_ids[lo:hi])
         return out_tokens
 
     # ---- decode --------------------------------------------------------------------------------------
@@ -187,11 +203,14 @@ class PagedDecodeEngine:
         self.context_lens[:B].add_(1)
         pos2 = pos[:, None]
         st.cos, st.sin = rope_tables(pos2, self.inv_freq, self.dtype)
-        h = self.ids_buf[:B]
+        h = self.ids_buf[:B] if self.is_first else self.h_in[:B]
         for shard, handles in zip(self.shards, self._handles):
             h, _ = shard.forward(h, position_ids=pos2, past_key_values=handles, use_cache=True)
-        logits = self.shards[-1].get_logits(h)[:, 0, :]
-        torch.argmax(logits, dim=-1, out=self.next_tokens[:B])
+        if self.is_last:
+            logits = self.shards[-1].get_logits(h)[:, 0, :]
+            torch.argmax(logits, dim=-1, out=self.next_tokens[:B])
+        else:
+            self.h_out[:B].copy_(h)
 
     def _view_state(self) -> None:
         B = self.batch
@@ -215,7 +234,7 @@ class PagedDecodeEngine:
         graph = torch.cuda.CUDAGraph()
         with torch.cuda.graph(graph):
             self._step_body()
-            if chained:
+            if chained and self.is_first and self.is_last:
                 self.ids_buf[: self.batch, 0].copy_(self.next_tokens[: self.batch])
         self.context_lens.copy_(saved)  # warm-up advanced the lengths; capture itself runs nothing
         return graph
@@ -230,9 +249,22 @@ class PagedDecodeEngine:
         else:
             self._view_state()
             self._step_body()
-            self.ids_buf[: self.batch, 0].copy_(self.next_tokens[: self.batch])
+            if self.is_first and self.is_last:
+                self.ids_buf[: self.batch, 0].copy_(self.next_tokens[: self.batch])
         for b in range(self.batch):
             self._host_lens[b] += 1
+
+    @torch.no_grad()
+    def stage_step(self) -> None:
+        """One decode step of a pipeline stage on its static buffers (``ids_buf`` or ``h_in`` → ``h_out`` or
+        ``next_tokens``); the caller moves activations between stages."""
+        if self.use_cuda_graph:
+            if self._graph is None:
+                self._graph = self._capture(chained=False)
+            self._graph.replay()
+        else:
+            self._view_state()
+            self._step_body()
 
     @torch.no_grad()
     def decode_step(self, token_ids: torch.Tensor) -> torch.Tensor:

@@ -1,0 +1,156 @@
+"""GPU, 2 ranks over NCCL (skipped with fewer than 2 devices): the layer-range pipeline and the P/D KV hand-off
+against the single-process results."""
+import os
+import socket
+
+import pytest
+import torch
+import torch.distributed as dist
+import torch.multiprocessing as mp
+
+pytestmark = pytest.mark.gpu
+
+
+def _free_port():
+    with socket.socket() as s:
+        s.bind(("127.0.0.1", 0))
+        return s.getsockname()[1]
+
+
+def _pipeline_worker(rank, world, port, q):
+    import sys
+    sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+    import json
+
+    import dgi_b200  # noqa: F401
+    from dgi_b200.engine import PagedDecodeEngine
+    from dgi_b200.pipeline import LayerPipeline, make_pipeline_groups
+    from dgi_b200.testing import build_product_shards
+    from dgi_b200.worker.distributed.model_shard import get_layer_range_for_worker
+    from oracle import llama_ref as L
+
+    os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port))
+    torch.cuda.set_device(rank)
+    dev = f"cuda:{rank}"
+    dist.init_process_group("nccl", rank=rank, world_size=world, device_id=torch.device(dev))
+    try:
+        g = json.load(open(os.path.join(os.path.dirname(__file__), "golden", "tiny_decode.json")))
+        cfg = L.RefConfig(**g["config"])
+        sd = L.make_weights(cfg, seed=0)
+        rng = get_layer_range_for_worker(cfg.num_hidden_layers, world, rank)
+        shard = build_product_shards(cfg, sd, [rng], dev, torch.float32)[0]
+        prompts = torch.tensor(g["prompt_ids"])
+        M, mb, n_new = 2, 2, 24
+        engines = [PagedDecodeEngine([shard], mb, 192, prefill_mode="eager") for _ in range(M)]
+        for e in engines:
+            e.allocate(mb, 192)
+        groups = make_pipeline_groups(world, warm_up_device=torch.device(dev))
+        pipe = LayerPipeline(engines, rank, world, groups)
+        chunks = [prompts[m * mb:(m + 1) * mb].to(dev) for m in range(M)]
+        firsts = pipe.prefill(chunks if rank == 0 else None, prompts.shape[1], chunk=1)
+        if rank == 0:
+            pipe.set_first_tokens(firsts)
+        toks = pipe.decode(n_new - 1)
+        toks2 = pipe.decode(3, host_roundtrip=True)  # continues the same sequences through the host path
+        torch.cuda.synchronize()
+        if rank == 0:
+            full = torch.cat([torch.stack(firsts)[:, :, None], toks, toks2], dim=2).reshape(M * mb, -1).cpu()
+            q.put(full.tolist())
+        dist.barrier()
+    finally:
+        dist.destroy_process_group()
+
+
+@pytest.mark.skipif(torch.cuda.device_count() < 2, reason="needs 2 GPUs")
+def test_two_rank_pipeline_tokens_identical_to_reference(golden):
+    g = golden("tiny_decode.json")
+    ctx = mp.get_context("spawn")
+    q = ctx.Queue()
+    port = _free_port()
+    procs = [ctx.Process(target=_pipeline_worker, args=(r, 2, port, q)) for r in range(2)]
+    for p in procs:
+        p.start()
+    got = q.get(timeout=300)
+    for p in procs:
+        p.join(timeout=120)
+        assert p.exitcode == 0
+    assert got == [row[:27] for row in g["tokens"]]
+
+
+def _transfer_worker(rank, world, port, q):
+    import sys
+    sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+    import dgi_b200  # noqa: F401
+    from dgi_b200.kv_transfer import KVTransferEndpoint
+    from dgi_b200.worker.distributed.kv_cache import KVCachePool
+
+    os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port))
+    torch.cuda.set_device(rank)
+    dev = f"cuda:{rank}"
+    dist.init_process_group("nccl", rank=rank, world_size=world, device_id=torch.device(dev))
+    try:
+        L_, Hkv, D, bs, max_blocks, seq_len = 6, 8, 128, 16, 40, 300
+        pool = KVCachePool(L_, Hkv, D, bs, max_blocks, device=dev, dtype=torch.bfloat16)
+        ep = KVTransferEndpoint(pool, chunks=3)
+        if rank == 0:  # prefill side: some unrelated allocations first so the slots differ from the receiver's
+            pool.allocate_sequence(50)
+            blocks = pool.allocate_sequence(seq_len)
+            table = torch.tensor(KVCachePool.block_table(blocks[0]), dtype=torch.int32, device=dev)
+            gen = torch.Generator(device=dev).manual_seed(3)
+            for l in range(L_):
+                for blk in blocks[l]:
+                    blk.keys.copy_(torch.randn(blk.keys.shape, generator=gen, device=dev))
+                    blk.values.copy_(torch.randn(blk.values.shape, generator=gen, device=dev))
+            for w in ep.send(table, dst=1):
+                w.wait()
+            torch.cuda.synchronize()
+            want = torch.stack([torch.stack([pool.layer(l).key_pool[table.long()], pool.layer(l).value_pool[table.long()]])
+                                for l in range(L_)]).cpu()
+            q.put(("sent", want.view(torch.int16).numpy().tobytes()))
+        else:
+            blocks = pool.allocate_sequence(seq_len)
+            table = torch.tensor(KVCachePool.block_table(blocks[0]), dtype=torch.int32, device=dev)
+            ep.recv(table, src=0)
+            torch.cuda.synchronize()
+            got = torch.stack([torch.stack([pool.layer(l).key_pool[table.long()], pool.layer(l).value_pool[table.long()]])
+                               for l in range(L_)]).cpu()
+            q.put(("received", got.view(torch.int16).numpy().tobytes()))
+        dist.barrier()
+    finally:
+        dist.destroy_process_group()
+
+
+@pytest.mark.skipif(torch.cuda.device_count() < 2, reason="needs 2 GPUs")
+def test_pd_handoff_over_nccl_is_bit_exact():
+    ctx = mp.get_context("spawn")
+    q = ctx.Queue()
+    port = _free_port()
+    procs = [ctx.Process(target=_transfer_worker, args=(r, 2, port, q)) for r in range(2)]
+    for p in procs:
+        p.start()
+    items = dict(q.get(timeout=300) for _ in range(2))
+    for p in procs:
+        p.join(timeout=120)
+        assert p.exitcode == 0
+    assert items["sent"] == items["received"]
+
+
+def test_same_device_handoff_between_two_pools_bit_exact():
+    import dgi_b200  # noqa: F401
+    from dgi_b200.kv_transfer import KVTransferEndpoint
+    from dgi_b200.worker.distributed.kv_cache import KVCachePool
+
+    dev = "cuda:0"
+    a = KVCachePool(4, 2, 64, 16, 30, device=dev, dtype=torch.float16)
+    b = KVCachePool(4, 2, 64, 16, 30, device=dev, dtype=torch.float16)
+    a.backing.normal_()
+    sa = a.allocate_sequence(200)
+    b.allocate_sequence(40)
+    sb = b.allocate_sequence(200)
+    ta = torch.tensor(KVCachePool.block_table(sa[0]), dtype=torch.int32, device=dev)
+    tb = torch.tensor(KVCachePool.block_table(sb[0]), dtype=torch.int32, device=dev)
+    assert ta.tolist() != tb.tolist()
+    KVTransferEndpoint(a, chunks=2).copy_to(KVTransferEndpoint(b, chunks=2), ta, tb)
+    for l in range(4):
+        assert torch.equal(b.layer(l).key_pool[tb.long()], a.layer(l).key_pool[ta.long()])
+        assert torch.equal(b.layer(l).value_pool[tb.long()], a.layer(l).value_pool[ta.long()])

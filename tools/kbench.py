@@ -1,0 +1,138 @@
+#!/usr/bin/env python
+"""Kernel micro-benchmarks on one B200: paged decode attention, append, pack/unpack as GB/s of algorithmic bytes.
+
+Pools are rotated over `--layers` independent copies so consecutive launches never re-read L2-resident data
+(one layer's KV at config 2 is 537 MB, the L2 is 126 MB).  Timing: CUDA events on the launching stream, after
+warm-up, mean over the timed launches.  Prints one JSON line per case.
+"""
+import argparse
+import json
+import os
+import sys
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, ROOT)
+import torch  # noqa: E402
+
+import dgi_b200  # noqa: E402,F401
+from dgi_b200 import ops  # noqa: E402
+
+DEV = "cuda:0"
+PEAK = 6546.6
+try:
+    PEAK = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))["hbm_gbs"]
+except Exception:  # noqa: BLE001
+    pass
+
+
+def timed(fn, n, warm=3):
+    for i in range(warm):
+        fn(i)
+    torch.cuda.synchronize()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for i in range(n):
+        fn(warm + i)
+    e1.record()
+    torch.cuda.synchronize()
+    return e0.elapsed_time(e1) / n
+
+
+def attn_case(name, B, Hq, Hkv, D, ctx_lens, layers, splits, flags=0, share_prefix=0, iters=64, dtype=torch.bfloat16):
+    bs = 16
+    nblk = [(c + bs - 1) // bs for c in ctx_lens]
+    uniq_blocks = share_prefix + sum(max(0, n - share_prefix) for n in nblk)
+    max_blocks = uniq_blocks + 16
+    g = torch.Generator().manual_seed(7)
+    perm = torch.randperm(max_blocks, generator=g)
+    rows, cur = [], share_prefix
+    for n in nblk:
+        own = max(0, n - share_prefix)
+        rows.append(torch.cat([perm[:min(n, share_prefix)], perm[cur:cur + own]]))
+        cur += own
+    width = max(nblk)
+    tables = torch.zeros((B, width), dtype=torch.int32)
+    for b, r in enumerate(rows):
+        tables[b, :len(r)] = r.to(torch.int32)
+    tables = tables.to(DEV)
+    lens = torch.tensor(ctx_lens, dtype=torch.int32, device=DEV)
+    pools = [(torch.randn((max_blocks, Hkv, bs, D), device=DEV, dtype=dtype),
+              torch.randn((max_blocks, Hkv, bs, D), device=DEV, dtype=dtype)) for _ in range(layers)]
+    q = torch.randn((B, Hq, D), device=DEV, dtype=dtype)
+    out = torch.empty_like(q)
+    max_ctx = max(ctx_lens)
+    if splits == 0:
+        splits = ops.attn_plan(B, Hq, Hkv, D, bs, max_ctx, dtype)
+    ws = torch.empty(max(16, ops.attn_workspace_bytes(B, Hq, D, splits)), dtype=torch.uint8, device=DEV)
+
+    def run(i):
+        k, v = pools[i % layers]
+        ops.paged_decode_attention(q, k, v, tables, lens, max_ctx, out=out, num_splits=splits, workspace=ws, flags=flags)
+
+    ms = timed(run, iters)
+    es = 2
+    logical = sum(ctx_lens) * 2 * Hkv * D * es + 2 * B * Hq * D * es
+    unique = uniq_blocks * 2 * Hkv * bs * D * es + 2 * B * Hq * D * es
+    gbs = (unique if share_prefix else logical) / ms / 1e6
+    print(json.dumps({"kernel": "paged_decode_attn", "case": name, "B": B, "Hq": Hq, "Hkv": Hkv, "D": D,
+                      "ctx_max": max_ctx, "splits": splits, "flags": flags, "ms": round(ms, 5),
+                      "logical_bytes": logical, "unique_bytes": unique, "GBps": round(gbs, 1),
+                      "frac_of_measured_peak": round(gbs / PEAK, 4)}), flush=True)
+    del pools
+
+
+def copy_cases():
+    # pack / unpack at config 3: one 4k-token sequence of the 8B shape = 256 blocks x 32 layers x 64 KiB = 512 MiB
+    L_, Hkv, D, bs, n = 32, 8, 128, 16, 256
+    max_blocks = 1024
+    backing = torch.randn((L_, 2, max_blocks, Hkv, bs, D), device=DEV, dtype=torch.bfloat16)
+    kp = ops.pool_pointer_array([backing[l, 0] for l in range(L_)])
+    vp = ops.pool_pointer_array([backing[l, 1] for l in range(L_)])
+    tables = [torch.randperm(max_blocks, generator=torch.Generator().manual_seed(s))[:n].to(torch.int32).to(DEV) for s in range(4)]
+    packed = torch.empty((L_, 2, n, Hkv, bs, D), dtype=torch.bfloat16, device=DEV)
+    shape = (max_blocks, Hkv, bs, D)
+    payload = packed.numel() * 2
+    ms = timed(lambda i: ops.kv_pack_layers(kp, vp, shape, torch.bfloat16, tables[i % 4], out=packed), 20)
+    print(json.dumps({"kernel": "kv_pack_layers", "payload_MiB": payload / 2 ** 20, "ms": round(ms, 4),
+                      "GBps_read_plus_write": round(2 * payload / ms / 1e6, 1),
+                      "frac_of_measured_peak": round(2 * payload / ms / 1e6 / PEAK, 4)}), flush=True)
+    ms = timed(lambda i: ops.kv_unpack_layers(packed, kp, vp, shape, tables[i % 4]), 20)
+    print(json.dumps({"kernel": "kv_unpack_layers", "payload_MiB": payload / 2 ** 20, "ms": round(ms, 4),
+                      "GBps_read_plus_write": round(2 * payload / ms / 1e6, 1),
+                      "frac_of_measured_peak": round(2 * payload / ms / 1e6 / PEAK, 4)}), flush=True)
+    a, b_ = torch.empty(payload, dtype=torch.uint8, device=DEV), torch.empty(payload, dtype=torch.uint8, device=DEV)
+    ms = timed(lambda i: b_.copy_(a), 20)
+    print(json.dumps({"kernel": "torch_copy_same_bytes", "ms": round(ms, 4), "GBps_read_plus_write": round(2 * payload / ms / 1e6, 1)}), flush=True)
+    # append at decode (64 tokens) and at prefill (8 x 2048 tokens)
+    for n_tok in (64, 16384):
+        k_new = torch.randn((n_tok, Hkv, D), device=DEV, dtype=torch.bfloat16)
+        v_new = torch.randn((n_tok, Hkv, D), device=DEV, dtype=torch.bfloat16)
+        slots = torch.randperm(max_blocks * bs, device=DEV)[:n_tok].to(torch.int64)
+        ms = timed(lambda i: ops.kv_append(k_new, v_new, backing[i % L_, 0], backing[i % L_, 1], slots), 50)
+        byt = 2 * (2 * n_tok * Hkv * D * 2) + 8 * n_tok
+        print(json.dumps({"kernel": "kv_append", "n_tok": n_tok, "ms": round(ms, 5), "GBps": round(byt / ms / 1e6, 1)}), flush=True)
+
+
+if __name__ == "__main__":
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--cases", default="cfg2,cfg4,cfg5,copy")
+    ap.add_argument("--splits", type=int, default=0)
+    ap.add_argument("--iters", type=int, default=64)
+    ap.add_argument("--layers", type=int, default=8)
+    ap.add_argument("--generic", action="store_true")
+    a = ap.parse_args()
+    fl = ops.ATTN_FORCE_GENERIC if a.generic else 0
+    for c in a.cases.split(","):
+        if c == "cfg2":
+            attn_case("cfg2 8B B64 ctx2k", 64, 32, 8, 128, [2048] * 64, a.layers, a.splits, fl, iters=a.iters)
+        elif c == "cfg4":
+            attn_case("cfg4 70B B128 ctx4k (per layer)", 128, 64, 8, 128, [4096] * 128, min(a.layers, 4), a.splits, fl, iters=a.iters)
+        elif c == "cfg4mb":
+            attn_case("cfg4 70B micro-batch 16 ctx4k", 16, 64, 8, 128, [4096] * 16, a.layers, a.splits, fl, iters=a.iters)
+        elif c == "cfg5":
+            lens = [24576 + 8192 - 512 * i for i in range(8)]
+            attn_case("cfg5 8B B8 ctx32k ragged, shared 24576 prefix", 8, 32, 8, 128, lens, a.layers, a.splits, fl,
+                      share_prefix=24576 // 16, iters=a.iters)
+            attn_case("cfg5 8B B8 ctx32k ragged, unshared", 8, 32, 8, 128, lens, min(a.layers, 4), a.splits, fl, iters=a.iters)
+        elif c == "copy":
+            copy_cases()
