@@ -33,6 +33,14 @@ SIGNATURES = {
     ),
     "b200_paged_decode_attn_workspace": (c_size_t, [c_int, c_int, c_int, c_int]),
     "b200_paged_decode_attn_plan": (c_int, [c_int, c_int, c_int, c_int, c_int, c_int, c_int]),
+    "b200_add_rmsnorm": (
+        c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_float, c_int, c_int, c_int64, c_int64, c_int, c_void_p]),
+    "b200_rope_kv_append": (
+        c_int,
+        [c_void_p, c_int64, c_void_p, c_int64, c_void_p, c_int64, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_int,
+         c_int, c_int, c_int, c_int, c_int64, c_int, c_void_p],
+    ),
+    "b200_silu_mul": (c_int, [c_void_p, c_void_p, c_void_p, c_int64, c_int, c_int64, c_int64, c_int, c_void_p]),
     "b200_kv_pack": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_int, c_int, c_int, c_int, c_int64, c_int, c_void_p]),
     "b200_kv_unpack": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_int, c_int, c_int, c_int, c_int64, c_int, c_void_p]),
     "b200_kv_pack_layers": (

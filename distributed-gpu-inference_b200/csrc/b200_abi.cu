@@ -150,4 +150,24 @@ int b200_kv_unpack_layers(void* const* k_pools, void* const* v_pools, int n_laye
                           dtype, static_cast<cudaStream_t>(stream));
 }
 
+int b200_add_rmsnorm(void* out, void* resid_out, const void* x, const void* delta, const void* weight, float eps,
+                     int rows, int hidden, int64_t x_stride, int64_t d_stride, int dtype, void* stream) {
+  return add_rmsnorm(out, resid_out, x, delta, weight, eps, rows, hidden, x_stride, d_stride, dtype,
+                     static_cast<cudaStream_t>(stream));
+}
+
+int b200_rope_kv_append(void* q, int64_t q_row_stride, const void* k, int64_t k_row_stride, const void* v,
+                        int64_t v_row_stride, const void* cos_table, const void* sin_table, void* k_pool, void* v_pool,
+                        const int64_t* slot_mapping, int n_tok, int Hq, int Hkv, int D, int block_size,
+                        int64_t max_blocks, int dtype, void* stream) {
+  return rope_kv_append(q, q_row_stride, k, k_row_stride, v, v_row_stride, cos_table, sin_table, k_pool, v_pool,
+                        slot_mapping, n_tok, Hq, Hkv, D, block_size, max_blocks, dtype,
+                        static_cast<cudaStream_t>(stream));
+}
+
+int b200_silu_mul(void* out, const void* gate, const void* up, int64_t rows, int cols, int64_t gate_row_stride,
+                  int64_t up_row_stride, int dtype, void* stream) {
+  return silu_mul(out, gate, up, rows, cols, gate_row_stride, up_row_stride, dtype, static_cast<cudaStream_t>(stream));
+}
+
 }  // extern "C"

@@ -1,0 +1,269 @@
+// Fused element-wise pieces of the decoder layer that ModelShard.forward calls once per owned layer
+// (reference: worker/distributed/model_shard.py:205-222 → the HF Llama layer): residual-add + RMSNorm,
+// RoPE + paged KV append, SiLU·up.  In torch each of these is 5-10 tiny launches; at decode (64..128 rows) the
+// step is launch-bound around the GEMMs, so each becomes ONE launch here.
+//
+// Rounding contract: every kernel reproduces the rounding points of the eager torch recipe in the storage
+// dtype T (each torch op computes in fp32 and rounds its result to T):
+//   add+norm : h = T(x + d);  y = T(w * T(float(h) * rsqrt(mean(float(h)^2) + eps)))
+//   rope     : out = T( T(x * cos) + T(rot(x) * sin) ),  rot(x) = cat(-x[D/2:], x[:D/2])
+//   silu·up  : out = T( T(silu(float(g))) * u ),          silu(x) = x / (1 + exp(-x))
+// Products of two 16-bit floats are exact in fp32 and the fp32 adds are done with explicit round-to-nearest
+// intrinsics (no FMA contraction), so RoPE and SiLU·up are bit-identical to torch; the norm differs from torch
+// only through the summation order of the fp32 mean (≤ 1 ulp of fp32 before the rounding to T).
+#include <algorithm>
+#include <type_traits>
+
+#include "b200_attn.cuh"
+#include "b200_common.cuh"
+
+namespace b200 {
+
+namespace {
+
+template <typename T>
+struct Vec16 {
+  static constexpr int N = 16 / sizeof(T);
+  union {
+    int4 raw;
+    T e[16 / sizeof(T)];
+  };
+};
+
+__device__ __forceinline__ float block_sum(float v, float* red) {
+  v = warp_sum(v);
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31, nw = blockDim.x >> 5;
+  if (lane == 0) red[warp] = v;
+  __syncthreads();
+  float t = (lane < nw) ? red[lane] : 0.f;
+  t = warp_sum(t);
+  return t;  // every thread holds the total
+}
+
+// ---- residual add + RMSNorm: one CTA per row ------------------------------------------------------------
+constexpr int kNormThreads = 256;
+constexpr int kNormMaxVec = 8;  // vectors cached in registers per thread: hidden <= 256 * 8 * (16 / sizeof(T))
+
+template <typename T>
+__global__ void __launch_bounds__(kNormThreads)
+add_rmsnorm_kernel(T* __restrict__ out, T* __restrict__ resid_out, const T* __restrict__ x, const T* __restrict__ delta,
+                   const T* __restrict__ weight, float eps, int hidden, int64_t x_stride, int64_t d_stride) {
+  constexpr int VN = Vec16<T>::N;
+  __shared__ float red[32];
+  const int row = blockIdx.x;
+  const T* xr = x + row * x_stride;
+  const T* dr = delta ? delta + row * d_stride : nullptr;
+  const int nvec = hidden / VN;
+  Vec16<T> cache[kNormMaxVec];
+  float ss = 0.f;
+#pragma unroll
+  for (int i = 0; i < kNormMaxVec; ++i) {
+    const int v = threadIdx.x + i * kNormThreads;
+    if (v < nvec) {
+      cache[i].raw = *reinterpret_cast<const int4*>(xr + v * VN);
+      if (dr) {
+        Vec16<T> dv;
+        dv.raw = *reinterpret_cast<const int4*>(dr + v * VN);
+#pragma unroll
+        for (int e = 0; e < VN; ++e)
+          cache[i].e[e] = Cvt<T>::from_f32(__fadd_rn(Cvt<T>::to_f32(cache[i].e[e]), Cvt<T>::to_f32(dv.e[e])));
+        if (resid_out) *reinterpret_cast<int4*>(resid_out + static_cast<int64_t>(row) * hidden + v * VN) = cache[i].raw;
+      }
+#pragma unroll
+      for (int e = 0; e < VN; ++e) {
+        const float f = Cvt<T>::to_f32(cache[i].e[e]);
+        ss = fmaf(f, f, ss);
+      }
+    }
+  }
+  const float total = block_sum(ss, red);
+  const float inv = rsqrtf(total * (1.0f / static_cast<float>(hidden)) + eps);  // torch's mean multiplies by 1/N
+#pragma unroll
+  for (int i = 0; i < kNormMaxVec; ++i) {
+    const int v = threadIdx.x + i * kNormThreads;
+    if (v < nvec) {
+      Vec16<T> wv, ov;
+      wv.raw = *reinterpret_cast<const int4*>(weight + v * VN);
+#pragma unroll
+      for (int e = 0; e < VN; ++e) {
+        const T n = Cvt<T>::from_f32(__fmul_rn(Cvt<T>::to_f32(cache[i].e[e]), inv));
+        ov.e[e] = Cvt<T>::from_f32(__fmul_rn(Cvt<T>::to_f32(wv.e[e]), Cvt<T>::to_f32(n)));
+      }
+      *reinterpret_cast<int4*>(out + static_cast<int64_t>(row) * hidden + v * VN) = ov.raw;
+    }
+  }
+}
+
+// ---- RoPE on q (in place) and k, then K/V scatter into the pools -----------------------------------------
+// One CTA per token; thread t handles one 16-byte vector of the first half of a head together with its partner
+// vector in the second half (rotate-half pairs d and d + D/2).
+template <typename T>
+__global__ void __launch_bounds__(256)
+rope_append_kernel(T* __restrict__ q, int64_t q_stride, const T* __restrict__ k, int64_t k_stride,
+                   const T* __restrict__ v, int64_t v_stride, const T* __restrict__ cos_t, const T* __restrict__ sin_t,
+                   T* __restrict__ k_pool, T* __restrict__ v_pool, const int64_t* __restrict__ slot_mapping, int Hq,
+                   int Hkv, int D, int block_size, int64_t max_blocks) {
+  constexpr int VN = Vec16<T>::N;
+  const int tok = blockIdx.x;
+  const int half_vecs = D / 2 / VN;            // vectors in half a head
+  const int per_head = half_vecs;              // work items per head (each covers both halves)
+  const int64_t slot = slot_mapping[tok];
+  const bool store = slot >= 0 && slot / block_size < max_blocks;
+  const int64_t blk = store ? slot / block_size : 0;
+  const int64_t off = store ? slot - blk * block_size : 0;
+  const T* cs = cos_t + static_cast<int64_t>(tok) * D;
+  const T* sn = sin_t + static_cast<int64_t>(tok) * D;
+
+  const int n_items = (Hq + 2 * Hkv) * per_head;
+  for (int it = threadIdx.x; it < n_items; it += blockDim.x) {
+    const int head = it / per_head;
+    const int hv = it - head * per_head;
+    const int d0 = hv * VN;
+    if (head < Hq + Hkv) {
+      const bool is_q = head < Hq;
+      const T* src = is_q ? q + tok * q_stride + static_cast<int64_t>(head) * D
+                          : k + tok * k_stride + static_cast<int64_t>(head - Hq) * D;
+      Vec16<T> lo, hi, c_lo, c_hi, s_lo, s_hi, o_lo, o_hi;
+      lo.raw = *reinterpret_cast<const int4*>(src + d0);
+      hi.raw = *reinterpret_cast<const int4*>(src + D / 2 + d0);
+      c_lo.raw = *reinterpret_cast<const int4*>(cs + d0);
+      c_hi.raw = *reinterpret_cast<const int4*>(cs + D / 2 + d0);
+      s_lo.raw = *reinterpret_cast<const int4*>(sn + d0);
+      s_hi.raw = *reinterpret_cast<const int4*>(sn + D / 2 + d0);
+#pragma unroll
+      for (int e = 0; e < VN; ++e) {
+        const float xl = Cvt<T>::to_f32(lo.e[e]), xh = Cvt<T>::to_f32(hi.e[e]);
+        // first half: x_lo * cos - x_hi * sin ; second half: x_hi * cos + x_lo * sin
+        const T a = Cvt<T>::from_f32(__fmul_rn(xl, Cvt<T>::to_f32(c_lo.e[e])));
+        const T b = Cvt<T>::from_f32(__fmul_rn(-xh, Cvt<T>::to_f32(s_lo.e[e])));
+        o_lo.e[e] = Cvt<T>::from_f32(__fadd_rn(Cvt<T>::to_f32(a), Cvt<T>::to_f32(b)));
+        const T c = Cvt<T>::from_f32(__fmul_rn(xh, Cvt<T>::to_f32(c_hi.e[e])));
+        const T d = Cvt<T>::from_f32(__fmul_rn(xl, Cvt<T>::to_f32(s_hi.e[e])));
+        o_hi.e[e] = Cvt<T>::from_f32(__fadd_rn(Cvt<T>::to_f32(c), Cvt<T>::to_f32(d)));
+      }
+      if (is_q) {
+        T* dst = q + tok * q_stride + static_cast<int64_t>(head) * D;
+        *reinterpret_cast<int4*>(dst + d0) = o_lo.raw;
+        *reinterpret_cast<int4*>(dst + D / 2 + d0) = o_hi.raw;
+      } else if (store) {
+        T* dst = k_pool + ((blk * Hkv + (head - Hq)) * block_size + off) * D;
+        *reinterpret_cast<int4*>(dst + d0) = o_lo.raw;
+        *reinterpret_cast<int4*>(dst + D / 2 + d0) = o_hi.raw;
+      }
+    } else if (store) {
+      const int h = head - Hq - Hkv;
+      const T* src = v + tok * v_stride + static_cast<int64_t>(h) * D;
+      T* dst = v_pool + ((blk * Hkv + h) * block_size + off) * D;
+      *reinterpret_cast<int4*>(dst + d0) = *reinterpret_cast<const int4*>(src + d0);
+      *reinterpret_cast<int4*>(dst + D / 2 + d0) = *reinterpret_cast<const int4*>(src + D / 2 + d0);
+    }
+  }
+}
+
+// ---- SiLU(gate) * up -------------------------------------------------------------------------------------
+template <typename T>
+__global__ void __launch_bounds__(256)
+silu_mul_kernel(T* __restrict__ out, const T* __restrict__ gate, const T* __restrict__ up, int64_t rows, int cols,
+                int64_t g_stride, int64_t u_stride) {
+  constexpr int VN = Vec16<T>::N;
+  const int vec_per_row = cols / VN;
+  const int64_t total = rows * vec_per_row;
+  for (int64_t i = static_cast<int64_t>(blockIdx.x) * blockDim.x + threadIdx.x; i < total;
+       i += static_cast<int64_t>(gridDim.x) * blockDim.x) {
+    const int64_t r = i / vec_per_row;
+    const int c = static_cast<int>(i - r * vec_per_row) * VN;
+    Vec16<T> g, u, o;
+    g.raw = *reinterpret_cast<const int4*>(gate + r * g_stride + c);
+    u.raw = *reinterpret_cast<const int4*>(up + r * u_stride + c);
+#pragma unroll
+    for (int e = 0; e < VN; ++e) {
+      const float x = Cvt<T>::to_f32(g.e[e]);
+      const T s = Cvt<T>::from_f32(x / (1.0f + expf(-x)));
+      o.e[e] = Cvt<T>::from_f32(__fmul_rn(Cvt<T>::to_f32(s), Cvt<T>::to_f32(u.e[e])));
+    }
+    *reinterpret_cast<int4*>(out + r * cols + c) = o.raw;
+  }
+}
+
+template <typename F>
+int by_dtype(int dtype, const char* name, F&& f) {
+  switch (dtype) {
+    case B200_DTYPE_F16:
+      return f(static_cast<__half*>(nullptr));
+    case B200_DTYPE_BF16:
+      return f(static_cast<__nv_bfloat16*>(nullptr));
+    case B200_DTYPE_F32:
+      return f(static_cast<float*>(nullptr));
+    default:
+      return fail(B200_EINVAL, "%s: unsupported dtype %d", name, dtype);
+  }
+}
+
+}  // namespace
+
+int add_rmsnorm(void* out, void* resid_out, const void* x, const void* delta, const void* weight, float eps, int rows,
+                int hidden, int64_t x_stride, int64_t d_stride, int dtype, cudaStream_t s) {
+  const int es = dtype_size(dtype);
+  if (es == 0) return fail(B200_EINVAL, "b200_add_rmsnorm: unsupported dtype %d", dtype);
+  if (rows < 0 || hidden <= 0) return fail(B200_EINVAL, "b200_add_rmsnorm: bad sizes");
+  if (rows == 0) return 0;
+  if (!out || !x || !weight) return fail(B200_EINVAL, "b200_add_rmsnorm: null pointer");
+  const int vn = 16 / es;
+  if (hidden % vn != 0 || hidden / vn > kNormThreads * kNormMaxVec || (x_stride * es) % 16 != 0 ||
+      (delta && (d_stride * es) % 16 != 0) || !aligned16(out) || !aligned16(x) || !aligned16(weight) ||
+      (delta && !aligned16(delta)) || (resid_out && !aligned16(resid_out)))
+    return fail(B200_ESHAPE, "b200_add_rmsnorm: hidden=%d / alignment not supported", hidden);
+  return by_dtype(dtype, "b200_add_rmsnorm", [&](auto* tag) {
+    using T = std::remove_pointer_t<decltype(tag)>;
+    add_rmsnorm_kernel<T><<<rows, kNormThreads, 0, s>>>(static_cast<T*>(out), static_cast<T*>(resid_out),
+                                                        static_cast<const T*>(x), static_cast<const T*>(delta),
+                                                        static_cast<const T*>(weight), eps, hidden, x_stride, d_stride);
+    return check_launch("b200_add_rmsnorm");
+  });
+}
+
+int rope_kv_append(void* q, int64_t q_stride, const void* k, int64_t k_stride, const void* v, int64_t v_stride,
+                   const void* cos_t, const void* sin_t, void* k_pool, void* v_pool, const int64_t* slot_mapping,
+                   int n_tok, int Hq, int Hkv, int D, int block_size, int64_t max_blocks, int dtype, cudaStream_t s) {
+  const int es = dtype_size(dtype);
+  if (es == 0) return fail(B200_EINVAL, "b200_rope_kv_append: unsupported dtype %d", dtype);
+  if (n_tok < 0 || Hq <= 0 || Hkv <= 0 || D <= 0 || block_size <= 0 || max_blocks <= 0)
+    return fail(B200_EINVAL, "b200_rope_kv_append: bad sizes");
+  if (n_tok == 0) return 0;
+  if (!q || !k || !v || !cos_t || !sin_t || !k_pool || !v_pool || !slot_mapping)
+    return fail(B200_EINVAL, "b200_rope_kv_append: null pointer");
+  const int vn = 16 / es;
+  if ((D / 2) % vn != 0 || (q_stride * es) % 16 || (k_stride * es) % 16 || (v_stride * es) % 16 || !aligned16(q) ||
+      !aligned16(k) || !aligned16(v) || !aligned16(cos_t) || !aligned16(sin_t) || !aligned16(k_pool) || !aligned16(v_pool))
+    return fail(B200_ESHAPE, "b200_rope_kv_append: head_dim %d / alignment not supported", D);
+  return by_dtype(dtype, "b200_rope_kv_append", [&](auto* tag) {
+    using T = std::remove_pointer_t<decltype(tag)>;
+    rope_append_kernel<T><<<n_tok, 256, 0, s>>>(static_cast<T*>(q), q_stride, static_cast<const T*>(k), k_stride,
+                                                static_cast<const T*>(v), v_stride, static_cast<const T*>(cos_t),
+                                                static_cast<const T*>(sin_t), static_cast<T*>(k_pool),
+                                                static_cast<T*>(v_pool), slot_mapping, Hq, Hkv, D, block_size, max_blocks);
+    return check_launch("b200_rope_kv_append");
+  });
+}
+
+int silu_mul(void* out, const void* gate, const void* up, int64_t rows, int cols, int64_t g_stride, int64_t u_stride,
+             int dtype, cudaStream_t s) {
+  const int es = dtype_size(dtype);
+  if (es == 0) return fail(B200_EINVAL, "b200_silu_mul: unsupported dtype %d", dtype);
+  if (rows < 0 || cols <= 0) return fail(B200_EINVAL, "b200_silu_mul: bad sizes");
+  if (rows == 0) return 0;
+  if (!out || !gate || !up) return fail(B200_EINVAL, "b200_silu_mul: null pointer");
+  const int vn = 16 / es;
+  if (cols % vn || (g_stride * es) % 16 || (u_stride * es) % 16 || !aligned16(out) || !aligned16(gate) || !aligned16(up))
+    return fail(B200_ESHAPE, "b200_silu_mul: cols=%d / alignment not supported", cols);
+  const int64_t total = rows * (cols / vn);
+  const int grid = static_cast<int>(std::min<int64_t>((total + 255) / 256, kNumSMs * 16));
+  return by_dtype(dtype, "b200_silu_mul", [&](auto* tag) {
+    using T = std::remove_pointer_t<decltype(tag)>;
+    silu_mul_kernel<T><<<grid, 256, 0, s>>>(static_cast<T*>(out), static_cast<const T*>(gate),
+                                            static_cast<const T*>(up), rows, cols, g_stride, u_stride);
+    return check_launch("b200_silu_mul");
+  });
+}
+
+}  // namespace b200

@@ -84,6 +84,70 @@ def kv_append(
     _lib.check(rc, "b200_kv_append")
 
 
+def add_rmsnorm(x: torch.Tensor, weight: torch.Tensor, eps: float, delta: Optional[torch.Tensor] = None,
+                want_residual: bool = False):
+    """``h = x + delta`` (if given) then ``weight * rmsnorm(h)``; returns ``out`` or ``(out, h)``.
+
+    ``x`` / ``delta``: ``[..., hidden]`` with a contiguous last dim and uniform row stride; outputs are contiguous.
+    """
+    _need_cuda(x, weight)
+    hidden = x.shape[-1]
+    x2 = x.reshape(-1, hidden) if x.is_contiguous() else x.view(-1, hidden)
+    rows = x2.shape[0]
+    out = torch.empty((rows, hidden), dtype=x.dtype, device=x.device)
+    d2 = None
+    resid = None
+    if delta is not None:
+        d2 = delta.reshape(-1, hidden) if delta.is_contiguous() else delta.view(-1, hidden)
+        if want_residual:
+            resid = torch.empty((rows, hidden), dtype=x.dtype, device=x.device)
+    rc = _lib.load().b200_add_rmsnorm(
+        out.data_ptr(), resid.data_ptr() if resid is not None else 0, x2.data_ptr(), d2.data_ptr() if d2 is not None else 0,
+        weight.data_ptr(), float(eps), rows, hidden, x2.stride(0) if rows > 1 else hidden,
+        (d2.stride(0) if rows > 1 else hidden) if d2 is not None else 0, _dtype_id(x), _stream())
+    _lib.check(rc, "b200_add_rmsnorm")
+    out = out.view(x.shape)
+    if want_residual:
+        return out, (resid.view(x.shape) if resid is not None else x)
+    return out
+
+
+def rope_kv_append(q: torch.Tensor, k: torch.Tensor, v: torch.Tensor, cos: torch.Tensor, sin: torch.Tensor,
+                   k_pool: torch.Tensor, v_pool: torch.Tensor, slot_mapping: torch.Tensor) -> None:
+    """Rotate ``q [n, Hq, D]`` in place, rotate ``k [n, Hkv, D]`` and scatter it and ``v`` into the pools.
+
+    ``cos`` / ``sin``: contiguous ``[n, D]`` tables in the storage dtype.
+    """
+    _need_cuda(q, k, v, cos, sin, k_pool, v_pool, slot_mapping)
+    max_blocks, Hkv, bs, D = _pool_dims(k_pool)
+    n, Hq = q.shape[0], q.shape[1]
+    if cos.shape != (n, D) or sin.shape != (n, D) or not cos.is_contiguous() or not sin.is_contiguous():
+        raise ValueError("cos / sin must be contiguous [n_tok, D]")
+    if slot_mapping.dtype != torch.int64 or slot_mapping.shape != (n,) or not slot_mapping.is_contiguous():
+        raise ValueError("slot_mapping must be a contiguous int64 [n_tok]")
+    if not (q.dtype == k.dtype == v.dtype == cos.dtype == sin.dtype == k_pool.dtype):
+        raise TypeError("q, k, v, cos, sin and the pools must share one dtype")
+    rc = _lib.load().b200_rope_kv_append(
+        q.data_ptr(), _row_stride(q, Hq, D), k.data_ptr(), _row_stride(k, Hkv, D), v.data_ptr(), _row_stride(v, Hkv, D),
+        cos.data_ptr(), sin.data_ptr(), k_pool.data_ptr(), v_pool.data_ptr(), slot_mapping.data_ptr(), n, Hq, Hkv, D, bs,
+        max_blocks, _dtype_id(k_pool), _stream())
+    _lib.check(rc, "b200_rope_kv_append")
+
+
+def silu_mul(gate: torch.Tensor, up: torch.Tensor) -> torch.Tensor:
+    """``silu(gate) * up`` for ``[..., cols]`` tensors with contiguous last dim; returns a contiguous tensor."""
+    _need_cuda(gate, up)
+    cols = gate.shape[-1]
+    g2, u2 = gate.reshape(-1, cols), up.reshape(-1, cols)
+    rows = g2.shape[0]
+    out = torch.empty((rows, cols), dtype=gate.dtype, device=gate.device)
+    rc = _lib.load().b200_silu_mul(out.data_ptr(), g2.data_ptr(), u2.data_ptr(), rows, cols,
+                                  g2.stride(0) if rows > 1 else cols, u2.stride(0) if rows > 1 else cols,
+                                  _dtype_id(gate), _stream())
+    _lib.check(rc, "b200_silu_mul")
+    return out.view(gate.shape)
+
+
 def attn_plan(B: int, Hq: int, Hkv: int, D: int, block_size: int, max_context_len: int, dtype: torch.dtype) -> int:
     """Number of context partitions the library would pick for this shape."""
     return _lib.load().b200_paged_decode_attn_plan(B, Hq, Hkv, D, block_size, max_context_len, DTYPE_ID[dtype])

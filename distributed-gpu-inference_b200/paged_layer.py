@@ -57,10 +57,8 @@ class RMSNorm(nn.Module):
         return out
 
     def forward(self, x: torch.Tensor) -> torch.Tensor:
-        in_dtype = x.dtype
-        xf = x.to(torch.float32)
-        xf = xf * torch.rsqrt(xf.pow(2).mean(-1, keepdim=True) + self.variance_epsilon)
-        return self.weight * xf.to(in_dtype)
+        # LlamaRMSNorm recipe (fp32 normalise, cast back, then weight) in one CUDA launch
+        return ops.add_rmsnorm(x, self.weight, self.variance_epsilon)
 
 
 def rope_tables(position_ids: torch.Tensor, inv_freq: torch.Tensor, dtype: torch.dtype):
@@ -185,24 +183,31 @@ class PagedLlamaDecoderLayer(nn.Module):
             if position_ids is None:
                 raise ValueError("position_ids (or precomputed RoPE tables in the batch state) are required")
             cos, sin = rope_tables(position_ids, self.inv_freq, x.dtype)
-        cos, sin = cos.unsqueeze(2), sin.unsqueeze(2)  # broadcast over heads: [B, T, 1, D]
-        q = q * cos + _rotate_half(q) * sin
-        k = k * cos + _rotate_half(k) * sin
-
-        ops.kv_append(k.reshape(B * T, Hkv, D), v.reshape(B * T, Hkv, D), past_key_value.k_pool,
-                      past_key_value.v_pool, st.slot_mapping)
 
         if T == 1:
+            # decode: RoPE on q (in place) and k, append of k / v, all in one launch; then paged attention
+            qf = q.view(B, Hq, D)
+            ops.rope_kv_append(qf, k.view(B, Hkv, D), v.view(B, Hkv, D), cos.reshape(B, D), sin.reshape(B, D),
+                               past_key_value.k_pool, past_key_value.v_pool, st.slot_mapping)
             attn = ops.paged_decode_attention(
-                q.reshape(B, Hq, D), past_key_value.k_pool, past_key_value.v_pool, st.block_tables, st.context_lens,
+                qf, past_key_value.k_pool, past_key_value.v_pool, st.block_tables, st.context_lens,
                 st.max_context_len, num_splits=st.num_splits, workspace=st.workspace, flags=st.attn_flags,
             ).view(B, 1, Hq * D)
         else:
+            # prompt pass: the rotated k is also needed densely for the causal attention among the new tokens
+            cos4, sin4 = cos.unsqueeze(2), sin.unsqueeze(2)  # broadcast over heads: [B, T, 1, D]
+            q = q * cos4 + _rotate_half(q) * sin4
+            k = k * cos4 + _rotate_half(k) * sin4
+            ops.kv_append(k.reshape(B * T, Hkv, D), v.reshape(B * T, Hkv, D), past_key_value.k_pool,
+                          past_key_value.v_pool, st.slot_mapping)
             attn = self._prefill_attention(q, k, v, attention_mask, st.prefill_mode)
 
-        h = hidden_states + self.self_attn.o_proj(attn)
-        y = self.post_attention_layernorm(h)
-        h = h + self.mlp.down_proj(F.silu(self.mlp.gate_proj(y)) * self.mlp.up_proj(y))
+        # h = x + o_proj(attn);  y = norm(h)   (one launch)
+        y, h = ops.add_rmsnorm(hidden_states, self.post_attention_layernorm.weight,
+                               self.post_attention_layernorm.variance_epsilon,
+                               delta=self.self_attn.o_proj(attn), want_residual=True)
+        act = ops.silu_mul(self.mlp.gate_proj(y), self.mlp.up_proj(y))
+        h = h + self.mlp.down_proj(act)
         return h, (past_key_value if use_cache else None)
 
     def _prefill_attention(self, q, k, v, attention_mask, mode: str) -> torch.Tensor:

@@ -111,6 +111,29 @@ int b200_paged_decode_attn_static(void* out, const void* q, int64_t q_row_stride
                                   int dtype, unsigned flags, void* stream);
 
 /*
+ * Fused element-wise pieces of the decoder layer invoked from ModelShard.forward
+ * (worker/distributed/model_shard.py:209-215; arithmetic of the HF Llama layer).  Each reproduces the rounding
+ * points of the eager torch recipe in the storage dtype; see csrc/b200_layer_ops.cu.
+ *
+ * b200_add_rmsnorm : h = x + delta (delta may be NULL), resid_out = h (may be NULL), out = weight * rmsnorm(h).
+ *                    x: [rows, hidden] with row stride x_stride, delta likewise with d_stride; out/resid_out
+ *                    contiguous.  Replaces the residual add + LlamaRMSNorm.
+ * b200_rope_kv_append : rotate-half RoPE on q (in place) and k with cos/sin tables [n_tok, D] (storage dtype),
+ *                    then scatter the rotated k and v into the pools through slot_mapping (as b200_kv_append).
+ *                    Replaces apply_rotary_pos_emb + the dense cache growth.
+ * b200_silu_mul    : out[r, c] = silu(gate[r, c]) * up[r, c]; gate/up row strides free, out contiguous.
+ *                    Replaces act_fn(gate_proj(x)) * up_proj(x) of LlamaMLP.
+ */
+int b200_add_rmsnorm(void* out, void* resid_out, const void* x, const void* delta, const void* weight, float eps,
+                     int rows, int hidden, int64_t x_stride, int64_t d_stride, int dtype, void* stream);
+int b200_rope_kv_append(void* q, int64_t q_row_stride, const void* k, int64_t k_row_stride,
+                        const void* v, int64_t v_row_stride, const void* cos_table, const void* sin_table,
+                        void* k_pool, void* v_pool, const int64_t* slot_mapping, int n_tok,
+                        int Hq, int Hkv, int D, int block_size, int64_t max_blocks, int dtype, void* stream);
+int b200_silu_mul(void* out, const void* gate, const void* up, int64_t rows, int cols,
+                  int64_t gate_row_stride, int64_t up_row_stride, int dtype, void* stream);
+
+/*
  * KV block pack / unpack for the prefill -> decode hand-off.  Replaces the per-block, per-layer
  * TensorSerializer.serialize -> wire -> deserialize -> block.keys.copy_ round trip of
  * InferenceServicer.TransferKVCache (worker/distributed/grpc_server.py:190-235) and

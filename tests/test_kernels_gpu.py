@@ -234,3 +234,70 @@ def test_attention_workspace_too_small_is_an_error():
     with pytest.raises(B200LibraryError, match="workspace"):
         ops.paged_decode_attention(q, k_pool, v_pool, tables, lens, 512, num_splits=4,
                                    workspace=torch.empty(16, dtype=torch.uint8, device=DEV))
+
+
+# ---- fused layer pieces: rounding-point parity with the eager torch recipe of the HF layer --------------------
+def _torch_rmsnorm(x, w, eps):
+    xf = x.to(torch.float32)
+    xf = xf * torch.rsqrt(xf.pow(2).mean(-1, keepdim=True) + eps)
+    return w * xf.to(x.dtype)
+
+
+def _rot_half(x):
+    h = x.shape[-1] // 2
+    return torch.cat((-x[..., h:], x[..., :h]), dim=-1)
+
+
+@pytest.mark.parametrize("dtype", [torch.bfloat16, torch.float16, torch.float32])
+@pytest.mark.parametrize("Hq,Hkv,D", [(32, 8, 128), (8, 2, 64), (64, 8, 128)])
+def test_rope_kv_append_bit_exact_vs_torch_recipe(dtype, Hq, Hkv, D):
+    n, bs, max_blocks = 37, 16, 20
+    g = torch.Generator(device=DEV).manual_seed(21)
+    qkv = torch.randn((n, (Hq + 2 * Hkv) * D), generator=g, device=DEV).to(dtype)
+    q = qkv[:, :Hq * D].view(n, Hq, D)
+    k = qkv[:, Hq * D:(Hq + Hkv) * D].view(n, Hkv, D)
+    v = qkv[:, (Hq + Hkv) * D:].view(n, Hkv, D)
+    pos = torch.randint(0, 5000, (n,), generator=g, device=DEV)
+    inv_freq = 1.0 / (500000.0 ** (torch.arange(0, D, 2, device=DEV).float() / D))
+    freqs = pos.float()[:, None] * inv_freq[None]
+    emb = torch.cat((freqs, freqs), -1)
+    cos, sin = emb.cos().to(dtype), emb.sin().to(dtype)
+    q_want = q * cos[:, None] + _rot_half(q) * sin[:, None]
+    k_want = k * cos[:, None] + _rot_half(k) * sin[:, None]
+    slots = torch.randperm(max_blocks * bs, generator=g, device=DEV)[:n].to(torch.int64)
+    slots[5] = -1
+    k_pool, v_pool = _pools(max_blocks, Hkv, bs, D, dtype, zero=True)
+    k_ref, v_ref = k_pool.clone(), v_pool.clone()
+    R.append_ref(k_want, v.clone(), k_ref, v_ref, slots)
+    ops.rope_kv_append(q, k, v, cos, sin, k_pool, v_pool, slots)
+    assert torch.equal(_bits(q), _bits(q_want))
+    assert torch.equal(_bits(k_pool), _bits(k_ref)) and torch.equal(_bits(v_pool), _bits(v_ref))
+
+
+@pytest.mark.parametrize("dtype", [torch.bfloat16, torch.float16, torch.float32])
+def test_silu_mul_bit_exact_vs_torch(dtype):
+    g = torch.Generator(device=DEV).manual_seed(22)
+    gu = (torch.randn((64, 2 * 14336), generator=g, device=DEV) * 3).to(dtype)
+    gate, up = gu[:, :14336], gu[:, 14336:]  # strided rows, as slices of a fused projection would be
+    want = torch.nn.functional.silu(gate) * up
+    got = ops.silu_mul(gate, up)
+    assert torch.equal(_bits(got), _bits(want))
+
+
+@pytest.mark.parametrize("dtype", [torch.bfloat16, torch.float16, torch.float32])
+@pytest.mark.parametrize("hidden", [512, 4096, 8192])
+def test_add_rmsnorm_matches_torch_recipe(dtype, hidden):
+    g = torch.Generator(device=DEV).manual_seed(23)
+    x = torch.randn((64, 1, hidden), generator=g, device=DEV).to(dtype)
+    d = torch.randn((64, 1, hidden), generator=g, device=DEV).to(dtype)
+    w = (1 + 0.1 * torch.randn((hidden,), generator=g, device=DEV)).to(dtype)
+    out, h = ops.add_rmsnorm(x, w, 1e-5, delta=d, want_residual=True)
+    h_want = x + d
+    assert torch.equal(_bits(h), _bits(h_want))  # the residual stream is bit-exact
+    want = _torch_rmsnorm(h_want, w, 1e-5)
+    # only the summation order of the fp32 mean differs: at most 1 ulp of the storage dtype, on very few elements
+    diff = (out.float() - want.float()).abs()
+    ulp = torch.finfo(dtype).eps * want.float().abs().clamp_min(1e-3)
+    assert (diff <= ulp * 1.01).all()
+    assert (diff > 0).float().mean().item() < 2e-3
+    assert torch.equal(_bits(ops.add_rmsnorm(h_want, w, 1e-5)), _bits(out))  # same result without the fused add
