@@ -1,0 +1,120 @@
+"""CPU: session surface (dgi_b200/worker/distributed/session.py) held to the behaviours the reference's own tests
+pin (tests/test_worker_distributed_inference_session.py:58-138, tests/test_worker_distributed_worker_session.py:
+91-115), using the same seam — patching the module-global ``WorkerSession`` — plus the in-process transport."""
+import asyncio
+from unittest.mock import patch
+
+import numpy as np
+import pytest
+
+import dgi_b200  # noqa: F401
+from dgi_b200.common.data_structures import SessionConfig, WorkerInfo, WorkerState
+from dgi_b200.worker.distributed import session as S
+
+MOD = "dgi_b200.worker.distributed.session"
+
+
+class _Fake:
+    def __init__(self, worker_info):
+        self.worker_info, self.session_id, self.state = worker_info, "s", S.SessionState.INITIALIZING
+        self.position, self.next_session, self.calls = 0, None, 0
+
+    async def connect(self, timeout=30.0):
+        self.state = S.SessionState.READY
+
+    async def forward(self, hidden_states, position, kv_cache_keys=None):
+        self.calls += 1
+        return hidden_states, (kv_cache_keys or [])
+
+    async def close(self):
+        self.state = S.SessionState.CLOSED
+
+
+class _Flaky(_Fake):
+    async def forward(self, hidden_states, position, kv_cache_keys=None):
+        self.calls += 1
+        if self.calls == 1:
+            raise RuntimeError("transient")
+        return hidden_states, (kv_cache_keys or [])
+
+
+class _Dead(_Fake):
+    async def forward(self, hidden_states, position, kv_cache_keys=None):
+        raise RuntimeError("permanent")
+
+
+def _cfg(**kw):
+    base = dict(model_name="m", max_length=10, max_retries=1, connect_timeout=1.0)
+    base.update(kw)
+    return SessionConfig(**base)
+
+
+ROUTE = [WorkerInfo(worker_id="w1", state=WorkerState.ONLINE, api_endpoint="http://w")]
+
+
+def test_step_advances_position_by_input_length_and_counts_stats():
+    async def run():
+        with patch(f"{MOD}.WorkerSession", _Fake):
+            s = S.DistributedInferenceSession(_cfg(), ROUTE)
+            await s.setup()
+            assert s.state == S.SessionState.READY
+            out = await s.step(np.zeros((1, 2), dtype=np.float32))
+            assert out.shape == (1, 2) and s.position == 2
+            st = s.get_stats()
+            assert st["total_steps"] == 1 and st["total_tokens"] == 2
+            assert {"avg_latency_ms", "tokens_per_second", "retries", "total_latency_ms"} <= set(st)
+            await s.close()
+            assert s.state == S.SessionState.CLOSED
+    asyncio.run(run())
+
+
+def test_retry_counter_and_length_guard_and_failure():
+    async def run():
+        with patch(f"{MOD}.WorkerSession", _Flaky), patch(f"{MOD}.asyncio.sleep", return_value=None):
+            s = S.DistributedInferenceSession(_cfg(max_retries=2), ROUTE)
+            await s.setup()
+            await s.step(np.zeros((1, 1), dtype=np.float32))
+            assert s.get_stats()["retries"] >= 1
+        with patch(f"{MOD}.WorkerSession", _Fake):
+            s = S.DistributedInferenceSession(_cfg(max_length=1), ROUTE)
+            await s.setup()
+            with pytest.raises(ValueError, match="Maximum length exceeded"):
+                await s.step(np.zeros((1, 2), dtype=np.float32))
+        with patch(f"{MOD}.WorkerSession", _Dead):
+            s = S.DistributedInferenceSession(_cfg(), ROUTE)
+            await s.setup()
+            with pytest.raises(RuntimeError, match="recovery not implemented"):
+                await s.step(np.zeros((1, 1), dtype=np.float32))
+    asyncio.run(run())
+
+
+def test_session_manager_cleanup_does_not_deadlock():
+    # the reference hangs here forever: create_session holds the lock and re-enters close_session
+    async def run():
+        with patch(f"{MOD}.WorkerSession", _Fake):
+            mgr = S.SessionManager(max_sessions=1)
+            s1 = await mgr.create_session(_cfg(), ROUTE)
+            s1.state = S.SessionState.CLOSED
+            s2 = await asyncio.wait_for(mgr.create_session(_cfg(), ROUTE), timeout=5)
+            assert s2 is not None and await mgr.get_session(s2.session_id) is s2
+            with pytest.raises(RuntimeError, match="Maximum sessions reached"):
+                await mgr.create_session(_cfg(), ROUTE)
+            await mgr.close_all()
+    asyncio.run(run())
+
+
+def test_in_process_transport_chains_two_stages_and_tracks_position():
+    async def run():
+        S.TRANSPORTS["a"] = S.InProcessTransport(lambda h, pos: h + 1)
+        S.TRANSPORTS["b"] = S.InProcessTransport(lambda h, pos: h * 2 + pos)
+        route = [WorkerInfo(worker_id="a"), WorkerInfo(worker_id="b")]
+        async with S.DistributedInferenceSession(_cfg(max_length=100), route) as s:
+            out = await s.step(np.ones((1, 3), dtype=np.float32))
+            assert (out == 4).all()
+            out = await s.step(np.ones((1, 1), dtype=np.float32))
+            assert (out == 7).all() and s.position == 4
+            assert [h.position for h in s._worker_sessions] == [4, 4]
+            assert s._worker_sessions[0].next_session is s._worker_sessions[1]
+        with pytest.raises(ConnectionError):
+            await S.DistributedInferenceSession(_cfg(), [WorkerInfo(worker_id="nobody")]).setup()
+    asyncio.run(run())
