@@ -17,19 +17,18 @@ namespace {
 inline int ceil_div(int a, int b) { return (a + b - 1) / b; }
 
 // How many partitions of the context each (sequence, kv head) pair gets.  Measured on B200 (tools/kbench.py,
-// profiles/r01_kbench.log): at config 2 (512 pairs) one partition streams at 98 % of the copy peak and every
-// extra split costs 4-20 % (partials + combine + ramp), so the context is only cut when the pairs alone cannot
-// give each of the 148 SMs its two resident CTAs; then it is cut to about `kTargetCtas` CTAs, keeping every
+// profiles/r01_kbench.md): a second launch (the combine) and the partials cost 10-25 % on these 50-170 us
+// kernels, so one partition wins whenever the pairs alone put a CTA on most SMs — 512 pairs (config 2): 98 % of
+// the copy peak with 1 split, 83 % with 3; 128 pairs (config 4, micro-batch 16): 86 % with 1, 76 % with 2.  Below
+// that the context is cut to roughly 3.5 CTAs per SM (64 pairs, config 5: 93-95 % for 4..12 splits), keeping every
 // partition at least 256 tokens long so the per-CTA pipeline ramp stays amortised.
-constexpr int kTargetCtas = kNumSMs * 4;
-
 int plan_splits(int B, int Hkv, int block_size, int max_context_len) {
   const int n_blocks = std::max(1, ceil_div(std::max(1, max_context_len), block_size));
   const int pairs = std::max(1, B * Hkv);
-  if (pairs >= kNumSMs * 2) return 1;
+  if (pairs >= 120) return 1;
   const int min_blocks = std::max(1, 256 / block_size);
   const int max_by_len = std::max(1, n_blocks / min_blocks);
-  int splits = std::max(1, ceil_div(kTargetCtas, pairs));
+  int splits = std::max(1, ceil_div(kNumSMs * 7 / 2, pairs));
   splits = std::min(splits, max_by_len);
   return std::min(splits, 128);
 }
@@ -148,6 +147,15 @@ int b200_kv_unpack_layers(void* const* k_pools, void* const* v_pools, int n_laye
                           int64_t max_blocks, int dtype, void* stream) {
   return kv_unpack_layers(k_pools, v_pools, n_layers, packed, block_table, n_blocks, Hkv, D, block_size, max_blocks,
                           dtype, static_cast<cudaStream_t>(stream));
+}
+
+int b200_kv_move_blocks_layers(void* const* dst_k_pools, void* const* dst_v_pools, const void* const* src_k_pools,
+                               const void* const* src_v_pools, int n_layers, const int32_t* src_table,
+                               const int32_t* dst_table, int n_blocks, int Hkv, int D, int block_size,
+                               int64_t src_max_blocks, int64_t dst_max_blocks, int dtype, void* stream) {
+  return kv_move_blocks_layers(dst_k_pools, dst_v_pools, src_k_pools, src_v_pools, n_layers, src_table, dst_table,
+                               n_blocks, Hkv, D, block_size, src_max_blocks, dst_max_blocks, dtype,
+                               static_cast<cudaStream_t>(stream));
 }
 
 int b200_add_rmsnorm(void* out, void* resid_out, const void* x, const void* delta, const void* weight, float eps,

@@ -210,6 +210,68 @@ int kv_block_copy(void* packed, PoolSet pools, int n_layers, const int32_t* bloc
   return check_launch(name);
 }
 
+// Block-to-block copy between two sets of pools: block src_table[j] of every source layer goes to block
+// dst_table[j] of the matching destination layer.  The destination pointers may be PEER memory (another GPU's
+// pools mapped over NVLink): the prefill rank then pushes a sequence straight into the decode rank's blocks with
+// 16-byte stores over NVSwitch and no staging buffer on either side.
+template <int UNROLL>
+__global__ void __launch_bounds__(256)
+kv_block_move_kernel(PoolSet dst, PoolSet src, const int32_t* __restrict__ src_table,
+                     const int32_t* __restrict__ dst_table, int n_blocks, int64_t src_max_blocks,
+                     int64_t dst_max_blocks, int vec_per_block, int chunks_per_block) {
+  const int64_t chunk = blockIdx.x;
+  const int64_t item = chunk / chunks_per_block;
+  const int c = static_cast<int>(chunk - item * chunks_per_block);
+  const int j = static_cast<int>(item % n_blocks);
+  const int lk = static_cast<int>(item / n_blocks);
+  const int layer = lk >> 1;
+  const bool is_v = lk & 1;
+  const int32_t s_slot = src_table[j], d_slot = dst_table[j];
+  if (s_slot < 0 || s_slot >= src_max_blocks || d_slot < 0 || d_slot >= dst_max_blocks) return;
+  const int64_t block_bytes = static_cast<int64_t>(vec_per_block) * 16;
+  const char* sp = static_cast<const char*>(is_v ? src.v_pools[layer] : src.k_pools[layer]) + s_slot * block_bytes;
+  char* dp = const_cast<char*>(static_cast<const char*>(is_v ? dst.v_pools[layer] : dst.k_pools[layer])) + d_slot * block_bytes;
+  const int v0 = c * (256 * UNROLL) + threadIdx.x;
+  int4 val[UNROLL];
+#pragma unroll
+  for (int u = 0; u < UNROLL; ++u) {
+    const int v = v0 + u * 256;
+    if (v < vec_per_block) val[u] = ld_stream16(sp + static_cast<int64_t>(v) * 16);
+  }
+#pragma unroll
+  for (int u = 0; u < UNROLL; ++u) {
+    const int v = v0 + u * 256;
+    if (v < vec_per_block) st_stream16(dp + static_cast<int64_t>(v) * 16, val[u]);
+  }
+}
+
+int kv_move_blocks_layers(void* const* dst_k_pools, void* const* dst_v_pools, const void* const* src_k_pools,
+                          const void* const* src_v_pools, int n_layers, const int32_t* src_table,
+                          const int32_t* dst_table, int n_blocks, int Hkv, int D, int bs, int64_t src_max_blocks,
+                          int64_t dst_max_blocks, int dtype, cudaStream_t s) {
+  const char* name = "b200_kv_move_blocks_layers";
+  const int es = dtype_size(dtype);
+  if (es == 0) return fail(B200_EINVAL, "%s: unsupported dtype %d", name, dtype);
+  if (n_blocks < 0 || n_layers <= 0 || Hkv <= 0 || D <= 0 || bs <= 0 || src_max_blocks <= 0 || dst_max_blocks <= 0)
+    return fail(B200_EINVAL, "%s: bad sizes", name);
+  if (n_blocks == 0) return 0;
+  if (!dst_k_pools || !dst_v_pools || !src_k_pools || !src_v_pools || !src_table || !dst_table)
+    return fail(B200_EINVAL, "%s: null pointer", name);
+  const int64_t block_bytes = static_cast<int64_t>(Hkv) * bs * D * es;
+  if (block_bytes % 16 != 0 || block_bytes / 16 > INT32_MAX) return fail(B200_ESHAPE, "%s: block size", name);
+  constexpr int UNROLL = 8;
+  const int vec_per_block = static_cast<int>(block_bytes / 16);
+  const int chunks_per_block = (vec_per_block + 256 * UNROLL - 1) / (256 * UNROLL);
+  const int64_t grid = 2ll * n_layers * n_blocks * chunks_per_block;
+  if (grid > INT32_MAX) return fail(B200_ESHAPE, "%s: too many chunks", name);
+  PoolSet d{const_cast<const void* const*>(dst_k_pools), const_cast<const void* const*>(dst_v_pools), nullptr, nullptr};
+  PoolSet sr{src_k_pools, src_v_pools, nullptr, nullptr};
+  kv_block_move_kernel<UNROLL><<<static_cast<unsigned>(grid), 256, 0, s>>>(d, sr, src_table, dst_table, n_blocks,
+                                                                         src_max_blocks, dst_max_blocks,
+                                                                         vec_per_block, chunks_per_block);
+  return check_launch(name);
+}
+
 int kv_pack(void* packed, const void* k_pool, const void* v_pool, const int32_t* table, int n_blocks, int Hkv, int D,
             int bs, int64_t max_blocks, int dtype, cudaStream_t s) {
   PoolSet p{nullptr, nullptr, k_pool, v_pool};

@@ -75,3 +75,55 @@ class KVTransferEndpoint:
         for (kp, vp, okp, ovp) in zip(self._k_ptrs, self._v_ptrs, other._k_ptrs, other._v_ptrs):
             buf = ops.kv_pack_layers(kp, vp, self.pool_shape, self.dtype, src_table)
             ops.kv_unpack_layers(buf, okp, ovp, other.pool_shape, dst_table)
+
+
+class PeerPushEndpoint:
+    """Hand-off without staging: the prefill GPU writes a sequence's blocks straight into the decode GPU's pools.
+
+    Every rank allocates the backing tensor of its ``KVCachePool`` from torch's symmetric memory and exchanges the
+    mappings once (``rendezvous``); afterwards a rank holds a device pointer to every peer's pools.  ``push`` is
+    then ONE kernel (b200_kv_move_blocks_layers) whose loads hit local HBM and whose 16-byte stores travel over
+    NVLink / NVSwitch into the blocks the receiver's own allocator handed out — the gather (pack), the transfer and
+    the scatter (unpack) of the NCCL path fused into one pass, with no packed buffer on either side.
+
+    Protocol per sequence: the receiver allocates blocks and tells the sender its block table (a few hundred
+    int32); the sender pushes and then signals completion (``barrier`` on the symmetric-memory handle orders the
+    two streams).
+    """
+
+    def __init__(self, num_layers: int, num_heads: int, head_dim: int, block_size: int, max_blocks_per_layer: int,
+                 device: str, dtype: torch.dtype, group=None):
+        import torch.distributed._symmetric_memory as symm_mem
+
+        self.group = group if group is not None else dist.group.WORLD
+        shape = (num_layers, 2, max_blocks_per_layer, num_heads, block_size, head_dim)
+        backing = symm_mem.empty(shape, dtype=dtype, device=device)
+        backing.zero_()
+        self.handle = symm_mem.rendezvous(backing, self.group)
+        self.pool = KVCachePool(num_layers, num_heads, head_dim, block_size, max_blocks_per_layer, device=device,
+                                dtype=dtype, backing=backing)
+        self.pool_shape = (max_blocks_per_layer, num_heads, block_size, head_dim)
+        self.dtype = dtype
+        self.device = torch.device(device)
+        es = backing.element_size()
+        plane = max_blocks_per_layer * num_heads * block_size * head_dim * es  # bytes of one K or V pool
+        self._ptrs = {}
+        for peer, base in enumerate(self.handle.buffer_ptrs):
+            k = torch.tensor([base + (2 * l) * plane for l in range(num_layers)], dtype=torch.int64).to(self.device)
+            v = torch.tensor([base + (2 * l + 1) * plane for l in range(num_layers)], dtype=torch.int64).to(self.device)
+            self._ptrs[peer] = (k, v)
+        self.rank = self.handle.rank
+
+    def payload_bytes(self, n_blocks: int) -> int:
+        _, Hkv, bs, D = self.pool_shape
+        return self.pool.num_layers * 2 * n_blocks * Hkv * bs * D * torch.empty((), dtype=self.dtype).element_size()
+
+    def push(self, src_table: torch.Tensor, dst_table: torch.Tensor, dst_rank: int) -> None:
+        """Enqueue the copy of local blocks ``src_table`` into blocks ``dst_table`` of rank ``dst_rank``'s pools."""
+        sk, sv = self._ptrs[self.rank]
+        dk, dv = self._ptrs[dst_rank]
+        ops.kv_move_blocks_layers(dk, dv, self.pool_shape, sk, sv, self.pool_shape, self.dtype, src_table, dst_table)
+
+    def barrier(self) -> None:
+        """Order the pushes issued so far on every rank before whatever the ranks enqueue next."""
+        self.handle.barrier()

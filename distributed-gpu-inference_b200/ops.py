@@ -338,3 +338,28 @@ def kv_unpack_layers(packed: torch.Tensor, k_ptrs: torch.Tensor, v_ptrs: torch.T
     rc = _lib.load().b200_kv_unpack_layers(k_ptrs.data_ptr(), v_ptrs.data_ptr(), L, packed.data_ptr(),
                                           block_table.data_ptr(), n, Hkv, D, bs, max_blocks, _dtype_id(packed), _stream())
     _lib.check(rc, "b200_kv_unpack_layers")
+
+
+def kv_move_blocks_layers(dst_k_ptrs: torch.Tensor, dst_v_ptrs: torch.Tensor, dst_pool_shape,
+                          src_k_ptrs: torch.Tensor, src_v_ptrs: torch.Tensor, src_pool_shape, dtype: torch.dtype,
+                          src_table: torch.Tensor, dst_table: torch.Tensor) -> None:
+    """Copy block ``src_table[j]`` of every source layer to block ``dst_table[j]`` of the matching destination layer.
+
+    The ``*_ptrs`` tensors are device int64 vectors of pool addresses (``pool_pointer_array``); destination
+    addresses may point into another GPU's memory (peer-mapped), which turns the call into a push over NVLink.
+    """
+    _need_cuda(dst_k_ptrs, dst_v_ptrs, src_k_ptrs, src_v_ptrs, src_table, dst_table)
+    n = _check_table(src_table)
+    if _check_table(dst_table) != n:
+        raise ValueError("source and destination tables differ in length")
+    smb, Hkv, bs, D = src_pool_shape
+    dmb = dst_pool_shape[0]
+    if tuple(dst_pool_shape[1:]) != (Hkv, bs, D):
+        raise ValueError("source and destination blocks differ in shape")
+    L = src_k_ptrs.shape[0]
+    if dst_k_ptrs.shape[0] != L:
+        raise ValueError("layer counts differ")
+    rc = _lib.load().b200_kv_move_blocks_layers(dst_k_ptrs.data_ptr(), dst_v_ptrs.data_ptr(), src_k_ptrs.data_ptr(),
+                                               src_v_ptrs.data_ptr(), L, src_table.data_ptr(), dst_table.data_ptr(), n,
+                                               Hkv, D, bs, smb, dmb, DTYPE_ID[dtype], _stream())
+    _lib.check(rc, "b200_kv_move_blocks_layers")

@@ -245,6 +245,7 @@ class KVCachePool:
         max_blocks_per_layer: int = 100,
         device: str = "cuda",
         dtype: torch.dtype = torch.float16,
+        backing: Optional[torch.Tensor] = None,
     ):
         self.num_layers = num_layers
         self.num_heads = num_heads
@@ -253,9 +254,13 @@ class KVCachePool:
         self.max_blocks_per_layer = max_blocks_per_layer
         self.device = device
         self.dtype = dtype
-        self.backing = torch.zeros(
-            (num_layers, 2, max_blocks_per_layer, num_heads, block_size, head_dim), dtype=dtype, device=device
-        )
+        shape = (num_layers, 2, max_blocks_per_layer, num_heads, block_size, head_dim)
+        if backing is None:
+            backing = torch.zeros(shape, dtype=dtype, device=device)
+        elif tuple(backing.shape) != shape or backing.dtype != dtype or not backing.is_contiguous():
+            # e.g. a symmetric-memory allocation whose peers can be written over NVLink (dgi_b200.kv_transfer)
+            raise ValueError(f"backing must be a contiguous {dtype} tensor of shape {shape}")
+        self.backing = backing
         self._layer_caches: List[PagedKVCache] = [
             PagedKVCache(
                 num_layers=1,

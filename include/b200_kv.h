@@ -111,6 +111,20 @@ int b200_paged_decode_attn_static(void* out, const void* q, int64_t q_row_stride
                                   int dtype, unsigned flags, void* stream);
 
 /*
+ * Block-to-block move between two sets of pools, all layers in one launch: block src_table[j] of source layer l
+ * is copied to block dst_table[j] of destination layer l.  The destination pool pointers may be peer memory —
+ * another GPU's pools mapped over NVLink — in which case the prefill GPU writes a sequence's KV straight into the
+ * blocks the decode GPU allocated, with no packed staging buffer and no unpack.  This is the fused form of the
+ * hand-off of InferenceServicer.TransferKVCache (worker/distributed/grpc_server.py:190-235); with local pointers
+ * it is a block copy (copy-on-write of shared blocks, CacheBlock.add_ref — kv_cache.py:67-68).
+ */
+int b200_kv_move_blocks_layers(void* const* dst_k_pools, void* const* dst_v_pools,
+                               const void* const* src_k_pools, const void* const* src_v_pools, int n_layers,
+                               const int32_t* src_table, const int32_t* dst_table, int n_blocks,
+                               int Hkv, int D, int block_size, int64_t src_max_blocks, int64_t dst_max_blocks,
+                               int dtype, void* stream);
+
+/*
  * Fused element-wise pieces of the decoder layer invoked from ModelShard.forward
  * (worker/distributed/model_shard.py:209-215; arithmetic of the HF Llama layer).  Each reproduces the rounding
  * points of the eager torch recipe in the storage dtype; see csrc/b200_layer_ops.cu.

@@ -154,3 +154,83 @@ def test_same_device_handoff_between_two_pools_bit_exact():
     for l in range(4):
         assert torch.equal(b.layer(l).key_pool[tb.long()], a.layer(l).key_pool[ta.long()])
         assert torch.equal(b.layer(l).value_pool[tb.long()], a.layer(l).value_pool[ta.long()])
+
+
+def _push_worker(rank, world, port, q):
+    import sys
+    sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+    import dgi_b200  # noqa: F401
+    from dgi_b200.kv_transfer import PeerPushEndpoint
+    from dgi_b200.worker.distributed.kv_cache import KVCachePool
+
+    os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port))
+    torch.cuda.set_device(rank)
+    dev = f"cuda:{rank}"
+    dist.init_process_group("nccl", rank=rank, world_size=world, device_id=torch.device(dev))
+    try:
+        L_, Hkv, D, bs, max_blocks, seq_len = 5, 8, 128, 16, 48, 333
+        pp = PeerPushEndpoint(L_, Hkv, D, bs, max_blocks, dev, torch.bfloat16)
+        n_blocks = (seq_len + bs - 1) // bs
+        tbl = torch.zeros(n_blocks, dtype=torch.int32, device=dev)
+        if rank == 1:  # decode side allocates and publishes its block table
+            pp.pool.allocate_sequence(64)
+            blocks = pp.pool.allocate_sequence(seq_len)
+            tbl.copy_(torch.tensor(KVCachePool.block_table(blocks[0]), dtype=torch.int32))
+        dist.broadcast(tbl, src=1)
+        if rank == 0:
+            blocks = pp.pool.allocate_sequence(seq_len)
+            src = torch.tensor(KVCachePool.block_table(blocks[0]), dtype=torch.int32, device=dev)
+            pp.pool.backing.normal_(generator=torch.Generator(device=dev).manual_seed(9))
+            pp.push(src, tbl, dst_rank=1)
+            want = pp.pool.backing[:, :, src.long()].cpu()
+            pp.barrier()
+            torch.cuda.synchronize()
+            q.put(("sent", want.view(torch.int16).numpy().tobytes()))
+        else:
+            pp.barrier()
+            torch.cuda.synchronize()
+            got = pp.pool.backing[:, :, tbl.long()].cpu()
+            untouched = torch.ones(max_blocks, dtype=torch.bool)
+            untouched[tbl.long().cpu()] = False
+            assert pp.pool.backing[:, :, untouched.to(dev)].eq(0).all()
+            q.put(("received", got.view(torch.int16).numpy().tobytes()))
+        dist.barrier()
+    finally:
+        dist.destroy_process_group()
+
+
+@pytest.mark.skipif(torch.cuda.device_count() < 2, reason="needs 2 GPUs")
+def test_peer_push_handoff_is_bit_exact():
+    ctx = mp.get_context("spawn")
+    q = ctx.Queue()
+    port = _free_port()
+    procs = [ctx.Process(target=_push_worker, args=(r, 2, port, q)) for r in range(2)]
+    for p in procs:
+        p.start()
+    items = dict(q.get(timeout=300) for _ in range(2))
+    for p in procs:
+        p.join(timeout=120)
+        assert p.exitcode == 0
+    assert items["sent"] == items["received"]
+
+
+def test_block_move_between_local_pools_bit_exact():
+    import dgi_b200  # noqa: F401
+    from dgi_b200 import ops
+    from dgi_b200.worker.distributed.kv_cache import KVCachePool
+
+    dev = "cuda:0"
+    a = KVCachePool(3, 8, 128, 16, 20, device=dev, dtype=torch.bfloat16)
+    b = KVCachePool(3, 8, 128, 16, 30, device=dev, dtype=torch.bfloat16)
+    a.backing.normal_()
+    src = torch.tensor([3, 7, 1, 19], dtype=torch.int32, device=dev)
+    dst = torch.tensor([29, 0, 5, 6], dtype=torch.int32, device=dev)
+    ak = ops.pool_pointer_array([a.layer(l).key_pool for l in range(3)])
+    av = ops.pool_pointer_array([a.layer(l).value_pool for l in range(3)])
+    bk = ops.pool_pointer_array([b.layer(l).key_pool for l in range(3)])
+    bv = ops.pool_pointer_array([b.layer(l).value_pool for l in range(3)])
+    ops.kv_move_blocks_layers(bk, bv, (30, 8, 16, 128), ak, av, (20, 8, 16, 128), torch.bfloat16, src, dst)
+    assert torch.equal(b.backing[:, :, dst.long()], a.backing[:, :, src.long()])
+    rest = torch.ones(30, dtype=torch.bool, device=dev)
+    rest[dst.long()] = False
+    assert b.backing[:, :, rest].eq(0).all()
