@@ -250,7 +250,8 @@ def run_single(args, workload):
         raise SystemExit("context too short for the requested steps")
     t_setup = time.time()
     shard = ModelShard.from_config(cfg, 0, cfg.num_hidden_layers, device=dev, dtype=torch.bfloat16, seed=0)
-    eng = PagedDecodeEngine([shard], max_batch=B, max_seq_len=ctx, block_size=16, prefill_chunk=args.prefill_chunk)
+    eng = PagedDecodeEngine([shard], max_batch=B, max_seq_len=ctx, block_size=16, prefill_chunk=args.prefill_chunk,
+                            fuse_projections=not args.no_fuse_projections)
     eng.allocate(B, ctx)
     prompts = torch.randint(0, cfg.vocab_size, (B, P), generator=torch.Generator().manual_seed(1234))
     if args.synthetic_kv:
@@ -335,6 +336,7 @@ def run_single(args, workload):
             "kv_fill": "synthetic normal(0,1)" if args.synthetic_kv else "real prefill of random prompts",
             "l2": "inputs larger than L2 (weights 16 GB + KV 17 GB streamed per step)",
             "attn_splits": eng.num_splits,
+            "projections": "separate q/k/v and gate/up GEMMs" if args.no_fuse_projections else "q|k|v and gate|up fused into one GEMM each",
             "setup_s": round(setup_s, 1),
         },
         "clocks": clocks,
@@ -375,6 +377,8 @@ def main():
     ap.add_argument("--synthetic-kv", action="store_true", help="fill KV pools with N(0,1) instead of a real prefill")
     ap.add_argument("--prefill-chunk", type=int, default=8)
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-fuse-projections", action="store_true",
+                    help="keep q/k/v and gate/up as separate GEMMs (the reference's GEMM shapes)")
     ap.add_argument("--micro-batches", type=int, default=0, help="pipeline micro-batches (default: one per rank)")
     ap.add_argument("--real-prefill", action="store_true", help="multi-GPU: run a real prompt pass instead of synthetic KV")
     args = ap.parse_args()

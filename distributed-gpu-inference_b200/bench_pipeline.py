@@ -47,7 +47,8 @@ def _run(args, workload, SHAPES, ShapeConfig, ClockSampler, measured_peaks, rank
     start, end = get_layer_range_for_worker(cfg.num_hidden_layers, world, rank)
     t0 = time.time()
     shard = ModelShard.from_config(cfg, start, end, device=dev, dtype=torch.bfloat16, seed=0)
-    engines = [PagedDecodeEngine([shard], max_batch=mb, max_seq_len=ctx, block_size=16, prefill_chunk=2) for _ in range(M)]
+    engines = [PagedDecodeEngine([shard], max_batch=mb, max_seq_len=ctx, block_size=16, prefill_chunk=2,
+                                 fuse_projections=not getattr(args, "no_fuse_projections", False)) for _ in range(M)]
     for e in engines:
         e.allocate(mb, ctx)
     groups = make_pipeline_groups(world, warm_up_device=torch.device(dev))

@@ -37,10 +37,16 @@ class PagedDecodeEngine:
         prefill_mode: str = "sdpa",
         prefill_chunk: int = 8,
         spare_blocks: int = 0,
+        fuse_projections: bool = False,
     ):
         if not shards:
             raise ValueError("need at least one shard")
         self.shards = list(shards)
+        if fuse_projections:
+            for sh in self.shards:
+                for layer in sh.layers:
+                    if hasattr(layer, "fuse_projections"):
+                        layer.fuse_projections()
         first = self.shards[0]
         self.device = torch.device(first.device)
         if self.device.type != "cuda":

@@ -97,9 +97,13 @@ class PeerPushEndpoint:
 
         self.group = group if group is not None else dist.group.WORLD
         shape = (num_layers, 2, max_blocks_per_layer, num_heads, block_size, head_dim)
+        try:  # needed by older torch releases, a deprecated no-op in newer ones
+            symm_mem.enable_symm_mem_for_group(self.group.group_name)
+        except Exception:  # noqa: BLE001
+            pass
         backing = symm_mem.empty(shape, dtype=dtype, device=device)
         backing.zero_()
-        self.handle = symm_mem.rendezvous(backing, self.group)
+        self.handle = symm_mem.rendezvous(backing, self.group.group_name)
         self.pool = KVCachePool(num_layers, num_heads, head_dim, block_size, max_blocks_per_layer, device=device,
                                 dtype=dtype, backing=backing)
         self.pool_shape = (max_blocks_per_layer, num_heads, block_size, head_dim)

@@ -138,8 +138,10 @@ def silu_mul(gate: torch.Tensor, up: torch.Tensor) -> torch.Tensor:
     """``silu(gate) * up`` for ``[..., cols]`` tensors with contiguous last dim; returns a contiguous tensor."""
     _need_cuda(gate, up)
     cols = gate.shape[-1]
-    g2, u2 = gate.reshape(-1, cols), up.reshape(-1, cols)
+    g2, u2 = gate.flatten(0, -2), up.flatten(0, -2)  # views when the leading dims collapse (uniform row stride)
     rows = g2.shape[0]
+    if g2.stride(-1) != 1 or u2.stride(-1) != 1:
+        raise ValueError("gate / up need a contiguous last dimension")
     out = torch.empty((rows, cols), dtype=gate.dtype, device=gate.device)
     rc = _lib.load().b200_silu_mul(out.data_ptr(), g2.data_ptr(), u2.data_ptr(), rows, cols,
                                   g2.stride(0) if rows > 1 else cols, u2.stride(0) if rows > 1 else cols,

@@ -154,6 +154,31 @@ class PagedLlamaDecoderLayer(nn.Module):
         layer.load_state_dict(sd, strict=True)
         return layer
 
+    def fuse_projections(self) -> None:
+        """Run q/k/v as one GEMM and gate/up as one GEMM.
+
+        The three (two) weight matrices are laid out back to back in one tensor and the ``nn.Linear`` parameters
+        become views of it, so memory use and ``state_dict`` are unchanged.  Every output element is the same
+        dot product as before; only cuBLAS' choice of kernel (and with it the fp32 summation order) may differ.
+        """
+        if getattr(self, "_qkv_w", None) is not None:
+            return
+        with torch.no_grad():
+            a = self.self_attn
+            self._qkv_w = torch.cat([a.q_proj.weight, a.k_proj.weight, a.v_proj.weight], dim=0).contiguous()
+            nq, nk = a.q_proj.weight.shape[0], a.k_proj.weight.shape[0]
+            a.q_proj.weight.data = self._qkv_w[:nq]
+            a.k_proj.weight.data = self._qkv_w[nq:nq + nk]
+            a.v_proj.weight.data = self._qkv_w[nq + nk:]
+            m = self.mlp
+            self._gu_w = torch.cat([m.gate_proj.weight, m.up_proj.weight], dim=0).contiguous()
+            nf = m.gate_proj.weight.shape[0]
+            m.gate_proj.weight.data = self._gu_w[:nf]
+            m.up_proj.weight.data = self._gu_w[nf:]
+
+    _qkv_w = None
+    _gu_w = None
+
     # ---- forward -----------------------------------------------------------------------------------
     def forward(
         self,
@@ -173,9 +198,15 @@ class PagedLlamaDecoderLayer(nn.Module):
         Hq, Hkv, D = self.num_heads, self.num_kv_heads, self.head_dim
 
         x = self.input_layernorm(hidden_states)
-        q = self.self_attn.q_proj(x).view(B, T, Hq, D)
-        k = self.self_attn.k_proj(x).view(B, T, Hkv, D)
-        v = self.self_attn.v_proj(x).view(B, T, Hkv, D)
+        if self._qkv_w is not None:
+            qkv = F.linear(x, self._qkv_w)  # [B, T, (Hq + 2 Hkv) D]; q / k / v are column slices (strided rows)
+            q = qkv[..., :Hq * D].unflatten(-1, (Hq, D))
+            k = qkv[..., Hq * D:(Hq + Hkv) * D].unflatten(-1, (Hkv, D))
+            v = qkv[..., (Hq + Hkv) * D:].unflatten(-1, (Hkv, D))
+        else:
+            q = self.self_attn.q_proj(x).view(B, T, Hq, D)
+            k = self.self_attn.k_proj(x).view(B, T, Hkv, D)
+            v = self.self_attn.v_proj(x).view(B, T, Hkv, D)
 
         if st.cos is not None:
             cos, sin = st.cos, st.sin
@@ -186,8 +217,8 @@ class PagedLlamaDecoderLayer(nn.Module):
 
         if T == 1:
             # decode: RoPE on q (in place) and k, append of k / v, all in one launch; then paged attention
-            qf = q.view(B, Hq, D)
-            ops.rope_kv_append(qf, k.view(B, Hkv, D), v.view(B, Hkv, D), cos.reshape(B, D), sin.reshape(B, D),
+            qf = q[:, 0]  # [B, Hq, D], row stride = projection width
+            ops.rope_kv_append(qf, k[:, 0], v[:, 0], cos.reshape(B, D), sin.reshape(B, D),
                                past_key_value.k_pool, past_key_value.v_pool, st.slot_mapping)
             attn = ops.paged_decode_attention(
                 qf, past_key_value.k_pool, past_key_value.v_pool, st.block_tables, st.context_lens,
@@ -206,7 +237,12 @@ class PagedLlamaDecoderLayer(nn.Module):
         y, h = ops.add_rmsnorm(hidden_states, self.post_attention_layernorm.weight,
                                self.post_attention_layernorm.variance_epsilon,
                                delta=self.self_attn.o_proj(attn), want_residual=True)
-        act = ops.silu_mul(self.mlp.gate_proj(y), self.mlp.up_proj(y))
+        if self._gu_w is not None:
+            gu = F.linear(y, self._gu_w)
+            nf = gu.shape[-1] // 2
+            act = ops.silu_mul(gu[..., :nf], gu[..., nf:])
+        else:
+            act = ops.silu_mul(self.mlp.gate_proj(y), self.mlp.up_proj(y))
         h = h + self.mlp.down_proj(act)
         return h, (past_key_value if use_cache else None)
 

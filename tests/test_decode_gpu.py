@@ -30,6 +30,19 @@ def test_config1_tokens_identical_to_reference_fp32(golden, ranges):
     assert toks.tolist() == g["tokens"]
 
 
+def test_fused_projections_give_the_reference_tokens(golden):
+    # q/k/v as one GEMM and gate/up as one GEMM: same dot products, possibly another cuBLAS kernel
+    g, cfg, sd = _tiny(golden)
+    prompts = torch.tensor(g["prompt_ids"])
+    shards = build_product_shards(cfg, sd, [(0, 2), (2, 4)], DEV, torch.float32)
+    eng = PagedDecodeEngine(shards, max_batch=4, max_seq_len=192, prefill_mode="eager", fuse_projections=True)
+    assert shards[0].layers[0]._qkv_w is not None
+    assert shards[0].layers[0].self_attn.k_proj.weight.data_ptr() != 0
+    assert eng.generate(prompts, 64).tolist() == g["tokens"]
+    sd2 = shards[0].layers[1].state_dict()
+    assert torch.equal(sd2["self_attn.v_proj.weight"].cpu(), sd["model.layers.1.self_attn.v_proj.weight"])
+
+
 def test_cuda_graph_and_eager_launch_agree(golden):
     g, cfg, sd = _tiny(golden)
     prompts = torch.tensor(g["prompt_ids"])[:, :48]

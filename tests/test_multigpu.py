@@ -11,6 +11,41 @@ import torch.multiprocessing as mp
 pytestmark = pytest.mark.gpu
 
 
+def _run_ranks(target, world, n_items, timeout=240):
+    """Spawn `world` ranks, collect `n_items` queue entries, and never leave a child behind (a rank stuck in a
+    collective after its peer died would otherwise hold its GPU until the NCCL watchdog fires)."""
+    ctx = mp.get_context("spawn")
+    q = ctx.Queue()
+    port = _free_port()
+    procs = [ctx.Process(target=_guard, args=(target, r, world, port, q)) for r in range(world)]
+    for p in procs:
+        p.start()
+    items = []
+    try:
+        for _ in range(n_items):
+            item = q.get(timeout=timeout)
+            if isinstance(item, tuple) and item and item[0] == "error":
+                raise AssertionError(item[1])
+            items.append(item)
+        for p in procs:
+            p.join(timeout=60)
+    finally:
+        for p in procs:
+            if p.is_alive():
+                p.kill()
+    assert all(p.exitcode == 0 for p in procs), [p.exitcode for p in procs]
+    return items
+
+
+def _guard(target, rank, world, port, q):
+    try:
+        target(rank, world, port, q)
+    except BaseException as exc:  # noqa: BLE001
+        import traceback
+        q.put(("error", f"rank {rank}: {exc!r}\n{traceback.format_exc()}"))
+        os._exit(1)
+
+
 def _free_port():
     with socket.socket() as s:
         s.bind(("127.0.0.1", 0))
@@ -64,16 +99,7 @@ def _pipeline_worker(rank, world, port, q):
 @pytest.mark.skipif(torch.cuda.device_count() < 2, reason="needs 2 GPUs")
 def test_two_rank_pipeline_tokens_identical_to_reference(golden):
     g = golden("tiny_decode.json")
-    ctx = mp.get_context("spawn")
-    q = ctx.Queue()
-    port = _free_port()
-    procs = [ctx.Process(target=_pipeline_worker, args=(r, 2, port, q)) for r in range(2)]
-    for p in procs:
-        p.start()
-    got = q.get(timeout=300)
-    for p in procs:
-        p.join(timeout=120)
-        assert p.exitcode == 0
+    (got,) = _run_ranks(_pipeline_worker, 2, 1)
     assert got == [row[:27] for row in g["tokens"]]
 
 
@@ -122,16 +148,7 @@ def _transfer_worker(rank, world, port, q):
 
 @pytest.mark.skipif(torch.cuda.device_count() < 2, reason="needs 2 GPUs")
 def test_pd_handoff_over_nccl_is_bit_exact():
-    ctx = mp.get_context("spawn")
-    q = ctx.Queue()
-    port = _free_port()
-    procs = [ctx.Process(target=_transfer_worker, args=(r, 2, port, q)) for r in range(2)]
-    for p in procs:
-        p.start()
-    items = dict(q.get(timeout=300) for _ in range(2))
-    for p in procs:
-        p.join(timeout=120)
-        assert p.exitcode == 0
+    items = dict(_run_ranks(_transfer_worker, 2, 2))
     assert items["sent"] == items["received"]
 
 
@@ -201,16 +218,7 @@ def _push_worker(rank, world, port, q):
 
 @pytest.mark.skipif(torch.cuda.device_count() < 2, reason="needs 2 GPUs")
 def test_peer_push_handoff_is_bit_exact():
-    ctx = mp.get_context("spawn")
-    q = ctx.Queue()
-    port = _free_port()
-    procs = [ctx.Process(target=_push_worker, args=(r, 2, port, q)) for r in range(2)]
-    for p in procs:
-        p.start()
-    items = dict(q.get(timeout=300) for _ in range(2))
-    for p in procs:
-        p.join(timeout=120)
-        assert p.exitcode == 0
+    items = dict(_run_ranks(_push_worker, 2, 2))
     assert items["sent"] == items["received"]
 
 
