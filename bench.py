@@ -313,7 +313,8 @@ def run_single(args, workload):
             traffic = json.load(open(tpath)).get(workload["key"])
         except Exception:  # noqa: BLE001
             traffic = None
-    launches_per_step = cfg.num_hidden_layers * (2 + (1 if eng.num_splits > 1 else 0))
+    # this repo's kernels per step: per layer add_rmsnorm x2, rope_kv_append, attention (+ combine), silu_mul; + final norm
+    launches_per_step = cfg.num_hidden_layers * (5 + (1 if eng.num_splits > 1 else 0)) + 1
 
     line = {
         "metric": "decode_tokens_per_s",

@@ -22,6 +22,7 @@
 // partial to the workspace for attn_combine_kernel.
 #include <cuda.h>
 
+#include <cstdlib>
 #include <mutex>
 #include <unordered_map>
 
@@ -128,7 +129,7 @@ struct Smem {
 };
 
 template <typename T, int D, int STAGES>
-__global__ void __launch_bounds__(kWarps * 32, 2)
+__global__ void __launch_bounds__(kWarps * 32, (STAGES <= 3 ? 2 : 1))
 paged_attn_tma_kernel(const __grid_constant__ CUtensorMap k_map, const __grid_constant__ CUtensorMap v_map,
                       T* __restrict__ out, const T* __restrict__ q, int64_t q_row_stride,
                       const int32_t* __restrict__ block_tables, int table_stride,
@@ -435,11 +436,24 @@ bool attn_tma_supported(const AttnArgs& a, int dtype) {
   return encode_fn() != nullptr;
 }
 
-int attn_tma(const AttnArgs& a, int dtype, cudaStream_t s) {
-  constexpr int STAGES = 3;
+template <int STAGES>
+int attn_tma_stages(const AttnArgs& a, int dtype, cudaStream_t s) {
   if (dtype == B200_DTYPE_BF16)
     return a.D == 128 ? launch_tma<__nv_bfloat16, 128, STAGES>(a, dtype, s) : launch_tma<__nv_bfloat16, 64, STAGES>(a, dtype, s);
   return a.D == 128 ? launch_tma<__half, 128, STAGES>(a, dtype, s) : launch_tma<__half, 64, STAGES>(a, dtype, s);
+}
+
+// Ring depth: 3 stages x 2 CTAs per SM when the grid has at least two CTAs for every SM; 6 stages x 1 CTA per SM
+// when it has not (then a second resident CTA never materialises and the deeper ring keeps the same number of
+// bytes in flight per SM).  B200_ATTN_STAGES=3|6 overrides the choice (used by tools/kbench.py sweeps).
+int attn_tma(const AttnArgs& a, int dtype, cudaStream_t s) {
+  static const int forced = [] {
+    const char* e = getenv("B200_ATTN_STAGES");
+    return e ? atoi(e) : 0;
+  }();
+  const long ctas = static_cast<long>(a.num_splits) * a.Hkv * a.B;
+  const int stages = forced ? forced : (ctas >= 2L * kNumSMs ? 3 : 6);
+  return stages >= 6 ? attn_tma_stages<6>(a, dtype, s) : attn_tma_stages<3>(a, dtype, s);
 }
 
 }  // namespace b200

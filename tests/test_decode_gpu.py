@@ -99,3 +99,26 @@ def test_half_precision_tokens_vs_reference_dense_path(golden, dtype):
     agree = float((got == want).float().mean())
     print(f"{dtype}: token agreement {agree:.3f}")
     assert not bad, f"divergence at a decided token: {bad}"
+
+
+def test_batch_inference_protocol_of_the_reference_batcher(golden):
+    """ContinuousBatcher._execute_batch (reference: worker/batch_processor.py:302-336) calls
+    engine.batch_inference(params_list) and treats Exception instances in the returned list as per-request
+    failures (:237-242).  The engine must honour both."""
+    g, cfg, sd = _tiny(golden)
+    prompts = torch.tensor(g["prompt_ids"])
+    shards = build_product_shards(cfg, sd, [(0, 4)], DEV, torch.float32)
+    eng = PagedDecodeEngine(shards, max_batch=4, max_seq_len=192, prefill_mode="eager")
+    reqs = [
+        {"input_ids": prompts[0].tolist(), "max_new_tokens": 8},
+        {"input_ids": prompts[1, :40].tolist(), "max_new_tokens": 5},
+        {"max_new_tokens": 3},  # malformed: no input_ids
+        {"input_ids": prompts[2].tolist(), "max_new_tokens": 6},
+    ]
+    out = eng.batch_inference(reqs)
+    assert len(out) == 4 and isinstance(out[2], Exception)
+    assert out[0]["output_ids"] == g["tokens"][0][:8]
+    assert out[3]["output_ids"] == g["tokens"][2][:6]
+    want = L.greedy_decode(L.build_shards(cfg, sd, [(0, 4)]), prompts[1:2, :40], 5)[0].tolist()
+    assert out[1]["output_ids"] == want
+    assert out[1]["usage"] == {"prompt_tokens": 40, "completion_tokens": 5}
