@@ -295,6 +295,9 @@ def run_single(args, workload):
     eng.ids_buf[:B, 0].copy_(nxt.to(dev))
     n_inst = min(K, 4)
     for _ in range(n_inst):
+        # park the GPU for ~30 ms first so the host is a whole step ahead: the event pairs then bracket pure
+        # device time instead of host launch latency
+        torch.cuda._sleep(60_000_000)
         eng.decode_step_device()
     torch.cuda.synchronize()
     ev = ops.ATTN_EVENTS

@@ -96,6 +96,7 @@ def _run(args, workload, SHAPES, ShapeConfig, ClockSampler, measured_peaks, rank
     eng.use_cuda_graph = False
     ops.ATTN_EVENTS = []
     for _ in range(2):
+        torch.cuda._sleep(60_000_000)  # let the host run ahead so the event pairs bracket device time only
         eng.stage_step()
     torch.cuda.synchronize()
     ev, ops.ATTN_EVENTS = ops.ATTN_EVENTS, None
