@@ -115,7 +115,8 @@ class ClockSampler:
 # ---------------------------------------------------------------------------------------------------------
 # reference CPU path (oracle port) — bounded sample
 # ---------------------------------------------------------------------------------------------------------
-def cpu_reference_tokens_per_s(shape: str, batch: int, ctx: int, steps: int, warmup: int, sample_layers: int = 2):
+def cpu_reference_tokens_per_s(shape: str, batch: int, ctx: int, steps: int, warmup: int, sample_layers: int = 2,
+                               sample_batch: int = 0):
     """Time the reference's torch path (oracle.llama_ref: ModelShard.forward restatement + legacy HF layer with
     dense (k, v) tuples, fp32) on the host cores for `sample_layers` layers of the named shape at the full batch
     and context, plus the embedding / final norm / lm_head once per step, and extrapolate to the full depth."""
@@ -123,6 +124,9 @@ def cpu_reference_tokens_per_s(shape: str, batch: int, ctx: int, steps: int, war
 
     cores = os.cpu_count() or 1
     torch.set_num_threads(cores)
+    full_batch = batch
+    if sample_batch and sample_batch < batch:
+        batch = sample_batch  # bounded sample: fewer sequences, same shape and context
     cfg = L.RefConfig(**SHAPES[shape])
     total_layers = cfg.num_hidden_layers
     g = torch.Generator().manual_seed(0)
@@ -163,7 +167,8 @@ def cpu_reference_tokens_per_s(shape: str, batch: int, ctx: int, steps: int, war
         "unit": "tokens/s",
         "cores": cores,
         "kind": "port",
-        "sample": (f"{sample_layers} of {total_layers} layers of the {shape} shape at batch {batch}, context "
+        "sample": (f"{sample_layers} of {total_layers} layers of the {shape} shape at batch {batch}"
+                   f"{'' if batch == full_batch else f' (of {full_batch}; throughput reported at the sampled batch)'}, context "
                    f"{start_ctx + warmup}..{ctx}, fp32, dense (k,v) cache, {steps} decode steps after {warmup} "
                    f"warm-up; per-layer time x {total_layers} + embed/norm/lm_head per step"),
         "ms_per_step_extrapolated": step_s * 1e3,
@@ -175,7 +180,9 @@ def run_reference(args, workload, rank, world):
     if rank != 0:
         return
     shape, batch, ctx = workload["shape"], workload["batch"], workload["context"]
-    res = cpu_reference_tokens_per_s(shape, batch, ctx, args.steps, args.warmup, sample_layers=2 if shape != "70b" else 1)
+    big = shape == "70b"
+    res = cpu_reference_tokens_per_s(shape, batch, ctx, args.steps, args.warmup, sample_layers=1 if big else 2,
+                                     sample_batch=16 if big else 0)
     line = {
         "impl": "reference",
         "metric": "decode_tokens_per_s",

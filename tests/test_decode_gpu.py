@@ -122,3 +122,35 @@ def test_batch_inference_protocol_of_the_reference_batcher(golden):
     want = L.greedy_decode(L.build_shards(cfg, sd, [(0, 4)]), prompts[1:2, :40], 5)[0].tolist()
     assert out[1]["output_ids"] == want
     assert out[1]["usage"] == {"prompt_tokens": 40, "completion_tokens": 5}
+
+
+def test_8b_shape_bf16_paged_path_vs_reference_dense_path():
+    """BASELINE config 2's shape (d 4096, 32 q / 8 kv heads, head_dim 128, ffn 14336, vocab 128256) cut to 4 layers,
+    bf16, batch 8, prompt 300, 24 greedy tokens: the paged CUDA path against the reference recipe (oracle dense
+    path) on the same GPU, same weights.  Divergences are only accepted at near-ties of the reference's logits."""
+    shape = dict(L.LLAMA3_8B)
+    shape["num_hidden_layers"] = 4
+    cfg = L.RefConfig(**shape)
+    sd = {k: v.to(torch.bfloat16) for k, v in L.make_weights(cfg, seed=3).items()}
+    B, P, n_new = 8, 300, 24
+    prompts = torch.randint(0, cfg.vocab_size, (B, P), generator=torch.Generator().manual_seed(77))
+    ref_shards = L.build_shards(cfg, sd, [(0, 2), (2, 4)], dtype=torch.bfloat16, device=DEV)
+    want, logits = L.greedy_decode(ref_shards, prompts.to(DEV), n_new, return_logits=True)
+    del ref_shards
+    shards = build_product_shards(cfg, sd, [(0, 2), (2, 4)], DEV, torch.bfloat16)
+    for fused in (False, True):
+        eng = PagedDecodeEngine(shards, B, P + n_new + 8, prefill_mode="eager", fuse_projections=fused)
+        got = eng.generate(prompts, n_new).to(DEV)
+        eps = torch.finfo(torch.bfloat16).eps
+        bad = []
+        for b in range(B):
+            diff = (got[b] != want[b]).nonzero()
+            if len(diff):
+                s = int(diff[0])
+                top2 = logits[b, s].topk(2).values
+                margin = float(top2[0] - top2[1])
+                if margin > 2 * eps * float(top2[0].abs()) + 1e-6:
+                    bad.append((b, s, margin, float(top2[0])))
+        print(f"8B-shape bf16 (fused projections={fused}): token agreement {float((got == want).float().mean()):.3f}")
+        assert not bad, f"divergence at a decided token: {bad}"
+        eng.release()
