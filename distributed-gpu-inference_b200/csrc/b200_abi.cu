@@ -123,6 +123,77 @@ int b200_paged_decode_attn(void* out, const void* q, int64_t q_row_stride, const
   return 0;
 }
 
+int b200_paged_decode_attn_prefix_plan(int B, int Hq, int Hkv, int D, int block_size, int prefix_blocks,
+                                       int max_context_len, int dtype, int* prefix_splits, int* suffix_splits) {
+  (void)D;
+  (void)dtype;
+  if (!prefix_splits || !suffix_splits) return fail(B200_EINVAL, "b200_paged_decode_attn_prefix_plan: null pointer");
+  if (B <= 0 || Hq <= 0 || Hkv <= 0 || block_size <= 0 || prefix_blocks < 0)
+    return fail(B200_EINVAL, "b200_paged_decode_attn_prefix_plan: bad sizes");
+  attn_prefix_plan(B, Hq, Hkv, block_size, prefix_blocks, max_context_len, prefix_splits, suffix_splits);
+  return 0;
+}
+
+int b200_paged_decode_attn_prefix(void* out, const void* q, int64_t q_row_stride, const void* k_pool,
+                                  const void* v_pool, const int32_t* block_tables, int table_stride,
+                                  const int32_t* context_lens, int B, int Hq, int Hkv, int D, int block_size,
+                                  int64_t max_blocks, float scale, int max_context_len, int prefix_blocks,
+                                  int prefix_splits, int suffix_splits, void* workspace, size_t workspace_bytes,
+                                  int dtype, unsigned flags, void* stream) {
+  const char* name = "b200_paged_decode_attn_prefix";
+  if (prefix_blocks < 0 || prefix_splits < 0 || suffix_splits < 0) return fail(B200_EINVAL, "%s: negative count", name);
+  if (prefix_blocks == 0)
+    return b200_paged_decode_attn(out, q, q_row_stride, k_pool, v_pool, block_tables, table_stride, context_lens, B, Hq,
+                                  Hkv, D, block_size, max_blocks, scale, max_context_len, suffix_splits, workspace,
+                                  workspace_bytes, dtype, flags, stream);
+  if (dtype_size(dtype) == 0) return fail(B200_EINVAL, "%s: unsupported dtype %d", name, dtype);
+  if (B <= 0 || Hq <= 0 || Hkv <= 0 || D <= 0 || block_size <= 0 || max_blocks <= 0 || Hq % Hkv != 0)
+    return fail(B200_EINVAL, "%s: bad sizes", name);
+  if (!out || !q || !k_pool || !v_pool || !block_tables || !context_lens || !workspace)
+    return fail(B200_EINVAL, "%s: null pointer (a workspace is always needed)", name);
+  if (prefix_blocks > table_stride || static_cast<int64_t>(prefix_blocks) * block_size > max_context_len)
+    return fail(B200_EINVAL, "%s: prefix of %d blocks exceeds the table / max_context_len", name, prefix_blocks);
+  int ps = prefix_splits, ss = suffix_splits;
+  if (ps == 0 || ss == 0) {
+    int aps, ass;
+    attn_prefix_plan(B, Hq, Hkv, block_size, prefix_blocks, max_context_len, &aps, &ass);
+    if (ps == 0) ps = aps;
+    if (ss == 0) ss = ass;
+  }
+  ps = std::min(ps, prefix_blocks);
+  const int suffix_blocks = std::max(1, ceil_div(std::max(1, max_context_len - prefix_blocks * block_size), block_size));
+  ss = std::min(ss, suffix_blocks);
+  const int total = ps + ss;
+  const size_t need = b200_paged_decode_attn_workspace(B, Hq, D, total);
+  if (workspace_bytes < need)
+    return fail(B200_ENOSPC, "%s: workspace of %zu bytes needed for %d + %d splits, got %zu", name, need, ps, ss,
+                workspace_bytes);
+  AttnArgs a{};
+  a.out = out;
+  a.q = q;
+  a.q_row_stride = q_row_stride;
+  a.k_pool = k_pool;
+  a.v_pool = v_pool;
+  a.block_tables = block_tables;
+  a.table_stride = table_stride;
+  a.context_lens = context_lens;
+  a.B = B;
+  a.Hq = Hq;
+  a.Hkv = Hkv;
+  a.D = D;
+  a.block_size = block_size;
+  a.max_blocks = max_blocks;
+  a.scale = scale;
+  a.num_splits = ss;
+  a.blocks_per_split = ceil_div(suffix_blocks, ss);
+  a.round_scores = (flags & B200_ATTN_ROUND_SCORES) ? 1 : 0;
+  a.ws_acc = static_cast<float*>(workspace);
+  a.ws_ml = a.ws_acc + static_cast<size_t>(B) * Hq * total * D;
+  if (!attn_prefix_supported(a, dtype))
+    return fail(B200_ESHAPE, "%s: needs f16/bf16, block_size 16, head_dim 64/128, group <= 8", name);
+  return attn_prefix(a, dtype, prefix_blocks, ps, ss, static_cast<cudaStream_t>(stream));
+}
+
 int b200_kv_pack(void* packed, const void* k_pool, const void* v_pool, const int32_t* block_table, int n_blocks,
                  int Hkv, int D, int block_size, int64_t max_blocks, int dtype, void* stream) {
   return kv_pack(packed, k_pool, v_pool, block_table, n_blocks, Hkv, D, block_size, max_blocks, dtype,

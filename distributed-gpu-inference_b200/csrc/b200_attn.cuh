@@ -23,6 +23,11 @@ struct AttnArgs {
   float* ws_acc;                // [B, Hq, num_splits, D] un-normalised partial outputs
   float* ws_ml;                 // [B, Hq, num_splits, 2] running max and sum
   int round_scores;
+  // shared-prefix cascade only (zero otherwise): skip blocks below first_block, file partials at
+  // split_offset + split out of splits_total
+  int first_block;
+  int split_offset;
+  int splits_total;
 };
 
 // shape-generic CUDA-core variant (b200_attn_generic.cu)
@@ -30,6 +35,11 @@ int attn_generic(const AttnArgs& a, int dtype, cudaStream_t s);
 // TMA + tensor-core variant (b200_attn_tma.cu); attn_tma_supported says whether it covers the shape
 bool attn_tma_supported(const AttnArgs& a, int dtype);
 int attn_tma(const AttnArgs& a, int dtype, cudaStream_t s);
+// shared-prefix cascade (b200_attn_prefix.cu): prefix blocks once for all sequences, then per-sequence suffixes
+bool attn_prefix_supported(const AttnArgs& a, int dtype);
+int attn_prefix(const AttnArgs& a, int dtype, int prefix_blocks, int prefix_splits, int suffix_splits, cudaStream_t s);
+void attn_prefix_plan(int B, int Hq, int Hkv, int block_size, int prefix_blocks, int max_context_len,
+                      int* prefix_splits, int* suffix_splits);
 // merge of split-K partials
 int attn_combine(void* out, const float* ws_acc, const float* ws_ml, int rows, int D, int num_splits, int dtype,
                  cudaStream_t stream);

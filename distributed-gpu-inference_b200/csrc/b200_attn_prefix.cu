@@ -1,0 +1,305 @@
+// Shared-prefix ("cascade") paged decode attention for sm_100a.
+//
+// When every sequence of a batch starts with the same blocks (a shared system prompt / radix prefix: the blocks
+// whose CacheBlock.ref_count > 1, reference worker/distributed/kv_cache.py:63-72), the plain kernel streams those
+// blocks once PER SEQUENCE; they come out of L2 after the first reader, but the launch is still paced by L2 and the
+// unique HBM bytes are a fraction of what moves.  Here the prefix is processed ONCE for all sequences:
+//
+//   launch 1 (this file)   grid (prefix_splits, Hkv, q-groups): a CTA takes a run of prefix blocks of one kv head
+//                          and NT*8 query rows at a time — rows are (sequence, q head of the group) pairs, so one
+//                          K/V tile staged by TMA feeds several sequences' queries through the same MMAs
+//                          (S^T = K Q^T with N = 16 instead of 8).  Partials go to the split-K workspace.
+//   launch 2               the plain kernel (b200_attn_tma.cu) over each sequence's own blocks after the prefix
+//                          (first_block = prefix_blocks), partials filed after launch 1's.
+//   launch 3               attn_combine_kernel over prefix_splits + suffix_splits partials per (sequence, q head).
+//
+// The caller guarantees: block_tables[b][0:prefix_blocks] are identical for all b, and every context_lens[b] >=
+// prefix_blocks * 16 (the prefix blocks are full for everybody, so launch 1 needs no masking).
+#include <algorithm>
+
+#include "b200_attn.cuh"
+#include "b200_common.cuh"
+#include "b200_tma_common.cuh"
+
+namespace b200 {
+
+using namespace tma;
+
+namespace {
+
+template <typename T, int D, int STAGES, int NT>
+__global__ void __launch_bounds__(kWarps * 32, 2)
+paged_attn_prefix_kernel(const __grid_constant__ CUtensorMap k_map, const __grid_constant__ CUtensorMap v_map,
+                         const T* __restrict__ q, int64_t q_row_stride, const int32_t* __restrict__ prefix_table,
+                         int prefix_blocks, int B, int Hq, int Hkv, int G, float scale, int blocks_per_split,
+                         int splits_total, float* __restrict__ ws_acc, float* __restrict__ ws_ml, int round_scores) {
+  using S = Smem<D, STAGES>;
+  constexpr int KSTEPS = D / 16;
+  constexpr int MTILES = D / 16;
+  constexpr int BOXES = D / 64;
+  constexpr int COLS = 8 * NT;  // query rows (sequence, head) handled by this CTA
+
+  const int split = blockIdx.x, kvh = blockIdx.y, qgroup = blockIdx.z;
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int quad = lane >> 2, tq = lane & 3;
+
+  extern __shared__ unsigned char smem_raw[];
+  unsigned char* smem = reinterpret_cast<unsigned char*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+  const uint32_t ring = smem_u32(smem) + warp * STAGES * S::kStageBytes;
+  const uint32_t bars = smem_u32(smem + S::kRingBytes) + warp * STAGES * 8;
+  if (lane == 0) {
+#pragma unroll
+    for (int s = 0; s < STAGES; ++s) mbar_init(bars + s * 8, 1);
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+  }
+  __syncwarp();
+
+  const int blk_begin = min(prefix_blocks, split * blocks_per_split);
+  const int blk_end = min(prefix_blocks, (split + 1) * blocks_per_split);
+  const int n_cta = blk_end - blk_begin;
+  const int n_mine = n_cta > warp ? (n_cta - warp + kWarps - 1) / kWarps : 0;
+  const int32_t* table = prefix_table + blk_begin + warp;
+
+  int win_base = 0;
+  int32_t win_slot = (lane < n_mine) ? table[lane * kWarps] : 0;
+  auto issue = [&](int j) {
+    if (j - win_base >= 32) {
+      win_base += 32;
+      win_slot = (win_base + lane < n_mine) ? table[(win_base + lane) * kWarps] : 0;
+    }
+    const int32_t slot = __shfl_sync(0xffffffffu, win_slot, j - win_base);
+    if (lane == 0) {
+      const int st = j % STAGES;
+      const uint32_t bar = bars + st * 8;
+      const uint32_t dst = ring + st * S::kStageBytes;
+      const int row = (slot * Hkv + kvh) * kTok;
+      mbar_expect_tx(bar, S::kStageBytes);
+#pragma unroll
+      for (int bx = 0; bx < BOXES; ++bx) {
+        tma_load_2d(dst + bx * (kTok * 128), &k_map, bx * 64, row, bar);
+        tma_load_2d(dst + S::kTileBytes + bx * (kTok * 128), &v_map, bx * 64, row, bar);
+      }
+    }
+  };
+  const int n_pro = min(STAGES, n_mine);
+  for (int j = 0; j < n_pro; ++j) issue(j);
+
+  // Q rows of this CTA as B operands: column c = nt * 8 + quad  <->  row r = qgroup * COLS + c  <->  (b, g)
+  uint32_t qf[KSTEPS][NT][2];
+#pragma unroll
+  for (int nt = 0; nt < NT; ++nt) {
+    const int r = qgroup * COLS + nt * 8 + quad;
+    const int bq = r / G, g = r - bq * G;
+    const bool ok = bq < B;
+    const T* qrow = q + static_cast<int64_t>(ok ? bq : 0) * q_row_stride + static_cast<int64_t>(kvh * G + g) * D;
+#pragma unroll
+    for (int kk = 0; kk < KSTEPS; ++kk) {
+      qf[kk][nt][0] = ok ? *reinterpret_cast<const uint32_t*>(qrow + kk * 16 + 2 * tq) : 0u;
+      qf[kk][nt][1] = ok ? *reinterpret_cast<const uint32_t*>(qrow + kk * 16 + 8 + 2 * tq) : 0u;
+    }
+  }
+
+  const float sl2 = scale * 1.4426950408889634f;
+  float m_run[NT][2], l_run[NT][2], o[MTILES][NT][4];
+#pragma unroll
+  for (int nt = 0; nt < NT; ++nt) {
+    m_run[nt][0] = m_run[nt][1] = -INFINITY;
+    l_run[nt][0] = l_run[nt][1] = 0.f;
+#pragma unroll
+    for (int mt = 0; mt < MTILES; ++mt) o[mt][nt][0] = o[mt][nt][1] = o[mt][nt][2] = o[mt][nt][3] = 0.f;
+  }
+
+  const int lm_mat = lane >> 3, lm_row = lane & 7;
+  const int k_row = (lm_mat & 1) * 8 + lm_row, k_chunk = lm_mat >> 1;
+  const int v_row = (lm_mat >> 1) * 8 + lm_row, v_chunk = lm_mat & 1;
+
+  for (int i = 0; i < n_mine; ++i) {
+    const int st = i % STAGES;
+    const uint32_t k_tile = ring + st * S::kStageBytes;
+    const uint32_t v_tile = k_tile + S::kTileBytes;
+    mbar_wait(bars + st * 8, (i / STAGES) & 1);
+
+    float s[NT][4];
+#pragma unroll
+    for (int nt = 0; nt < NT; ++nt) s[nt][0] = s[nt][1] = s[nt][2] = s[nt][3] = 0.f;
+#pragma unroll
+    for (int kk = 0; kk < KSTEPS; ++kk) {
+      uint32_t a[4];
+      ldmatrix_x4(a, k_tile + tile_off(k_row, 2 * kk + k_chunk));
+#pragma unroll
+      for (int nt = 0; nt < NT; ++nt) Mma<T>::run(s[nt], a, qf[kk][nt][0], qf[kk][nt][1]);
+    }
+
+    float corr[NT][2];
+    uint32_t pb[NT][2];
+#pragma unroll
+    for (int nt = 0; nt < NT; ++nt) {
+      float x[4];
+#pragma unroll
+      for (int e = 0; e < 4; ++e)
+        x[e] = round_scores ? Mma<T>::round(Mma<T>::round(s[nt][e]) * scale) * 1.4426950408889634f : s[nt][e] * sl2;
+#pragma unroll
+      for (int c = 0; c < 2; ++c) {
+        float mx = fmaxf(x[c], x[c + 2]);
+        mx = fmaxf(mx, __shfl_xor_sync(0xffffffffu, mx, 4));
+        mx = fmaxf(mx, __shfl_xor_sync(0xffffffffu, mx, 8));
+        mx = fmaxf(mx, __shfl_xor_sync(0xffffffffu, mx, 16));
+        const float m_new = fmaxf(m_run[nt][c], mx);
+        corr[nt][c] = exp2f(m_run[nt][c] - m_new);
+        m_run[nt][c] = m_new;
+        x[c] = exp2f(x[c] - m_new);
+        x[c + 2] = exp2f(x[c + 2] - m_new);
+        l_run[nt][c] = l_run[nt][c] * corr[nt][c] + x[c] + x[c + 2];
+      }
+      pb[nt][0] = movmatrix_trans(Mma<T>::pack(x[0], x[1]));
+      pb[nt][1] = movmatrix_trans(Mma<T>::pack(x[2], x[3]));
+    }
+
+#pragma unroll
+    for (int mt = 0; mt < MTILES; ++mt) {
+      uint32_t a[4];
+      ldmatrix_x4_trans(a, v_tile + tile_off(v_row, 2 * mt + v_chunk));
+#pragma unroll
+      for (int nt = 0; nt < NT; ++nt) {
+        o[mt][nt][0] *= corr[nt][0];
+        o[mt][nt][1] *= corr[nt][1];
+        o[mt][nt][2] *= corr[nt][0];
+        o[mt][nt][3] *= corr[nt][1];
+        Mma<T>::run(o[mt][nt], a, pb[nt][0], pb[nt][1]);
+      }
+    }
+    __syncwarp();
+    if (i + STAGES < n_mine) issue(i + STAGES);
+  }
+
+  // merge the 4 warps, then file one partial per (sequence, q head) of this CTA's columns
+#pragma unroll
+  for (int nt = 0; nt < NT; ++nt)
+#pragma unroll
+    for (int c = 0; c < 2; ++c) {
+      l_run[nt][c] += __shfl_xor_sync(0xffffffffu, l_run[nt][c], 4);
+      l_run[nt][c] += __shfl_xor_sync(0xffffffffu, l_run[nt][c], 8);
+      l_run[nt][c] += __shfl_xor_sync(0xffffffffu, l_run[nt][c], 16);
+    }
+  __syncthreads();
+  float* o_s = reinterpret_cast<float*>(smem);   // [W][COLS][D]
+  float* m_s = o_s + kWarps * COLS * D;          // [W][COLS]
+  float* l_s = m_s + kWarps * COLS;              // [W][COLS]
+#pragma unroll
+  for (int mt = 0; mt < MTILES; ++mt)
+#pragma unroll
+    for (int nt = 0; nt < NT; ++nt)
+#pragma unroll
+      for (int e = 0; e < 4; ++e) {
+        const int c = nt * 8 + 2 * tq + (e & 1);
+        const int d = 16 * mt + quad + ((e >> 1) << 3);
+        o_s[(warp * COLS + c) * D + d] = o[mt][nt][e];
+      }
+  if (quad == 0) {
+#pragma unroll
+    for (int nt = 0; nt < NT; ++nt)
+#pragma unroll
+      for (int c = 0; c < 2; ++c) {
+        m_s[warp * COLS + nt * 8 + 2 * tq + c] = m_run[nt][c];
+        l_s[warp * COLS + nt * 8 + 2 * tq + c] = l_run[nt][c];
+      }
+  }
+  __syncthreads();
+  const float ln2 = 0.6931471805599453f;
+  for (int idx = threadIdx.x; idx < COLS * D; idx += kWarps * 32) {
+    const int c = idx / D, d = idx - c * D;
+    const int r = qgroup * COLS + c;
+    const int bq = r / G, g = r - bq * G;
+    if (bq >= B) continue;
+    float M = -INFINITY;
+#pragma unroll
+    for (int w = 0; w < kWarps; ++w) M = fmaxf(M, m_s[w * COLS + c]);
+    float acc = 0.f, L = 0.f;
+#pragma unroll
+    for (int w = 0; w < kWarps; ++w) {
+      const float mw = m_s[w * COLS + c];
+      const float wgt = (mw == -INFINITY) ? 0.f : exp2f(mw - M);
+      acc = fmaf(wgt, o_s[(w * COLS + c) * D + d], acc);
+      L = fmaf(wgt, l_s[w * COLS + c], L);
+    }
+    const int64_t pidx = (static_cast<int64_t>(bq) * Hq + kvh * G + g) * splits_total + split;
+    ws_acc[pidx * D + d] = acc;
+    if (d == 0) {
+      ws_ml[pidx * 2 + 0] = M * ln2;  // natural-log domain, as attn_combine_kernel expects
+      ws_ml[pidx * 2 + 1] = L;
+    }
+  }
+}
+
+inline int ceil_div(int a, int b) { return (a + b - 1) / b; }
+
+constexpr int kPrefixNT = 2;      // 16 query rows per CTA
+constexpr int kPrefixStages = 3;
+
+template <typename T, int D>
+int launch_prefix(const AttnArgs& a, int dtype, int prefix_blocks, int prefix_splits, int splits_total, cudaStream_t stream) {
+  using S = Smem<D, kPrefixStages>;
+  const uint64_t rows = static_cast<uint64_t>(a.max_blocks) * a.Hkv * kTok;
+  CUtensorMap km, vm;
+  int rc = get_tensor_map(a.k_pool, rows, D, dtype, &km);
+  if (rc) return rc;
+  rc = get_tensor_map(a.v_pool, rows, D, dtype, &vm);
+  if (rc) return rc;
+  auto kern = paged_attn_prefix_kernel<T, D, kPrefixStages, kPrefixNT>;
+  cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, S::kTotal);
+  if (e != cudaSuccess) return fail(static_cast<int>(e), "cudaFuncSetAttribute: %s", cudaGetErrorString(e));
+  const int G = a.Hq / a.Hkv;
+  const int qgroups = ceil_div(a.B * G, 8 * kPrefixNT);
+  dim3 grid(prefix_splits, a.Hkv, qgroups);
+  kern<<<grid, kWarps * 32, S::kTotal, stream>>>(km, vm, static_cast<const T*>(a.q), a.q_row_stride, a.block_tables,
+                                                  prefix_blocks, a.B, a.Hq, a.Hkv, G, a.scale,
+                                                  ceil_div(prefix_blocks, prefix_splits), splits_total, a.ws_acc, a.ws_ml,
+                                                  a.round_scores);
+  return check_launch("b200_paged_decode_attn_prefix(prefix)");
+}
+
+}  // namespace
+
+bool attn_prefix_supported(const AttnArgs& a, int dtype) { return attn_tma_supported(a, dtype); }
+
+// Split counts for the two launches: the prefix launch wants ~2 CTAs per SM out of (splits x Hkv x q-groups) with
+// at least 256 tokens per split; the suffix launch follows the plain kernel's rule on the remaining context.
+void attn_prefix_plan(int B, int Hq, int Hkv, int block_size, int prefix_blocks, int max_context_len,
+                      int* prefix_splits, int* suffix_splits) {
+  const int G = std::max(1, Hq / std::max(1, Hkv));
+  const int qgroups = std::max(1, ceil_div(B * G, 8 * kPrefixNT));
+  const int min_blocks = std::max(1, 256 / block_size);
+  int ps = ceil_div(2 * kNumSMs, std::max(1, Hkv * qgroups));
+  ps = std::max(1, std::min(ps, std::max(1, prefix_blocks / min_blocks)));
+  *prefix_splits = std::min(ps, 96);
+  const int suffix_tokens = std::max(0, max_context_len - prefix_blocks * block_size);
+  const int suffix_blocks = std::max(1, ceil_div(std::max(1, suffix_tokens), block_size));
+  const int pairs = std::max(1, B * Hkv);
+  int ss = pairs >= 120 ? 1 : ceil_div(kNumSMs * 7 / 2, pairs);
+  ss = std::max(1, std::min(ss, std::max(1, suffix_blocks / min_blocks)));
+  *suffix_splits = std::min(ss, 96);
+}
+
+int attn_prefix(const AttnArgs& a_in, int dtype, int prefix_blocks, int prefix_splits, int suffix_splits, cudaStream_t s) {
+  AttnArgs a = a_in;
+  const int total = prefix_splits + suffix_splits;
+  int rc;
+  if (dtype == B200_DTYPE_BF16)
+    rc = a.D == 128 ? launch_prefix<__nv_bfloat16, 128>(a, dtype, prefix_blocks, prefix_splits, total, s)
+                    : launch_prefix<__nv_bfloat16, 64>(a, dtype, prefix_blocks, prefix_splits, total, s);
+  else
+    rc = a.D == 128 ? launch_prefix<__half, 128>(a, dtype, prefix_blocks, prefix_splits, total, s)
+                    : launch_prefix<__half, 64>(a, dtype, prefix_blocks, prefix_splits, total, s);
+  if (rc) return rc;
+  // per-sequence suffixes with the plain kernel
+  a.first_block = prefix_blocks;
+  a.split_offset = prefix_splits;
+  a.splits_total = total;
+  a.num_splits = suffix_splits;
+  rc = attn_tma(a, dtype, s);
+  if (rc) return rc;
+  return attn_combine(a.out, a.ws_acc, a.ws_ml, a.B * a.Hq, a.D, total, dtype, s);
+}
+
+}  // namespace b200

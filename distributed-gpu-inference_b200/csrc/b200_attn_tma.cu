@@ -28,105 +28,87 @@
 
 #include "b200_attn.cuh"
 #include "b200_common.cuh"
+#include "b200_tma_common.cuh"
 
 namespace b200 {
 
+namespace tma {
+
 namespace {
+// ---- host side: tensor maps -------------------------------------------------------------------------------
+using EncodeTiledFn = CUresult (*)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*,
+                                   const cuuint64_t*, const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave,
+                                   CUtensorMapSwizzle, CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
 
-constexpr int kWarps = 4;
-constexpr int kTok = 16;  // tokens per tile == block_size
-
-// ---- PTX wrappers ---------------------------------------------------------------------------------------
-__device__ __forceinline__ uint32_t smem_u32(const void* p) { return static_cast<uint32_t>(__cvta_generic_to_shared(p)); }
-
-__device__ __forceinline__ void mbar_init(uint32_t bar, uint32_t count) {
-  asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(bar), "r"(count));
-}
-__device__ __forceinline__ void mbar_expect_tx(uint32_t bar, uint32_t bytes) {
-  asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar), "r"(bytes) : "memory");
-}
-__device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity) {
-  asm volatile(
-      "{\n"
-      ".reg .pred p;\n"
-      "WAIT_LOOP:\n"
-      "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n"
-      "@p bra WAIT_DONE;\n"
-      "bra WAIT_LOOP;\n"
-      "WAIT_DONE:\n"
-      "}\n" ::"r"(bar),
-      "r"(parity)
-      : "memory");
-}
-__device__ __forceinline__ void tma_load_2d(uint32_t dst, const CUtensorMap* map, int c0, int c1, uint32_t bar) {
-  asm volatile(
-      "cp.async.bulk.tensor.2d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%2, %3}], [%4];" ::"r"(dst),
-      "l"(map), "r"(c0), "r"(c1), "r"(bar)
-      : "memory");
-}
-__device__ __forceinline__ void ldmatrix_x4(uint32_t (&r)[4], uint32_t addr) {
-  asm volatile("ldmatrix.sync.aligned.m8n8.x4.shared.b16 {%0,%1,%2,%3}, [%4];"
-               : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3])
-               : "r"(addr));
-}
-__device__ __forceinline__ void ldmatrix_x4_trans(uint32_t (&r)[4], uint32_t addr) {
-  asm volatile("ldmatrix.sync.aligned.m8n8.x4.trans.shared.b16 {%0,%1,%2,%3}, [%4];"
-               : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3])
-               : "r"(addr));
-}
-__device__ __forceinline__ uint32_t movmatrix_trans(uint32_t a) {
-  uint32_t d;
-  asm volatile("movmatrix.sync.aligned.m8n8.trans.b16 %0, %1;" : "=r"(d) : "r"(a));
-  return d;
+EncodeTiledFn encode_fn() {
+  static EncodeTiledFn fn = [] {
+    void* p = nullptr;
+    cudaDriverEntryPointQueryResult qr;
+    if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &p, cudaEnableDefault, &qr) != cudaSuccess ||
+        qr != cudaDriverEntryPointSuccess)
+      p = nullptr;
+    return reinterpret_cast<EncodeTiledFn>(p);
+  }();
+  return fn;
 }
 
-template <typename T>
-struct Mma;
-template <>
-struct Mma<__nv_bfloat16> {
-  static __device__ __forceinline__ void run(float (&c)[4], const uint32_t (&a)[4], uint32_t b0, uint32_t b1) {
-    asm volatile(
-        "mma.sync.aligned.m16n8k16.row.col.f32.bf16.bf16.f32 {%0,%1,%2,%3}, {%4,%5,%6,%7}, {%8,%9}, {%0,%1,%2,%3};"
-        : "+f"(c[0]), "+f"(c[1]), "+f"(c[2]), "+f"(c[3])
-        : "r"(a[0]), "r"(a[1]), "r"(a[2]), "r"(a[3]), "r"(b0), "r"(b1));
-  }
-  static __device__ __forceinline__ uint32_t pack(float lo, float hi) {
-    __nv_bfloat162 v = __floats2bfloat162_rn(lo, hi);
-    return *reinterpret_cast<uint32_t*>(&v);
-  }
-  static __device__ __forceinline__ float round(float x) { return __bfloat162float(__float2bfloat16_rn(x)); }
+struct MapKey {
+  const void* ptr;
+  uint64_t rows;
+  int D;
+  int dtype;
+  bool operator==(const MapKey& o) const { return ptr == o.ptr && rows == o.rows && D == o.D && dtype == o.dtype; }
 };
-template <>
-struct Mma<__half> {
-  static __device__ __forceinline__ void run(float (&c)[4], const uint32_t (&a)[4], uint32_t b0, uint32_t b1) {
-    asm volatile(
-        "mma.sync.aligned.m16n8k16.row.col.f32.f16.f16.f32 {%0,%1,%2,%3}, {%4,%5,%6,%7}, {%8,%9}, {%0,%1,%2,%3};"
-        : "+f"(c[0]), "+f"(c[1]), "+f"(c[2]), "+f"(c[3])
-        : "r"(a[0]), "r"(a[1]), "r"(a[2]), "r"(a[3]), "r"(b0), "r"(b1));
+struct MapKeyHash {
+  size_t operator()(const MapKey& k) const {
+    return std::hash<const void*>()(k.ptr) ^ (std::hash<uint64_t>()(k.rows) * 1315423911u) ^ (k.D * 2654435761u) ^
+           static_cast<size_t>(k.dtype);
   }
-  static __device__ __forceinline__ uint32_t pack(float lo, float hi) {
-    __half2 v = __floats2half2_rn(lo, hi);
-    return *reinterpret_cast<uint32_t*>(&v);
-  }
-  static __device__ __forceinline__ float round(float x) { return __half2float(__float2half_rn(x)); }
 };
 
-// Byte offset of (row, 16-byte chunk) inside a K or V tile staged by TMA with 128-byte swizzle.
-// The tile is stored as D/64 boxes of [16 rows][128 B]; inside a box chunk c of row r sits at c ^ (r & 7).
-__device__ __forceinline__ uint32_t tile_off(int row, int chunk) {
-  return static_cast<uint32_t>((chunk >> 3) * (kTok * 128) + row * 128 + (((chunk & 7) ^ (row & 7)) << 4));
+}  // namespace
+
+// Pools are long-lived (one pair per layer), so descriptors are cached by (pointer, rows, D, dtype).
+int get_tensor_map(const void* pool, uint64_t rows, int D, int dtype, CUtensorMap* out) {
+  static std::mutex mu;
+  static std::unordered_map<MapKey, CUtensorMap, MapKeyHash> cache;
+  const MapKey key{pool, rows, D, dtype};
+  {
+    std::lock_guard<std::mutex> lk(mu);
+    auto it = cache.find(key);
+    if (it != cache.end()) {
+      *out = it->second;
+      return 0;
+    }
+  }
+  EncodeTiledFn enc = encode_fn();
+  if (!enc) return fail(B200_EINVAL, "cuTensorMapEncodeTiled is not available from this driver");
+  const cuuint64_t dims[2] = {static_cast<cuuint64_t>(D), rows};
+  const cuuint64_t strides[1] = {static_cast<cuuint64_t>(D) * 2};
+  const cuuint32_t box[2] = {64, static_cast<cuuint32_t>(kTok)};
+  const cuuint32_t estr[2] = {1, 1};
+  CUtensorMap m;
+  CUresult r = enc(&m, dtype == B200_DTYPE_BF16 ? CU_TENSOR_MAP_DATA_TYPE_BFLOAT16 : CU_TENSOR_MAP_DATA_TYPE_FLOAT16, 2,
+                   const_cast<void*>(pool), dims, strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
+                   CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  if (r != CUDA_SUCCESS) return fail(B200_EINVAL, "cuTensorMapEncodeTiled failed with CUresult %d", static_cast<int>(r));
+  {
+    std::lock_guard<std::mutex> lk(mu);
+    if (cache.size() > 8192) cache.clear();
+    cache.emplace(key, m);
+  }
+  *out = m;
+  return 0;
 }
 
-template <int D, int STAGES>
-struct Smem {
-  static constexpr int kTileBytes = kTok * D * 2;       // one K or V tile
-  static constexpr int kStageBytes = 2 * kTileBytes;    // K then V
-  static constexpr int kRingBytes = kWarps * STAGES * kStageBytes;
-  static constexpr int kBarBytes = kWarps * STAGES * 8;
-  static constexpr int kTotal = kRingBytes + kBarBytes + 1024 /* alignment slack */;
-  // the merge buffers alias the ring after the main loop: [W][8][D] floats + 2 * [W][8]
-  static_assert(kWarps * 8 * (D + 2) * 4 <= kRingBytes, "merge buffers must fit in the ring");
-};
+
+bool tensor_maps_available() { return encode_fn() != nullptr; }
+
+}  // namespace tma
+
+using namespace tma;
+
+namespace {
 
 template <typename T, int D, int STAGES>
 __global__ void __launch_bounds__(kWarps * 32, (STAGES <= 3 ? 2 : 1))
@@ -135,7 +117,10 @@ paged_attn_tma_kernel(const __grid_constant__ CUtensorMap k_map, const __grid_co
                       const int32_t* __restrict__ block_tables, int table_stride,
                       const int32_t* __restrict__ context_lens, int Hq, int Hkv, int G, float scale,
                       int blocks_per_split, int num_splits, float* __restrict__ ws_acc, float* __restrict__ ws_ml,
-                      int round_scores) {
+                      int round_scores, int first_block, int split_offset, int splits_total) {
+  // first_block / split_offset / splits_total serve the shared-prefix cascade (b200_attn_prefix.cu): this launch
+  // then covers only blocks >= first_block and files its partials after the prefix launch's.  Plain calls pass
+  // 0, 0, num_splits.
   using S = Smem<D, STAGES>;
   constexpr int KSTEPS = D / 16;   // mma k-steps over head_dim for S^T
   constexpr int MTILES = D / 16;   // mma m-tiles over head_dim for O^T
@@ -161,8 +146,8 @@ paged_attn_tma_kernel(const __grid_constant__ CUtensorMap k_map, const __grid_co
   // ---- this CTA's slice of the sequence ----
   const int ctx = context_lens[b];
   const int n_blocks = (ctx + kTok - 1) / kTok;
-  const int blk_begin = min(n_blocks, split * blocks_per_split);
-  const int blk_end = (split == num_splits - 1) ? n_blocks : min(n_blocks, (split + 1) * blocks_per_split);
+  const int blk_begin = min(n_blocks, first_block + split * blocks_per_split);
+  const int blk_end = (split == num_splits - 1) ? n_blocks : min(n_blocks, first_block + (split + 1) * blocks_per_split);
   const int n_cta = blk_end - blk_begin;
   const int n_mine = n_cta > warp ? (n_cta - warp + kWarps - 1) / kWarps : 0;  // tiles warp, warp+4, ...
   const int32_t* table = block_tables + static_cast<int64_t>(b) * table_stride + blk_begin + warp;
@@ -326,10 +311,10 @@ paged_attn_tma_kernel(const __grid_constant__ CUtensorMap k_map, const __grid_co
       L = fmaf(wgt, l_s[w * 8 + g], L);
     }
     const int hq = kvh * G + g;
-    if (num_splits == 1) {
+    if (splits_total == 1) {
       out[(static_cast<int64_t>(b) * Hq + hq) * D + d] = Cvt<T>::from_f32(L > 0.f ? acc / L : 0.f);
     } else {
-      const int64_t pidx = (static_cast<int64_t>(b) * Hq + hq) * num_splits + split;
+      const int64_t pidx = (static_cast<int64_t>(b) * Hq + hq) * splits_total + split_offset + split;
       ws_acc[pidx * D + d] = acc;
       if (d == 0) {
         ws_ml[pidx * 2 + 0] = M * inv_l2;  // natural-log domain, as attn_combine_kernel expects
@@ -337,70 +322,6 @@ paged_attn_tma_kernel(const __grid_constant__ CUtensorMap k_map, const __grid_co
       }
     }
   }
-}
-
-// ---- host side: tensor maps -------------------------------------------------------------------------------
-using EncodeTiledFn = CUresult (*)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*,
-                                   const cuuint64_t*, const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave,
-                                   CUtensorMapSwizzle, CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
-
-EncodeTiledFn encode_fn() {
-  static EncodeTiledFn fn = [] {
-    void* p = nullptr;
-    cudaDriverEntryPointQueryResult qr;
-    if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &p, cudaEnableDefault, &qr) != cudaSuccess ||
-        qr != cudaDriverEntryPointSuccess)
-      p = nullptr;
-    return reinterpret_cast<EncodeTiledFn>(p);
-  }();
-  return fn;
-}
-
-struct MapKey {
-  const void* ptr;
-  uint64_t rows;
-  int D;
-  int dtype;
-  bool operator==(const MapKey& o) const { return ptr == o.ptr && rows == o.rows && D == o.D && dtype == o.dtype; }
-};
-struct MapKeyHash {
-  size_t operator()(const MapKey& k) const {
-    return std::hash<const void*>()(k.ptr) ^ (std::hash<uint64_t>()(k.rows) * 1315423911u) ^ (k.D * 2654435761u) ^
-           static_cast<size_t>(k.dtype);
-  }
-};
-
-// Pools are long-lived (one pair per layer), so descriptors are cached by (pointer, rows, D, dtype).
-int get_tensor_map(const void* pool, uint64_t rows, int D, int dtype, CUtensorMap* out) {
-  static std::mutex mu;
-  static std::unordered_map<MapKey, CUtensorMap, MapKeyHash> cache;
-  const MapKey key{pool, rows, D, dtype};
-  {
-    std::lock_guard<std::mutex> lk(mu);
-    auto it = cache.find(key);
-    if (it != cache.end()) {
-      *out = it->second;
-      return 0;
-    }
-  }
-  EncodeTiledFn enc = encode_fn();
-  if (!enc) return fail(B200_EINVAL, "cuTensorMapEncodeTiled is not available from this driver");
-  const cuuint64_t dims[2] = {static_cast<cuuint64_t>(D), rows};
-  const cuuint64_t strides[1] = {static_cast<cuuint64_t>(D) * 2};
-  const cuuint32_t box[2] = {64, static_cast<cuuint32_t>(kTok)};
-  const cuuint32_t estr[2] = {1, 1};
-  CUtensorMap m;
-  CUresult r = enc(&m, dtype == B200_DTYPE_BF16 ? CU_TENSOR_MAP_DATA_TYPE_BFLOAT16 : CU_TENSOR_MAP_DATA_TYPE_FLOAT16, 2,
-                   const_cast<void*>(pool), dims, strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
-                   CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
-  if (r != CUDA_SUCCESS) return fail(B200_EINVAL, "cuTensorMapEncodeTiled failed with CUresult %d", static_cast<int>(r));
-  {
-    std::lock_guard<std::mutex> lk(mu);
-    if (cache.size() > 8192) cache.clear();
-    cache.emplace(key, m);
-  }
-  *out = m;
-  return 0;
 }
 
 template <typename T, int D, int STAGES>
@@ -419,7 +340,8 @@ int launch_tma(const AttnArgs& a, int dtype, cudaStream_t stream) {
   kern<<<grid, kWarps * 32, S::kTotal, stream>>>(km, vm, static_cast<T*>(a.out), static_cast<const T*>(a.q),
                                                   a.q_row_stride, a.block_tables, a.table_stride, a.context_lens, a.Hq,
                                                   a.Hkv, a.Hq / a.Hkv, a.scale, a.blocks_per_split, a.num_splits,
-                                                  a.ws_acc, a.ws_ml, a.round_scores);
+                                                  a.ws_acc, a.ws_ml, a.round_scores, a.first_block, a.split_offset,
+                                                  a.splits_total > 0 ? a.splits_total : a.num_splits);
   return check_launch("b200_paged_decode_attn(tma)");
 }
 
@@ -433,7 +355,7 @@ bool attn_tma_supported(const AttnArgs& a, int dtype) {
   if (!aligned16(a.k_pool) || !aligned16(a.v_pool)) return false;
   if ((reinterpret_cast<uintptr_t>(a.q) & 3u) || (a.q_row_stride & 1)) return false;
   if (static_cast<uint64_t>(a.max_blocks) * a.Hkv * kTok >= (1ull << 31)) return false;
-  return encode_fn() != nullptr;
+  return tensor_maps_available();
 }
 
 template <int STAGES>

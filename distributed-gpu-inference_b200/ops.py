@@ -226,6 +226,65 @@ def paged_decode_attention(
     return out
 
 
+def attn_prefix_plan(B: int, Hq: int, Hkv: int, D: int, block_size: int, prefix_blocks: int, max_context_len: int,
+                     dtype: torch.dtype):
+    """``(prefix_splits, suffix_splits)`` the library would choose for the shared-prefix variant."""
+    import ctypes
+
+    ps, ss = ctypes.c_int(0), ctypes.c_int(0)
+    rc = _lib.load().b200_paged_decode_attn_prefix_plan(B, Hq, Hkv, D, block_size, prefix_blocks, max_context_len,
+                                                       DTYPE_ID[dtype], ctypes.byref(ps), ctypes.byref(ss))
+    _lib.check(rc, "b200_paged_decode_attn_prefix_plan")
+    return ps.value, ss.value
+
+
+def paged_decode_attention_prefix(
+    q: torch.Tensor,
+    k_pool: torch.Tensor,
+    v_pool: torch.Tensor,
+    block_tables: torch.Tensor,
+    context_lens: torch.Tensor,
+    max_context_len: int,
+    prefix_blocks: int,
+    scale: Optional[float] = None,
+    out: Optional[torch.Tensor] = None,
+    prefix_splits: int = 0,
+    suffix_splits: int = 0,
+    workspace: Optional[torch.Tensor] = None,
+    flags: int = 0,
+) -> torch.Tensor:
+    """``paged_decode_attention`` for a batch whose first ``prefix_blocks`` table entries are shared by all
+    sequences: the shared blocks are read from HBM once for the whole batch."""
+    _need_cuda(q, k_pool, v_pool, block_tables, context_lens)
+    max_blocks, Hkv, bs, D = _pool_dims(k_pool)
+    B, Hq = q.shape[0], q.shape[1]
+    q_stride = _row_stride(q, Hq, D)
+    if block_tables.dtype != torch.int32 or block_tables.dim() != 2 or block_tables.shape[0] != B:
+        raise ValueError("block_tables must be int32 [B, n]")
+    if context_lens.dtype != torch.int32 or context_lens.shape != (B,) or not context_lens.is_contiguous():
+        raise ValueError("context_lens must be a contiguous int32 [B]")
+    if out is None:
+        out = torch.empty((B, Hq, D), dtype=q.dtype, device=q.device)
+    dt = _dtype_id(k_pool)
+    if prefix_splits == 0 or suffix_splits == 0:
+        ps, ss = attn_prefix_plan(B, Hq, Hkv, D, bs, prefix_blocks, max_context_len, q.dtype)
+        prefix_splits = prefix_splits or ps
+        suffix_splits = suffix_splits or ss
+    lib = _lib.load()
+    need = max(16, lib.b200_paged_decode_attn_workspace(B, Hq, D, prefix_splits + suffix_splits))
+    if workspace is None:
+        workspace = torch.empty(need, dtype=torch.uint8, device=q.device)
+    table_stride = block_tables.stride(0) if B > 1 else block_tables.shape[1]
+    rc = lib.b200_paged_decode_attn_prefix(
+        out.data_ptr(), q.data_ptr(), q_stride, k_pool.data_ptr(), v_pool.data_ptr(), block_tables.data_ptr(),
+        table_stride, context_lens.data_ptr(), B, Hq, Hkv, D, bs, max_blocks,
+        float(D) ** -0.5 if scale is None else float(scale), int(max_context_len), int(prefix_blocks),
+        int(prefix_splits), int(suffix_splits), workspace.data_ptr(), workspace.numel() * workspace.element_size(), dt,
+        int(flags), _stream())
+    _lib.check(rc, "b200_paged_decode_attn_prefix")
+    return out
+
+
 STATIC_SCRATCH_BYTES = 8 * 1024 * 1024
 
 

@@ -85,6 +85,28 @@ size_t b200_paged_decode_attn_workspace(int B, int Hq, int D, int num_splits);
 int b200_paged_decode_attn_plan(int B, int Hq, int Hkv, int D, int block_size, int max_context_len, int dtype);
 
 /*
+ * Shared-prefix ("cascade") variant of b200_paged_decode_attn: when block_tables[b][0:prefix_blocks] are the same
+ * slots for every sequence (a shared system prompt — the blocks the reference's allocator would hold with
+ * CacheBlock.ref_count > 1, worker/distributed/kv_cache.py:63-72, README "RadixAttention" prefix sharing), those
+ * blocks are streamed from HBM once for the whole batch instead of once per sequence, then each sequence's own
+ * blocks are processed as usual and the partials are merged.  Requirements: every context_lens[b] >=
+ * prefix_blocks * block_size; f16/bf16, block_size 16, head_dim 64/128, group <= 8 (else B200_ESHAPE — use the
+ * plain entry point, which gives the same result).  A workspace is always needed:
+ * b200_paged_decode_attn_workspace(B, Hq, D, prefix_splits + suffix_splits); 0 for a split count = library's choice
+ * (b200_paged_decode_attn_prefix_plan).  prefix_blocks = 0 forwards to b200_paged_decode_attn.
+ */
+int b200_paged_decode_attn_prefix(void* out, const void* q, int64_t q_row_stride,
+                                  const void* k_pool, const void* v_pool,
+                                  const int32_t* block_tables, int table_stride, const int32_t* context_lens,
+                                  int B, int Hq, int Hkv, int D, int block_size, int64_t max_blocks,
+                                  float scale, int max_context_len, int prefix_blocks,
+                                  int prefix_splits, int suffix_splits,
+                                  void* workspace, size_t workspace_bytes,
+                                  int dtype, unsigned flags, void* stream);
+int b200_paged_decode_attn_prefix_plan(int B, int Hq, int Hkv, int D, int block_size, int prefix_blocks,
+                                       int max_context_len, int dtype, int* prefix_splits, int* suffix_splits);
+
+/*
  * Paged decode attention for callers that cannot allocate device memory.  No counterpart in the reference: it
  * exists for hosts that are handed pointers and nothing else — a plugin inside another runtime's serving loop
  * where cudaMalloc is off limits because it stalls the whole device, or a binding without an allocator behind it

@@ -305,3 +305,46 @@ def test_add_rmsnorm_matches_torch_recipe(dtype, hidden):
         assert (diff <= ulp * 2.01).all()
         assert (diff > 0).float().mean().item() < 1e-2
     assert torch.equal(_bits(ops.add_rmsnorm(h_want, w, 1e-5)), _bits(out))  # same result without the fused add
+
+
+# ---- shared-prefix (cascade) variant -----------------------------------------------------------------------------
+PREFIX_CASES = [
+    # B, Hq, Hkv, D, prefix_blocks, suffix token counts
+    (8, 32, 8, 128, 40, [100, 1, 0, 555, 16, 17, 300, 64]),   # config-5 style: 8B shape, ragged tails, one empty tail
+    (3, 32, 8, 128, 7, [5, 90, 33]),                          # 12 query rows < 16 columns: partly filled q-group
+    (5, 64, 8, 128, 33, [0, 0, 10, 200, 47]),                 # 70B shape: group 8, 40 rows = 2.5 q-groups
+    (4, 8, 2, 64, 20, [128, 129, 1, 77]),                     # head_dim 64
+    (2, 8, 8, 64, 3, [9, 40]),                                # MHA (group 1)
+]
+
+
+@pytest.mark.parametrize("case", PREFIX_CASES)
+@pytest.mark.parametrize("dtype,tol", [(torch.bfloat16, 1e-2), (torch.float16, 2e-3)])
+@pytest.mark.parametrize("splits", [(0, 0), (1, 1), (3, 2)])
+def test_prefix_attention_matches_oracle_and_plain_kernel(case, dtype, tol, splits):
+    B, Hq, Hkv, D, pb, tails = case
+    bs = 16
+    ctx = [pb * bs + t for t in tails]
+    q, k_pool, v_pool, tables, lens = _attn_case(B, Hq, Hkv, D, bs, ctx, dtype, seed=B * 13 + D, share_prefix_blocks=pb)
+    assert (tables[:, :pb] == tables[0, :pb]).all()
+    out = ops.paged_decode_attention_prefix(q, k_pool, v_pool, tables, lens, max(ctx), pb,
+                                            prefix_splits=splits[0], suffix_splits=splits[1])
+    want = R.paged_attention_ref(q, k_pool, v_pool, tables, lens, mode="fp32")
+    assert torch.isfinite(out.float()).all()
+    assert _rel_err(out, want) <= tol
+    plain = ops.paged_decode_attention(q, k_pool, v_pool, tables, lens, max(ctx))
+    assert _rel_err(out, plain) <= tol
+
+
+def test_prefix_attention_zero_prefix_and_unsupported_shapes():
+    from dgi_b200._lib import B200LibraryError
+
+    q, k_pool, v_pool, tables, lens = _attn_case(2, 8, 2, 64, 16, [100, 50], torch.bfloat16, seed=5)
+    a = ops.paged_decode_attention_prefix(q, k_pool, v_pool, tables, lens, 100, 0)
+    b = ops.paged_decode_attention(q, k_pool, v_pool, tables, lens, 100, num_splits=1)
+    assert torch.equal(_bits(a), _bits(b))
+    qf, kf, vf, tf, lf = _attn_case(2, 8, 2, 64, 16, [100, 50], torch.float32, seed=5, share_prefix_blocks=2)
+    with pytest.raises(B200LibraryError, match="f16/bf16"):
+        ops.paged_decode_attention_prefix(qf, kf, vf, tf, lf, 100, 2)
+    with pytest.raises(B200LibraryError, match="exceeds"):
+        ops.paged_decode_attention_prefix(q, k_pool, v_pool, tables, lens, 100, 50)

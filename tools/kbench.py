@@ -38,7 +38,8 @@ def timed(fn, n, warm=3):
     return e0.elapsed_time(e1) / n
 
 
-def attn_case(name, B, Hq, Hkv, D, ctx_lens, layers, splits, flags=0, share_prefix=0, iters=64, dtype=torch.bfloat16):
+def attn_case(name, B, Hq, Hkv, D, ctx_lens, layers, splits, flags=0, share_prefix=0, iters=64, dtype=torch.bfloat16,
+              cascade=False):
     bs = 16
     nblk = [(c + bs - 1) // bs for c in ctx_lens]
     uniq_blocks = share_prefix + sum(max(0, n - share_prefix) for n in nblk)
@@ -65,9 +66,17 @@ def attn_case(name, B, Hq, Hkv, D, ctx_lens, layers, splits, flags=0, share_pref
         splits = ops.attn_plan(B, Hq, Hkv, D, bs, max_ctx, dtype)
     ws = torch.empty(max(16, ops.attn_workspace_bytes(B, Hq, D, splits)), dtype=torch.uint8, device=DEV)
 
+    if cascade:
+        ps, ss = ops.attn_prefix_plan(B, Hq, Hkv, D, bs, share_prefix, max_ctx, dtype)
+        splits = f"{ps}+{ss}"
+        ws = torch.empty(max(16, ops.attn_workspace_bytes(B, Hq, D, ps + ss)), dtype=torch.uint8, device=DEV)
+
     def run(i):
         k, v = pools[i % layers]
-        ops.paged_decode_attention(q, k, v, tables, lens, max_ctx, out=out, num_splits=splits, workspace=ws, flags=flags)
+        if cascade:
+            ops.paged_decode_attention_prefix(q, k, v, tables, lens, max_ctx, share_prefix, out=out, workspace=ws, flags=flags)
+        else:
+            ops.paged_decode_attention(q, k, v, tables, lens, max_ctx, out=out, num_splits=splits, workspace=ws, flags=flags)
 
     ms = timed(run, iters)
     es = 2
@@ -133,6 +142,14 @@ if __name__ == "__main__":
             lens = [24576 + 8192 - 512 * i for i in range(8)]
             attn_case("cfg5 8B B8 ctx32k ragged, shared 24576 prefix", 8, 32, 8, 128, lens, a.layers, a.splits, fl,
                       share_prefix=24576 // 16, iters=a.iters)
+            attn_case("cfg5 8B B8 ctx32k ragged, shared 24576 prefix, CASCADE kernel", 8, 32, 8, 128, lens, a.layers,
+                      a.splits, fl, share_prefix=24576 // 16, iters=a.iters, cascade=True)
             attn_case("cfg5 8B B8 ctx32k ragged, unshared", 8, 32, 8, 128, lens, min(a.layers, 4), a.splits, fl, iters=a.iters)
+        elif c == "prefix64":
+            lens64 = [2048 + 64 + 16 * (i % 8) for i in range(64)]
+            attn_case("8B B64, shared 2048-token system prompt + short tails, plain", 64, 32, 8, 128, lens64, a.layers,
+                      a.splits, fl, share_prefix=128, iters=a.iters)
+            attn_case("8B B64, shared 2048-token system prompt + short tails, CASCADE", 64, 32, 8, 128, lens64, a.layers,
+                      a.splits, fl, share_prefix=128, iters=a.iters, cascade=True)
         elif c == "copy":
             copy_cases()
