@@ -161,39 +161,68 @@ paged_attn_generic_kernel(T* __restrict__ out, const T* __restrict__ q, int64_t 
   }
 }
 
-// Merge split-K partials: one warp per (sequence, q head).
+// Merge split-K partials: one CTA per (sequence, q head) row.  The weights exp(m_s - M) are computed once per row
+// into shared memory; then thread d streams acc[s][d] over all splits with four independent accumulators, so a row
+// of S partials is S coalesced 4*D-byte reads in flight rather than a serial chain (the first version walked the
+// splits with one warp per row and cost 13-26 us at 9-28 splits; profiles/r01_cascade_launches.csv).
+constexpr int kCombineThreads = 128;
+constexpr int kCombineMaxSplits = 256;
+
 template <typename T>
-__global__ void __launch_bounds__(128)
+__global__ void __launch_bounds__(kCombineThreads)
 attn_combine_kernel(T* __restrict__ out, const float* __restrict__ ws_acc, const float* __restrict__ ws_ml,
-                    int rows /* B*Hq */, int D, int num_splits) {
-  const int row = blockIdx.x * 4 + (threadIdx.x >> 5);
-  const int lane = threadIdx.x & 31;
-  if (row >= rows) return;
+                    int D, int num_splits) {
+  __shared__ float w_s[kCombineMaxSplits];
+  __shared__ float red[2][kCombineThreads / 32];
+  const int row = blockIdx.x;
+  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
   const float* ml = ws_ml + static_cast<int64_t>(row) * num_splits * 2;
-  float M = -INFINITY;
-  for (int s = 0; s < num_splits; ++s) M = fmaxf(M, ml[2 * s]);
-  float L = 0.f;
-  for (int s = 0; s < num_splits; ++s) {
+
+  float m_loc = -INFINITY;
+  for (int s = tid; s < num_splits; s += kCombineThreads) m_loc = fmaxf(m_loc, ml[2 * s]);
+  m_loc = warp_max(m_loc);
+  if (lane == 0) red[0][warp] = m_loc;
+  __syncthreads();
+  float M = red[0][0];
+#pragma unroll
+  for (int w = 1; w < kCombineThreads / 32; ++w) M = fmaxf(M, red[0][w]);
+
+  float l_loc = 0.f;
+  for (int s = tid; s < num_splits; s += kCombineThreads) {
     const float ms = ml[2 * s];
-    L += (ms == -INFINITY) ? 0.f : __expf(ms - M) * ml[2 * s + 1];
+    const float w = (ms == -INFINITY) ? 0.f : __expf(ms - M);
+    w_s[s] = w;
+    l_loc = fmaf(w, ml[2 * s + 1], l_loc);
   }
+  l_loc = warp_sum(l_loc);
+  if (lane == 0) red[1][warp] = l_loc;
+  __syncthreads();
+  float L = 0.f;
+#pragma unroll
+  for (int w = 0; w < kCombineThreads / 32; ++w) L += red[1][w];
   const float inv = L > 0.f ? 1.f / L : 0.f;
+
   const float* acc = ws_acc + static_cast<int64_t>(row) * num_splits * D;
-  for (int d = lane; d < D; d += 32) {
-    float o = 0.f;
-    for (int s = 0; s < num_splits; ++s) {
-      const float ms = ml[2 * s];
-      const float w = (ms == -INFINITY) ? 0.f : __expf(ms - M);
-      o = fmaf(w, acc[static_cast<int64_t>(s) * D + d], o);
+  for (int d = tid; d < D; d += kCombineThreads) {
+    float o0 = 0.f, o1 = 0.f, o2 = 0.f, o3 = 0.f;
+    int s = 0;
+    for (; s + 4 <= num_splits; s += 4) {
+      o0 = fmaf(w_s[s], acc[static_cast<int64_t>(s) * D + d], o0);
+      o1 = fmaf(w_s[s + 1], acc[static_cast<int64_t>(s + 1) * D + d], o1);
+      o2 = fmaf(w_s[s + 2], acc[static_cast<int64_t>(s + 2) * D + d], o2);
+      o3 = fmaf(w_s[s + 3], acc[static_cast<int64_t>(s + 3) * D + d], o3);
     }
-    out[static_cast<int64_t>(row) * D + d] = Cvt<T>::from_f32(o * inv);
+    for (; s < num_splits; ++s) o0 = fmaf(w_s[s], acc[static_cast<int64_t>(s) * D + d], o0);
+    out[static_cast<int64_t>(row) * D + d] = Cvt<T>::from_f32(((o0 + o1) + (o2 + o3)) * inv);
   }
 }
 
 template <typename T>
 int launch_combine(void* out, const float* ws_acc, const float* ws_ml, int rows, int D, int num_splits,
                    cudaStream_t stream) {
-  attn_combine_kernel<T><<<(rows + 3) / 4, 128, 0, stream>>>(static_cast<T*>(out), ws_acc, ws_ml, rows, D, num_splits);
+  if (num_splits > kCombineMaxSplits)
+    return fail(B200_ESHAPE, "b200_paged_decode_attn: more than %d splits cannot be merged", kCombineMaxSplits);
+  attn_combine_kernel<T><<<rows, kCombineThreads, 0, stream>>>(static_cast<T*>(out), ws_acc, ws_ml, D, num_splits);
   return check_launch("b200_paged_decode_attn(combine)");
 }
 

@@ -5,17 +5,20 @@
 // blocks once PER SEQUENCE; they come out of L2 after the first reader, but the launch is still paced by L2 and the
 // unique HBM bytes are a fraction of what moves.  Here the prefix is processed ONCE for all sequences:
 //
-//   launch 1 (this file)   grid (prefix_splits, Hkv, q-groups): a CTA takes a run of prefix blocks of one kv head
-//                          and NT*8 query rows at a time — rows are (sequence, q head of the group) pairs, so one
-//                          K/V tile staged by TMA feeds several sequences' queries through the same MMAs
-//                          (S^T = K Q^T with N = 16 instead of 8).  Partials go to the split-K workspace.
-//   launch 2               the plain kernel (b200_attn_tma.cu) over each sequence's own blocks after the prefix
-//                          (first_block = prefix_blocks), partials filed after launch 1's.
-//   launch 3               attn_combine_kernel over prefix_splits + suffix_splits partials per (sequence, q head).
+//   launch 1 (this file)   ONE grid with two kinds of CTAs (measured: as separate launches the two phases cost
+//                          46 + 37 us back to back; fused they overlap and share the machine):
+//       prefix CTAs  (prefix_splits x Hkv x q-groups): a run of prefix blocks of one kv head against NT*8 query
+//                    rows at a time — rows are (sequence, q head of the group) pairs, so one K/V tile staged by
+//                    TMA feeds several sequences' queries through the same MMAs (S^T = K Q^T with N = 8 NT);
+//       suffix CTAs  (suffix_splits x Hkv x B): a sequence's own blocks after the prefix, one kv head, its group
+//                    of q heads — the plain kernel's work item.
+//                    Every CTA files a partial (m, l, O) in the split-K workspace.
+//   launch 2               attn_combine_kernel over prefix_splits + suffix_splits partials per (sequence, q head).
 //
 // The caller guarantees: block_tables[b][0:prefix_blocks] are identical for all b, and every context_lens[b] >=
 // prefix_blocks * 16 (the prefix blocks are full for everybody, so launch 1 needs no masking).
 #include <algorithm>
+#include <cstdlib>
 
 #include "b200_attn.cuh"
 #include "b200_common.cuh"
@@ -27,19 +30,42 @@ using namespace tma;
 
 namespace {
 
-template <typename T, int D, int STAGES, int NT>
-__global__ void __launch_bounds__(kWarps * 32, 2)
-paged_attn_prefix_kernel(const __grid_constant__ CUtensorMap k_map, const __grid_constant__ CUtensorMap v_map,
-                         const T* __restrict__ q, int64_t q_row_stride, const int32_t* __restrict__ prefix_table,
-                         int prefix_blocks, int B, int Hq, int Hkv, int G, float scale, int blocks_per_split,
-                         int splits_total, float* __restrict__ ws_acc, float* __restrict__ ws_ml, int round_scores) {
+struct CascadeParams {
+  const void* q;
+  int64_t q_row_stride;
+  const int32_t* block_tables;
+  int table_stride;
+  const int32_t* context_lens;
+  int prefix_blocks, B, Hq, Hkv, G;
+  float scale;
+  int prefix_splits, prefix_bps;   // prefix role: splits and blocks per split
+  int suffix_splits, suffix_bps;   // suffix role
+  int n_prefix_ctas;               // CTAs [0, n_prefix_ctas) run the prefix role
+  float* ws_acc;
+  float* ws_ml;
+  int round_scores;
+};
+
+// One CTA's work in either role.  SUFFIX = false: prefix role, columns are (sequence, head) pairs of q-group `zi`.
+// SUFFIX = true (NT = 1): columns are the q heads of sequence `zi`; tiles past the context are masked.
+template <typename T, int D, int STAGES, int NT, bool SUFFIX>
+__device__ __forceinline__ void cascade_role(const CUtensorMap& k_map, const CUtensorMap& v_map, const CascadeParams& p,
+                                             int split, int kvh, int zi) {
   using S = Smem<D, STAGES>;
   constexpr int KSTEPS = D / 16;
   constexpr int MTILES = D / 16;
   constexpr int BOXES = D / 64;
-  constexpr int COLS = 8 * NT;  // query rows (sequence, head) handled by this CTA
+  constexpr int COLS = 8 * NT;  // query rows handled by this CTA
 
-  const int split = blockIdx.x, kvh = blockIdx.y, qgroup = blockIdx.z;
+  const T* __restrict__ q = static_cast<const T*>(p.q);
+  const int64_t q_row_stride = p.q_row_stride;
+  const int B = p.B, Hq = p.Hq, Hkv = p.Hkv, G = p.G;
+  const float scale = p.scale;
+  const int round_scores = p.round_scores;
+  float* __restrict__ ws_acc = p.ws_acc;
+  float* __restrict__ ws_ml = p.ws_ml;
+  const int splits_total = p.prefix_splits + p.suffix_splits;
+  const int qgroup = zi;
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int quad = lane >> 2, tq = lane & 3;
 
@@ -55,11 +81,22 @@ paged_attn_prefix_kernel(const __grid_constant__ CUtensorMap k_map, const __grid
   }
   __syncwarp();
 
-  const int blk_begin = min(prefix_blocks, split * blocks_per_split);
-  const int blk_end = min(prefix_blocks, (split + 1) * blocks_per_split);
-  const int n_cta = blk_end - blk_begin;
+  int blk_begin, blk_end, ctx = 0x7fffffff;
+  const int32_t* table_row;
+  if constexpr (SUFFIX) {
+    ctx = p.context_lens[zi];
+    const int n_blocks = (ctx + kTok - 1) / kTok;
+    blk_begin = min(n_blocks, p.prefix_blocks + split * p.suffix_bps);
+    blk_end = (split == p.suffix_splits - 1) ? n_blocks : min(n_blocks, p.prefix_blocks + (split + 1) * p.suffix_bps);
+    table_row = p.block_tables + static_cast<int64_t>(zi) * p.table_stride;
+  } else {
+    blk_begin = min(p.prefix_blocks, split * p.prefix_bps);
+    blk_end = min(p.prefix_blocks, (split + 1) * p.prefix_bps);
+    table_row = p.block_tables;  // the prefix entries are the same in every row
+  }
+  const int n_cta = max(0, blk_end - blk_begin);
   const int n_mine = n_cta > warp ? (n_cta - warp + kWarps - 1) / kWarps : 0;
-  const int32_t* table = prefix_table + blk_begin + warp;
+  const int32_t* table = table_row + blk_begin + warp;
 
   int win_base = 0;
   int32_t win_slot = (lane < n_mine) ? table[lane * kWarps] : 0;
@@ -89,9 +126,18 @@ paged_attn_prefix_kernel(const __grid_constant__ CUtensorMap k_map, const __grid
   uint32_t qf[KSTEPS][NT][2];
 #pragma unroll
   for (int nt = 0; nt < NT; ++nt) {
-    const int r = qgroup * COLS + nt * 8 + quad;
-    const int bq = r / G, g = r - bq * G;
-    const bool ok = bq < B;
+    int bq, g;
+    bool ok;
+    if constexpr (SUFFIX) {
+      bq = zi;
+      g = quad;
+      ok = quad < G;
+    } else {
+      const int r = qgroup * COLS + nt * 8 + quad;
+      bq = r / G;
+      g = r - bq * G;
+      ok = bq < B;
+    }
     const T* qrow = q + static_cast<int64_t>(ok ? bq : 0) * q_row_stride + static_cast<int64_t>(kvh * G + g) * D;
 #pragma unroll
     for (int kk = 0; kk < KSTEPS; ++kk) {
@@ -134,11 +180,16 @@ paged_attn_prefix_kernel(const __grid_constant__ CUtensorMap k_map, const __grid
     float corr[NT][2];
     uint32_t pb[NT][2];
 #pragma unroll
+    const int tok0 = (blk_begin + warp + i * kWarps) * kTok + quad;
+    const bool ok_lo = !SUFFIX || tok0 < ctx, ok_hi = !SUFFIX || tok0 + 8 < ctx;
+#pragma unroll
     for (int nt = 0; nt < NT; ++nt) {
       float x[4];
 #pragma unroll
-      for (int e = 0; e < 4; ++e)
-        x[e] = round_scores ? Mma<T>::round(Mma<T>::round(s[nt][e]) * scale) * 1.4426950408889634f : s[nt][e] * sl2;
+      for (int e = 0; e < 4; ++e) {
+        const float v = round_scores ? Mma<T>::round(Mma<T>::round(s[nt][e]) * scale) * 1.4426950408889634f : s[nt][e] * sl2;
+        x[e] = ((e < 2) ? ok_lo : ok_hi) ? v : -INFINITY;
+      }
 #pragma unroll
       for (int c = 0; c < 2; ++c) {
         float mx = fmaxf(x[c], x[c + 2]);
@@ -209,9 +260,17 @@ paged_attn_prefix_kernel(const __grid_constant__ CUtensorMap k_map, const __grid
   const float ln2 = 0.6931471805599453f;
   for (int idx = threadIdx.x; idx < COLS * D; idx += kWarps * 32) {
     const int c = idx / D, d = idx - c * D;
-    const int r = qgroup * COLS + c;
-    const int bq = r / G, g = r - bq * G;
-    if (bq >= B) continue;
+    int bq, g;
+    if constexpr (SUFFIX) {
+      bq = zi;
+      g = c;
+      if (c >= G) continue;
+    } else {
+      const int r = qgroup * COLS + c;
+      bq = r / G;
+      g = r - bq * G;
+      if (bq >= B) continue;
+    }
     float M = -INFINITY;
 #pragma unroll
     for (int w = 0; w < kWarps; ++w) M = fmaxf(M, m_s[w * COLS + c]);
@@ -223,7 +282,7 @@ paged_attn_prefix_kernel(const __grid_constant__ CUtensorMap k_map, const __grid
       acc = fmaf(wgt, o_s[(w * COLS + c) * D + d], acc);
       L = fmaf(wgt, l_s[w * COLS + c], L);
     }
-    const int64_t pidx = (static_cast<int64_t>(bq) * Hq + kvh * G + g) * splits_total + split;
+    const int64_t pidx = (static_cast<int64_t>(bq) * Hq + kvh * G + g) * splits_total + (SUFFIX ? p.prefix_splits : 0) + split;
     ws_acc[pidx * D + d] = acc;
     if (d == 0) {
       ws_ml[pidx * 2 + 0] = M * ln2;  // natural-log domain, as attn_combine_kernel expects
@@ -232,13 +291,40 @@ paged_attn_prefix_kernel(const __grid_constant__ CUtensorMap k_map, const __grid
   }
 }
 
+template <typename T, int D, int STAGES, int NT>
+__global__ void __launch_bounds__(kWarps * 32, (NT <= 2 ? 2 : 1))
+paged_attn_cascade_kernel(const __grid_constant__ CUtensorMap k_map, const __grid_constant__ CUtensorMap v_map,
+                          const __grid_constant__ CascadeParams p) {
+  const int id = blockIdx.x;
+  if (id < p.n_prefix_ctas) {  // heavier CTAs first
+    const int split = id % p.prefix_splits;
+    const int rest = id / p.prefix_splits;
+    cascade_role<T, D, STAGES, NT, false>(k_map, v_map, p, split, rest % p.Hkv, rest / p.Hkv);
+  } else {
+    const int j = id - p.n_prefix_ctas;
+    const int split = j % p.suffix_splits;
+    const int rest = j / p.suffix_splits;
+    cascade_role<T, D, STAGES, 1, true>(k_map, v_map, p, split, rest % p.Hkv, rest / p.Hkv);
+  }
+}
+
 inline int ceil_div(int a, int b) { return (a + b - 1) / b; }
 
-constexpr int kPrefixNT = 2;      // 16 query rows per CTA
 constexpr int kPrefixStages = 3;
 
-template <typename T, int D>
-int launch_prefix(const AttnArgs& a, int dtype, int prefix_blocks, int prefix_splits, int splits_total, cudaStream_t stream) {
+// Query rows per CTA = 8 * NT.  NT = 2 by default; B200_PREFIX_NT=1|2|4 overrides (tools/kbench.py sweeps).
+int prefix_nt() {
+  static const int nt = [] {
+    const char* e = getenv("B200_PREFIX_NT");
+    const int v = e ? atoi(e) : 2;
+    return (v == 1 || v == 2 || v == 4) ? v : 2;
+  }();
+  return nt;
+}
+
+template <typename T, int D, int NT>
+int launch_cascade(const AttnArgs& a, int dtype, int prefix_blocks, int prefix_splits, int suffix_splits,
+                   cudaStream_t stream) {
   using S = Smem<D, kPrefixStages>;
   const uint64_t rows = static_cast<uint64_t>(a.max_blocks) * a.Hkv * kTok;
   CUtensorMap km, vm;
@@ -246,17 +332,33 @@ int launch_prefix(const AttnArgs& a, int dtype, int prefix_blocks, int prefix_sp
   if (rc) return rc;
   rc = get_tensor_map(a.v_pool, rows, D, dtype, &vm);
   if (rc) return rc;
-  auto kern = paged_attn_prefix_kernel<T, D, kPrefixStages, kPrefixNT>;
+  auto kern = paged_attn_cascade_kernel<T, D, kPrefixStages, NT>;
   cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, S::kTotal);
   if (e != cudaSuccess) return fail(static_cast<int>(e), "cudaFuncSetAttribute: %s", cudaGetErrorString(e));
-  const int G = a.Hq / a.Hkv;
-  const int qgroups = ceil_div(a.B * G, 8 * kPrefixNT);
-  dim3 grid(prefix_splits, a.Hkv, qgroups);
-  kern<<<grid, kWarps * 32, S::kTotal, stream>>>(km, vm, static_cast<const T*>(a.q), a.q_row_stride, a.block_tables,
-                                                  prefix_blocks, a.B, a.Hq, a.Hkv, G, a.scale,
-                                                  ceil_div(prefix_blocks, prefix_splits), splits_total, a.ws_acc, a.ws_ml,
-                                                  a.round_scores);
-  return check_launch("b200_paged_decode_attn_prefix(prefix)");
+  CascadeParams p{};
+  p.q = a.q;
+  p.q_row_stride = a.q_row_stride;
+  p.block_tables = a.block_tables;
+  p.table_stride = a.table_stride;
+  p.context_lens = a.context_lens;
+  p.prefix_blocks = prefix_blocks;
+  p.B = a.B;
+  p.Hq = a.Hq;
+  p.Hkv = a.Hkv;
+  p.G = a.Hq / a.Hkv;
+  p.scale = a.scale;
+  p.prefix_splits = prefix_splits;
+  p.prefix_bps = ceil_div(prefix_blocks, prefix_splits);
+  p.suffix_splits = suffix_splits;
+  p.suffix_bps = a.blocks_per_split;
+  const int qgroups = ceil_div(a.B * p.G, 8 * NT);
+  p.n_prefix_ctas = prefix_splits * a.Hkv * qgroups;
+  p.ws_acc = a.ws_acc;
+  p.ws_ml = a.ws_ml;
+  p.round_scores = a.round_scores;
+  const int grid = p.n_prefix_ctas + suffix_splits * a.Hkv * a.B;
+  kern<<<grid, kWarps * 32, S::kTotal, stream>>>(km, vm, p);
+  return check_launch("b200_paged_decode_attn_prefix(cascade)");
 }
 
 }  // namespace
@@ -268,7 +370,7 @@ bool attn_prefix_supported(const AttnArgs& a, int dtype) { return attn_tma_suppo
 void attn_prefix_plan(int B, int Hq, int Hkv, int block_size, int prefix_blocks, int max_context_len,
                       int* prefix_splits, int* suffix_splits) {
   const int G = std::max(1, Hq / std::max(1, Hkv));
-  const int qgroups = std::max(1, ceil_div(B * G, 8 * kPrefixNT));
+  const int qgroups = std::max(1, ceil_div(B * G, 8 * prefix_nt()));
   const int min_blocks = std::max(1, 256 / block_size);
   int ps = ceil_div(2 * kNumSMs, std::max(1, Hkv * qgroups));
   ps = std::max(1, std::min(ps, std::max(1, prefix_blocks / min_blocks)));
@@ -281,23 +383,26 @@ void attn_prefix_plan(int B, int Hq, int Hkv, int block_size, int prefix_blocks,
   *suffix_splits = std::min(ss, 96);
 }
 
-int attn_prefix(const AttnArgs& a_in, int dtype, int prefix_blocks, int prefix_splits, int suffix_splits, cudaStream_t s) {
-  AttnArgs a = a_in;
+int attn_prefix(const AttnArgs& a, int dtype, int prefix_blocks, int prefix_splits, int suffix_splits, cudaStream_t s) {
   const int total = prefix_splits + suffix_splits;
   int rc;
-  if (dtype == B200_DTYPE_BF16)
-    rc = a.D == 128 ? launch_prefix<__nv_bfloat16, 128>(a, dtype, prefix_blocks, prefix_splits, total, s)
-                    : launch_prefix<__nv_bfloat16, 64>(a, dtype, prefix_blocks, prefix_splits, total, s);
-  else
-    rc = a.D == 128 ? launch_prefix<__half, 128>(a, dtype, prefix_blocks, prefix_splits, total, s)
-                    : launch_prefix<__half, 64>(a, dtype, prefix_blocks, prefix_splits, total, s);
-  if (rc) return rc;
-  // per-sequence suffixes with the plain kernel
-  a.first_block = prefix_blocks;
-  a.split_offset = prefix_splits;
-  a.splits_total = total;
-  a.num_splits = suffix_splits;
-  rc = attn_tma(a, dtype, s);
+#define B200_CASCADE_DISPATCH(NT)                                                                                       \
+  (dtype == B200_DTYPE_BF16                                                                                             \
+       ? (a.D == 128 ? launch_cascade<__nv_bfloat16, 128, NT>(a, dtype, prefix_blocks, prefix_splits, suffix_splits, s) \
+                     : launch_cascade<__nv_bfloat16, 64, NT>(a, dtype, prefix_blocks, prefix_splits, suffix_splits, s)) \
+       : (a.D == 128 ? launch_cascade<__half, 128, NT>(a, dtype, prefix_blocks, prefix_splits, suffix_splits, s)        \
+                     : launch_cascade<__half, 64, NT>(a, dtype, prefix_blocks, prefix_splits, suffix_splits, s)))
+  switch (prefix_nt()) {
+    case 1:
+      rc = B200_CASCADE_DISPATCH(1);
+      break;
+    case 4:
+      rc = B200_CASCADE_DISPATCH(4);
+      break;
+    default:
+      rc = B200_CASCADE_DISPATCH(2);
+  }
+#undef B200_CASCADE_DISPATCH
   if (rc) return rc;
   return attn_combine(a.out, a.ws_acc, a.ws_ml, a.B * a.Hq, a.D, total, dtype, s);
 }

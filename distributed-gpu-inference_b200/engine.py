@@ -114,14 +114,26 @@ class PagedDecodeEngine:
         self.batch = 0
 
     # ---- allocation ----------------------------------------------------------------------------------
-    def allocate(self, batch: int, total_len: int) -> None:
-        """Hand every sequence blocks for ``total_len`` tokens (prompt + tokens to generate)."""
+    def allocate(self, batch: int, total_len: int, shared_prefix_len: int = 0) -> None:
+        """Hand every sequence blocks for ``total_len`` tokens (prompt + tokens to generate).
+
+        With ``shared_prefix_len`` > 0 all sequences start with the same ``shared_prefix_len`` tokens: sequence 0
+        owns the blocks that hold them, the others take references to those blocks (``ref_count`` sharing) and
+        allocate only the rest.  Only whole blocks are shared.  Decode then uses the cascade attention kernel.
+        """
         if batch > self.max_batch or total_len > self.max_seq_len:
             raise ValueError("batch / length beyond the engine's capacity")
         self.release()
+        n_shared = (shared_prefix_len // self.block_size) if batch > 1 else 0
         rows = []
         for b in range(batch):
-            per_shard = [pool.allocate_sequence(total_len) for pool in self.pools]
+            if b == 0 or n_shared == 0:
+                per_shard = [pool.allocate_sequence(total_len) for pool in self.pools]
+            else:
+                per_shard = [
+                    pool.allocate_sequence(total_len, shared_prefix=[lb[:n_shared] for lb in self._seq_blocks[0][si]])
+                    for si, pool in enumerate(self.pools)
+                ]
             self._seq_blocks[b] = per_shard
             row = KVCachePool.block_table(per_shard[0][0])
             for shard_blocks in per_shard:
@@ -139,6 +151,22 @@ class PagedDecodeEngine:
         self.batch = batch
         self._graph = None
         self._graph_chained = None
+        self._set_prefix(n_shared)
+
+    def _set_prefix(self, n_shared: int) -> None:
+        """Configure decode attention for ``n_shared`` leading blocks common to all sequences (0 = none)."""
+        st = self.state
+        st.prefix_blocks = 0
+        self.prefix_blocks = n_shared
+        if n_shared > 0 and self.dtype in (torch.bfloat16, torch.float16) and self.block_size == 16 \
+                and self.D in (64, 128) and self.Hq // self.Hkv <= 8:
+            ps, ss = ops.attn_prefix_plan(self.batch, self.Hq, self.Hkv, self.D, self.block_size, n_shared,
+                                          self.max_seq_len, self.dtype)
+            need = ops.attn_workspace_bytes(self.batch, self.Hq, self.D, ps + ss)
+            if self.workspace.numel() < need:
+                self.workspace = torch.empty(need, dtype=torch.uint8, device=self.device)
+                st.workspace = self.workspace
+            st.prefix_blocks, st.prefix_splits, st.suffix_splits = n_shared, ps, ss
 
     def release(self) -> None:
         for b, per_shard in enumerate(self._seq_blocks):
@@ -151,32 +179,35 @@ class PagedDecodeEngine:
 
     # ---- prefill -------------------------------------------------------------------------------------
     @torch.no_grad()
-    def prefill_chunk(self, lo: int, hi: int, inputs: torch.Tensor) -> torch.Tensor:
+    def prefill_chunk(self, lo: int, hi: int, inputs: torch.Tensor, past_len: int = 0) -> torch.Tensor:
         """Prompt pass for sequences ``lo..hi-1`` through this engine's shards.
 
         ``inputs`` is ``[n, P]`` token ids on a first stage, ``[n, P, hidden]`` hidden states otherwise.  Returns the
-        first generated token ``[n]`` on a last stage, the hidden states ``[n, P, hidden]`` otherwise.
+        first generated token ``[n]`` on a last stage, the hidden states ``[n, P, hidden]`` otherwise.  With
+        ``past_len`` > 0 the ``P`` tokens continue after ``past_len`` tokens whose KV is already in the sequences'
+        (shared) blocks.
         """
         n, P = inputs.shape[0], inputs.shape[1]
         bs = self.block_size
-        t = torch.arange(P, device=self.device)
+        t = torch.arange(past_len, past_len + P, device=self.device)
         tables = self.block_tables[lo:hi].to(torch.int64)
         slots = tables[:, t // bs] * bs + (t % bs)[None, :]
         pos = t[None, :].expand(n, P)
         chunk_state = PagedBatchState(
             block_tables=self.block_tables[lo:hi],
-            context_lens=torch.full((n,), P, dtype=torch.int32, device=self.device),
+            context_lens=torch.full((n,), past_len + P, dtype=torch.int32, device=self.device),
             slot_mapping=slots.reshape(-1).contiguous(),
-            max_context_len=P,
+            max_context_len=past_len + P,
             prefill_mode=self.prefill_mode,
+            past_len=past_len,
         )
         chunk_state.cos, chunk_state.sin = rope_tables(pos, self.inv_freq, self.dtype)
         h = inputs.to(self.device)
         for shard, handles in zip(self.shards, self._handles):
             hs = [PagedLayerKV(hd.k_pool, hd.v_pool, chunk_state) for hd in handles]
             h, _ = shard.forward(h, position_ids=pos, past_key_values=hs, use_cache=True)
-        self.context_lens[lo:hi] = P
-        self._host_lens[lo:hi] = [P] * n
+        self.context_lens[lo:hi] = past_len + P
+        self._host_lens[lo:hi] = [past_len + P] * n
         if self.is_last:
             return self.shards[-1].get_logits(h[:, -1:, :])[:, 0, :].argmax(dim=-1)
         return h
@@ -191,9 +222,17 @@ class PagedDecodeEngine:
             raise RuntimeError("prefill() drives a whole model; pipeline stages use prefill_chunk()")
         prompt_ids = prompt_ids.to(self.device)
         out_tokens = torch.empty((B,), dtype=torch.int64, device=self.device)
-        for lo in range(0, B, self.prefill_chunk_size):
+        start = 0
+        shared = getattr(self, "prefix_blocks", 0) * self.block_size
+        if shared > 0:
+            # sequence 0 computes the shared blocks once; the others only run their own tokens over them
+            if not bool((prompt_ids[:, :shared] == prompt_ids[0, :shared]).all()):
+                raise ValueError("sequences do not share the declared prefix")
+            out_tokens[0:1] = self.prefill_chunk(0, 1, prompt_ids[0:1])
+            start = 1
+        for lo in range(start, B, self.prefill_chunk_size):
             hi = min(B, lo + self.prefill_chunk_size)
-            out_tokens[lo:hi] = self.prefill_chunk(lo, hi, prompt_ids[lo:hi])
+            out_tokens[lo:hi] = self.prefill_chunk(lo, hi, prompt_ids[lo:hi, shared:], past_len=shared)
         return out_tokens
 
     # ---- decode --------------------------------------------------------------------------------------
@@ -292,10 +331,11 @@ class PagedDecodeEngine:
         return self._pin_out[:B].clone()
 
     @torch.no_grad()
-    def generate(self, prompt_ids: torch.Tensor, max_new_tokens: int) -> torch.Tensor:
-        """Greedy generation: tokens [B, max_new_tokens] on the host."""
+    def generate(self, prompt_ids: torch.Tensor, max_new_tokens: int, shared_prefix_len: int = 0) -> torch.Tensor:
+        """Greedy generation: tokens [B, max_new_tokens] on the host.  ``shared_prefix_len``: leading tokens that are
+        identical in every prompt and whose KV blocks should be shared (computed once, reference-counted)."""
         B, P = prompt_ids.shape
-        self.allocate(B, P + max_new_tokens)
+        self.allocate(B, P + max_new_tokens, shared_prefix_len=min(shared_prefix_len, P - 1))
         nxt = self.prefill(prompt_ids).cpu()
         out = [nxt]
         for _ in range(max_new_tokens - 1):

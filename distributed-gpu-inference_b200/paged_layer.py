@@ -95,6 +95,12 @@ class PagedBatchState:
     num_splits: int = 0
     attn_flags: int = 0
     prefill_mode: str = "sdpa"  # "sdpa" or "eager" (the reference's exact recipe; O(T^2) memory)
+    # prefix sharing: the first `prefix_blocks` table entries are the same slots for every sequence (decode then
+    # uses the cascade kernel); `past_len` > 0 marks a prompt pass that continues after `past_len` cached tokens
+    prefix_blocks: int = 0
+    prefix_splits: int = 0
+    suffix_splits: int = 0
+    past_len: int = 0
 
 
 @dataclass
@@ -220,10 +226,17 @@ class PagedLlamaDecoderLayer(nn.Module):
             qf = q[:, 0]  # [B, Hq, D], row stride = projection width
             ops.rope_kv_append(qf, k[:, 0], v[:, 0], cos.reshape(B, D), sin.reshape(B, D),
                                past_key_value.k_pool, past_key_value.v_pool, st.slot_mapping)
-            attn = ops.paged_decode_attention(
-                qf, past_key_value.k_pool, past_key_value.v_pool, st.block_tables, st.context_lens,
-                st.max_context_len, num_splits=st.num_splits, workspace=st.workspace, flags=st.attn_flags,
-            ).view(B, 1, Hq * D)
+            if st.prefix_blocks > 0:
+                attn = ops.paged_decode_attention_prefix(
+                    qf, past_key_value.k_pool, past_key_value.v_pool, st.block_tables, st.context_lens,
+                    st.max_context_len, st.prefix_blocks, prefix_splits=st.prefix_splits,
+                    suffix_splits=st.suffix_splits, workspace=st.workspace, flags=st.attn_flags,
+                ).view(B, 1, Hq * D)
+            else:
+                attn = ops.paged_decode_attention(
+                    qf, past_key_value.k_pool, past_key_value.v_pool, st.block_tables, st.context_lens,
+                    st.max_context_len, num_splits=st.num_splits, workspace=st.workspace, flags=st.attn_flags,
+                ).view(B, 1, Hq * D)
         else:
             # prompt pass: the rotated k is also needed densely for the causal attention among the new tokens
             cos4, sin4 = cos.unsqueeze(2), sin.unsqueeze(2)  # broadcast over heads: [B, T, 1, D]
@@ -231,6 +244,10 @@ class PagedLlamaDecoderLayer(nn.Module):
             k = k * cos4 + _rotate_half(k) * sin4
             ops.kv_append(k.reshape(B * T, Hkv, D), v.reshape(B * T, Hkv, D), past_key_value.k_pool,
                           past_key_value.v_pool, st.slot_mapping)
+            if st.past_len > 0:
+                # prompt pass that continues a cached prefix: the new tokens also attend to the `past_len` tokens
+                # already sitting in the (shared) blocks, read back densely through the block table
+                k, v = self._with_cached_prefix(k, v, past_key_value, st)
             attn = self._prefill_attention(q, k, v, attention_mask, st.prefill_mode)
 
         # h = x + o_proj(attn);  y = norm(h)   (one launch)
@@ -246,19 +263,34 @@ class PagedLlamaDecoderLayer(nn.Module):
         h = h + self.mlp.down_proj(act)
         return h, (past_key_value if use_cache else None)
 
+    def _with_cached_prefix(self, k, v, handle: PagedLayerKV, st: PagedBatchState):
+        """Prepend the first ``st.past_len`` cached tokens (gathered through the block table) to k and v."""
+        B = k.shape[0]
+        bs = handle.k_pool.shape[2]
+        n_blk = (st.past_len + bs - 1) // bs
+        idx = st.block_tables[:, :n_blk].reshape(-1).to(torch.int64)
+
+        def dense(pool):  # [B * n_blk, Hkv, bs, D] -> [B, past_len, Hkv, D]
+            x = pool.index_select(0, idx).view(B, n_blk, pool.shape[1], bs, pool.shape[3])
+            return x.permute(0, 1, 3, 2, 4).reshape(B, n_blk * bs, pool.shape[1], pool.shape[3])[:, :st.past_len]
+
+        return torch.cat((dense(handle.k_pool), k), dim=1), torch.cat((dense(handle.v_pool), v), dim=1)
+
     def _prefill_attention(self, q, k, v, attention_mask, mode: str) -> torch.Tensor:
-        """Causal attention among the T new tokens of sequences that start empty (the prompt pass)."""
+        """Causal attention of the T new tokens over the S >= T tokens in k / v (the last T of which are the new
+        ones): S == T for a prompt pass from scratch, S > T when a cached prefix was prepended."""
         B, T, Hq, D = q.shape
+        S = k.shape[1]
         g = Hq // self.num_kv_heads
         qh, kh, vh = q.transpose(1, 2), k.transpose(1, 2), v.transpose(1, 2)
+        if attention_mask is None and (mode == "eager" or S != T):
+            attention_mask = torch.triu(
+                torch.full((T, S), float("-inf"), dtype=q.dtype, device=q.device), diagonal=S - T + 1
+            )[None, None]
         if mode == "eager":
             kh = kh.repeat_interleave(g, dim=1)
             vh = vh.repeat_interleave(g, dim=1)
             w = torch.matmul(qh, kh.transpose(2, 3)) * (D ** -0.5)
-            if attention_mask is None:
-                attention_mask = torch.triu(
-                    torch.full((T, T), float("-inf"), dtype=q.dtype, device=q.device), diagonal=1
-                )[None, None]
             w = F.softmax(w + attention_mask, dim=-1, dtype=torch.float32).to(q.dtype)
             out = torch.matmul(w, vh)
         else:

@@ -275,13 +275,25 @@ class KVCachePool:
             for l in range(num_layers)
         ]
 
-    def allocate_sequence(self, seq_len: int, prefix_hash: str = "") -> List[List[CacheBlock]]:
+    def allocate_sequence(self, seq_len: int, prefix_hash: str = "",
+                          shared_prefix: Optional[List[List[CacheBlock]]] = None) -> List[List[CacheBlock]]:
+        """Blocks for ``seq_len`` tokens in every layer (reference :283-313).
+
+        ``shared_prefix`` (addition): per layer, blocks of an existing sequence that hold the
+        same leading tokens.  They are reused with ``add_ref`` — the copy-on-write sharing ``CacheBlock.ref_count``
+        was designed for (reference :63-72) — and only the remainder is freshly allocated, so the sequences' block
+        tables start with identical slots.  Shared blocks (ref_count > 1) are never evicted (reference :232-234).
+        """
         bs = self._layer_caches[0].block_size
         n_blocks = (seq_len + bs - 1) // bs
         out: List[List[CacheBlock]] = []
         for layer_idx, cache in enumerate(self._layer_caches):
             mine: List[CacheBlock] = []
-            for _ in range(n_blocks):
+            if shared_prefix is not None:
+                for blk in shared_prefix[layer_idx][:n_blocks]:
+                    blk.add_ref()
+                    mine.append(blk)
+            for _ in range(n_blocks - len(mine)):
                 blk = cache.allocate_block(layer_idx, prefix_hash)
                 if blk is None:
                     cache.unpin(b.block_id for b in mine)
@@ -455,3 +467,57 @@ class DistributedKVCacheManager:
             "gpu_memory_gb": self.gpu_cache.get_total_memory_gb(),
             "cpu_cache_items": len(self.cpu_cache),
         }
+
+
+# ---------------------------------------------------------------------------------------------------------
+# Prefix reuse per block.  The reference keeps ONE block per (prefix hash, layer) in
+# ``_prefix_index`` and hashes ``bytes(token_ids)``, which fails for ids >= 256 (reference :384-387, :462).
+# ---------------------------------------------------------------------------------------------------------
+def chained_block_hashes(token_ids: Sequence[int], block_size: int) -> List[str]:
+    """One hash per FULL block of tokens, each chained on the previous one, so equal hashes mean equal prefixes
+    up to and including that block.  Tokens are encoded as little-endian uint32 (any vocabulary size)."""
+    out: List[str] = []
+    prev = b""
+    for i in range(len(token_ids) // block_size):
+        chunk = token_ids[i * block_size:(i + 1) * block_size]
+        h = hashlib.sha256(prev + b"".join(int(t).to_bytes(4, "little") for t in chunk)).digest()
+        out.append(h.hex()[:16])
+        prev = h
+    return out
+
+
+class RadixPrefixIndex:
+    """Chained block hash → the blocks (one per layer) that hold that block of tokens.
+
+    ``match(token_ids)`` returns how many leading full blocks are already cached and the per-layer block lists to
+    pass as ``KVCachePool.allocate_sequence(shared_prefix=...)``; ``insert`` registers a sequence's full blocks.
+    Entries whose blocks were freed are dropped lazily on lookup.
+    """
+
+    def __init__(self, pool: "KVCachePool"):
+        self.pool = pool
+        self._by_hash: Dict[str, List[str]] = {}  # hash -> block id per layer
+
+    def insert(self, token_ids: Sequence[int], blocks: List[List[CacheBlock]]) -> int:
+        hashes = chained_block_hashes(token_ids, self.pool.block_size)
+        for i, h in enumerate(hashes):
+            if i < len(blocks[0]):
+                self._by_hash.setdefault(h, [layer_blocks[i].block_id for layer_blocks in blocks])
+        return len(hashes)
+
+    def match(self, token_ids: Sequence[int]) -> Tuple[int, Optional[List[List[CacheBlock]]]]:
+        hashes = chained_block_hashes(token_ids, self.pool.block_size)
+        per_layer: List[List[CacheBlock]] = [[] for _ in range(self.pool.num_layers)]
+        n = 0
+        for h in hashes:
+            ids = self._by_hash.get(h)
+            if ids is None:
+                break
+            blks = [self.pool.layer(l)._blocks.get(bid) for l, bid in enumerate(ids)]
+            if any(b is None for b in blks):
+                del self._by_hash[h]  # freed since it was indexed
+                break
+            for l, b in enumerate(blks):
+                per_layer[l].append(b)
+            n += 1
+        return n, (per_layer if n else None)

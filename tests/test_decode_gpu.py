@@ -154,3 +154,35 @@ def test_8b_shape_bf16_paged_path_vs_reference_dense_path():
         print(f"8B-shape bf16 (fused projections={fused}): token agreement {float((got == want).float().mean()):.3f}")
         assert not bad, f"divergence at a decided token: {bad}"
         eng.release()
+
+
+@pytest.mark.parametrize("dtype", [torch.float32, torch.bfloat16])
+def test_shared_prefix_blocks_give_the_same_tokens(golden, dtype):
+    """Radix-style prefix sharing: 4 prompts with a common 80-token system prompt.  The shared blocks are computed
+    once and reference-counted (block tables start with identical slots); decode goes through the cascade kernel
+    (bf16) or the plain one (fp32).  Tokens must equal those of fully independent sequences."""
+    g, cfg, sd = _tiny(golden)
+    base = torch.tensor(g["prompt_ids"])
+    prompts = base[:, :112].clone()
+    prompts[:, :80] = base[0, :80]
+    shards = build_product_shards(cfg, sd, [(0, 2), (2, 4)], DEV, dtype)
+    eng = PagedDecodeEngine(shards, 4, 160, prefill_mode="eager")
+    want = eng.generate(prompts, 24)
+    got = eng.generate(prompts, 24, shared_prefix_len=80)
+    assert eng.prefix_blocks == 5
+    tables = eng.block_tables[:4].cpu()
+    assert (tables[:, :5] == tables[0, :5]).all() and len(set(tables[:, 5].tolist())) == 4
+    shared_blk = eng._seq_blocks[1][0][0][0]
+    assert shared_blk.ref_count == 4 and shared_blk is eng._seq_blocks[0][0][0][0]
+    if dtype == torch.float32:
+        assert eng.state.prefix_blocks == 0  # cascade kernel covers f16/bf16; fp32 keeps the plain kernel
+        assert torch.equal(got, want)
+        ref = L.greedy_decode(L.build_shards(cfg, sd, [(0, 4)]), prompts, 24)
+        assert torch.equal(got, ref)
+    else:
+        assert eng.state.prefix_blocks == 5
+        # bf16: same tokens up to near-ties; demand agreement of the first tokens and a high overall rate
+        assert torch.equal(got[:, :4], want[:, :4])
+        assert float((got == want).float().mean()) > 0.6
+    eng.release()
+    assert all(c.get_stats()["free_blocks"] == c.max_blocks for pool in eng.pools for c in pool._layer_caches)
