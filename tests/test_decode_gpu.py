@@ -186,3 +186,45 @@ def test_shared_prefix_blocks_give_the_same_tokens(golden, dtype):
         assert float((got == want).float().mean()) > 0.6
     eng.release()
     assert all(c.get_stats()["free_blocks"] == c.max_blocks for pool in eng.pools for c in pool._layer_caches)
+
+
+def test_batcher_to_engine_adapter_end_to_end(golden):
+    """The reference's serving chain for this path, all pieces from this repo: ContinuousBatcher.submit →
+    engine.batch_inference (one GPU batch, shared system-prompt blocks) → result dicts in the reference's format
+    (worker/engines/llm_base.py:152-161)."""
+    import asyncio
+
+    from dgi_b200.worker.batch_processor import ContinuousBatcher
+    from dgi_b200.worker.engines import ENGINE_REGISTRY, ByteTokenizer
+
+    g, cfg, sd = _tiny(golden)
+    shards = build_product_shards(cfg, sd, [(0, 4)], DEV, torch.float32)
+    eng = ENGINE_REGISTRY["llm_paged_b200"]({"shards": shards, "max_batch_size": 4, "max_model_len": 256,
+                                             "prefill_mode": "eager", "fuse_projections": False})
+    eng.load_model()
+    system = "You are a terse assistant. " * 3  # 81 bytes + BOS = 82 ids = 5 full shared blocks
+    questions = ["aaaa", "bbbb", "cccc", "dddd"]  # equal lengths: one batch
+    reqs = [{"messages": [{"role": "system", "content": system}, {"role": "user", "content": qn}], "max_tokens": 6}
+            for qn in questions]
+
+    async def run():
+        b = ContinuousBatcher(eng, max_batch_size=4, max_wait_ms=10)
+        await b.start()
+        out = await asyncio.gather(*[b.submit(f"job{i}", r) for i, r in enumerate(reqs)])
+        stats = b.get_stats()
+        await b.stop()
+        return out, stats
+
+    out, stats = asyncio.run(run())
+    assert stats["total_batches"] == 1 and stats["avg_batch_size"] == 4
+    tok = ByteTokenizer()
+    for r, qn in zip(out, questions):
+        ids = tok.encode(system) + tok.encode(f"user: {qn}")[1:]
+        want = L.greedy_decode(L.build_shards(cfg, sd, [(0, 4)]), torch.tensor([ids]), 6)[0].tolist()
+        assert r["output_ids"] == want
+        assert r["usage"]["prompt_tokens"] == len(ids) and r["usage"]["completion_tokens"] == 6
+        assert r["finish_reason"] == "length" and isinstance(r["response"], str)
+    assert out[0]["usage"]["cached_tokens"] == 0 and out[1]["usage"]["cached_tokens"] == 80
+    assert eng.engine.prefix_blocks == 5
+    assert eng.get_backend_info()["supports_batch_inference"] is True
+    eng.unload_model()

@@ -118,3 +118,72 @@ def test_in_process_transport_chains_two_stages_and_tracks_position():
         with pytest.raises(ConnectionError):
             await S.DistributedInferenceSession(_cfg(), [WorkerInfo(worker_id="nobody")]).setup()
     asyncio.run(run())
+
+
+# ---- ContinuousBatcher mirror: the behaviours the reference's tests pin (tests/test_worker_batch_processor.py:17-54,
+# tests/test_worker_batch_processor_flow.py:33-109) -------------------------------------------------------------------
+from dgi_b200.worker import batch_processor as BP  # noqa: E402
+
+
+def test_batcher_prefix_hash_only_from_system_messages():
+    b = BP.ContinuousBatcher(engine=object())
+    assert b._compute_prefix_hash({"messages": [{"role": "user", "content": "hi"}]}) == ""
+    h1 = b._compute_prefix_hash({"messages": [{"role": "system", "content": "S"}, {"role": "user", "content": "a"}]})
+    h2 = b._compute_prefix_hash({"messages": [{"role": "system", "content": "S"}, {"role": "user", "content": "b"}]})
+    assert h1 == h2 and len(h1) == 16
+
+
+def test_batcher_dispatch_grouping_exceptions_timeout_and_queue_full():
+    class SyncEngine:
+        def __init__(self):
+            self.batches = []
+
+        def batch_inference(self, params_list):
+            self.batches.append([p["id"] for p in params_list])
+            return [ValueError("bad") if p.get("fail") else {"ok": p["id"]} for p in params_list]
+
+    class AsyncEngine:
+        async def batch_inference_async(self, params_list):
+            return [{"ok": p["id"]} for p in params_list]
+
+    class SlowSerial:
+        def inference(self, params):
+            import time as _t
+            _t.sleep(0.3)
+            return {"ok": params["id"]}
+
+    async def run():
+        eng = SyncEngine()
+        b = BP.ContinuousBatcher(eng, max_batch_size=3, max_wait_ms=20)
+        with pytest.raises(RuntimeError, match="not running"):
+            await b.submit("x", {"id": 0})
+        await b.start()
+        sys_a = [{"role": "system", "content": "A"}]
+        sys_b = [{"role": "system", "content": "B"}]
+        reqs = [b.submit("1", {"id": 1, "messages": sys_b}), b.submit("2", {"id": 2, "messages": sys_a}),
+                b.submit("3", {"id": 3, "messages": sys_a, "fail": True}), b.submit("4", {"id": 4, "messages": sys_a})]
+        res = await asyncio.gather(*reqs, return_exceptions=True)
+        assert res[0] == {"ok": 1} and res[1] == {"ok": 2} and isinstance(res[2], ValueError) and res[3] == {"ok": 4}
+        assert sorted(eng.batches[0]) == [2, 3, 4]  # the largest prefix group goes first, as one batch
+        st = b.get_stats()
+        assert st["total_requests"] == 4 and st["total_batches"] == 2 and st["queue_size"] == 0
+        await b.stop()
+
+        b2 = BP.ContinuousBatcher(AsyncEngine(), max_batch_size=2, max_wait_ms=5)
+        await b2.start()
+        assert await b2.submit("a", {"id": 7}) == {"ok": 7}
+        await b2.stop()
+
+        b3 = BP.ContinuousBatcher(SlowSerial(), max_batch_size=8, max_wait_ms=200, max_queue_size=1)
+        await b3.start()
+        with pytest.raises(asyncio.TimeoutError):
+            await b3.submit("t", {"id": 9}, timeout=0.05)  # still queued when the timeout fires: removed from the queue
+        assert b3.get_stats()["queue_size"] == 0
+        first = asyncio.ensure_future(b3.submit("q1", {"id": 1}))
+        await asyncio.sleep(0.01)
+        with pytest.raises(RuntimeError, match="Queue full"):
+            await b3.submit("q2", {"id": 2})
+        assert await first == {"ok": 1}
+        await b3.stop()
+
+    asyncio.run(run())
