@@ -40,6 +40,10 @@ SIGNATURES = {
     ),
     "b200_paged_decode_attn_workspace": (c_size_t, [c_int, c_int, c_int, c_int]),
     "b200_paged_decode_attn_plan": (c_int, [c_int, c_int, c_int, c_int, c_int, c_int, c_int]),
+    "b200_kv_pack_layers_wire": (
+        c_int, [c_void_p, c_void_p, c_void_p, c_int, c_void_p, c_int, c_int, c_int, c_int, c_int64, c_void_p]),
+    "b200_kv_unpack_layers_wire": (
+        c_int, [c_void_p, c_void_p, c_int, c_void_p, c_void_p, c_int, c_int, c_int, c_int, c_int64, c_void_p]),
     "b200_kv_move_blocks_layers": (
         c_int,
         [c_void_p, c_void_p, c_void_p, c_void_p, c_int, c_void_p, c_void_p, c_int, c_int, c_int, c_int, c_int64, c_int64,

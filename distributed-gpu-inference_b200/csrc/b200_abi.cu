@@ -229,6 +229,20 @@ int b200_kv_move_blocks_layers(void* const* dst_k_pools, void* const* dst_v_pool
                                static_cast<cudaStream_t>(stream));
 }
 
+int b200_kv_pack_layers_wire(void* packed_f16, const void* const* k_pools, const void* const* v_pools, int n_layers,
+                             const int32_t* block_table, int n_blocks, int Hkv, int D, int block_size,
+                             int64_t max_blocks, void* stream) {
+  return kv_pack_layers_wire(packed_f16, k_pools, v_pools, n_layers, block_table, n_blocks, Hkv, D, block_size,
+                             max_blocks, static_cast<cudaStream_t>(stream));
+}
+
+int b200_kv_unpack_layers_wire(void* const* k_pools, void* const* v_pools, int n_layers, const void* packed_f16,
+                               const int32_t* block_table, int n_blocks, int Hkv, int D, int block_size,
+                               int64_t max_blocks, void* stream) {
+  return kv_unpack_layers_wire(k_pools, v_pools, n_layers, packed_f16, block_table, n_blocks, Hkv, D, block_size,
+                               max_blocks, static_cast<cudaStream_t>(stream));
+}
+
 int b200_add_rmsnorm(void* out, void* resid_out, const void* x, const void* delta, const void* weight, float eps,
                      int rows, int hidden, int64_t x_stride, int64_t d_stride, int dtype, void* stream) {
   return add_rmsnorm(out, resid_out, x, delta, weight, eps, rows, hidden, x_stride, d_stride, dtype,

@@ -63,6 +63,11 @@ int kv_move_blocks_layers(void* const* dst_k_pools, void* const* dst_v_pools, co
                           const void* const* src_v_pools, int n_layers, const int32_t* src_table,
                           const int32_t* dst_table, int n_blocks, int Hkv, int D, int bs, int64_t src_max_blocks,
                           int64_t dst_max_blocks, int dtype, cudaStream_t s);
+int kv_pack_layers_wire(void* packed_f16, const void* const* k_pools, const void* const* v_pools, int n_layers,
+                        const int32_t* table, int n_blocks, int Hkv, int D, int bs, int64_t max_blocks, cudaStream_t s);
+int kv_unpack_layers_wire(void* const* k_pools, void* const* v_pools, int n_layers, const void* packed_f16,
+                          const int32_t* table, int n_blocks, int Hkv, int D, int bs, int64_t max_blocks,
+                          cudaStream_t s);
 
 // fused layer pieces (b200_layer_ops.cu)
 int add_rmsnorm(void* out, void* resid_out, const void* x, const void* delta, const void* weight, float eps, int rows,

@@ -272,6 +272,82 @@ int kv_move_blocks_layers(void* const* dst_k_pools, void* const* dst_v_pools, co
   return check_launch(name);
 }
 
+// Wire-format pack / unpack: as pack / unpack, but the packed side is float16 while the pools are bfloat16 — the
+// byte stream the reference's host serializer produces for a bf16 tensor (common/serialization.py:73-76 casts
+// bf16 to fp16 before tobytes(); :143-155 widens it back on receipt).  One pass over the data instead of
+// pack -> .to(float16) (-> D2H): each thread converts one 16-byte vector of 8 elements.  Same rounding as torch's
+// cast: bf16 -> fp32 is exact, fp32 -> fp16 rounds to nearest even, overflow gives inf, fp16 -> bf16 rounds to
+// nearest even.
+template <bool PACK, int UNROLL>
+__global__ void __launch_bounds__(256)
+kv_block_wire_kernel(__half* __restrict__ packed, PoolSet pools, const int32_t* __restrict__ block_table, int n_blocks,
+                     int64_t max_blocks, int vec_per_block, int chunks_per_block) {
+  const int64_t chunk = blockIdx.x;
+  const int64_t item = chunk / chunks_per_block;
+  const int c = static_cast<int>(chunk - item * chunks_per_block);
+  const int j = static_cast<int>(item % n_blocks);
+  const int lk = static_cast<int>(item / n_blocks);
+  const int layer = lk >> 1;
+  const bool is_v = lk & 1;
+  const int32_t slot = block_table[j];
+  if (slot < 0 || slot >= max_blocks) return;
+  const void* pool_base = is_v ? pools.v_pools[layer] : pools.k_pools[layer];
+  const int64_t block_elems = static_cast<int64_t>(vec_per_block) * 8;
+  __nv_bfloat16* pool_ptr = const_cast<__nv_bfloat16*>(static_cast<const __nv_bfloat16*>(pool_base)) + slot * block_elems;
+  __half* pack_ptr = packed + item * block_elems;
+#pragma unroll
+  for (int u = 0; u < UNROLL; ++u) {
+    const int v = c * (256 * UNROLL) + threadIdx.x + u * 256;
+    if (v >= vec_per_block) continue;
+    union { int4 raw; __nv_bfloat16 b[8]; __half h[8]; } in, out;
+    if (PACK) {
+      in.raw = ld_stream16(pool_ptr + static_cast<int64_t>(v) * 8);
+#pragma unroll
+      for (int e = 0; e < 8; ++e) out.h[e] = __float2half_rn(__bfloat162float(in.b[e]));
+      st_stream16(pack_ptr + static_cast<int64_t>(v) * 8, out.raw);
+    } else {
+      in.raw = ld_stream16(pack_ptr + static_cast<int64_t>(v) * 8);
+#pragma unroll
+      for (int e = 0; e < 8; ++e) out.b[e] = __float2bfloat16_rn(__half2float(in.h[e]));
+      st_stream16(pool_ptr + static_cast<int64_t>(v) * 8, out.raw);
+    }
+  }
+}
+
+template <bool PACK>
+int kv_wire(void* packed_f16, const void* const* k_pools, const void* const* v_pools, int n_layers,
+            const int32_t* table, int n_blocks, int Hkv, int D, int bs, int64_t max_blocks, cudaStream_t s,
+            const char* name) {
+  if (n_blocks < 0 || n_layers <= 0 || Hkv <= 0 || D <= 0 || bs <= 0 || max_blocks <= 0)
+    return fail(B200_EINVAL, "%s: bad sizes", name);
+  if (n_blocks == 0) return 0;
+  if (!packed_f16 || !k_pools || !v_pools || !table) return fail(B200_EINVAL, "%s: null pointer", name);
+  const int64_t block_elems = static_cast<int64_t>(Hkv) * bs * D;
+  if (block_elems % 8 != 0 || !aligned16(packed_f16)) return fail(B200_ESHAPE, "%s: block size / alignment", name);
+  constexpr int UNROLL = 8;
+  const int vec_per_block = static_cast<int>(block_elems / 8);
+  const int chunks_per_block = (vec_per_block + 256 * UNROLL - 1) / (256 * UNROLL);
+  const int64_t grid = 2ll * n_layers * n_blocks * chunks_per_block;
+  if (grid > INT32_MAX) return fail(B200_ESHAPE, "%s: too many chunks", name);
+  PoolSet p{k_pools, v_pools, nullptr, nullptr};
+  kv_block_wire_kernel<PACK, UNROLL><<<static_cast<unsigned>(grid), 256, 0, s>>>(
+      static_cast<__half*>(packed_f16), p, table, n_blocks, max_blocks, vec_per_block, chunks_per_block);
+  return check_launch(name);
+}
+
+int kv_pack_layers_wire(void* packed_f16, const void* const* k_pools, const void* const* v_pools, int n_layers,
+                        const int32_t* table, int n_blocks, int Hkv, int D, int bs, int64_t max_blocks, cudaStream_t s) {
+  return kv_wire<true>(packed_f16, k_pools, v_pools, n_layers, table, n_blocks, Hkv, D, bs, max_blocks, s,
+                       "b200_kv_pack_layers_wire");
+}
+int kv_unpack_layers_wire(void* const* k_pools, void* const* v_pools, int n_layers, const void* packed_f16,
+                          const int32_t* table, int n_blocks, int Hkv, int D, int bs, int64_t max_blocks,
+                          cudaStream_t s) {
+  return kv_wire<false>(const_cast<void*>(packed_f16), const_cast<const void* const*>(k_pools),
+                        const_cast<const void* const*>(v_pools), n_layers, table, n_blocks, Hkv, D, bs, max_blocks, s,
+                        "b200_kv_unpack_layers_wire");
+}
+
 int kv_pack(void* packed, const void* k_pool, const void* v_pool, const int32_t* table, int n_blocks, int Hkv, int D,
             int bs, int64_t max_blocks, int dtype, cudaStream_t s) {
   PoolSet p{nullptr, nullptr, k_pool, v_pool};

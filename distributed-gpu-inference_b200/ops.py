@@ -424,3 +424,35 @@ def kv_move_blocks_layers(dst_k_ptrs: torch.Tensor, dst_v_ptrs: torch.Tensor, ds
                                                src_v_ptrs.data_ptr(), L, src_table.data_ptr(), dst_table.data_ptr(), n,
                                                Hkv, D, bs, smb, dmb, DTYPE_ID[dtype], _stream())
     _lib.check(rc, "b200_kv_move_blocks_layers")
+
+
+def kv_pack_layers_wire(k_ptrs: torch.Tensor, v_ptrs: torch.Tensor, pool_shape, block_table: torch.Tensor,
+                        out: Optional[torch.Tensor] = None) -> torch.Tensor:
+    """bf16 pools → float16 ``[L, 2, n_blocks, Hkv, bs, D]``: the reference serializer's bytes for these blocks."""
+    _need_cuda(k_ptrs, v_ptrs, block_table)
+    max_blocks, Hkv, bs, D = pool_shape
+    L = k_ptrs.shape[0]
+    n = _check_table(block_table)
+    shape = (L, 2, n, Hkv, bs, D)
+    if out is None:
+        out = torch.empty(shape, dtype=torch.float16, device=block_table.device)
+    elif tuple(out.shape) != shape or out.dtype != torch.float16 or not out.is_contiguous():
+        raise ValueError(f"out must be contiguous float16 {shape}")
+    rc = _lib.load().b200_kv_pack_layers_wire(out.data_ptr(), k_ptrs.data_ptr(), v_ptrs.data_ptr(), L,
+                                             block_table.data_ptr(), n, Hkv, D, bs, max_blocks, _stream())
+    _lib.check(rc, "b200_kv_pack_layers_wire")
+    return out
+
+
+def kv_unpack_layers_wire(packed: torch.Tensor, k_ptrs: torch.Tensor, v_ptrs: torch.Tensor, pool_shape,
+                          block_table: torch.Tensor) -> None:
+    """float16 wire payload → bf16 pools at the slots of ``block_table``."""
+    _need_cuda(packed, k_ptrs, v_ptrs, block_table)
+    max_blocks, Hkv, bs, D = pool_shape
+    L = k_ptrs.shape[0]
+    n = _check_table(block_table)
+    if tuple(packed.shape) != (L, 2, n, Hkv, bs, D) or packed.dtype != torch.float16 or not packed.is_contiguous():
+        raise ValueError("packed must be contiguous float16 [L, 2, n_blocks, Hkv, bs, D]")
+    rc = _lib.load().b200_kv_unpack_layers_wire(k_ptrs.data_ptr(), v_ptrs.data_ptr(), L, packed.data_ptr(),
+                                               block_table.data_ptr(), n, Hkv, D, bs, max_blocks, _stream())
+    _lib.check(rc, "b200_kv_unpack_layers_wire")

@@ -133,6 +133,20 @@ int b200_paged_decode_attn_static(void* out, const void* q, int64_t q_row_stride
                                   int dtype, unsigned flags, void* stream);
 
 /*
+ * Wire-format pack / unpack for hand-offs that leave the box (no NVLink): bfloat16 pools <-> a float16 packed
+ * buffer [n_layers, 2, n_blocks, Hkv, block_size, D], i.e. exactly the bytes TensorSerializer.serialize emits for a
+ * bf16 block (common/serialization.py:73-76: bf16 is cast to fp16 before tobytes(); :143-155 widens it back), in
+ * the per-layer keys/values order of KVCacheLayer (proto/inference.proto:110-127).  Gather + cast in one pass on
+ * the GPU instead of per-block .to(float16).cpu().  Lossy outside the fp16 range exactly like the reference.
+ */
+int b200_kv_pack_layers_wire(void* packed_f16, const void* const* k_pools, const void* const* v_pools, int n_layers,
+                             const int32_t* block_table, int n_blocks, int Hkv, int D, int block_size,
+                             int64_t max_blocks, void* stream);
+int b200_kv_unpack_layers_wire(void* const* k_pools, void* const* v_pools, int n_layers, const void* packed_f16,
+                               const int32_t* block_table, int n_blocks, int Hkv, int D, int block_size,
+                               int64_t max_blocks, void* stream);
+
+/*
  * Block-to-block move between two sets of pools, all layers in one launch: block src_table[j] of source layer l
  * is copied to block dst_table[j] of destination layer l.  The destination pool pointers may be peer memory —
  * another GPU's pools mapped over NVLink — in which case the prefill GPU writes a sequence's KV straight into the

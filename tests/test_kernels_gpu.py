@@ -348,3 +348,35 @@ def test_prefix_attention_zero_prefix_and_unsupported_shapes():
         ops.paged_decode_attention_prefix(qf, kf, vf, tf, lf, 100, 2)
     with pytest.raises(B200LibraryError, match="exceeds"):
         ops.paged_decode_attention_prefix(q, k_pool, v_pool, tables, lens, 100, 50)
+
+
+# ---- wire-format pack / unpack: the reference serializer's bytes, produced on the GPU ------------------------------
+def test_wire_pack_emits_the_reference_serializer_bytes_and_unpack_inverts_it():
+    from dgi_b200.common.serialization import TensorSerializer
+
+    L_, Hkv, D, bs, max_blocks, n = 3, 8, 128, 16, 24, 7
+    backing = torch.randn((L_, 2, max_blocks, Hkv, bs, D), device=DEV,
+                          generator=torch.Generator(device=DEV).manual_seed(31)).to(torch.bfloat16)
+    backing[0, 0, 3, 0, 0, :4] = torch.tensor([1e-8, 70144.0, -1e5, 3.140625], dtype=torch.bfloat16)  # outside fp16
+    kp = ops.pool_pointer_array([backing[l, 0] for l in range(L_)])
+    vp = ops.pool_pointer_array([backing[l, 1] for l in range(L_)])
+    table = torch.tensor([3, 20, 0, 7, 11, 23, 5], dtype=torch.int32, device=DEV)
+    wire = ops.kv_pack_layers_wire(kp, vp, (max_blocks, Hkv, bs, D), table)
+    assert wire.dtype == torch.float16 and wire.shape == (L_, 2, n, Hkv, bs, D)
+    # per (layer, K|V, block): identical to TensorSerializer.serialize(block) — reference common/serialization.py:55-104
+    for l in range(L_):
+        for kv_ in range(2):
+            for j, slot in enumerate(table.tolist()):
+                data, shape, dt = TensorSerializer.serialize(backing[l, kv_, slot])
+                assert dt == "bfloat16" and tuple(shape) == (Hkv, bs, D)
+                assert wire[l, kv_, j].cpu().numpy().tobytes() == data
+    # receive side: what deserialize would yield (bf16 widened back from the fp16 wire), scattered into fresh pools
+    dst_backing = torch.zeros_like(backing)
+    dk = ops.pool_pointer_array([dst_backing[l, 0] for l in range(L_)])
+    dv = ops.pool_pointer_array([dst_backing[l, 1] for l in range(L_)])
+    dst = torch.tensor([1, 2, 3, 4, 5, 6, 9], dtype=torch.int32, device=DEV)
+    ops.kv_unpack_layers_wire(wire, dk, dv, (max_blocks, Hkv, bs, D), dst)
+    want = backing[:, :, table.long()].to(torch.float16).to(torch.bfloat16)
+    got = dst_backing[:, :, dst.long()]
+    assert torch.equal(_bits(got), _bits(want))
+    assert torch.isinf(got[0, 0, 0, 0, 0, 1]) and got[0, 0, 0, 0, 0, 0] == 0  # the reference's lossy cases, reproduced
