@@ -360,9 +360,11 @@ def run_single(args, workload):
             "workload": workload["name"],
             "block_size": 16,
             "batch": B,
-            "context": f"{P + 1 + W}..{P + W + K} during the timed steps",
+            "context": (f"{P + 1 + W}..{P + W + K} during the timed steps" if ragged is None else
+                        f"shared prefix {eng.prefix_blocks * 16} + ragged tails, longest sequence {ragged[0] + 1 + W}.."
+                        f"{ragged[0] + W + K}, shortest {ragged[-1] + 1 + W}..{ragged[-1] + W + K} during the timed steps"),
             "kv_fill": "synthetic normal(0,1)" if args.synthetic_kv else "real prefill of random prompts",
-            "l2": "inputs larger than L2 (weights 16 GB + KV 17 GB streamed per step)",
+            "l2": "inputs larger than L2 (all weights and the batch's KV are streamed every step)",
             "attn_splits": (f"cascade {eng.state.prefix_splits}+{eng.state.suffix_splits}, {eng.prefix_blocks} shared blocks"
                             if eng.state.prefix_blocks else eng.num_splits),
             "projections": "separate q/k/v and gate/up GEMMs" if args.no_fuse_projections else "q|k|v and gate|up fused into one GEMM each",
@@ -374,7 +376,8 @@ def run_single(args, workload):
         "gpu_launches": launches_per_step * K,
         "roofline": {
             "bound": "hbm",
-            "kernel": "paged_attn_tma_kernel (b200_paged_decode_attn)",
+            "kernel": ("paged_attn_cascade_kernel + attn_combine_kernel (b200_paged_decode_attn_prefix), unique bytes"
+                       if eng.state.prefix_blocks else "paged_attn_tma_kernel (b200_paged_decode_attn)"),
             "achieved": achieved,
             "peak": peaks["hbm_gbs"],
             "peak_source": f"MEASURED_PEAKS.json ({peak_kind})",

@@ -275,12 +275,19 @@ def paged_decode_attention_prefix(
     if workspace is None:
         workspace = torch.empty(need, dtype=torch.uint8, device=q.device)
     table_stride = block_tables.stride(0) if B > 1 else block_tables.shape[1]
+    events = ATTN_EVENTS
+    if events is not None:
+        ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        ev0.record()
     rc = lib.b200_paged_decode_attn_prefix(
         out.data_ptr(), q.data_ptr(), q_stride, k_pool.data_ptr(), v_pool.data_ptr(), block_tables.data_ptr(),
         table_stride, context_lens.data_ptr(), B, Hq, Hkv, D, bs, max_blocks,
         float(D) ** -0.5 if scale is None else float(scale), int(max_context_len), int(prefix_blocks),
         int(prefix_splits), int(suffix_splits), workspace.data_ptr(), workspace.numel() * workspace.element_size(), dt,
         int(flags), _stream())
+    if events is not None:
+        ev1.record()
+        events.append((ev0, ev1))
     _lib.check(rc, "b200_paged_decode_attn_prefix")
     return out
 
