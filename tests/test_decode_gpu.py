@@ -228,3 +228,32 @@ def test_batcher_to_engine_adapter_end_to_end(golden):
     assert eng.engine.prefix_blocks == 5
     assert eng.get_backend_info()["supports_batch_inference"] is True
     eng.unload_model()
+
+
+def test_from_pretrained_loads_an_hf_checkpoint_and_matches_hf_generate(tmp_path):
+    """Drop-in check of ModelShard.from_pretrained (reference: worker/distributed/model_shard.py:61-148): a tiny
+    HuggingFace Llama checkpoint written to disk is loaded as two layer-range shards of paged layers; greedy
+    tokens must equal transformers' own generate() on that checkpoint."""
+    from transformers import LlamaConfig, LlamaForCausalLM
+
+    from dgi_b200.worker.distributed.model_shard import ModelShard
+
+    torch.manual_seed(0)
+    hf_cfg = LlamaConfig(hidden_size=256, num_attention_heads=4, num_key_value_heads=2, intermediate_size=512,
+                         vocab_size=320, num_hidden_layers=4, rms_norm_eps=1e-5, rope_theta=10000.0,
+                         tie_word_embeddings=False, max_position_embeddings=512)
+    hf_cfg._attn_implementation = "eager"
+    hf = LlamaForCausalLM(hf_cfg).eval()
+    hf.save_pretrained(tmp_path)
+    prompts = torch.randint(0, 320, (3, 40), generator=torch.Generator().manual_seed(5))
+    with torch.no_grad():
+        want = hf.generate(prompts, max_new_tokens=12, do_sample=False, pad_token_id=0)[:, 40:]
+    shards = [ModelShard.from_pretrained(str(tmp_path), s, e, device=DEV, dtype=torch.float32) for s, e in ((0, 2), (2, 4))]
+    assert shards[0].is_first_shard and not shards[0].is_last_shard and shards[1].get_layer_count() == 2
+    assert shards[0].hidden_size == 256 and shards[1].total_layers == 4
+    with pytest.raises(ValueError):
+        ModelShard.from_pretrained(str(tmp_path), 2, 5, device=DEV, dtype=torch.float32)
+    with pytest.raises(RuntimeError, match="only be called on the last shard"):
+        shards[0].get_logits(torch.zeros(1, 1, 256, device=DEV))
+    eng = PagedDecodeEngine(shards, 3, 64, prefill_mode="eager")
+    assert torch.equal(eng.generate(prompts, 12), want)
