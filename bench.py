@@ -237,7 +237,7 @@ def fill_pools_synthetic(engine, batch, ctx_len):
     for pool in engine.pools:
         pool.backing.normal_(0.0, 1.0)
     engine.context_lens[:batch] = ctx_len
-    engine._host_lens[:batch] = [ctx_len] * batch
+    engine._host_lens[:batch] = [min(ctx_len, engine.max_seq_len - 1)] * batch
 
 
 def run_single(args, workload):

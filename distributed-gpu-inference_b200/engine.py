@@ -284,9 +284,14 @@ class PagedDecodeEngine:
         self.context_lens.copy_(saved)  # warm-up advanced the lengths; capture itself runs nothing
         return graph
 
+    def _check_room(self) -> None:
+        if self.batch and max(self._host_lens[: self.batch]) + 1 > self.max_seq_len:
+            raise ValueError(f"Maximum length exceeded: {max(self._host_lens[:self.batch])} + 1 > {self.max_seq_len}")
+
     @torch.no_grad()
     def decode_step_device(self) -> None:
         """One step with input and output staying on the device (``ids_buf`` → ``next_tokens`` → ``ids_buf``)."""
+        self._check_room()
         if self.use_cuda_graph:
             if self._graph_chained is None:
                 self._graph_chained = self._capture(chained=True)
@@ -315,6 +320,7 @@ class PagedDecodeEngine:
     def decode_step(self, token_ids: torch.Tensor) -> torch.Tensor:
         """Public per-step call: host token ids [B] in (pinned copy → device), host next-token ids [B] out."""
         B = self.batch
+        self._check_room()
         self._pin_in[:B].copy_(token_ids.reshape(-1)[:B])
         self.ids_buf[:B, 0].copy_(self._pin_in[:B], non_blocking=True)
         if self.use_cuda_graph:

@@ -68,13 +68,16 @@ def attn_case(name, B, Hq, Hkv, D, ctx_lens, layers, splits, flags=0, share_pref
 
     if cascade:
         ps, ss = ops.attn_prefix_plan(B, Hq, Hkv, D, bs, share_prefix, max_ctx, dtype)
+        ps = int(os.environ.get("KBENCH_PSPLITS", ps))
+        ss = int(os.environ.get("KBENCH_SSPLITS", ss))
         splits = f"{ps}+{ss}"
         ws = torch.empty(max(16, ops.attn_workspace_bytes(B, Hq, D, ps + ss)), dtype=torch.uint8, device=DEV)
 
     def run(i):
         k, v = pools[i % layers]
         if cascade:
-            ops.paged_decode_attention_prefix(q, k, v, tables, lens, max_ctx, share_prefix, out=out, workspace=ws, flags=flags)
+            ops.paged_decode_attention_prefix(q, k, v, tables, lens, max_ctx, share_prefix, out=out, workspace=ws, flags=flags,
+                                              prefix_splits=ps, suffix_splits=ss)
         else:
             ops.paged_decode_attention(q, k, v, tables, lens, max_ctx, out=out, num_splits=splits, workspace=ws, flags=flags)
 
@@ -145,6 +148,10 @@ if __name__ == "__main__":
             attn_case("cfg5 8B B8 ctx32k ragged, shared 24576 prefix, CASCADE kernel", 8, 32, 8, 128, lens, a.layers,
                       a.splits, fl, share_prefix=24576 // 16, iters=a.iters, cascade=True)
             attn_case("cfg5 8B B8 ctx32k ragged, unshared", 8, 32, 8, 128, lens, min(a.layers, 4), a.splits, fl, iters=a.iters)
+        elif c == "cfg5c":
+            lens = [24576 + 8192 - 512 * i for i in range(8)]
+            attn_case("cfg5 cascade", 8, 32, 8, 128, lens, a.layers, a.splits, fl, share_prefix=24576 // 16, iters=a.iters,
+                      cascade=True)
         elif c == "prefix64":
             lens64 = [2048 + 64 + 16 * (i % 8) for i in range(64)]
             attn_case("8B B64, shared 2048-token system prompt + short tails, plain", 64, 32, 8, 128, lens64, a.layers,
