@@ -120,3 +120,21 @@ def test_chained_block_hashes_and_radix_index():
     assert [x.ref_count for x in b[0]] == [1, 1, 1, 1] and idx.match(toks)[0] == 2  # the third block went with a
     pool.free_sequence(b)
     assert idx.match(toks)[0] == 0 and all(c.get_stats()["free_blocks"] == 16 for c in pool._layer_caches)
+
+
+def test_batched_free_equals_block_by_block_free():
+    a = kv.PagedKVCache(1, 2, 8, block_size=4, max_blocks=8, device="cpu", dtype=torch.float32)
+    b = kv.PagedKVCache(1, 2, 8, block_size=4, max_blocks=8, device="cpu", dtype=torch.float32)
+    ids_a = [a.allocate_block(0).block_id for _ in range(6)]
+    ids_b = [b.allocate_block(0).block_id for _ in range(6)]
+    for c in (a, b):
+        c.key_pool.fill_(1.0)
+        c._blocks["block_5"].add_ref()  # shared: must survive one free
+    order = ["block_6", "block_5", "block_3", "nope", "block_7"]
+    for bid in order:
+        a.free_block(bid)
+    b.free_blocks(order)
+    assert a._free_blocks == b._free_blocks and sorted(a._blocks) == sorted(b._blocks)
+    assert torch.equal(a.key_pool, b.key_pool) and b.key_pool[5].eq(1).all() and b.key_pool[6].eq(0).all()
+    assert a.get_stats() == b.get_stats()
+    assert ids_a == ids_b
