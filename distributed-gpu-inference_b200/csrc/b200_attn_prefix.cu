@@ -365,14 +365,16 @@ int launch_cascade(const AttnArgs& a, int dtype, int prefix_blocks, int prefix_s
 
 bool attn_prefix_supported(const AttnArgs& a, int dtype) { return attn_tma_supported(a, dtype); }
 
-// Split counts for the two launches: the prefix launch wants ~2 CTAs per SM out of (splits x Hkv x q-groups) with
-// at least 256 tokens per split; the suffix launch follows the plain kernel's rule on the remaining context.
+// Split counts for the two roles.  Measured on B200 at config 5 (tools/kbench.py --cases cfg5c, sweep in
+// profiles/r01_kbench_cascade_splits.txt): about ONE prefix CTA per SM is best (8-10 prefix splits: 64 us; 19: 78 us;
+// 38: 87 us; 4: 94 us) — the suffix CTAs of the same launch fill the second CTA slot of every SM — with at least
+// 256 tokens per split; the suffix role follows the plain kernel's rule on the context left after the prefix.
 void attn_prefix_plan(int B, int Hq, int Hkv, int block_size, int prefix_blocks, int max_context_len,
                       int* prefix_splits, int* suffix_splits) {
   const int G = std::max(1, Hq / std::max(1, Hkv));
   const int qgroups = std::max(1, ceil_div(B * G, 8 * prefix_nt()));
   const int min_blocks = std::max(1, 256 / block_size);
-  int ps = ceil_div(2 * kNumSMs, std::max(1, Hkv * qgroups));
+  int ps = ceil_div(kNumSMs, std::max(1, Hkv * qgroups));
   ps = std::max(1, std::min(ps, std::max(1, prefix_blocks / min_blocks)));
   *prefix_splits = std::min(ps, 96);
   const int suffix_tokens = std::max(0, max_context_len - prefix_blocks * block_size);
