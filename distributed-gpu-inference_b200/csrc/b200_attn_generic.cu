@@ -70,8 +70,11 @@ paged_attn_generic_kernel(T* __restrict__ out, const T* __restrict__ q, int64_t 
 #pragma unroll
     for (int g = 0; g < GP; ++g) s[g] = 0.f;
     int64_t row = 0;
-    if (valid) {
-      const int64_t slot = table[t / block_size];
+    int64_t slot = 0;
+    if (valid) slot = table[t / block_size];
+    // a slot outside the pool (corrupt block table) is treated like a masked token instead of being dereferenced
+    const bool in_pool = slot >= 0 && slot < max_blocks;
+    if (valid && in_pool) {
       row = ((slot * Hkv + kvh) * block_size + (t % block_size)) * D;
       const T* kp = k_pool + row;
 #pragma unroll 2
@@ -96,9 +99,9 @@ paged_attn_generic_kernel(T* __restrict__ out, const T* __restrict__ q, int64_t 
       } else {
         sv *= scale;
       }
-      sv = valid ? sv : -INFINITY;
+      sv = (valid && in_pool) ? sv : -INFINITY;
       const float m_new = fmaxf(m[g], warp_max(sv));
-      const float p = valid ? __expf(sv - m_new) : 0.f;
+      const float p = (valid && in_pool && m_new > -INFINITY) ? __expf(sv - m_new) : 0.f;
       const float corr = (m[g] == -INFINITY) ? 0.f : __expf(m[g] - m_new);
       l[g] = l[g] * corr + warp_sum(p);
       m[g] = m_new;

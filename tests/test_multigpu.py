@@ -242,3 +242,71 @@ def test_block_move_between_local_pools_bit_exact():
     rest = torch.ones(30, dtype=torch.bool, device=dev)
     rest[dst.long()] = False
     assert b.backing[:, :, rest].eq(0).all()
+
+
+def _pipeline70b_worker(rank, world, port, q):
+    import sys
+    sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+    import dgi_b200  # noqa: F401
+    from dgi_b200.engine import PagedDecodeEngine
+    from dgi_b200.pipeline import LayerPipeline, make_pipeline_groups
+    from dgi_b200.worker.distributed.model_shard import ModelShard, get_layer_range_for_worker
+    from oracle import llama_ref as L
+
+    os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port))
+    torch.cuda.set_device(rank)
+    dev = f"cuda:{rank}"
+    dist.init_process_group("nccl", rank=rank, world_size=world, device_id=torch.device(dev))
+    try:
+        shape = dict(L.LLAMA3_70B)
+        shape["num_hidden_layers"] = 4
+        shape["vocab_size"] = 32000
+        cfg = L.RefConfig(**shape)
+        s, e = get_layer_range_for_worker(4, world, rank)
+        shard = ModelShard.from_config(cfg, s, e, device=dev, dtype=torch.bfloat16, seed=11)
+        M, mb, P, n_new = 2, 2, 48, 10
+        prompts = torch.randint(0, cfg.vocab_size, (M * mb, P), generator=torch.Generator().manual_seed(3))
+        engines = [PagedDecodeEngine([shard], mb, 96, prefill_mode="eager") for _ in range(M)]
+        for en in engines:
+            en.allocate(mb, 96)
+        pipe = LayerPipeline(engines, rank, world, make_pipeline_groups(world, warm_up_device=torch.device(dev)))
+        firsts = pipe.prefill([prompts[m * mb:(m + 1) * mb].to(dev) for m in range(M)] if rank == 0 else None, P, chunk=2)
+        if rank == 0:
+            pipe.set_first_tokens(firsts)
+        toks = pipe.decode(n_new - 1)
+        torch.cuda.synchronize()
+        if rank == 0:
+            got = torch.cat([torch.stack(firsts)[:, :, None], toks], dim=2).reshape(M * mb, -1)
+            # the reference recipe on the same weights: every partition of from_config(seed) holds identical weights
+            full = ModelShard.from_config(cfg, 0, 4, device=dev, dtype=torch.bfloat16, seed=11)
+            sd = {}
+            for i, layer in enumerate(full.layers):
+                for k, v in layer.state_dict().items():
+                    sd[f"model.layers.{i}.{k}"] = v
+            sd["model.embed_tokens.weight"] = full.embed_tokens.weight
+            sd["model.norm.weight"] = full.norm.weight
+            sd["lm_head.weight"] = full.lm_head.weight
+            ref = L.build_shards(cfg, sd, [(0, 2), (2, 4)], dtype=torch.bfloat16, device=dev)
+            want, logits = L.greedy_decode(ref, prompts.to(dev), n_new, return_logits=True)
+            eps = torch.finfo(torch.bfloat16).eps
+            bad = []
+            for b in range(M * mb):
+                diff = (got[b] != want[b]).nonzero()
+                if len(diff):
+                    st = int(diff[0])
+                    top2 = logits[b, st].topk(2).values
+                    margin = float(top2[0] - top2[1])
+                    if margin > 2 * eps * float(top2[0].abs()) + 1e-6:
+                        bad.append((b, st, margin))
+            q.put(("result", float((got == want).float().mean()), bad))
+        dist.barrier()
+    finally:
+        dist.destroy_process_group()
+
+
+@pytest.mark.skipif(torch.cuda.device_count() < 2, reason="needs 2 GPUs")
+def test_two_rank_70b_shape_bf16_pipeline_vs_reference_recipe():
+    (item,) = _run_ranks(_pipeline70b_worker, 2, 1, timeout=400)
+    _, agreement, bad = item
+    print(f"70B-shape (4 layers) bf16, 2 ranks x 2 micro-batches: token agreement {agreement:.3f}")
+    assert not bad, f"divergence at a decided token: {bad}"
