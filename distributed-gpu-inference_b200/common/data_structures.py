@@ -103,54 +103,6 @@ class WorkerInfo:
 
 
 @dataclass
-class InferenceState:
-    """Per-session cursor handed between stages (reference: common/data_structures.py:123-143)."""
-
-    session_id: str
-    position: int = 0
-    kv_cache_keys: List[str] = field(default_factory=list)
-    hidden_states_data: Optional[bytes] = None
-    hidden_states_shape: Optional[Tuple[int, ...]] = None
-    hidden_states_dtype: str = "float16"
-    input_tokens: int = 0
-    output_tokens: int = 0
-    created_at: float = field(default_factory=time.time)
-    updated_at: float = field(default_factory=time.time)
-
-    def update_position(self, new_tokens: int) -> None:
-        self.position += new_tokens
-        self.updated_at = time.time()
-
-
-@dataclass
-class KVCacheBlock:
-    """Wire-level description of one KV block (reference: common/data_structures.py:146-180)."""
-
-    block_id: str
-    layer_idx: int
-    block_size: int = 16
-    keys_data: Optional[bytes] = None
-    values_data: Optional[bytes] = None
-    num_heads: int = 0
-    head_dim: int = 0
-    ref_count: int = 1
-    prefix_hash: str = ""
-    location: str = "gpu"
-
-    @property
-    def is_shared(self) -> bool:
-        return self.ref_count > 1
-
-    def increment_ref(self) -> None:
-        self.ref_count += 1
-
-    def decrement_ref(self) -> int:
-        # Floors at zero, as the reference does (tests/test_common_data_structures.py:57-65).
-        self.ref_count = max(0, self.ref_count - 1)
-        return self.ref_count
-
-
-@dataclass
 class SessionConfig:
     """Knobs of a distributed session (reference: common/data_structures.py:231-254)."""
 
@@ -166,31 +118,6 @@ class SessionConfig:
     max_retries: int = 3
     use_speculative_decoding: bool = False
     speculative_depth: int = 5
-
-
-@dataclass
-class ModelShardConfig:
-    """Layer → worker map (reference: common/data_structures.py:257-290)."""
-
-    model_id: str
-    total_layers: int
-    shard_mapping: Dict[str, BlockRange] = field(default_factory=dict)
-    hidden_size: int = 0
-    num_attention_heads: int = 0
-    num_key_value_heads: int = 0
-    intermediate_size: int = 0
-    vocab_size: int = 0
-    memory_per_layer_gb: float = 0.0
-    kv_cache_per_token_bytes: int = 0
-
-    def get_worker_for_layer(self, layer_idx: int) -> Optional[str]:
-        for worker_id, rng in self.shard_mapping.items():
-            if layer_idx in rng:
-                return worker_id
-        return None
-
-    def get_inference_route(self) -> List[Tuple[str, BlockRange]]:
-        return sorted(self.shard_mapping.items(), key=lambda kv: kv[1].start)
 
 
 def compute_prefix_hash(token_ids: List[int]) -> str:
@@ -221,3 +148,8 @@ def estimate_kv_cache_size(
 ) -> int:
     """Bytes of K+V for a batch (reference: common/data_structures.py:299-309)."""
     return 2 * num_layers * batch_size * seq_length * num_heads * head_dim * dtype_bytes
+
+
+# Records the decode path itself never touches (per-session cursor, wire-level block description, layer→worker
+# map) live in records.py; they stay importable from here, as in the reference.
+from .records import InferenceState, KVCacheBlock, ModelShardConfig  # noqa: E402,F401
