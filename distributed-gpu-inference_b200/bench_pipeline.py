@@ -27,11 +27,22 @@ def run_pipeline(args, workload, SHAPES, ShapeConfig, ClockSampler, measured_pea
     local = int(os.environ.get("LOCAL_RANK", str(rank)))
     torch.cuda.set_device(local)
     dev = f"cuda:{local}"
+    # stdout must carry exactly one JSON line; NCCL prints its version banner to fd 1, so everything goes to
+    # stderr for the duration of the run and the line is written to the saved descriptor
+    import sys
+    sys.stdout.flush()
+    saved_stdout = os.dup(1)
+    os.dup2(2, 1)
     dist.init_process_group("nccl", device_id=torch.device(dev))
     try:
-        _run(args, workload, SHAPES, ShapeConfig, ClockSampler, measured_peaks, rank, world, local, dev)
+        line = _run(args, workload, SHAPES, ShapeConfig, ClockSampler, measured_peaks, rank, world, local, dev)
+        if line is not None:
+            os.write(saved_stdout, (json.dumps(line) + "\n").encode())
     finally:
         dist.destroy_process_group()
+        sys.stdout.flush()
+        os.dup2(saved_stdout, 1)
+        os.close(saved_stdout)
 
 
 def _run(args, workload, SHAPES, ShapeConfig, ClockSampler, measured_peaks, rank, world, local, dev):
@@ -104,7 +115,7 @@ def _run(args, workload, SHAPES, ShapeConfig, ClockSampler, measured_peaks, rank
     ctx_now = P + 2 * (K + W) + 1
     algo = mb * ctx_now * 2 * eng.Hkv * eng.D * 2 + 2 * mb * eng.Hq * eng.D * 2
     if rank != 0:
-        return
+        return None
     peaks, kind = measured_peaks()
     achieved = algo / (attn_ms * 1e-3) / 1e9
     layers_here = end - start
@@ -151,4 +162,4 @@ def _run(args, workload, SHAPES, ShapeConfig, ClockSampler, measured_peaks, rank
             "launches_timed": len(ev),
         },
     }
-    print(json.dumps(line), flush=True)
+    return line
