@@ -47,6 +47,10 @@ class PagedDecodeEngine:
                 for layer in sh.layers:
                     if hasattr(layer, "fuse_projections"):
                         layer.fuse_projections()
+                head = getattr(sh, "lm_head", None)
+                if isinstance(head, torch.nn.Linear) and head.weight.is_contiguous():
+                    with torch.no_grad():  # K-major storage for the vocabulary projection as well
+                        head.weight.data = head.weight.t().contiguous().t()
         first = self.shards[0]
         self.device = torch.device(first.device)
         if self.device.type != "cuda":
