@@ -54,8 +54,13 @@ add_rmsnorm_kernel(T* __restrict__ out, T* __restrict__ resid_out, const T* __re
   const T* xr = x + row * x_stride;
   const T* dr = delta ? delta + row * d_stride : nullptr;
   const int nvec = hidden / VN;
-  Vec16<T> cache[kNormMaxVec];
+  Vec16<T> cache[kNormMaxVec], wcache[kNormMaxVec];
   float ss = 0.f;
+#pragma unroll
+  for (int i = 0; i < kNormMaxVec; ++i) {  // weights first: their latency hides behind the row loads + reduction
+    const int v = threadIdx.x + i * kNormThreads;
+    if (v < nvec) wcache[i].raw = *reinterpret_cast<const int4*>(weight + v * VN);
+  }
 #pragma unroll
   for (int i = 0; i < kNormMaxVec; ++i) {
     const int v = threadIdx.x + i * kNormThreads;
@@ -82,12 +87,11 @@ add_rmsnorm_kernel(T* __restrict__ out, T* __restrict__ resid_out, const T* __re
   for (int i = 0; i < kNormMaxVec; ++i) {
     const int v = threadIdx.x + i * kNormThreads;
     if (v < nvec) {
-      Vec16<T> wv, ov;
-      wv.raw = *reinterpret_cast<const int4*>(weight + v * VN);
+      Vec16<T> ov;
 #pragma unroll
       for (int e = 0; e < VN; ++e) {
         const T n = Cvt<T>::from_f32(__fmul_rn(Cvt<T>::to_f32(cache[i].e[e]), inv));
-        ov.e[e] = Cvt<T>::from_f32(__fmul_rn(Cvt<T>::to_f32(wv.e[e]), Cvt<T>::to_f32(n)));
+        ov.e[e] = Cvt<T>::from_f32(__fmul_rn(Cvt<T>::to_f32(wcache[i].e[e]), Cvt<T>::to_f32(n)));
       }
       *reinterpret_cast<int4*>(out + static_cast<int64_t>(row) * hidden + v * VN) = ov.raw;
     }
@@ -95,10 +99,10 @@ add_rmsnorm_kernel(T* __restrict__ out, T* __restrict__ resid_out, const T* __re
 }
 
 // ---- RoPE on q (in place) and k, then K/V scatter into the pools -----------------------------------------
-// One CTA per token; thread t handles one 16-byte vector of the first half of a head together with its partner
-// vector in the second half (rotate-half pairs d and d + D/2).
+// Grid (tokens, chunks of 128 work items); a thread handles one 16-byte vector of the first half of a head together
+// with its partner vector in the second half (rotate-half pairs d and d + D/2).
 template <typename T>
-__global__ void __launch_bounds__(256)
+__global__ void __launch_bounds__(128)
 rope_append_kernel(T* __restrict__ q, int64_t q_stride, const T* __restrict__ k, int64_t k_stride,
                    const T* __restrict__ v, int64_t v_stride, const T* __restrict__ cos_t, const T* __restrict__ sin_t,
                    T* __restrict__ k_pool, T* __restrict__ v_pool, const int64_t* __restrict__ slot_mapping, int Hq,
@@ -115,7 +119,9 @@ rope_append_kernel(T* __restrict__ q, int64_t q_stride, const T* __restrict__ k,
   const T* sn = sin_t + static_cast<int64_t>(tok) * D;
 
   const int n_items = (Hq + 2 * Hkv) * per_head;
-  for (int it = threadIdx.x; it < n_items; it += blockDim.x) {
+  {
+    const int it = blockIdx.y * blockDim.x + threadIdx.x;  // one (head, vector pair) per thread
+    if (it >= n_items) return;
     const int head = it / per_head;
     const int hv = it - head * per_head;
     const int d0 = hv * VN;
@@ -238,7 +244,10 @@ int rope_kv_append(void* q, int64_t q_stride, const void* k, int64_t k_stride, c
     return fail(B200_ESHAPE, "b200_rope_kv_append: head_dim %d / alignment not supported", D);
   return by_dtype(dtype, "b200_rope_kv_append", [&](auto* tag) {
     using T = std::remove_pointer_t<decltype(tag)>;
-    rope_append_kernel<T><<<n_tok, 256, 0, s>>>(static_cast<T*>(q), q_stride, static_cast<const T*>(k), k_stride,
+    const int n_items = (Hq + 2 * Hkv) * ((D / 2) / (16 / static_cast<int>(sizeof(T))));
+    const int threads = 128;
+    dim3 grid(n_tok, (n_items + threads - 1) / threads);
+    rope_append_kernel<T><<<grid, threads, 0, s>>>(static_cast<T*>(q), q_stride, static_cast<const T*>(k), k_stride,
                                                 static_cast<const T*>(v), v_stride, static_cast<const T*>(cos_t),
                                                 static_cast<const T*>(sin_t), static_cast<T*>(k_pool),
                                                 static_cast<T*>(v_pool), slot_mapping, Hq, Hkv, D, block_size, max_blocks);
