@@ -310,3 +310,71 @@ def test_two_rank_70b_shape_bf16_pipeline_vs_reference_recipe():
     _, agreement, bad = item
     print(f"70B-shape (4 layers) bf16, 2 ranks x 2 micro-batches: token agreement {agreement:.3f}")
     assert not bad, f"divergence at a decided token: {bad}"
+
+
+def _pd_worker(rank, world, port, q):
+    """BASELINE config 3 in miniature: rank 0 runs the prompt pass, ships every sequence's KV blocks to rank 1,
+    rank 1 decodes.  Tokens must equal the reference's (golden) tokens for the same prompts."""
+    import sys
+    sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+    import json
+
+    import dgi_b200  # noqa: F401
+    from dgi_b200.engine import PagedDecodeEngine
+    from dgi_b200.kv_transfer import KVTransferEndpoint
+    from dgi_b200.testing import build_product_shards
+    from oracle import llama_ref as L
+
+    os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port))
+    torch.cuda.set_device(rank)
+    dev = f"cuda:{rank}"
+    dist.init_process_group("nccl", rank=rank, world_size=world, device_id=torch.device(dev))
+    try:
+        g = json.load(open(os.path.join(os.path.dirname(__file__), "golden", "tiny_decode.json")))
+        cfg = L.RefConfig(**g["config"])
+        sd = L.make_weights(cfg, seed=0)
+        shards = build_product_shards(cfg, sd, [(0, 4)], dev, torch.float32)  # both roles hold the full model
+        prompts = torch.tensor(g["prompt_ids"])
+        B, P, n_new = 4, prompts.shape[1], 20
+        eng = PagedDecodeEngine(shards, B, 192, prefill_mode="eager")
+        if rank == 1:
+            eng.pools[0].allocate_sequence(48)  # decode side already holds other data: its slots will differ
+        eng.allocate(B, P + n_new)
+        ep = KVTransferEndpoint(eng.pools[0], chunks=2)
+        n_blk = (P + 15) // 16
+        first = torch.empty(B, dtype=torch.int64, device=dev)
+        if rank == 0:  # prefill role
+            first.copy_(eng.prefill(prompts))
+            works = []
+            for b in range(B):
+                works += ep.send(eng.block_tables[b, :n_blk].contiguous(), dst=1)
+            dist.send(first, dst=1)
+            for w in works:
+                w.wait()
+            torch.cuda.synchronize()
+            q.put(("tables0", eng.block_tables[:B, :n_blk].cpu().tolist()))
+        else:  # decode role
+            for b in range(B):
+                ep.recv(eng.block_tables[b, :n_blk].contiguous(), src=0)
+            dist.recv(first, src=0)
+            eng.context_lens[:B] = P
+            eng._host_lens[:B] = [P] * B
+            out = [first.cpu()]
+            nxt = first.cpu()
+            for _ in range(n_new - 1):
+                nxt = eng.decode_step(nxt)
+                out.append(nxt)
+            q.put(("tokens", torch.stack(out, 1).tolist(), eng.block_tables[:B, :n_blk].cpu().tolist()))
+        dist.barrier()
+    finally:
+        dist.destroy_process_group()
+
+
+@pytest.mark.skipif(torch.cuda.device_count() < 2, reason="needs 2 GPUs")
+def test_prefill_rank_to_decode_rank_handoff_gives_reference_tokens(golden):
+    g = golden("tiny_decode.json")
+    items = {i[0]: i[1:] for i in _run_ranks(_pd_worker, 2, 2)}
+    toks, tables1 = items["tokens"]
+    (tables0,) = items["tables0"]
+    assert toks == [row[:20] for row in g["tokens"]]
+    assert tables0 != tables1  # the decode rank put the blocks where ITS allocator said
