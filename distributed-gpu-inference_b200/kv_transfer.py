@@ -17,7 +17,7 @@ serializer, common/serialization.py:73-76).
 """
 from __future__ import annotations
 
-from typing import List, Optional, Sequence
+from typing import List, Optional
 
 import torch
 import torch.distributed as dist

@@ -6,7 +6,7 @@ anything itself and none falls back to torch: a missing library or a non-CUDA te
 """
 from __future__ import annotations
 
-from typing import List, Optional, Sequence
+from typing import Optional, Sequence
 
 import torch
 

@@ -3,7 +3,6 @@
 70B-shape projections, default cuBLAS vs cuBLASLt, GB/s of weight bytes.  (The projections stay torch GEMMs by
 design; this only tells which library path bench.py should select.)"""
 import json
-import sys
 
 import torch
 import torch.nn.functional as F
