@@ -240,6 +240,36 @@ def fill_pools_synthetic(engine, batch, ctx_len):
     engine._host_lens[:batch] = [min(ctx_len, engine.max_seq_len - 1)] * batch
 
 
+def measure_pack_unpack(dev):
+    """Second hand-off figure available on one GPU: pack / unpack of one 4k-token 8B-shape sequence
+    (32 layers x 256 blocks x 64 KiB = 512 MiB), GB/s of bytes read + written."""
+    from dgi_b200 import ops
+
+    L_, Hkv, D, bs, n, max_blocks = 32, 8, 128, 16, 256, 320
+    backing = torch.empty((L_, 2, max_blocks, Hkv, bs, D), device=dev, dtype=torch.bfloat16).normal_()
+    kp = ops.pool_pointer_array([backing[l, 0] for l in range(L_)])
+    vp = ops.pool_pointer_array([backing[l, 1] for l in range(L_)])
+    table = torch.randperm(max_blocks, generator=torch.Generator().manual_seed(3))[:n].to(torch.int32).to(dev)
+    packed = torch.empty((L_, 2, n, Hkv, bs, D), dtype=torch.bfloat16, device=dev)
+    out = {}
+    for name, fn in (("pack", lambda: ops.kv_pack_layers(kp, vp, (max_blocks, Hkv, bs, D), torch.bfloat16, table, out=packed)),
+                     ("unpack", lambda: ops.kv_unpack_layers(packed, kp, vp, (max_blocks, Hkv, bs, D), table))):
+        for _ in range(3):
+            fn()
+        torch.cuda.synchronize()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        for _ in range(10):
+            fn()
+        e1.record()
+        torch.cuda.synchronize()
+        ms = e0.elapsed_time(e1) / 10
+        out[name + "_GBps"] = 2 * packed.numel() * 2 / ms / 1e6
+    out["payload_MiB"] = packed.numel() * 2 / 2 ** 20
+    out["unit"] = "GB/s of bytes read + written (HBM roofline: the same copy peak)"
+    return out
+
+
 def run_single(args, workload):
     import dgi_b200  # noqa: F401
     from dgi_b200 import ops
@@ -391,6 +421,7 @@ def run_single(args, workload):
             "how": "CUDA events around each attention launch of eagerly launched decode steps (same state as the timed loop)",
         },
     }
+    line["kv_pack"] = measure_pack_unpack(dev)
     if not args.no_cpu_baseline:
         res = cpu_reference_tokens_per_s(workload["shape"], B, ctx, steps=2, warmup=1)
         line["cpu_baseline"] = {k: res[k] for k in ("value", "unit", "cores", "kind", "sample")}

@@ -45,6 +45,54 @@ def run_pipeline(args, workload, SHAPES, ShapeConfig, ClockSampler, measured_pea
         os.close(saved_stdout)
 
 
+def _measure_pd_handoff(rank, world, dev):
+    """Third part of BASELINE's metric: prefill -> decode KV hand-off, rank i -> rank i + N/2 on all pairs at once,
+    one fused peer-push launch per sequence (8B-shape blocks, 8 layers x 4 sequences of 4k tokens = 512 MiB per
+    pair), CUDA events between barriers, max over ranks."""
+    if world < 2 or world % 2:
+        return None
+    try:
+        from .kv_transfer import PeerPushEndpoint
+
+        half = world // 2
+        layers, Hkv, D, bs, n_blocks, seqs = 8, 8, 128, 16, 256, 4
+        max_blocks = n_blocks * seqs + 32
+        pp = PeerPushEndpoint(layers, Hkv, D, bs, max_blocks, dev, torch.bfloat16)
+        sender = rank < half
+        peer = rank + half if sender else rank - half
+        if sender:
+            pp.pool.backing.normal_()
+        mk = lambda seed: [torch.randperm(max_blocks, generator=torch.Generator().manual_seed(seed * 100 + i))[:n_blocks]
+                           .to(torch.int32).to(dev) for i in range(seqs)]
+        src_tables, dst_tables = mk(rank), mk(peer)
+
+        def go():
+            if sender:
+                for st, dt in zip(src_tables, dst_tables):
+                    pp.push(st, dt, peer)
+            pp.barrier()
+
+        for _ in range(2):
+            go()
+        torch.cuda.synchronize()
+        dist.barrier()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        go()
+        e1.record()
+        torch.cuda.synchronize()
+        ms = torch.tensor([e0.elapsed_time(e1)], device=dev)
+        dist.all_reduce(ms, op=dist.ReduceOp.MAX)
+        payload = pp.payload_bytes(n_blocks) * seqs
+        gbs = payload / (ms.item() * 1e-3) / 1e9
+        del pp
+        return {"value": gbs, "unit": "GB/s per (prefill, decode) pair", "aggregate": gbs * half, "pairs": half,
+                "payload_MiB_per_pair": payload / 2 ** 20, "ms": ms.item(), "frac_of_nvlink_900": gbs / 900.0,
+                "path": "fused peer push (b200_kv_move_blocks_layers) into the decode rank's pools"}
+    except Exception as exc:  # noqa: BLE001 - the hand-off figure is an extra; never lose the decode line over it
+        return {"unavailable": repr(exc)}
+
+
 def _run(args, workload, SHAPES, ShapeConfig, ClockSampler, measured_peaks, rank, world, local, dev):
     cfg = ShapeConfig(**SHAPES[workload["shape"]])
     B, ctx = workload["batch"], workload["context"]
@@ -114,6 +162,7 @@ def _run(args, workload, SHAPES, ShapeConfig, ClockSampler, measured_peaks, rank
     attn_ms = statistics.mean(a.elapsed_time(b) for a, b in ev)
     ctx_now = P + 2 * (K + W) + 1
     algo = mb * ctx_now * 2 * eng.Hkv * eng.D * 2 + 2 * mb * eng.Hq * eng.D * 2
+    pd = _measure_pd_handoff(rank, world, dev)
     if rank != 0:
         return None
     peaks, kind = measured_peaks()
@@ -148,6 +197,7 @@ def _run(args, workload, SHAPES, ShapeConfig, ClockSampler, measured_peaks, rank
         "e2e": {"value": B * K / (e2e_ms * 1e-3), "unit": "tokens/s", "h2d_bytes_per_step": B * 8,
                 "d2h_bytes_per_step": B * 8, "ms_per_step": e2e_ms / K},
         "gpu_launches": per_step * K,
+        "pd_transfer": pd,
         "roofline": {
             "bound": "hbm",
             "kernel": "paged_attn_tma_kernel (b200_paged_decode_attn), one micro-batch on rank 0",
