@@ -51,6 +51,15 @@ class PagedDecodeEngine:
                 if isinstance(head, torch.nn.Linear) and head.weight.is_contiguous():
                     with torch.no_grad():  # K-major storage for the vocabulary projection as well
                         head.weight.data = head.weight.t().contiguous().t()
+        if fuse_projections:
+            # the last residual add of a layer is fused into the next layer's input norm; the final layer of each
+            # shard keeps its add so ModelShard.forward hands out complete hidden states
+            for sh in self.shards:
+                owned = [l for l in sh.layers if hasattr(l, "defer_residual")]
+                for layer in owned[:-1]:
+                    layer.defer_residual = True
+                if owned:
+                    owned[-1].defer_residual = False
         first = self.shards[0]
         self.device = torch.device(first.device)
         if self.device.type != "cuda":

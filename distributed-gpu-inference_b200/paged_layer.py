@@ -101,6 +101,8 @@ class PagedBatchState:
     prefix_splits: int = 0
     suffix_splits: int = 0
     past_len: int = 0
+    # MLP output of the previous layer whose residual add was deferred (see PagedLlamaDecoderLayer.defer_residual)
+    pending_residual: Optional[torch.Tensor] = None
 
 
 @dataclass
@@ -191,6 +193,7 @@ class PagedLlamaDecoderLayer(nn.Module):
 
     _qkv_w = None
     _gu_w = None
+    defer_residual = False
 
     # ---- forward -----------------------------------------------------------------------------------
     def forward(
@@ -210,7 +213,15 @@ class PagedLlamaDecoderLayer(nn.Module):
         B, T, _ = hidden_states.shape
         Hq, Hkv, D = self.num_heads, self.num_kv_heads, self.head_dim
 
-        x = self.input_layernorm(hidden_states)
+        if st.pending_residual is not None:
+            # the previous layer of this shard left its last residual add to us: h_in = hidden + pending, and the
+            # input norm of h_in, in one launch (same rounding as the separate add: h_in is rounded first)
+            x, hidden_states = ops.add_rmsnorm(hidden_states, self.input_layernorm.weight,
+                                               self.input_layernorm.variance_epsilon, delta=st.pending_residual,
+                                               want_residual=True)
+            st.pending_residual = None
+        else:
+            x = self.input_layernorm(hidden_states)
         if self._qkv_w is not None:
             qkv = F.linear(x, self._qkv_w)  # [B, T, (Hq + 2 Hkv) D]; q / k / v are column slices (strided rows)
             q = qkv[..., :Hq * D].unflatten(-1, (Hq, D))
@@ -267,7 +278,13 @@ class PagedLlamaDecoderLayer(nn.Module):
             act = ops.silu_mul(gu[..., :nf], gu[..., nf:])
         else:
             act = ops.silu_mul(self.mlp.gate_proj(y), self.mlp.up_proj(y))
-        h = h + self.mlp.down_proj(act)
+        if self.defer_residual:
+            # hand `h` on without the MLP output added; the next layer of the shard fuses that add into its input
+            # norm.  Only set (by the engine) on layers that are directly followed by another layer of the same
+            # shard inside ModelShard.forward's loop.
+            st.pending_residual = self.mlp.down_proj(act)
+        else:
+            h = h + self.mlp.down_proj(act)
         return h, (past_key_value if use_cache else None)
 
     def _with_cached_prefix(self, k, v, handle: PagedLayerKV, st: PagedBatchState):
