@@ -380,3 +380,40 @@ def test_wire_pack_emits_the_reference_serializer_bytes_and_unpack_inverts_it():
     got = dst_backing[:, :, dst.long()]
     assert torch.equal(_bits(got), _bits(want))
     assert torch.isinf(got[0, 0, 0, 0, 0, 1]) and got[0, 0, 0, 0, 0, 0] == 0  # the reference's lossy cases, reproduced
+
+
+# ---- randomised sweep: many small ragged configurations against the oracle ---------------------------------------
+def test_attention_random_configurations_against_oracle():
+    import random
+
+    rnd = random.Random(2024)
+    worst = 0.0
+    for it in range(40):
+        D = rnd.choice([64, 128])
+        Hkv = rnd.choice([1, 2, 4, 8])
+        G = rnd.choice([1, 2, 3, 4, 8])
+        B = rnd.randint(1, 9)
+        dtype, tol = rnd.choice([(torch.bfloat16, 1e-2), (torch.float16, 2e-3)])
+        ctx = [rnd.choice([0, 1, 15, 16, 17, rnd.randint(1, 700), rnd.randint(1, 3000)]) for _ in range(B)]
+        if max(ctx) == 0:
+            ctx[0] = 33
+        splits = rnd.choice([0, 1, 2, 5, 9])
+        q, k_pool, v_pool, tables, lens = _attn_case(B, Hkv * G, Hkv, D, 16, ctx, dtype, seed=1000 + it,
+                                                     q_strided=rnd.random() < 0.5)
+        out = ops.paged_decode_attention(q, k_pool, v_pool, tables, lens, max(ctx), num_splits=splits)
+        want = R.paged_attention_ref(q, k_pool, v_pool, tables, lens, mode="fp32")
+        err = _rel_err(out, want)
+        worst = max(worst, err / tol)
+        assert err <= tol, (it, B, Hkv, G, D, ctx, splits, dtype, err)
+        for b, c in enumerate(ctx):
+            if c == 0:
+                assert out[b].eq(0).all()
+        # the shared-prefix variant on the same data, when a common prefix can be declared
+        pb = min(ctx) // 16
+        if pb >= 1 and G <= 8:
+            shared_tables = tables.clone()
+            shared_tables[:, :pb] = tables[0, :pb]
+            want2 = R.paged_attention_ref(q, k_pool, v_pool, shared_tables, lens, mode="fp32")
+            out2 = ops.paged_decode_attention_prefix(q, k_pool, v_pool, shared_tables, lens, max(ctx), pb)
+            assert _rel_err(out2, want2) <= tol, (it, "prefix", pb)
+    print(f"worst error / tolerance over 40 random configurations: {worst:.2f}")
