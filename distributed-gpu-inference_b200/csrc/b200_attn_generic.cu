@@ -40,7 +40,7 @@ paged_attn_generic_kernel(T* __restrict__ out, const T* __restrict__ q, int64_t 
   float* l_s = m_s + kGenWarps * GP;                               // [W][GP]
   int64_t* row_s = reinterpret_cast<int64_t*>(l_s + kGenWarps * GP);  // [W][32]
 
-  const int ctx = context_lens[b];
+  const int ctx = min(context_lens[b], table_stride * block_size);  // never walk past the end of the table row
   const int t_begin = min(ctx, split * blocks_per_split * block_size);
   const int t_end = (split == num_splits - 1) ? ctx : min(ctx, (split + 1) * blocks_per_split * block_size);
 

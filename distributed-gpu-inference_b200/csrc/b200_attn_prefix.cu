@@ -84,7 +84,7 @@ __device__ __forceinline__ void cascade_role(const CUtensorMap& k_map, const CUt
   int blk_begin, blk_end, ctx = 0x7fffffff;
   const int32_t* table_row;
   if constexpr (SUFFIX) {
-    ctx = p.context_lens[zi];
+    ctx = min(p.context_lens[zi], p.table_stride * kTok);  // never walk past the end of the block-table row
     const int n_blocks = (ctx + kTok - 1) / kTok;
     blk_begin = min(n_blocks, p.prefix_blocks + split * p.suffix_bps);
     blk_end = (split == p.suffix_splits - 1) ? n_blocks : min(n_blocks, p.prefix_blocks + (split + 1) * p.suffix_bps);

@@ -144,7 +144,7 @@ paged_attn_tma_kernel(const __grid_constant__ CUtensorMap k_map, const __grid_co
   __syncwarp();
 
   // ---- this CTA's slice of the sequence ----
-  const int ctx = context_lens[b];
+  const int ctx = min(context_lens[b], table_stride * kTok);  // never walk past the end of the block-table row
   const int n_blocks = (ctx + kTok - 1) / kTok;
   const int blk_begin = min(n_blocks, first_block + split * blocks_per_split);
   const int blk_end = (split == num_splits - 1) ? n_blocks : min(n_blocks, first_block + (split + 1) * blocks_per_split);
