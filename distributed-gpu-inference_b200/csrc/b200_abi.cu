@@ -123,6 +123,70 @@ int b200_paged_decode_attn(void* out, const void* q, int64_t q_row_stride, const
   return 0;
 }
 
+int b200_rope_append_decode_attn(void* out, const void* q, int64_t q_row_stride, const void* k_new,
+                                 int64_t k_row_stride, const void* v_new, int64_t v_row_stride, const void* cos_table,
+                                 const void* sin_table, void* k_pool, void* v_pool, const int32_t* block_tables,
+                                 int table_stride, const int32_t* context_lens, int B, int Hq, int Hkv, int D,
+                                 int block_size, int64_t max_blocks, float scale, int max_context_len, int num_splits,
+                                 void* workspace, size_t workspace_bytes, int dtype, unsigned flags, void* stream) {
+  const char* name = "b200_rope_append_decode_attn";
+  if (dtype_size(dtype) == 0) return fail(B200_EINVAL, "%s: unsupported dtype %d", name, dtype);
+  if (B < 0 || Hq <= 0 || Hkv <= 0 || D <= 0 || block_size <= 0 || max_blocks <= 0 || Hq % Hkv != 0 || num_splits < 0)
+    return fail(B200_EINVAL, "%s: bad sizes", name);
+  if (B == 0) return 0;
+  if (!out || !q || !k_new || !v_new || !cos_table || !sin_table || !k_pool || !v_pool || !block_tables || !context_lens)
+    return fail(B200_EINVAL, "%s: null pointer", name);
+  if (q_row_stride < static_cast<int64_t>(Hq) * D || k_row_stride < static_cast<int64_t>(Hkv) * D ||
+      v_row_stride < static_cast<int64_t>(Hkv) * D)
+    return fail(B200_EINVAL, "%s: row stride smaller than heads * D", name);
+  if (num_splits == 0) num_splits = workspace ? plan_splits(B, Hkv, block_size, max_context_len) : 1;
+  const int n_blocks = std::max(1, ceil_div(std::max(1, max_context_len), block_size));
+  num_splits = std::min(num_splits, n_blocks);
+  AttnArgs a{};
+  a.out = out;
+  a.q = q;
+  a.q_row_stride = q_row_stride;
+  a.k_pool = k_pool;
+  a.v_pool = v_pool;
+  a.block_tables = block_tables;
+  a.table_stride = table_stride;
+  a.context_lens = context_lens;
+  a.B = B;
+  a.Hq = Hq;
+  a.Hkv = Hkv;
+  a.D = D;
+  a.block_size = block_size;
+  a.max_blocks = max_blocks;
+  a.scale = scale;
+  a.num_splits = num_splits;
+  a.blocks_per_split = ceil_div(n_blocks, num_splits);
+  a.round_scores = (flags & B200_ATTN_ROUND_SCORES) ? 1 : 0;
+  a.k_new = k_new;
+  a.k_new_stride = k_row_stride;
+  a.v_new = v_new;
+  a.v_new_stride = v_row_stride;
+  a.cos_t = cos_table;
+  a.sin_t = sin_table;
+  const int es = dtype_size(dtype);
+  if (!attn_tma_supported(a, dtype) || (k_row_stride * es) % 16 || (v_row_stride * es) % 16 || !aligned16(k_new) ||
+      !aligned16(v_new) || !aligned16(cos_table) || !aligned16(sin_table))
+    return fail(B200_ESHAPE, "%s: needs f16/bf16, block_size 16, head_dim 64/128, group <= 8, 16-byte aligned rows; "
+                "use b200_rope_kv_append + b200_paged_decode_attn for other shapes", name);
+  if (num_splits > 1) {
+    const size_t need = b200_paged_decode_attn_workspace(B, Hq, D, num_splits);
+    if (!workspace || workspace_bytes < need)
+      return fail(B200_ENOSPC, "%s: workspace of %zu bytes needed for %d splits, got %zu", name, need, num_splits,
+                  workspace_bytes);
+    a.ws_acc = static_cast<float*>(workspace);
+    a.ws_ml = a.ws_acc + static_cast<size_t>(B) * Hq * num_splits * D;
+  }
+  cudaStream_t s = static_cast<cudaStream_t>(stream);
+  const int rc = attn_tma(a, dtype, s);
+  if (rc != 0) return rc;
+  if (num_splits > 1) return attn_combine(out, a.ws_acc, a.ws_ml, B * Hq, D, num_splits, dtype, s);
+  return 0;
+}
+
 int b200_paged_decode_attn_prefix_plan(int B, int Hq, int Hkv, int D, int block_size, int prefix_blocks,
                                        int max_context_len, int dtype, int* prefix_splits, int* suffix_splits) {
   (void)D;

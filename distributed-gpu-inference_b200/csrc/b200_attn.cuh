@@ -23,11 +23,13 @@ struct AttnArgs {
   float* ws_acc;                // [B, Hq, num_splits, D] un-normalised partial outputs
   float* ws_ml;                 // [B, Hq, num_splits, 2] running max and sum
   int round_scores;
-  // shared-prefix cascade only (zero otherwise): skip blocks below first_block, file partials at
-  // split_offset + split out of splits_total
-  int first_block;
-  int split_offset;
-  int splits_total;
+  // fused RoPE + KV append (b200_rope_append_decode_attn); all null / zero for the plain entry points
+  const void* k_new;   // [B, Hkv, D] un-rotated k of the new token, row stride k_new_stride
+  int64_t k_new_stride;
+  const void* v_new;
+  int64_t v_new_stride;
+  const void* cos_t;   // [B, D]
+  const void* sin_t;
 };
 
 // shape-generic CUDA-core variant (b200_attn_generic.cu)

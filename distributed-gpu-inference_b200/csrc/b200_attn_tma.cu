@@ -110,17 +110,42 @@ using namespace tma;
 
 namespace {
 
-template <typename T, int D, int STAGES>
+// Operands of the fused variant (FUSED = true): this step's un-rotated q, the new token's k and v rows and the RoPE
+// tables.  The kernel then rotates q in registers, and the one warp that owns a sequence's last KV tile rotates the
+// new k row, writes it and the v row into the pool AND into its staged tile — so RoPE, the KV append and the
+// attention of a decode step are one launch instead of two.
+template <typename T>
+struct FusedAppend {
+  const T* k_new;       // [B, Hkv, D], row stride k_stride
+  int64_t k_stride;
+  const T* v_new;
+  int64_t v_stride;
+  const T* cos_t;       // [B, D]
+  const T* sin_t;
+  T* k_pool;            // writable views of the pools behind k_map / v_map
+  T* v_pool;
+};
+
+// rotate-half RoPE on one element pair with torch's rounding points (see b200_layer_ops.cu)
+template <typename T>
+__device__ __forceinline__ void rope_pair(T x_lo, T x_hi, T c_lo, T s_lo, T c_hi, T s_hi, T& o_lo, T& o_hi) {
+  const float xl = Cvt<T>::to_f32(x_lo), xh = Cvt<T>::to_f32(x_hi);
+  const T a = Cvt<T>::from_f32(__fmul_rn(xl, Cvt<T>::to_f32(c_lo)));
+  const T b = Cvt<T>::from_f32(__fmul_rn(-xh, Cvt<T>::to_f32(s_lo)));
+  o_lo = Cvt<T>::from_f32(__fadd_rn(Cvt<T>::to_f32(a), Cvt<T>::to_f32(b)));
+  const T c = Cvt<T>::from_f32(__fmul_rn(xh, Cvt<T>::to_f32(c_hi)));
+  const T d = Cvt<T>::from_f32(__fmul_rn(xl, Cvt<T>::to_f32(s_hi)));
+  o_hi = Cvt<T>::from_f32(__fadd_rn(Cvt<T>::to_f32(c), Cvt<T>::to_f32(d)));
+}
+
+template <typename T, int D, int STAGES, bool FUSED>
 __global__ void __launch_bounds__(kWarps * 32, (STAGES <= 3 ? 2 : 1))
 paged_attn_tma_kernel(const __grid_constant__ CUtensorMap k_map, const __grid_constant__ CUtensorMap v_map,
                       T* __restrict__ out, const T* __restrict__ q, int64_t q_row_stride,
                       const int32_t* __restrict__ block_tables, int table_stride,
                       const int32_t* __restrict__ context_lens, int Hq, int Hkv, int G, float scale,
                       int blocks_per_split, int num_splits, float* __restrict__ ws_acc, float* __restrict__ ws_ml,
-                      int round_scores, int first_block, int split_offset, int splits_total) {
-  // first_block / split_offset / splits_total serve the shared-prefix cascade (b200_attn_prefix.cu): this launch
-  // then covers only blocks >= first_block and files its partials after the prefix launch's.  Plain calls pass
-  // 0, 0, num_splits.
+                      int round_scores, const FusedAppend<T> fa) {
   using S = Smem<D, STAGES>;
   constexpr int KSTEPS = D / 16;   // mma k-steps over head_dim for S^T
   constexpr int MTILES = D / 16;   // mma m-tiles over head_dim for O^T
@@ -146,8 +171,8 @@ paged_attn_tma_kernel(const __grid_constant__ CUtensorMap k_map, const __grid_co
   // ---- this CTA's slice of the sequence ----
   const int ctx = min(context_lens[b], table_stride * kTok);  // never walk past the end of the block-table row
   const int n_blocks = (ctx + kTok - 1) / kTok;
-  const int blk_begin = min(n_blocks, first_block + split * blocks_per_split);
-  const int blk_end = (split == num_splits - 1) ? n_blocks : min(n_blocks, first_block + (split + 1) * blocks_per_split);
+  const int blk_begin = min(n_blocks, split * blocks_per_split);
+  const int blk_end = (split == num_splits - 1) ? n_blocks : min(n_blocks, (split + 1) * blocks_per_split);
   const int n_cta = blk_end - blk_begin;
   const int n_mine = n_cta > warp ? (n_cta - warp + kWarps - 1) / kWarps : 0;  // tiles warp, warp+4, ...
   const int32_t* table = block_tables + static_cast<int64_t>(b) * table_stride + blk_begin + warp;
@@ -190,6 +215,35 @@ paged_attn_tma_kernel(const __grid_constant__ CUtensorMap k_map, const __grid_co
     }
   }
 
+  if constexpr (FUSED) {
+    // RoPE on q in registers: the rotate-half partner of d is d + D/2, i.e. k-step kk + KSTEPS/2 at the same
+    // register slot of the same lane, so the rotation is lane-local.
+    const T* cs = fa.cos_t + static_cast<int64_t>(b) * D;
+    const T* sn = fa.sin_t + static_cast<int64_t>(b) * D;
+#pragma unroll
+    for (int kk = 0; kk < KSTEPS / 2; ++kk) {
+#pragma unroll
+      for (int j = 0; j < 2; ++j) {
+        const int d = kk * 16 + 8 * j + 2 * tq;
+        union { uint32_t u; T e[2]; } lo, hi, c_lo, s_lo, c_hi, s_hi, o_lo, o_hi;
+        lo.u = qf[kk][j];
+        hi.u = qf[kk + KSTEPS / 2][j];
+        c_lo.u = *reinterpret_cast<const uint32_t*>(cs + d);
+        s_lo.u = *reinterpret_cast<const uint32_t*>(sn + d);
+        c_hi.u = *reinterpret_cast<const uint32_t*>(cs + D / 2 + d);
+        s_hi.u = *reinterpret_cast<const uint32_t*>(sn + D / 2 + d);
+        rope_pair<T>(lo.e[0], hi.e[0], c_lo.e[0], s_lo.e[0], c_hi.e[0], s_hi.e[0], o_lo.e[0], o_hi.e[0]);
+        rope_pair<T>(lo.e[1], hi.e[1], c_lo.e[1], s_lo.e[1], c_hi.e[1], s_hi.e[1], o_lo.e[1], o_hi.e[1]);
+        qf[kk][j] = o_lo.u;
+        qf[kk + KSTEPS / 2][j] = o_hi.u;
+      }
+    }
+  }
+  // the warp that owns the sequence's last KV tile (the one the new token lands in) does the append
+  const int last_blk = n_blocks - 1;
+  const bool append_here = FUSED && ctx > 0 && last_blk >= blk_begin && last_blk < blk_end &&
+                           ((last_blk - blk_begin) % kWarps) == warp;
+
   // per-lane state for the two q heads g = 2 tq, 2 tq + 1: running max (scaled log2 domain), partial sum, O^T
   const float sl2 = scale * 1.4426950408889634f;
   float m_run[2] = {-INFINITY, -INFINITY};
@@ -210,6 +264,49 @@ paged_attn_tma_kernel(const __grid_constant__ CUtensorMap k_map, const __grid_co
     const uint32_t k_tile = ring + st * S::kStageBytes;
     const uint32_t v_tile = k_tile + S::kTileBytes;
     mbar_wait(bars + st * 8, (i / STAGES) & 1);
+
+    if constexpr (FUSED) {
+      if (append_here && i == n_mine - 1) {
+        // Row r of this tile is the new token.  Lanes 0..D/8-1 rotate one 16-byte chunk of k each, lanes 16.. copy
+        // one chunk of v; both go to the pool (for later steps) and into the staged tile (for this step), after the
+        // TMA copy of the tile has completed, so nothing is written concurrently with the async proxy.
+        constexpr int CH = D / 8;  // 16-byte chunks per row
+        const int r = (ctx - 1) & (kTok - 1);
+        const int64_t slot = block_tables[static_cast<int64_t>(b) * table_stride + last_blk];
+        const int64_t row_elems = ((slot * Hkv + kvh) * kTok + r) * static_cast<int64_t>(D);
+        if (lane < CH) {
+          const int c = lane, pc = (c + CH / 2) % CH;
+          const T* kr = fa.k_new + static_cast<int64_t>(b) * fa.k_stride + static_cast<int64_t>(kvh) * D;
+          union { int4 raw; T e[8]; } x, xp, cv, sv, o;
+          x.raw = *reinterpret_cast<const int4*>(kr + 8 * c);
+          xp.raw = *reinterpret_cast<const int4*>(kr + 8 * pc);
+          cv.raw = *reinterpret_cast<const int4*>(fa.cos_t + static_cast<int64_t>(b) * D + 8 * c);
+          sv.raw = *reinterpret_cast<const int4*>(fa.sin_t + static_cast<int64_t>(b) * D + 8 * c);
+          const bool first_half = c < CH / 2;
+#pragma unroll
+          for (int e = 0; e < 8; ++e) {
+            const float xf = Cvt<T>::to_f32(x.e[e]);
+            const float pf = first_half ? -Cvt<T>::to_f32(xp.e[e]) : Cvt<T>::to_f32(xp.e[e]);
+            const T a = Cvt<T>::from_f32(__fmul_rn(xf, Cvt<T>::to_f32(cv.e[e])));
+            const T bb = Cvt<T>::from_f32(__fmul_rn(pf, Cvt<T>::to_f32(sv.e[e])));
+            o.e[e] = Cvt<T>::from_f32(__fadd_rn(Cvt<T>::to_f32(a), Cvt<T>::to_f32(bb)));
+          }
+          *reinterpret_cast<int4*>(fa.k_pool + row_elems + 8 * c) = o.raw;
+          asm volatile("st.shared.v4.b32 [%0], {%1,%2,%3,%4};" ::"r"(k_tile + tile_off(r, c)), "r"(o.raw.x), "r"(o.raw.y),
+                       "r"(o.raw.z), "r"(o.raw.w)
+                       : "memory");
+        } else if (lane >= 16 && lane < 16 + CH) {
+          const int c = lane - 16;
+          const T* vr = fa.v_new + static_cast<int64_t>(b) * fa.v_stride + static_cast<int64_t>(kvh) * D;
+          const int4 raw = *reinterpret_cast<const int4*>(vr + 8 * c);
+          *reinterpret_cast<int4*>(fa.v_pool + row_elems + 8 * c) = raw;
+          asm volatile("st.shared.v4.b32 [%0], {%1,%2,%3,%4};" ::"r"(v_tile + tile_off(r, c)), "r"(raw.x), "r"(raw.y),
+                       "r"(raw.z), "r"(raw.w)
+                       : "memory");
+        }
+        __syncwarp();
+      }
+    }
 
     // S^T = K Q^T
     float s[4] = {0.f, 0.f, 0.f, 0.f};
@@ -311,10 +408,10 @@ paged_attn_tma_kernel(const __grid_constant__ CUtensorMap k_map, const __grid_co
       L = fmaf(wgt, l_s[w * 8 + g], L);
     }
     const int hq = kvh * G + g;
-    if (splits_total == 1) {
+    if (num_splits == 1) {
       out[(static_cast<int64_t>(b) * Hq + hq) * D + d] = Cvt<T>::from_f32(L > 0.f ? acc / L : 0.f);
     } else {
-      const int64_t pidx = (static_cast<int64_t>(b) * Hq + hq) * splits_total + split_offset + split;
+      const int64_t pidx = (static_cast<int64_t>(b) * Hq + hq) * num_splits + split;
       ws_acc[pidx * D + d] = acc;
       if (d == 0) {
         ws_ml[pidx * 2 + 0] = M * inv_l2;  // natural-log domain, as attn_combine_kernel expects
@@ -324,7 +421,7 @@ paged_attn_tma_kernel(const __grid_constant__ CUtensorMap k_map, const __grid_co
   }
 }
 
-template <typename T, int D, int STAGES>
+template <typename T, int D, int STAGES, bool FUSED>
 int launch_tma(const AttnArgs& a, int dtype, cudaStream_t stream) {
   using S = Smem<D, STAGES>;
   const uint64_t rows = static_cast<uint64_t>(a.max_blocks) * a.Hkv * kTok;
@@ -333,15 +430,25 @@ int launch_tma(const AttnArgs& a, int dtype, cudaStream_t stream) {
   if (rc) return rc;
   rc = get_tensor_map(a.v_pool, rows, D, dtype, &vm);
   if (rc) return rc;
-  auto kern = paged_attn_tma_kernel<T, D, STAGES>;
+  auto kern = paged_attn_tma_kernel<T, D, STAGES, FUSED>;
+  FusedAppend<T> fa{};
+  if (FUSED) {
+    fa.k_new = static_cast<const T*>(a.k_new);
+    fa.k_stride = a.k_new_stride;
+    fa.v_new = static_cast<const T*>(a.v_new);
+    fa.v_stride = a.v_new_stride;
+    fa.cos_t = static_cast<const T*>(a.cos_t);
+    fa.sin_t = static_cast<const T*>(a.sin_t);
+    fa.k_pool = static_cast<T*>(const_cast<void*>(a.k_pool));
+    fa.v_pool = static_cast<T*>(const_cast<void*>(a.v_pool));
+  }
   cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, S::kTotal);
   if (e != cudaSuccess) return fail(static_cast<int>(e), "cudaFuncSetAttribute: %s", cudaGetErrorString(e));
   dim3 grid(a.num_splits, a.Hkv, a.B);
   kern<<<grid, kWarps * 32, S::kTotal, stream>>>(km, vm, static_cast<T*>(a.out), static_cast<const T*>(a.q),
                                                   a.q_row_stride, a.block_tables, a.table_stride, a.context_lens, a.Hq,
                                                   a.Hkv, a.Hq / a.Hkv, a.scale, a.blocks_per_split, a.num_splits,
-                                                  a.ws_acc, a.ws_ml, a.round_scores, a.first_block, a.split_offset,
-                                                  a.splits_total > 0 ? a.splits_total : a.num_splits);
+                                                  a.ws_acc, a.ws_ml, a.round_scores, fa);
   return check_launch("b200_paged_decode_attn(tma)");
 }
 
@@ -358,11 +465,12 @@ bool attn_tma_supported(const AttnArgs& a, int dtype) {
   return tensor_maps_available();
 }
 
-template <int STAGES>
+template <int STAGES, bool FUSED>
 int attn_tma_stages(const AttnArgs& a, int dtype, cudaStream_t s) {
   if (dtype == B200_DTYPE_BF16)
-    return a.D == 128 ? launch_tma<__nv_bfloat16, 128, STAGES>(a, dtype, s) : launch_tma<__nv_bfloat16, 64, STAGES>(a, dtype, s);
-  return a.D == 128 ? launch_tma<__half, 128, STAGES>(a, dtype, s) : launch_tma<__half, 64, STAGES>(a, dtype, s);
+    return a.D == 128 ? launch_tma<__nv_bfloat16, 128, STAGES, FUSED>(a, dtype, s)
+                      : launch_tma<__nv_bfloat16, 64, STAGES, FUSED>(a, dtype, s);
+  return a.D == 128 ? launch_tma<__half, 128, STAGES, FUSED>(a, dtype, s) : launch_tma<__half, 64, STAGES, FUSED>(a, dtype, s);
 }
 
 // Ring depth: 3 stages x 2 CTAs per SM when the grid has at least two CTAs for every SM; 6 stages x 1 CTA per SM
@@ -375,7 +483,9 @@ int attn_tma(const AttnArgs& a, int dtype, cudaStream_t s) {
   }();
   const long ctas = static_cast<long>(a.num_splits) * a.Hkv * a.B;
   const int stages = forced ? forced : (ctas >= 2L * kNumSMs ? 3 : 6);
-  return stages >= 6 ? attn_tma_stages<6>(a, dtype, s) : attn_tma_stages<3>(a, dtype, s);
+  if (a.k_new != nullptr)  // fused RoPE + append + attention (3-stage ring only)
+    return attn_tma_stages<3, true>(a, dtype, s);
+  return stages >= 6 ? attn_tma_stages<6, false>(a, dtype, s) : attn_tma_stages<3, false>(a, dtype, s);
 }
 
 }  // namespace b200

@@ -226,6 +226,71 @@ def paged_decode_attention(
     return out
 
 
+def fused_decode_supported(k_pool: torch.Tensor, Hq: int) -> bool:
+    """Shapes the one-launch RoPE + append + attention entry point covers."""
+    _, Hkv, bs, D = k_pool.shape
+    return k_pool.dtype in (torch.bfloat16, torch.float16) and bs == 16 and D in (64, 128) and Hq // Hkv <= 8
+
+
+def rope_append_decode_attention(
+    q: torch.Tensor,
+    k_new: torch.Tensor,
+    v_new: torch.Tensor,
+    cos: torch.Tensor,
+    sin: torch.Tensor,
+    k_pool: torch.Tensor,
+    v_pool: torch.Tensor,
+    block_tables: torch.Tensor,
+    context_lens: torch.Tensor,
+    max_context_len: int,
+    scale: Optional[float] = None,
+    out: Optional[torch.Tensor] = None,
+    num_splits: int = 0,
+    workspace: Optional[torch.Tensor] = None,
+    flags: int = 0,
+) -> torch.Tensor:
+    """RoPE(q), RoPE(k_new), append of k_new / v_new at each sequence's last slot, and paged attention — one launch.
+
+    ``q [B, Hq, D]`` un-rotated (left untouched), ``k_new / v_new [B, Hkv, D]``, ``cos / sin [B, D]``;
+    ``context_lens`` already counts the new token.
+    """
+    _need_cuda(q, k_new, v_new, cos, sin, k_pool, v_pool, block_tables, context_lens)
+    max_blocks, Hkv, bs, D = _pool_dims(k_pool)
+    B, Hq = q.shape[0], q.shape[1]
+    if cos.shape != (B, D) or sin.shape != (B, D) or not cos.is_contiguous() or not sin.is_contiguous():
+        raise ValueError("cos / sin must be contiguous [B, D]")
+    if block_tables.dtype != torch.int32 or context_lens.dtype != torch.int32:
+        raise ValueError("block_tables and context_lens must be int32")
+    if out is None:
+        out = torch.empty((B, Hq, D), dtype=q.dtype, device=q.device)
+    lib = _lib.load()
+    dt = _dtype_id(k_pool)
+    if num_splits == 0:
+        num_splits = lib.b200_paged_decode_attn_plan(B, Hq, Hkv, D, bs, max_context_len, dt)
+    ws_ptr, ws_bytes = 0, 0
+    if num_splits > 1:
+        need = lib.b200_paged_decode_attn_workspace(B, Hq, D, num_splits)
+        if workspace is None:
+            workspace = torch.empty(need, dtype=torch.uint8, device=q.device)
+        ws_ptr, ws_bytes = workspace.data_ptr(), workspace.numel() * workspace.element_size()
+    table_stride = block_tables.stride(0) if B > 1 else block_tables.shape[1]
+    events = ATTN_EVENTS
+    if events is not None:
+        ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        ev0.record()
+    rc = lib.b200_rope_append_decode_attn(
+        out.data_ptr(), q.data_ptr(), _row_stride(q, Hq, D), k_new.data_ptr(), _row_stride(k_new, Hkv, D),
+        v_new.data_ptr(), _row_stride(v_new, Hkv, D), cos.data_ptr(), sin.data_ptr(), k_pool.data_ptr(),
+        v_pool.data_ptr(), block_tables.data_ptr(), table_stride, context_lens.data_ptr(), B, Hq, Hkv, D, bs, max_blocks,
+        float(D) ** -0.5 if scale is None else float(scale), int(max_context_len), int(num_splits), ws_ptr, ws_bytes, dt,
+        int(flags), _stream())
+    if events is not None:
+        ev1.record()
+        events.append((ev0, ev1))
+    _lib.check(rc, "b200_rope_append_decode_attn")
+    return out
+
+
 def attn_prefix_plan(B: int, Hq: int, Hkv: int, D: int, block_size: int, prefix_blocks: int, max_context_len: int,
                      dtype: torch.dtype):
     """``(prefix_splits, suffix_splits)`` the library would choose for the shared-prefix variant."""

@@ -242,19 +242,28 @@ class PagedLlamaDecoderLayer(nn.Module):
         if T == 1:
             # decode: RoPE on q (in place) and k, append of k / v, all in one launch; then paged attention
             qf = q[:, 0]  # [B, Hq, D], row stride = projection width
-            ops.rope_kv_append(qf, k[:, 0], v[:, 0], cos.reshape(B, D), sin.reshape(B, D),
-                               past_key_value.k_pool, past_key_value.v_pool, st.slot_mapping)
-            if st.prefix_blocks > 0:
-                attn = ops.paged_decode_attention_prefix(
-                    qf, past_key_value.k_pool, past_key_value.v_pool, st.block_tables, st.context_lens,
-                    st.max_context_len, st.prefix_blocks, prefix_splits=st.prefix_splits,
-                    suffix_splits=st.suffix_splits, workspace=st.workspace, flags=st.attn_flags,
+            cos2, sin2 = cos.reshape(B, D), sin.reshape(B, D)
+            if st.prefix_blocks == 0 and ops.fused_decode_supported(past_key_value.k_pool, Hq):
+                # RoPE, the append of k / v and the attention in ONE launch
+                attn = ops.rope_append_decode_attention(
+                    qf, k[:, 0], v[:, 0], cos2, sin2, past_key_value.k_pool, past_key_value.v_pool, st.block_tables,
+                    st.context_lens, st.max_context_len, num_splits=st.num_splits, workspace=st.workspace,
+                    flags=st.attn_flags,
                 ).view(B, 1, Hq * D)
             else:
-                attn = ops.paged_decode_attention(
-                    qf, past_key_value.k_pool, past_key_value.v_pool, st.block_tables, st.context_lens,
-                    st.max_context_len, num_splits=st.num_splits, workspace=st.workspace, flags=st.attn_flags,
-                ).view(B, 1, Hq * D)
+                ops.rope_kv_append(qf, k[:, 0], v[:, 0], cos2, sin2, past_key_value.k_pool, past_key_value.v_pool,
+                                   st.slot_mapping)
+                if st.prefix_blocks > 0:
+                    attn = ops.paged_decode_attention_prefix(
+                        qf, past_key_value.k_pool, past_key_value.v_pool, st.block_tables, st.context_lens,
+                        st.max_context_len, st.prefix_blocks, prefix_splits=st.prefix_splits,
+                        suffix_splits=st.suffix_splits, workspace=st.workspace, flags=st.attn_flags,
+                    ).view(B, 1, Hq * D)
+                else:
+                    attn = ops.paged_decode_attention(
+                        qf, past_key_value.k_pool, past_key_value.v_pool, st.block_tables, st.context_lens,
+                        st.max_context_len, num_splits=st.num_splits, workspace=st.workspace, flags=st.attn_flags,
+                    ).view(B, 1, Hq * D)
         else:
             # prompt pass: the rotated k is also needed densely for the causal attention among the new tokens
             cos4, sin4 = cos.unsqueeze(2), sin.unsqueeze(2)  # broadcast over heads: [B, T, 1, D]

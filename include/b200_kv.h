@@ -85,6 +85,26 @@ size_t b200_paged_decode_attn_workspace(int B, int Hq, int D, int num_splits);
 int b200_paged_decode_attn_plan(int B, int Hq, int Hkv, int D, int block_size, int max_context_len, int dtype);
 
 /*
+ * One decode step of a layer's attention in ONE launch: RoPE on q and on the new token's k, the append of that k and
+ * v into the pools, and the paged attention over the result — b200_rope_kv_append followed by
+ * b200_paged_decode_attn, fused (same rounding points, bit-identical output and pool contents).  q is read
+ * un-rotated and left untouched; context_lens[b] already counts the new token, whose slot is the last one of the
+ * sequence (block_tables[b][(ctx-1)/16], row (ctx-1)%16).  Replaces apply_rotary_pos_emb + torch.cat + eager
+ * attention of the HF layer called from ModelShard.forward (worker/distributed/model_shard.py:209-215).
+ * Shapes: f16/bf16, block_size 16, head_dim 64/128, group <= 8, 16-byte aligned rows; anything else returns
+ * B200_ESHAPE and the two separate entry points apply.
+ */
+int b200_rope_append_decode_attn(void* out, const void* q, int64_t q_row_stride,
+                                 const void* k_new, int64_t k_row_stride, const void* v_new, int64_t v_row_stride,
+                                 const void* cos_table, const void* sin_table,
+                                 void* k_pool, void* v_pool,
+                                 const int32_t* block_tables, int table_stride, const int32_t* context_lens,
+                                 int B, int Hq, int Hkv, int D, int block_size, int64_t max_blocks,
+                                 float scale, int max_context_len, int num_splits,
+                                 void* workspace, size_t workspace_bytes,
+                                 int dtype, unsigned flags, void* stream);
+
+/*
  * Shared-prefix ("cascade") variant of b200_paged_decode_attn: when block_tables[b][0:prefix_blocks] are the same
  * slots for every sequence (a shared system prompt — the blocks the reference's allocator would hold with
  * CacheBlock.ref_count > 1, worker/distributed/kv_cache.py:63-72, README "RadixAttention" prefix sharing), those

@@ -417,3 +417,47 @@ def test_attention_random_configurations_against_oracle():
             out2 = ops.paged_decode_attention_prefix(q, k_pool, v_pool, shared_tables, lens, max(ctx), pb)
             assert _rel_err(out2, want2) <= tol, (it, "prefix", pb)
     print(f"worst error / tolerance over 40 random configurations: {worst:.2f}")
+
+
+# ---- one-launch decode attention: RoPE + append + attention ----------------------------------------------------
+@pytest.mark.parametrize("dtype", [torch.bfloat16, torch.float16])
+@pytest.mark.parametrize("B,Hq,Hkv,D,ctx,splits", [
+    (64, 32, 8, 128, [2048] * 64, 1),                        # config 2
+    (5, 32, 8, 128, [1, 16, 17, 600, 2047], 0),              # new token first in a block / last in a block / ragged
+    (3, 64, 8, 128, [4096, 33, 1000], 3),                    # 70B shape, split-K
+    (4, 8, 2, 64, [128, 129, 1, 77], 2),                     # head_dim 64
+    (2, 12, 4, 128, [50, 310], 0),                           # group 3
+])
+def test_fused_rope_append_attention_equals_the_separate_kernels(dtype, B, Hq, Hkv, D, ctx, splits):
+    bs = 16
+    q, k_pool, v_pool, tables, lens = _attn_case(B, Hq, Hkv, D, bs, ctx, dtype, seed=B + D + len(ctx), q_strided=True)
+    g = torch.Generator(device=DEV).manual_seed(99)
+    kv_new = torch.randn((B, 2 * Hkv * D), generator=g, device=DEV).to(dtype)
+    k_new, v_new = kv_new[:, :Hkv * D].view(B, Hkv, D), kv_new[:, Hkv * D:].view(B, Hkv, D)  # strided rows
+    pos = (lens - 1).to(torch.int64)
+    inv_freq = 1.0 / (500000.0 ** (torch.arange(0, D, 2, device=DEV).float() / D))
+    emb = torch.cat((pos.float()[:, None] * inv_freq[None],) * 2, -1)
+    cos, sin = emb.cos().to(dtype), emb.sin().to(dtype)
+    slots = tables.long().gather(1, (pos // bs)[:, None]).squeeze(1) * bs + pos % bs
+    # reference: the two separate kernels (rope_kv_append rotates q in place, so give it a copy)
+    k_ref, v_ref, q_ref = k_pool.clone(), v_pool.clone(), q.clone()
+    ops.rope_kv_append(q_ref, k_new, v_new, cos, sin, k_ref, v_ref, slots)
+    want = ops.paged_decode_attention(q_ref, k_ref, v_ref, tables, lens, max(ctx), num_splits=splits)
+    # fused
+    q_before = q.clone()
+    got = ops.rope_append_decode_attention(q, k_new, v_new, cos, sin, k_pool, v_pool, tables, lens, max(ctx),
+                                           num_splits=splits)
+    assert torch.equal(_bits(got), _bits(want))
+    assert torch.equal(_bits(k_pool), _bits(k_ref)) and torch.equal(_bits(v_pool), _bits(v_ref))
+    assert torch.equal(_bits(q), _bits(q_before))  # q is left un-rotated
+
+
+def test_fused_decode_entry_rejects_other_shapes():
+    from dgi_b200._lib import B200LibraryError
+
+    q, k_pool, v_pool, tables, lens = _attn_case(2, 8, 2, 64, 16, [40, 9], torch.float32, seed=3)
+    z = torch.zeros((2, 2, 64), device=DEV)
+    cs = torch.zeros((2, 64), device=DEV)
+    assert not ops.fused_decode_supported(k_pool, 8)
+    with pytest.raises(B200LibraryError, match="f16/bf16"):
+        ops.rope_append_decode_attention(q, z, z, cs, cs, k_pool, v_pool, tables, lens, 40)
