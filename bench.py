@@ -370,8 +370,10 @@ def run_single(args, workload):
             traffic = json.load(open(tpath)).get(workload["key"])
         except Exception:  # noqa: BLE001
             traffic = None
-    # this repo's kernels per step: per layer add_rmsnorm x2, rope_kv_append, attention (+ combine), silu_mul; + final norm
-    launches_per_step = cfg.num_hidden_layers * (5 + (1 if eng.num_splits > 1 else 0)) + 1
+    # this repo's kernels per step: per layer add_rmsnorm x2, the one-launch RoPE + append + attention (+ combine when
+    # split), silu_mul; + the final norm.  With a shared prefix: rope_kv_append + cascade + combine instead.
+    per_layer = 6 if eng.state.prefix_blocks else 4 + (1 if eng.num_splits > 1 else 0)
+    launches_per_step = cfg.num_hidden_layers * per_layer + 1
 
     line = {
         "metric": "decode_tokens_per_s",

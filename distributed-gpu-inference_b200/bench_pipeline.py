@@ -168,7 +168,7 @@ def _run(args, workload, SHAPES, ShapeConfig, ClockSampler, measured_peaks, rank
     peaks, kind = measured_peaks()
     achieved = algo / (attn_ms * 1e-3) / 1e9
     layers_here = end - start
-    per_step = M * layers_here * (5 + (1 if eng.num_splits > 1 else 0))  # rank 0's kernels from this repo
+    per_step = M * layers_here * (4 + (1 if eng.num_splits > 1 else 0))  # rank 0's kernels from this repo
     line = {
         "metric": "decode_tokens_per_s",
         "value": B * K / (dev_ms * 1e-3),
