@@ -192,6 +192,9 @@ def _run(args, workload, SHAPES, ShapeConfig, ClockSampler, measured_peaks, rank
             "l2": "inputs larger than L2 (each rank streams its weights once per micro-batch plus its KV per step)",
             "attn_splits": eng.num_splits,
             "setup_s": round(setup_s, 1),
+            "note": ("the 70B shape (141 GB of bf16 weights + 172 GB of KV at this batch and context) does not fit one "
+                     "GPU, so --gpus 1 runs config 2 (8B shape); compare the N = 2 / 4 / 8 lines among themselves. "
+                     "Bound for layer-range decode: B*N*BW / (M*W + KV) with M = N micro-batches"),
         },
         "clocks": clocks,
         "e2e": {"value": B * K / (e2e_ms * 1e-3), "unit": "tokens/s", "h2d_bytes_per_step": B * 8,
