@@ -187,3 +187,33 @@ def test_batcher_dispatch_grouping_exceptions_timeout_and_queue_full():
         await b3.stop()
 
     asyncio.run(run())
+
+
+# ---- shared dataclasses: the reference's pins (tests/test_common_data_structures.py:21-65) -----------------------
+def test_block_range_worker_info_and_ref_count_floor():
+    import time
+
+    from dgi_b200.common import data_structures as ds
+
+    r = ds.BlockRange(2, 5)
+    assert r.length == 3 and 2 in r and 4 in r and 5 not in r and 1 not in r
+    assert ds.BlockRange.from_dict(r.to_dict()) == r
+    w = ds.WorkerInfo(worker_id="w", blocks=r, state=ds.WorkerState.ONLINE, cache_tokens_available=100,
+                      cache_tokens_used=25, gpu_memory_gb=80.0, gpu_memory_used_gb=20.0)
+    assert w.cache_utilization == 0.25 and w.gpu_utilization == 0.25 and w.is_healthy()
+    w.last_heartbeat = time.time() - 120
+    assert not w.is_healthy(timeout_seconds=60)
+    w.state = ds.WorkerState.ERROR
+    w.last_heartbeat = time.time()
+    assert not w.is_healthy()
+    d = w.to_dict()
+    assert d["blocks"] == {"start": 2, "end": 5} and d["role"] == "hybrid" and d["state"] == 4 and "rank" not in d
+    assert ds.WorkerInfo(worker_id="x").cache_utilization == 0.0
+    blk = ds.KVCacheBlock(block_id="b", layer_idx=0)
+    blk.increment_ref()
+    assert blk.is_shared and blk.decrement_ref() == 1 and blk.decrement_ref() == 0 and blk.decrement_ref() == 0
+    st = ds.InferenceState(session_id="s")
+    st.update_position(3)
+    assert st.position == 3
+    cfg = ds.SessionConfig(model_name="m")
+    assert (cfg.max_length, cfg.max_retries, cfg.connect_timeout) == (4096, 3, 30.0)
