@@ -310,7 +310,10 @@ paged_attn_cascade_kernel(const __grid_constant__ CUtensorMap k_map, const __gri
 
 inline int ceil_div(int a, int b) { return (a + b - 1) / b; }
 
-constexpr int kPrefixStages = 3;
+// ring depth: 3 stages at 2 CTAs per SM (NT <= 2); the 32-row variant (NT = 4) needs the whole register file of an SM
+// for one CTA, so it gets a 6-stage ring to keep the same number of bytes in flight
+template <int NT>
+constexpr int prefix_stages() { return NT <= 2 ? 3 : 6; }
 
 // Query rows per CTA = 8 * NT.  NT = 2 by default; B200_PREFIX_NT=1|2|4 overrides (tools/kbench.py sweeps).
 int prefix_nt() {
@@ -325,14 +328,14 @@ int prefix_nt() {
 template <typename T, int D, int NT>
 int launch_cascade(const AttnArgs& a, int dtype, int prefix_blocks, int prefix_splits, int suffix_splits,
                    cudaStream_t stream) {
-  using S = Smem<D, kPrefixStages>;
+  using S = Smem<D, prefix_stages<NT>()>;
   const uint64_t rows = static_cast<uint64_t>(a.max_blocks) * a.Hkv * kTok;
   CUtensorMap km, vm;
   int rc = get_tensor_map(a.k_pool, rows, D, dtype, &km);
   if (rc) return rc;
   rc = get_tensor_map(a.v_pool, rows, D, dtype, &vm);
   if (rc) return rc;
-  auto kern = paged_attn_cascade_kernel<T, D, kPrefixStages, NT>;
+  auto kern = paged_attn_cascade_kernel<T, D, prefix_stages<NT>(), NT>;
   cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, S::kTotal);
   if (e != cudaSuccess) return fail(static_cast<int>(e), "cudaFuncSetAttribute: %s", cudaGetErrorString(e));
   CascadeParams p{};
