@@ -362,32 +362,70 @@ class PagedDecodeEngine:
             out.append(nxt)
         return torch.stack(out, dim=1)
 
+    @torch.no_grad()
+    def generate_ragged(self, prompts: Sequence[Sequence[int]], max_new_tokens: int) -> List[List[int]]:
+        """Greedy generation for prompts of DIFFERENT lengths as one decode batch.
+
+        The prompt pass runs once per distinct length (sequences are ordered by length so that each length is a
+        contiguous slice of the batch); the decode steps then run over all sequences together — context lengths,
+        positions and slots are per sequence on the device anyway.  Returns the new tokens in the callers' order.
+        """
+        order = sorted(range(len(prompts)), key=lambda i: len(prompts[i]))
+        lens = [len(prompts[i]) for i in order]
+        B = len(order)
+        if B == 0:
+            return []
+        if min(lens) < 1:
+            raise ValueError("empty prompt")
+        self.allocate(B, max(lens) + max_new_tokens)
+        first = torch.empty((B,), dtype=torch.int64, device=self.device)
+        lo = 0
+        while lo < B:
+            hi = lo
+            while hi < B and lens[hi] == lens[lo]:
+                hi += 1
+            for c0 in range(lo, hi, self.prefill_chunk_size):
+                c1 = min(hi, c0 + self.prefill_chunk_size)
+                ids = torch.tensor([list(prompts[order[i]]) for i in range(c0, c1)], dtype=torch.int64, device=self.device)
+                first[c0:c1] = self.prefill_chunk(c0, c1, ids)
+            lo = hi
+        out = [first.cpu()]
+        nxt = out[0]
+        for _ in range(max_new_tokens - 1):
+            nxt = self.decode_step(nxt)
+            out.append(nxt)
+        toks = torch.stack(out, dim=1).tolist()
+        result: List[List[int]] = [[] for _ in range(B)]
+        for pos, i in enumerate(order):
+            result[i] = toks[pos]
+        return result
+
     # ---- ContinuousBatcher protocol (reference: worker/batch_processor.py:302-336) ---------------------
     def batch_inference(self, params_list: List[Dict[str, Any]]) -> List[Any]:
         """Engine hook the reference's batcher looks for: one result (or Exception) per request.
 
-        Each request carries ``input_ids`` (list[int]) and ``max_new_tokens``; requests are grouped by prompt
-        length so every group is one equal-length batch.
+        Each request carries ``input_ids`` (list[int]) and ``max_new_tokens``; prompts of different lengths are
+        decoded together as one batch (``generate_ragged``).
         """
         results: List[Any] = [None] * len(params_list)
-        groups: Dict[int, List[int]] = {}
+        good: List[int] = []
         for i, p in enumerate(params_list):
             try:
-                groups.setdefault(len(p["input_ids"]), []).append(i)
+                if len(p["input_ids"]) < 1:
+                    raise ValueError("empty input_ids")
+                good.append(i)
             except Exception as exc:  # noqa: BLE001 - per-item failure is part of the protocol
                 results[i] = exc
-        for plen, idxs in groups.items():
-            for lo in range(0, len(idxs), self.max_batch):
-                part = idxs[lo:lo + self.max_batch]
-                try:
-                    n_new = max(int(params_list[i].get("max_new_tokens", 16)) for i in part)
-                    ids = torch.tensor([params_list[i]["input_ids"] for i in part], dtype=torch.int64)
-                    toks = self.generate(ids, n_new)
-                    for row, i in enumerate(part):
-                        want = int(params_list[i].get("max_new_tokens", 16))
-                        results[i] = {"output_ids": toks[row, :want].tolist(),
-                                      "usage": {"prompt_tokens": plen, "completion_tokens": want}}
-                except Exception as exc:  # noqa: BLE001
-                    for i in part:
-                        results[i] = exc
+        for lo in range(0, len(good), self.max_batch):
+            part = good[lo:lo + self.max_batch]
+            try:
+                n_new = max(int(params_list[i].get("max_new_tokens", 16)) for i in part)
+                toks = self.generate_ragged([params_list[i]["input_ids"] for i in part], n_new)
+                for row, i in enumerate(part):
+                    want = int(params_list[i].get("max_new_tokens", 16))
+                    results[i] = {"output_ids": toks[row][:want],
+                                  "usage": {"prompt_tokens": len(params_list[i]["input_ids"]), "completion_tokens": want}}
+            except Exception as exc:  # noqa: BLE001
+                for i in part:
+                    results[i] = exc
         return results

@@ -141,19 +141,29 @@ class PagedLLMEngine:
             except Exception as exc:  # noqa: BLE001
                 results[i] = exc
         eng = self.engine
+        # requests without a system prompt form one ragged batch whatever their lengths; requests that share a system
+        # prompt AND a length are decoded with the prompt's blocks shared
+        merged: Dict[Any, List[int]] = {}
         for (plen, sys_ids), idxs in groups.items():
+            merged.setdefault((plen, sys_ids) if sys_ids else ("ragged", ()), []).extend(idxs)
+        for (plen, sys_ids), idxs in merged.items():
             for lo in range(0, len(idxs), eng.max_batch):
                 part = idxs[lo:lo + eng.max_batch]
                 try:
                     n_new = max(parsed[i][2] for i in part)
-                    if plen + n_new > eng.max_seq_len:
-                        raise ValueError(f"prompt of {plen} tokens + {n_new} new tokens exceeds max_model_len")
-                    ids = torch.tensor([parsed[i][0] for i in part], dtype=torch.int64)
-                    shared = len(sys_ids) if len(part) > 1 else 0
-                    toks = eng.generate(ids, n_new, shared_prefix_len=shared)
-                    cached = (min(shared, plen - 1) // eng.block_size) * eng.block_size
+                    longest = max(len(parsed[i][0]) for i in part)
+                    if longest + n_new > eng.max_seq_len:
+                        raise ValueError(f"prompt of {longest} tokens + {n_new} new tokens exceeds max_model_len")
+                    if plen == "ragged":
+                        rows = eng.generate_ragged([parsed[i][0] for i in part], n_new)
+                        cached = 0
+                    else:
+                        ids = torch.tensor([parsed[i][0] for i in part], dtype=torch.int64)
+                        shared = len(sys_ids) if len(part) > 1 else 0
+                        rows = eng.generate(ids, n_new, shared_prefix_len=shared).tolist()
+                        cached = (min(shared, plen - 1) // eng.block_size) * eng.block_size
                     for row, i in enumerate(part):
-                        results[i] = self._result(toks[row, :parsed[i][2]].tolist(), plen, cached if row > 0 else 0)
+                        results[i] = self._result(rows[row][:parsed[i][2]], len(parsed[i][0]), cached if row > 0 else 0)
                 except Exception as exc:  # noqa: BLE001
                     for i in part:
                         results[i] = exc

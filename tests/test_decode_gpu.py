@@ -257,3 +257,18 @@ def test_from_pretrained_loads_an_hf_checkpoint_and_matches_hf_generate(tmp_path
         shards[0].get_logits(torch.zeros(1, 1, 256, device=DEV))
     eng = PagedDecodeEngine(shards, 3, 64, prefill_mode="eager")
     assert torch.equal(eng.generate(prompts, 12), want)
+
+
+def test_ragged_prompt_lengths_decode_as_one_batch(golden):
+    g, cfg, sd = _tiny(golden)
+    base = torch.tensor(g["prompt_ids"])
+    prompts = [base[0, :128].tolist(), base[1, :37].tolist(), base[2, :128].tolist(), base[3, :5].tolist()]
+    shards = build_product_shards(cfg, sd, [(0, 2), (2, 4)], DEV, torch.float32)
+    eng = PagedDecodeEngine(shards, 4, 192, prefill_mode="eager")
+    got = eng.generate_ragged(prompts, 12)
+    ref_shards = L.build_shards(cfg, sd, [(0, 4)])
+    for p, toks in zip(prompts, got):
+        want = L.greedy_decode(ref_shards, torch.tensor([p]), 12)[0].tolist()
+        assert toks == want
+    assert got[0] == g["tokens"][0][:12] and got[2] == g["tokens"][2][:12]
+    assert sorted(eng.context_lens[:4].tolist()) == sorted(len(p) + 11 for p in prompts)
