@@ -38,6 +38,7 @@ class PagedDecodeEngine:
         prefill_chunk: int = 8,
         spare_blocks: int = 0,
         fuse_projections: bool = False,
+        kv_pools: Optional[Sequence[KVCachePool]] = None,
     ):
         if not shards:
             raise ValueError("need at least one shard")
@@ -78,7 +79,8 @@ class PagedDecodeEngine:
         self.Hkv = getattr(cfg, "num_key_value_heads", self.Hq) or self.Hq
         self.D = getattr(cfg, "head_dim", None) or cfg.hidden_size // self.Hq
 
-        self.pools: List[KVCachePool] = [
+        # kv_pools: pools somebody else created, e.g. over symmetric memory so that a peer GPU can write into them
+        self.pools: List[KVCachePool] = list(kv_pools) if kv_pools is not None else [
             KVCachePool(
                 num_layers=s.get_layer_count(),
                 num_heads=self.Hkv,
@@ -125,6 +127,10 @@ class PagedDecodeEngine:
         self._pin_in = torch.zeros((max_batch,), dtype=torch.int64).pin_memory()
         self._pin_out = torch.zeros((max_batch,), dtype=torch.int64).pin_memory()
         self.batch = 0
+        self._borrowed = False
+        if len(self.pools) != len(self.shards) or any(
+                p.num_layers != s.get_layer_count() for p, s in zip(self.pools, self.shards)):
+            raise ValueError("kv_pools must hold one pool per shard with that shard's layer count")
 
     # ---- allocation ----------------------------------------------------------------------------------
     def allocate(self, batch: int, total_len: int, shared_prefix_len: int = 0) -> None:
@@ -185,10 +191,46 @@ class PagedDecodeEngine:
         for b, per_shard in enumerate(self._seq_blocks):
             if per_shard is None:
                 continue
-            for pool, shard_blocks in zip(self.pools, per_shard):
-                pool.free_sequence(shard_blocks)
+            if not self._borrowed:
+                for pool, shard_blocks in zip(self.pools, per_shard):
+                    pool.free_sequence(shard_blocks)
             self._seq_blocks[b] = None
         self.batch = 0
+        self._borrowed = False
+
+    def adopt_sequences(self, per_seq_blocks: Sequence[Sequence[List[List[CacheBlock]]]],
+                        context_lens: Sequence[int]) -> None:
+        """Decode over blocks the caller allocated from this engine's pools and somebody else filled — the receiving
+        side of a prefill→decode hand-off.  ``per_seq_blocks[b][shard]`` is what ``KVCachePool.allocate_sequence``
+        returned; ``context_lens[b]`` tokens of KV are already in them.  The blocks stay the caller's: ``release``
+        (and the next ``allocate`` / ``adopt_sequences``) drops them without freeing.  Captured graphs are kept when
+        the batch size is unchanged, since tables and lengths are read from the static buffers at replay."""
+        batch = len(per_seq_blocks)
+        if batch > self.max_batch or batch != len(context_lens):
+            raise ValueError("batch beyond the engine's capacity / lengths do not match")
+        same_shape = getattr(self, "_graph_key", None) == (batch, 0)
+        self.release()
+        rows = []
+        for b, per_shard in enumerate(per_seq_blocks):
+            row = KVCachePool.block_table(per_shard[0][0])
+            if len(row) > self.blocks_per_seq or context_lens[b] > len(row) * self.block_size:
+                raise ValueError("sequence does not fit its blocks / the engine's table")
+            for shard_blocks in per_shard:
+                for layer_blocks in shard_blocks:
+                    if KVCachePool.block_table(layer_blocks) != row:
+                        raise RuntimeError("layers disagree on block slots; per-layer tables are not supported here")
+            self._seq_blocks[b] = list(per_shard)
+            rows.append(row + [0] * (self.blocks_per_seq - len(row)))
+        self._borrowed = True
+        self.block_tables[:batch].copy_(torch.tensor(rows, dtype=torch.int32))
+        self.context_lens.zero_()
+        self.context_lens[:batch].copy_(torch.tensor(list(context_lens), dtype=torch.int32))
+        self._host_lens = [int(n) for n in context_lens] + [0] * (self.max_batch - batch)
+        self.batch = batch
+        if not same_shape:
+            self._graph = None
+            self._graph_chained = None
+        self._set_prefix(0)
 
     # ---- prefill -------------------------------------------------------------------------------------
     @torch.no_grad()
@@ -281,6 +323,7 @@ class PagedDecodeEngine:
 
     def _capture(self, chained: bool) -> torch.cuda.CUDAGraph:
         self._view_state()
+        self._graph_key = (self.batch, getattr(self, "prefix_blocks", 0))  # what a captured graph is valid for
         saved = self.context_lens.clone()
         side = torch.cuda.Stream(device=self.device)
         side.wait_stream(torch.cuda.current_stream())

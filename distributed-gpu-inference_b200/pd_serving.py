@@ -1,0 +1,167 @@
+"""Prefill/decode-separated serving over one (prefill GPU, decode GPU) pair: the data plane behind the reference's
+P/D scheduler (server/app/services/pd_scheduler.py:207-323) and the workload of its benchmark
+(benchmarks/pd_separation.py: prefill on one worker, KV migration, decode on another).
+
+Both ranks of a pair hold the whole model.  A *wave* is a batch of requests with equal prompt length:
+
+  prefill rank   prompt pass chunk by chunk into its own blocks; after each chunk, on a side stream, ONE kernel
+                 (b200_kv_move_blocks_layers) writes that chunk's blocks of all layers over NVLink straight into the
+                 blocks the DECODE rank's allocator handed out; first tokens follow as a peer copy; then a signal.
+  decode rank    waits for the signal on its stream, adopts the blocks (``PagedDecodeEngine.adopt_sequences``) and
+                 decodes; then signals the slot set free.
+
+No NCCL call and no host synchronisation sits between the two ranks on the data path: block tables, first tokens and
+the two semaphores ("KV ready", "slot set free") all live in symmetric memory, so the prefill rank never waits for
+the decode rank unless both slot sets are still in use (back-pressure), and prompt passes overlap decode steps of
+the previous wave.
+"""
+from __future__ import annotations
+
+from typing import List, Optional, Sequence
+
+import torch
+import torch.distributed as dist
+
+from .engine import PagedDecodeEngine
+from .kv_transfer import PeerPushEndpoint
+from .worker.distributed.kv_cache import KVCachePool
+
+# signal channels of the KV handle (channel 0 is what handle.barrier() uses):
+# READY prefill→decode "the wave is in your blocks", FREE decode→prefill "that slot set can be overwritten"
+READY, FREE = 2, 3
+
+
+class PDPairWorker:
+    """One side of a prefill/decode pair.  ``group`` holds exactly the two ranks; group rank 0 prefills, 1 decodes."""
+
+    def __init__(self, shard, group, max_batch: int, prompt_len: int, max_new_tokens: int, block_size: int = 16,
+                 prefill_chunk: int = 4, slot_sets: int = 2, fuse_projections: bool = False,
+                 prefill_mode: str = "sdpa", use_cuda_graph: bool = True):
+        import torch.distributed._symmetric_memory as symm_mem
+
+        if dist.get_world_size(group) != 2:
+            raise ValueError("a P/D pair is two ranks")
+        self.group = group
+        self.me = dist.get_rank(group)
+        self.is_prefill = self.me == 0
+        self.peer = 1 - self.me
+        self.B, self.P, self.n_new, self.sets = max_batch, prompt_len, max_new_tokens, slot_sets
+        cfg = shard.config
+        Hq = cfg.num_attention_heads
+        Hkv = getattr(cfg, "num_key_value_heads", Hq) or Hq
+        D = getattr(cfg, "head_dim", None) or cfg.hidden_size // Hq
+        total = prompt_len + max_new_tokens
+        self.n_blk = (total + block_size - 1) // block_size        # blocks a decode-side sequence owns
+        self.n_blk_prompt = (prompt_len + block_size - 1) // block_size  # blocks that travel
+        dev = str(shard.device)
+        self.endpoint = PeerPushEndpoint(shard.get_layer_count(), Hkv, D, block_size,
+                                         slot_sets * max_batch * self.n_blk, dev, shard.dtype, group=group)
+        self.handle = self.endpoint.handle
+        self.engine = PagedDecodeEngine([shard], max_batch, total, block_size=block_size, prefill_chunk=prefill_chunk,
+                                        prefill_mode=prefill_mode, fuse_projections=fuse_projections,
+                                        use_cuda_graph=use_cuda_graph, kv_pools=[self.endpoint.pool])
+        # mailbox in symmetric memory: the decode rank's block tables per slot set + the first tokens per slot set
+        n_tab = (slot_sets * max_batch * self.n_blk + 1) // 2 * 2  # even, so the int64 token area is 8-byte aligned
+        words = n_tab + 2 * slot_sets * max_batch
+        self._mail = symm_mem.empty((words,), dtype=torch.int32, device=dev)
+        self._mail.zero_()
+        self._mail_handle = symm_mem.rendezvous(self._mail, group.group_name)
+        n_used = slot_sets * max_batch * self.n_blk
+        self._tables = self._mail[:n_used].view(slot_sets, max_batch, self.n_blk)
+        self._tokens = self._mail[n_tab:].view(torch.int64).view(slot_sets, max_batch)
+        peer_mail = self._mail_handle.get_buffer(self.peer, (words,), torch.int32)
+        self._peer_tokens = peer_mail[n_tab:].view(torch.int64).view(slot_sets, max_batch)
+        self._side = torch.cuda.Stream(device=dev)
+        self._slot_blocks: List[List] = []
+        if not self.is_prefill:
+            pool: KVCachePool = self.endpoint.pool
+            for s in range(slot_sets):
+                seqs = [[pool.allocate_sequence(total)] for _ in range(max_batch)]
+                for per_shard in seqs:
+                    for li, layer_blocks in enumerate(per_shard[0]):
+                        pool.layer(li).pin(b.block_id for b in layer_blocks)  # never an eviction candidate
+                self._slot_blocks.append(seqs)
+                rows = [KVCachePool.block_table(per_shard[0][0]) for per_shard in seqs]
+                self._tables[s].copy_(torch.tensor(rows, dtype=torch.int32))
+            peer_tables = peer_mail[:n_used].view(slot_sets, max_batch, self.n_blk)
+            peer_tables.copy_(self._tables)  # publish where each slot set's blocks are
+        torch.cuda.synchronize()
+        self.handle.barrier()
+        torch.cuda.synchronize()
+
+    # ---- prefill side -------------------------------------------------------------------------------------
+    @torch.no_grad()
+    def prefill_wave(self, wave: int, prompt_ids: torch.Tensor, events: Optional[dict] = None) -> None:
+        """Prompt pass of ``prompt_ids`` [n, P] and the push of its KV into slot set ``wave % slot_sets`` of the peer."""
+        assert self.is_prefill
+        eng, s = self.engine, wave % self.sets
+        n, P = prompt_ids.shape
+        if n > self.B or P != self.P:
+            raise ValueError("wave does not match the pair's shape")
+        self._side.synchronize()  # the previous wave's pushes read blocks that allocate() is about to free
+        eng.allocate(n, P)
+        cur = torch.cuda.current_stream()
+        if wave >= self.sets:
+            with torch.cuda.stream(self._side):
+                self.handle.wait_signal(self.peer, FREE)  # the decode rank is done with this slot set
+        dst_tables = self._tables[s]
+        for lo in range(0, n, eng.prefill_chunk_size):
+            hi = min(n, lo + eng.prefill_chunk_size)
+            first = eng.prefill_chunk(lo, hi, prompt_ids[lo:hi])
+            done = torch.cuda.Event(enable_timing=events is not None)
+            done.record(cur)
+            self._side.wait_event(done)
+            with torch.cuda.stream(self._side):
+                p0 = torch.cuda.Event(enable_timing=True) if events is not None else None
+                if p0 is not None:
+                    p0.record(self._side)
+                src = eng.block_tables[lo:hi, :self.n_blk_prompt].reshape(-1).contiguous()
+                dst = dst_tables[lo:hi, :self.n_blk_prompt].reshape(-1).contiguous()
+                self.endpoint.push(src, dst, self.peer)
+                self._peer_tokens[s, lo:hi].copy_(first)
+                first.record_stream(self._side)
+                if events is not None:
+                    p1 = torch.cuda.Event(enable_timing=True)
+                    p1.record(self._side)
+                    events.setdefault("prefill_end", []).append((wave, lo, hi, done))
+                    events.setdefault("push", []).append((wave, lo, hi, p0, p1))
+        with torch.cuda.stream(self._side):
+            self.handle.put_signal(self.peer, READY)
+
+    # ---- decode side --------------------------------------------------------------------------------------
+    @torch.no_grad()
+    def decode_wave(self, wave: int, n: int, n_waves: int, events: Optional[dict] = None) -> torch.Tensor:
+        """Decode ``max_new_tokens`` tokens for the ``n`` sequences of ``wave``; returns them [n, max_new_tokens] on
+        the device (column 0 is the token the prompt pass produced)."""
+        assert not self.is_prefill
+        eng, s = self.engine, wave % self.sets
+        self.handle.wait_signal(self.peer, READY)
+        if events is not None:
+            e0 = torch.cuda.Event(enable_timing=True)
+            e0.record()
+        eng.adopt_sequences(self._slot_blocks[s][:n], [self.P] * n)
+        out = torch.empty((n, self.n_new), dtype=torch.int64, device=eng.device)
+        out[:, 0] = self._tokens[s, :n]
+        eng.ids_buf[:n, 0].copy_(out[:, 0])
+        for i in range(1, self.n_new):
+            eng.decode_step_device()
+            out[:, i] = eng.next_tokens[:n]
+        if wave + self.sets < n_waves:
+            self.handle.put_signal(self.peer, FREE)
+        if events is not None:
+            e1 = torch.cuda.Event(enable_timing=True)
+            e1.record()
+            events.setdefault("decode", []).append((wave, e0, e1))
+        return out
+
+
+def make_pair_groups(world: int):
+    """Pair (i, i + world/2) for i < world/2; returns this rank's group (every rank creates every group)."""
+    half = world // 2
+    mine = None
+    rank = dist.get_rank()
+    for i in range(half):
+        g = dist.new_group([i, i + half])
+        if rank in (i, i + half):
+            mine = g
+    return mine

@@ -272,3 +272,41 @@ def test_ragged_prompt_lengths_decode_as_one_batch(golden):
         assert toks == want
     assert got[0] == g["tokens"][0][:12] and got[2] == g["tokens"][2][:12]
     assert sorted(eng.context_lens[:4].tolist()) == sorted(len(p) + 11 for p in prompts)
+
+
+def test_adopted_blocks_decode_like_own_blocks(golden):
+    """Receiving side of a hand-off on one GPU: engine A runs the prompt pass, its blocks are copied into blocks that
+    were taken from engine B's pool by the caller, B adopts them and decodes; B's graphs survive a second adoption."""
+    from dgi_b200.kv_transfer import KVTransferEndpoint
+
+    g, cfg, sd = _tiny(golden)
+    prompts = torch.tensor(g["prompt_ids"])
+    B, P, n_new = prompts.shape[0], prompts.shape[1], 16
+    shards = build_product_shards(cfg, sd, [(0, 4)], DEV, torch.float32)
+    a = PagedDecodeEngine(shards, B, 192, prefill_mode="eager")
+    b = PagedDecodeEngine(shards, B, 192, prefill_mode="eager", spare_blocks=2 * 12 * B)
+    b.pools[0].allocate_sequence(40)  # B's allocator is in a different state than A's
+    ep_a, ep_b = KVTransferEndpoint(a.pools[0]), KVTransferEndpoint(b.pools[0])
+    n_blk = (P + 15) // 16
+    for rnd in range(2):
+        order = list(range(B)) if rnd == 0 else list(reversed(range(B)))
+        a.allocate(B, P)
+        first = a.prefill(prompts[order])
+        mine = [[b.pools[0].allocate_sequence(P + n_new)] for _ in range(B)]
+        for i in range(B):
+            dst = torch.tensor(b.pools[0].block_table(mine[i][0][0])[:n_blk], dtype=torch.int32, device=DEV)
+            ep_a.copy_to(ep_b, a.block_tables[i, :n_blk].contiguous(), dst)
+        graph_before = b._graph
+        b.adopt_sequences(mine, [P] * B)
+        out = [first.cpu()]
+        for _ in range(n_new - 1):
+            out.append(b.decode_step(out[-1]))
+        toks = torch.stack(out, 1).tolist()
+        assert toks == [g["tokens"][i][:n_new] for i in order]
+        if rnd == 1:
+            assert graph_before is not None and b._graph is graph_before  # no re-capture for the same batch size
+        free_before = b.pools[0].layer(0).get_stats()["free_blocks"]
+        b.release()  # adopted blocks are the caller's: nothing is freed
+        assert b.pools[0].layer(0).get_stats()["free_blocks"] == free_before
+        for per_shard in mine:
+            b.pools[0].free_sequence(per_shard[0])

@@ -378,3 +378,52 @@ def test_prefill_rank_to_decode_rank_handoff_gives_reference_tokens(golden):
     (tables0,) = items["tables0"]
     assert toks == [row[:20] for row in g["tokens"]]
     assert tables0 != tables1  # the decode rank put the blocks where ITS allocator said
+
+
+def _pd_serving_worker(rank, world, port, q):
+    """Three waves through a PDPairWorker pair with two slot sets: prompt passes on rank 0, pushes into rank 1's
+    blocks, decode on rank 1 — overlapping, ordered only by the symmetric-memory signals."""
+    import sys
+    sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+    import json
+
+    import dgi_b200  # noqa: F401
+    from dgi_b200.pd_serving import PDPairWorker, make_pair_groups
+    from dgi_b200.testing import build_product_shards
+    from oracle import llama_ref as L
+
+    os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port))
+    torch.cuda.set_device(rank)
+    dev = f"cuda:{rank}"
+    dist.init_process_group("nccl", rank=rank, world_size=world, device_id=torch.device(dev))
+    try:
+        g = json.load(open(os.path.join(os.path.dirname(__file__), "golden", "tiny_decode.json")))
+        cfg = L.RefConfig(**g["config"])
+        sd = L.make_weights(cfg, seed=0)
+        shard = build_product_shards(cfg, sd, [(0, 4)], dev, torch.float32)[0]
+        prompts = torch.tensor(g["prompt_ids"]).to(dev)
+        B, P, n_new, waves = 4, prompts.shape[1], 20, 3
+        group = make_pair_groups(world)
+        w = PDPairWorker(shard, group, B, P, n_new, prefill_chunk=3, slot_sets=2, prefill_mode="eager")
+        got = []
+        for i in range(waves):
+            if w.is_prefill:
+                w.prefill_wave(i, prompts.roll(i, dims=0))
+            else:
+                got.append(w.decode_wave(i, B, waves))
+        torch.cuda.synchronize()
+        w._side.synchronize()
+        if not w.is_prefill:
+            q.put(("tokens", [t.cpu().tolist() for t in got]))
+        dist.barrier()
+    finally:
+        dist.destroy_process_group()
+
+
+@pytest.mark.skipif(torch.cuda.device_count() < 2, reason="needs 2 GPUs")
+def test_pd_serving_waves_give_reference_tokens(golden):
+    g = golden("tiny_decode.json")
+    ((_, waves),) = _run_ranks(_pd_serving_worker, 2, 1)
+    want = [row[:20] for row in g["tokens"]]
+    for i, toks in enumerate(waves):
+        assert toks == want[-i:] + want[:-i] if i else toks == want
