@@ -240,6 +240,28 @@ def fill_pools_synthetic(engine, batch, ctx_len):
     engine._host_lens[:batch] = [min(ctx_len, engine.max_seq_len - 1)] * batch
 
 
+def cpu_handoff_reference(layers: int = 2, n_blocks: int = 256):
+    """The reference's own hand-off (serialize → bytes → deserialize → copy into a pool slot, per block per layer,
+    on the host; oracle/handoff_ref.py) timed on a bounded sample of the 512 MiB sequence: ``layers`` of its 32."""
+    from oracle import handoff_ref as H
+
+    Hkv, D, bs, max_blocks = 8, 128, 16, n_blocks + 16
+    gen = torch.Generator().manual_seed(7)
+    src_k = [torch.randn(max_blocks, Hkv, bs, D, generator=gen).to(torch.bfloat16) for _ in range(layers)]
+    src_v = [torch.randn(max_blocks, Hkv, bs, D, generator=gen).to(torch.bfloat16) for _ in range(layers)]
+    dst_k = [torch.zeros_like(t) for t in src_k]
+    dst_v = [torch.zeros_like(t) for t in src_v]
+    st = torch.randperm(max_blocks, generator=gen)[:n_blocks].tolist()
+    dt = torch.randperm(max_blocks, generator=gen)[:n_blocks].tolist()
+    H.handoff_sequence(src_k[:1], src_v[:1], st[:16], dst_k[:1], dst_v[:1], dt[:16])  # warm-up
+    t0 = time.perf_counter()
+    moved = H.handoff_sequence(src_k, src_v, st, dst_k, dst_v, dt)
+    sec = time.perf_counter() - t0
+    return {"GBps": moved / sec / 1e9, "kind": "port", "cores": 1,
+            "sample": f"{layers} of 32 layers x {n_blocks} blocks x 64 KiB = {moved / 2**20:.0f} MiB on the wire "
+                      f"(fp16 bytes), host serializer per block, {sec:.2f} s"}
+
+
 def measure_pack_unpack(dev):
     """Second hand-off figure available on one GPU: pack / unpack of one 4k-token 8B-shape sequence
     (32 layers x 256 blocks x 64 KiB = 512 MiB), GB/s of bytes read + written."""
@@ -427,6 +449,7 @@ def run_single(args, workload):
     if not args.no_cpu_baseline:
         res = cpu_reference_tokens_per_s(workload["shape"], B, ctx, steps=2, warmup=1)
         line["cpu_baseline"] = {k: res[k] for k in ("value", "unit", "cores", "kind", "sample")}
+        line["kv_pack"]["cpu_reference_handoff"] = cpu_handoff_reference()
     print(json.dumps(line), flush=True)
 
 
@@ -460,7 +483,8 @@ def main():
     else:
         from dgi_b200.bench_pipeline import run_pipeline  # multi-GPU layer-sharded decode
 
-        run_pipeline(args, workload, SHAPES, ShapeConfig, ClockSampler, measured_peaks, cpu_reference_tokens_per_s)
+        run_pipeline(args, workload, SHAPES, ShapeConfig, ClockSampler, measured_peaks, cpu_reference_tokens_per_s,
+                     cpu_handoff=cpu_handoff_reference)
 
 
 if __name__ == "__main__":

@@ -21,7 +21,7 @@ from .pipeline import LayerPipeline, make_pipeline_groups
 from .worker.distributed.model_shard import ModelShard, get_layer_range_for_worker
 
 
-def run_pipeline(args, workload, SHAPES, ShapeConfig, ClockSampler, measured_peaks, cpu_reference):
+def run_pipeline(args, workload, SHAPES, ShapeConfig, ClockSampler, measured_peaks, cpu_reference, cpu_handoff=None):
     rank = int(os.environ.get("RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))
     local = int(os.environ.get("LOCAL_RANK", str(rank)))
@@ -36,6 +36,8 @@ def run_pipeline(args, workload, SHAPES, ShapeConfig, ClockSampler, measured_pea
     dist.init_process_group("nccl", device_id=torch.device(dev))
     try:
         line = _run(args, workload, SHAPES, ShapeConfig, ClockSampler, measured_peaks, rank, world, local, dev)
+        if line is not None and cpu_handoff is not None and isinstance(line.get("pd_transfer"), dict):
+            line["pd_transfer"]["cpu_reference_handoff"] = cpu_handoff()  # bench.py's host-side baseline leg
         if line is not None:
             os.write(saved_stdout, (json.dumps(line) + "\n").encode())
     finally:

@@ -188,3 +188,43 @@ class ContinuousBatcher:
 
     def get_stats(self) -> Dict[str, Any]:
         return {**self._stats, "queue_size": len(self._pending), "prefix_groups": len(self._pending_by_prefix)}
+
+
+class AdaptiveBatcher(ContinuousBatcher):
+    """Batcher that steers its batch size toward a latency target (reference: worker/batch_processor.py:368-433).
+
+    Starts at half of ``max_batch_size``; once ten batch latencies are known, the mean of the last ten moves the
+    working size by ×0.8 (above 1.2 × target) or ×1.2 (below 0.8 × target) within ``[min_batch_size,
+    max_batch_size]``.  At most the last 100 latencies are kept.
+    """
+
+    def __init__(self, engine, min_batch_size: int = 1, max_batch_size: int = 64, target_latency_ms: float = 100,
+                 **kwargs):
+        super().__init__(engine, max_batch_size=max_batch_size, **kwargs)
+        self.min_batch_size = min_batch_size
+        self.target_latency_ms = target_latency_ms
+        self._current_batch_size = max_batch_size // 2
+        self._latency_history: List[float] = []
+        self._max_history = 100
+
+    async def _process_batch(self) -> None:
+        t0 = time.time()
+        ceiling, self.max_batch_size = self.max_batch_size, self._current_batch_size
+        try:
+            await super()._process_batch()
+        finally:
+            self.max_batch_size = ceiling
+        self._latency_history.append((time.time() - t0) * 1000)
+        del self._latency_history[:-self._max_history]
+        self._adapt_batch_size()
+
+    def _adapt_batch_size(self) -> None:
+        recent = self._latency_history[-10:]
+        if len(self._latency_history) < 10:
+            return
+        mean = sum(recent) / 10
+        if mean > 1.2 * self.target_latency_ms:
+            self._current_batch_size = max(self.min_batch_size, int(self._current_batch_size * 0.8))
+        elif mean < 0.8 * self.target_latency_ms:
+            self._current_batch_size = min(self.max_batch_size, int(self._current_batch_size * 1.2))
+        logger.debug(f"Adaptive batch size: {self._current_batch_size} (avg latency: {mean:.1f}ms)")

@@ -31,7 +31,7 @@ import logging
 import pickle
 import time
 from collections import OrderedDict
-from dataclasses import dataclass, field
+from dataclasses import dataclass, field  # noqa: F401
 from enum import Enum
 from typing import Any, Dict, Iterable, List, Optional, Sequence, Set, Tuple
 
@@ -47,24 +47,61 @@ class CacheLocation(Enum):
     REMOTE = "remote"
 
 
-@dataclass
 class CacheBlock:
     """One fixed-size page of K and V for one layer (reference: worker/distributed/kv_cache.py:34-76).
 
-    ``keys`` / ``values`` are views into the owning pool, shape ``[num_heads, block_size, head_dim]``.
+    Same constructor, fields and defaults as the reference's dataclass.  ``keys`` / ``values`` are views into the
+    owning pool, shape ``[num_heads, block_size, head_dim]``; for blocks handed out by ``PagedKVCache`` the views are
+    made on first access (a 4k-token sequence of a 32-layer model is 8192 blocks — building 16384 tensor views
+    nobody reads was most of the cost of ``allocate_sequence``), the device path only needs ``slot``.
     """
 
-    block_id: str
-    block_size: int = 16
-    keys: Optional[torch.Tensor] = None
-    values: Optional[torch.Tensor] = None
-    layer_idx: int = 0
-    num_tokens: int = 0
-    ref_count: int = 1
-    prefix_hash: str = ""
-    location: CacheLocation = CacheLocation.GPU
-    last_access: float = field(default_factory=time.time)
-    created_at: float = field(default_factory=time.time)
+    __slots__ = ("block_id", "block_size", "_keys", "_values", "layer_idx", "num_tokens", "ref_count", "prefix_hash",
+                 "location", "last_access", "created_at", "_owner", "_slot")
+
+    def __init__(self, block_id: str, block_size: int = 16, keys: Optional[torch.Tensor] = None,
+                 values: Optional[torch.Tensor] = None, layer_idx: int = 0, num_tokens: int = 0, ref_count: int = 1,
+                 prefix_hash: str = "", location: CacheLocation = CacheLocation.GPU,
+                 last_access: Optional[float] = None, created_at: Optional[float] = None):
+        now = time.time() if last_access is None or created_at is None else 0.0
+        self.block_id = block_id
+        self.block_size = block_size
+        self._keys = keys
+        self._values = values
+        self.layer_idx = layer_idx
+        self.num_tokens = num_tokens
+        self.ref_count = ref_count
+        self.prefix_hash = prefix_hash
+        self.location = location
+        self.last_access = now if last_access is None else last_access
+        self.created_at = now if created_at is None else created_at
+        self._owner = None  # the PagedKVCache whose pool rows back this block, if any
+        self._slot = -1
+
+    @property
+    def keys(self) -> Optional[torch.Tensor]:
+        if self._keys is None and self._owner is not None:
+            self._keys = self._owner._key_pool[self._slot]
+        return self._keys
+
+    @keys.setter
+    def keys(self, t: Optional[torch.Tensor]) -> None:
+        self._keys = t
+
+    @property
+    def values(self) -> Optional[torch.Tensor]:
+        if self._values is None and self._owner is not None:
+            self._values = self._owner._value_pool[self._slot]
+        return self._values
+
+    @values.setter
+    def values(self, t: Optional[torch.Tensor]) -> None:
+        self._values = t
+
+    def __repr__(self) -> str:
+        return (f"CacheBlock(block_id={self.block_id!r}, block_size={self.block_size}, layer_idx={self.layer_idx}, "
+                f"num_tokens={self.num_tokens}, ref_count={self.ref_count}, prefix_hash={self.prefix_hash!r}, "
+                f"location={self.location})")
 
     @property
     def is_full(self) -> bool:
@@ -77,7 +114,9 @@ class CacheBlock:
     @property
     def slot(self) -> int:
         """Pool row this block occupies (the integer after ``block_``)."""
-        return int(self.block_id.rsplit("_", 1)[1])
+        if self._slot < 0:
+            self._slot = int(self.block_id.rsplit("_", 1)[1])
+        return self._slot
 
     def add_ref(self) -> None:
         self.ref_count += 1
@@ -137,6 +176,7 @@ class PagedKVCache:
             self._key_pool = torch.zeros(shape, dtype=self.dtype, device=self.device)
             self._value_pool = torch.zeros(shape, dtype=self.dtype, device=self.device)
         self._free_blocks = [f"block_{i}" for i in range(self.max_blocks)]
+        self._slot_of_id = {bid: i for i, bid in enumerate(self._free_blocks)}
 
     def _get_pool_memory_gb(self) -> float:
         if self._key_pool is None:
@@ -157,20 +197,40 @@ class PagedKVCache:
             logger.warning("No free blocks and eviction failed")
             return None
         block_id = self._free_blocks.pop()
-        slot = int(block_id.split("_")[1])
-        blk = CacheBlock(
-            block_id=block_id,
-            block_size=self.block_size,
-            layer_idx=layer_idx,
-            prefix_hash=prefix_hash,
-            keys=self._key_pool[slot],
-            values=self._value_pool[slot],
-        )
+        now = time.time()
+        blk = CacheBlock(block_id, self.block_size, None, None, layer_idx, 0, 1, prefix_hash, CacheLocation.GPU, now, now)
+        blk._owner = self
+        slot = blk._slot = self._slot_of_id[block_id]
         self._blocks[block_id] = blk
         self._block_to_slot[block_id] = slot
-        self._lru_queue[block_id] = time.time()
+        self._lru_queue[block_id] = now
         self._stats["allocations"] += 1
         return blk
+
+    def allocate_blocks(self, layer_idx: int, n: int, prefix_hash: str = "") -> Optional[List[CacheBlock]]:
+        """``n`` × ``allocate_block`` with the same observable result (ids in pop order, LRU order, statistics) when
+        the free list already holds ``n`` ids; returns None — having changed nothing — when it does not, so that the
+        caller falls back to the block-by-block path with its eviction."""
+        if n > len(self._free_blocks):
+            return None
+        if n <= 0:
+            return []
+        ids = self._free_blocks[-n:]
+        ids.reverse()
+        del self._free_blocks[-n:]
+        now = time.time()
+        slot_of, bs, gpu = self._slot_of_id, self.block_size, CacheLocation.GPU
+        out = []
+        for block_id in ids:
+            blk = CacheBlock(block_id, bs, None, None, layer_idx, 0, 1, prefix_hash, gpu, now, now)
+            blk._owner = self
+            blk._slot = slot_of[block_id]
+            out.append(blk)
+        self._blocks.update(zip(ids, out))
+        self._block_to_slot.update((i, slot_of[i]) for i in ids)
+        self._lru_queue.update((i, now) for i in ids)
+        self._stats["allocations"] += n
+        return out
 
     def free_block(self, block_id: str) -> None:
         blk = self._blocks.get(block_id)
@@ -315,6 +375,11 @@ class KVCachePool:
                 for blk in shared_prefix[layer_idx][:n_blocks]:
                     blk.add_ref()
                     mine.append(blk)
+            fresh = cache.allocate_blocks(layer_idx, n_blocks - len(mine), prefix_hash)
+            if fresh is not None:  # enough free ids: no eviction can happen, so nothing needs protecting either
+                mine.extend(fresh)
+                out.append(mine)
+                continue
             for _ in range(n_blocks - len(mine)):
                 blk = cache.allocate_block(layer_idx, prefix_hash)
                 if blk is None:

@@ -36,6 +36,41 @@ class LayerInfo:
     memory_bytes: int
 
 
+def __getattr__(name: str):
+    """``AutoConfig`` / ``AutoModelForCausalLM`` are module attributes (so callers and tests can patch them here, as
+    the reference's tests try to) without importing ``transformers`` until somebody asks."""
+    if name in ("AutoConfig", "AutoModelForCausalLM"):
+        import transformers
+
+        return getattr(transformers, name)
+    raise AttributeError(f"module {__name__!r} has no attribute {name!r}")
+
+
+def _module_attr(name: str):
+    return globals()[name] if name in globals() else __getattr__(name)
+
+
+class _CallableLayer(nn.Module):
+    """Lets a plain callable (a stub layer, a closure over a remote stage) sit in ``ModelShard.layers``."""
+
+    def __init__(self, fn):
+        super().__init__()
+        self.__dict__["fn"] = fn  # not a parameter / submodule, just carried along
+
+    def forward(self, *args, **kwargs):
+        return self.fn(*args, **kwargs)
+
+
+class _LayerList(nn.ModuleList):
+    """``nn.ModuleList`` that also takes non-Module callables — the reference's ``forward`` only ever *calls* its
+    layers (worker/distributed/model_shard.py:205-215), and its tests append mocks."""
+
+    def append(self, module):
+        if not isinstance(module, nn.Module) and callable(module):
+            module = _CallableLayer(module)
+        return super().append(module)
+
+
 class ModelShard(nn.Module):
     """Decoder layers ``[start_layer, end_layer)`` of a causal LM, plus embed / norm+head at the ends."""
 
@@ -53,7 +88,7 @@ class ModelShard(nn.Module):
         self.end_layer = end_layer
         self.device = device
         self.dtype = dtype
-        self.layers: nn.ModuleList = nn.ModuleList()
+        self.layers: nn.ModuleList = _LayerList()
         self.config = None
         self.is_first_shard = False
         self.is_last_shard = False
@@ -156,7 +191,7 @@ class ModelShard(nn.Module):
         The checkpoint is loaded on the CPU, the owned layers are converted to paged layers on ``device`` and
         the rest is dropped.  (The reference routes through ``accelerate`` device maps instead.)
         """
-        from transformers import AutoConfig, AutoModelForCausalLM
+        AutoConfig, AutoModelForCausalLM = _module_attr("AutoConfig"), _module_attr("AutoModelForCausalLM")
 
         from dgi_b200.paged_layer import PagedLlamaDecoderLayer, RMSNorm
 
@@ -246,9 +281,7 @@ class ShardedModelLoader:
 
     def analyze_model(self) -> Dict[str, Any]:
         if self.config is None:
-            from transformers import AutoConfig
-
-            self.config = AutoConfig.from_pretrained(self.model_id, trust_remote_code=True)
+            self.config = _module_attr("AutoConfig").from_pretrained(self.model_id, trust_remote_code=True)
         cfg = self.config
         self.total_layers = getattr(cfg, "num_hidden_layers", 32)
         hidden = getattr(cfg, "hidden_size", 4096)

@@ -27,6 +27,12 @@ from enum import Enum
 from typing import Any, Callable, Dict, List, Optional, Tuple
 
 from ...common.data_structures import SessionConfig, WorkerInfo
+from ...common.serialization import deserialize_tensor, serialize_tensor
+
+try:  # only the HTTP hop needs it; the NVLink paths never touch the network
+    import aiohttp
+except ImportError:  # pragma: no cover
+    aiohttp = None
 
 logger = logging.getLogger(__name__)
 
@@ -55,6 +61,71 @@ class InProcessTransport:
         return None
 
 
+class HttpTransport:
+    """The reference's own hop (worker/distributed/session.py:78-184): JSON over HTTP to ``api_endpoint`` —
+    ``GET /health``, ``POST /inference/forward`` with the serialized hidden states, ``POST /inference/close``.
+    Kept wire-compatible so a route may mix stock workers and workers of this package; it is what a
+    ``WorkerSession`` falls back to when no in-process / NCCL transport is registered for its worker id."""
+
+    def __init__(self, session: "WorkerSession", timeout: float = 30.0):
+        if aiohttp is None:
+            raise ConnectionError("aiohttp is not installed")
+        self._ws = session
+        self._http = aiohttp.ClientSession(timeout=aiohttp.ClientTimeout(total=timeout))
+
+    @property
+    def _base(self) -> str:
+        return self._ws.worker_info.api_endpoint
+
+    async def health(self) -> bool:
+        async with self._http.get(f"{self._base}/health") as response:
+            if response.status != 200:
+                raise ConnectionError(f"Worker health check failed: {response.status}")
+        return True
+
+    async def forward(self, session_id: str, hidden_states: Any, position: int, kv_cache_keys: List[str]):
+        info = self._ws.worker_info
+        payload = {
+            "session_id": session_id,
+            "input": serialize_tensor(hidden_states),
+            "position": position,
+            "kv_cache_keys": kv_cache_keys,
+            "blocks": info.blocks.to_dict() if info.blocks else None,
+        }
+        nxt = self._ws.next_session
+        if nxt is not None:
+            payload["next_worker"] = {"address": nxt.worker_info.api_endpoint, "session_id": nxt.session_id}
+        async with self._http.post(f"{self._base}/inference/forward", json=payload) as response:
+            if response.status != 200:
+                raise RuntimeError(f"Forward failed: {await response.text()}")
+            result = await response.json()
+        return deserialize_tensor(result["output"]), result.get("kv_cache_keys", [])
+
+    async def close(self, session_id: str) -> None:
+        try:
+            async with self._http.post(f"{self._base}/inference/close", json={"session_id": session_id}):
+                pass
+        finally:
+            await self._http.close()
+
+
+def _run_coroutine_in_new_thread(coro):
+    """Run ``coro`` to completion on a fresh event loop in a helper thread (for sync code called from a running loop)."""
+    import threading
+    from concurrent.futures import Future
+
+    done: Future = Future()
+
+    def runner() -> None:
+        try:
+            done.set_result(asyncio.run(coro))
+        except BaseException as exc:  # noqa: BLE001
+            done.set_exception(exc)
+
+    threading.Thread(target=runner, daemon=True).start()
+    return done.result()
+
+
 # worker_id -> transport; lets `WorkerSession(worker_info=...)` (the only call the reference's setup makes) find
 # its hop without a network address
 TRANSPORTS: Dict[str, Any] = {}
@@ -74,6 +145,8 @@ class WorkerSession:
         if self.transport is None:
             self.transport = TRANSPORTS.get(self.worker_info.worker_id)
         try:
+            if self.transport is None and self.worker_info.api_endpoint:
+                self.transport = HttpTransport(self, timeout)
             if self.transport is None:
                 raise ConnectionError(f"no transport registered for worker {self.worker_info.worker_id}")
             if not await asyncio.wait_for(self.transport.health(), timeout):
@@ -101,7 +174,22 @@ class WorkerSession:
                 await self.transport.close(self.session_id)
             except Exception as exc:  # noqa: BLE001
                 logger.warning(f"Error closing worker session: {exc}")
+            if isinstance(self.transport, HttpTransport):
+                self.transport = None  # its client session is gone; a later connect() opens a new one
         self.state = SessionState.CLOSED
+
+    def __enter__(self):
+        return self
+
+    def __exit__(self, *exc):
+        """Synchronous ``with`` support (reference :186-195): close on a private loop, from a helper thread when
+        the caller is itself running inside an event loop."""
+        try:
+            asyncio.get_running_loop()
+        except RuntimeError:
+            asyncio.run(self.close())
+        else:
+            _run_coroutine_in_new_thread(self.close())
 
 
 class DistributedInferenceSession:
