@@ -317,7 +317,16 @@ int b200_rope_kv_append(void* q, int64_t q_row_stride, const void* k, int64_t k_
                         int64_t v_row_stride, const void* cos_table, const void* sin_table, void* k_pool, void* v_pool,
                         const int64_t* slot_mapping, int n_tok, int Hq, int Hkv, int D, int block_size,
                         int64_t max_blocks, int dtype, void* stream) {
-  return rope_kv_append(q, q_row_stride, k, k_row_stride, v, v_row_stride, cos_table, sin_table, k_pool, v_pool,
+  return rope_kv_append(q, q_row_stride, k, k_row_stride, nullptr, v, v_row_stride, cos_table, sin_table, k_pool,
+                        v_pool, slot_mapping, n_tok, Hq, Hkv, D, block_size, max_blocks, dtype,
+                        static_cast<cudaStream_t>(stream));
+}
+
+int b200_rope_kv_append_prompt(void* q, int64_t q_row_stride, void* k, int64_t k_row_stride, const void* v,
+                               int64_t v_row_stride, const void* cos_table, const void* sin_table, void* k_pool,
+                               void* v_pool, const int64_t* slot_mapping, int n_tok, int Hq, int Hkv, int D,
+                               int block_size, int64_t max_blocks, int dtype, void* stream) {
+  return rope_kv_append(q, q_row_stride, k, k_row_stride, k, v, v_row_stride, cos_table, sin_table, k_pool, v_pool,
                         slot_mapping, n_tok, Hq, Hkv, D, block_size, max_blocks, dtype,
                         static_cast<cudaStream_t>(stream));
 }

@@ -74,7 +74,8 @@ int kv_unpack_layers_wire(void* const* k_pools, void* const* v_pools, int n_laye
 // fused layer pieces (b200_layer_ops.cu)
 int add_rmsnorm(void* out, void* resid_out, const void* x, const void* delta, const void* weight, float eps, int rows,
                 int hidden, int64_t x_stride, int64_t d_stride, int dtype, cudaStream_t s);
-int rope_kv_append(void* q, int64_t q_stride, const void* k, int64_t k_stride, const void* v, int64_t v_stride,
+int rope_kv_append(void* q, int64_t q_stride, const void* k, int64_t k_stride, void* k_rot, const void* v,
+                   int64_t v_stride,
                    const void* cos_t, const void* sin_t, void* k_pool, void* v_pool, const int64_t* slot_mapping,
                    int n_tok, int Hq, int Hkv, int D, int block_size, int64_t max_blocks, int dtype, cudaStream_t s);
 int silu_mul(void* out, const void* gate, const void* up, int64_t rows, int cols, int64_t g_stride, int64_t u_stride,

@@ -103,7 +103,7 @@ add_rmsnorm_kernel(T* __restrict__ out, T* __restrict__ resid_out, const T* __re
 // with its partner vector in the second half (rotate-half pairs d and d + D/2).
 template <typename T>
 __global__ void __launch_bounds__(128)
-rope_append_kernel(T* __restrict__ q, int64_t q_stride, const T* __restrict__ k, int64_t k_stride,
+rope_append_kernel(T* __restrict__ q, int64_t q_stride, const T* k, int64_t k_stride, T* k_rot,
                    const T* __restrict__ v, int64_t v_stride, const T* __restrict__ cos_t, const T* __restrict__ sin_t,
                    T* __restrict__ k_pool, T* __restrict__ v_pool, const int64_t* __restrict__ slot_mapping, int Hq,
                    int Hkv, int D, int block_size, int64_t max_blocks) {
@@ -151,10 +151,17 @@ rope_append_kernel(T* __restrict__ q, int64_t q_stride, const T* __restrict__ k,
         T* dst = q + tok * q_stride + static_cast<int64_t>(head) * D;
         *reinterpret_cast<int4*>(dst + d0) = o_lo.raw;
         *reinterpret_cast<int4*>(dst + D / 2 + d0) = o_hi.raw;
-      } else if (store) {
-        T* dst = k_pool + ((blk * Hkv + (head - Hq)) * block_size + off) * D;
-        *reinterpret_cast<int4*>(dst + d0) = o_lo.raw;
-        *reinterpret_cast<int4*>(dst + D / 2 + d0) = o_hi.raw;
+      } else {
+        if (k_rot != nullptr) {  // prompt pass: the rotated k is also needed densely (may alias k: same thread, read first)
+          T* dense = k_rot + tok * k_stride + static_cast<int64_t>(head - Hq) * D;
+          *reinterpret_cast<int4*>(dense + d0) = o_lo.raw;
+          *reinterpret_cast<int4*>(dense + D / 2 + d0) = o_hi.raw;
+        }
+        if (store) {
+          T* dst = k_pool + ((blk * Hkv + (head - Hq)) * block_size + off) * D;
+          *reinterpret_cast<int4*>(dst + d0) = o_lo.raw;
+          *reinterpret_cast<int4*>(dst + D / 2 + d0) = o_hi.raw;
+        }
       }
     } else if (store) {
       const int h = head - Hq - Hkv;
@@ -228,8 +235,8 @@ int add_rmsnorm(void* out, void* resid_out, const void* x, const void* delta, co
   });
 }
 
-int rope_kv_append(void* q, int64_t q_stride, const void* k, int64_t k_stride, const void* v, int64_t v_stride,
-                   const void* cos_t, const void* sin_t, void* k_pool, void* v_pool, const int64_t* slot_mapping,
+int rope_kv_append(void* q, int64_t q_stride, const void* k, int64_t k_stride, void* k_rot, const void* v,
+                   int64_t v_stride, const void* cos_t, const void* sin_t, void* k_pool, void* v_pool, const int64_t* slot_mapping,
                    int n_tok, int Hq, int Hkv, int D, int block_size, int64_t max_blocks, int dtype, cudaStream_t s) {
   const int es = dtype_size(dtype);
   if (es == 0) return fail(B200_EINVAL, "b200_rope_kv_append: unsupported dtype %d", dtype);
@@ -248,7 +255,7 @@ int rope_kv_append(void* q, int64_t q_stride, const void* k, int64_t k_stride, c
     const int threads = 128;
     dim3 grid(n_tok, (n_items + threads - 1) / threads);
     rope_append_kernel<T><<<grid, threads, 0, s>>>(static_cast<T*>(q), q_stride, static_cast<const T*>(k), k_stride,
-                                                static_cast<const T*>(v), v_stride, static_cast<const T*>(cos_t),
+                                                static_cast<T*>(k_rot), static_cast<const T*>(v), v_stride, static_cast<const T*>(cos_t),
                                                 static_cast<const T*>(sin_t), static_cast<T*>(k_pool),
                                                 static_cast<T*>(v_pool), slot_mapping, Hq, Hkv, D, block_size, max_blocks);
     return check_launch("b200_rope_kv_append");

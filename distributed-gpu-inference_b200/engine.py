@@ -199,12 +199,14 @@ class PagedDecodeEngine:
         self._borrowed = False
 
     def adopt_sequences(self, per_seq_blocks: Sequence[Sequence[List[List[CacheBlock]]]],
-                        context_lens: Sequence[int]) -> None:
+                        context_lens: Sequence[int], table_rows: Optional[torch.Tensor] = None) -> None:
         """Decode over blocks the caller allocated from this engine's pools and somebody else filled — the receiving
         side of a prefill→decode hand-off.  ``per_seq_blocks[b][shard]`` is what ``KVCachePool.allocate_sequence``
         returned; ``context_lens[b]`` tokens of KV are already in them.  The blocks stay the caller's: ``release``
         (and the next ``allocate`` / ``adopt_sequences``) drops them without freeing.  Captured graphs are kept when
-        the batch size is unchanged, since tables and lengths are read from the static buffers at replay."""
+        the batch size is unchanged, since tables and lengths are read from the static buffers at replay.
+        ``table_rows`` (int32 ``[batch, <= blocks_per_seq]`` on the device): the block-table rows of these sequences
+        if the caller already has them — skips rebuilding and cross-checking them from the block objects."""
         batch = len(per_seq_blocks)
         if batch > self.max_batch or batch != len(context_lens):
             raise ValueError("batch beyond the engine's capacity / lengths do not match")
@@ -212,6 +214,9 @@ class PagedDecodeEngine:
         self.release()
         rows = []
         for b, per_shard in enumerate(per_seq_blocks):
+            self._seq_blocks[b] = list(per_shard)
+            if table_rows is not None:
+                continue
             row = KVCachePool.block_table(per_shard[0][0])
             if len(row) > self.blocks_per_seq or context_lens[b] > len(row) * self.block_size:
                 raise ValueError("sequence does not fit its blocks / the engine's table")
@@ -219,12 +224,20 @@ class PagedDecodeEngine:
                 for layer_blocks in shard_blocks:
                     if KVCachePool.block_table(layer_blocks) != row:
                         raise RuntimeError("layers disagree on block slots; per-layer tables are not supported here")
-            self._seq_blocks[b] = list(per_shard)
             rows.append(row + [0] * (self.blocks_per_seq - len(row)))
         self._borrowed = True
-        self.block_tables[:batch].copy_(torch.tensor(rows, dtype=torch.int32))
+        if table_rows is not None:
+            if table_rows.shape[0] != batch or table_rows.shape[1] > self.blocks_per_seq:
+                raise ValueError("table_rows does not match the batch / the engine's table")
+            self.block_tables[:batch, :table_rows.shape[1]].copy_(table_rows)
+        else:
+            self.block_tables[:batch].copy_(torch.tensor(rows, dtype=torch.int32))
         self.context_lens.zero_()
-        self.context_lens[:batch].copy_(torch.tensor(list(context_lens), dtype=torch.int32))
+        if len(set(context_lens)) == 1:
+            if context_lens[0]:
+                self.context_lens[:batch].fill_(int(context_lens[0]))  # no host→device copy, no stream sync
+        else:
+            self.context_lens[:batch].copy_(torch.tensor(list(context_lens), dtype=torch.int32))
         self._host_lens = [int(n) for n in context_lens] + [0] * (self.max_batch - batch)
         self.batch = batch
         if not same_shape:

@@ -113,10 +113,12 @@ def add_rmsnorm(x: torch.Tensor, weight: torch.Tensor, eps: float, delta: Option
 
 
 def rope_kv_append(q: torch.Tensor, k: torch.Tensor, v: torch.Tensor, cos: torch.Tensor, sin: torch.Tensor,
-                   k_pool: torch.Tensor, v_pool: torch.Tensor, slot_mapping: torch.Tensor) -> None:
+                   k_pool: torch.Tensor, v_pool: torch.Tensor, slot_mapping: torch.Tensor,
+                   rotate_k_in_place: bool = False) -> None:
     """Rotate ``q [n, Hq, D]`` in place, rotate ``k [n, Hkv, D]`` and scatter it and ``v`` into the pools.
 
-    ``cos`` / ``sin``: contiguous ``[n, D]`` tables in the storage dtype.
+    ``cos`` / ``sin``: contiguous ``[n, D]`` tables in the storage dtype.  ``rotate_k_in_place``: also overwrite
+    ``k`` with its rotated value (prompt pass, where the new tokens attend to each other densely).
     """
     _need_cuda(q, k, v, cos, sin, k_pool, v_pool, slot_mapping)
     max_blocks, Hkv, bs, D = _pool_dims(k_pool)
@@ -127,7 +129,8 @@ def rope_kv_append(q: torch.Tensor, k: torch.Tensor, v: torch.Tensor, cos: torch
         raise ValueError("slot_mapping must be a contiguous int64 [n_tok]")
     if not (q.dtype == k.dtype == v.dtype == cos.dtype == sin.dtype == k_pool.dtype):
         raise TypeError("q, k, v, cos, sin and the pools must share one dtype")
-    rc = _lib.load().b200_rope_kv_append(
+    fn = _lib.load().b200_rope_kv_append_prompt if rotate_k_in_place else _lib.load().b200_rope_kv_append
+    rc = fn(
         q.data_ptr(), _row_stride(q, Hq, D), k.data_ptr(), _row_stride(k, Hkv, D), v.data_ptr(), _row_stride(v, Hkv, D),
         cos.data_ptr(), sin.data_ptr(), k_pool.data_ptr(), v_pool.data_ptr(), slot_mapping.data_ptr(), n, Hq, Hkv, D, bs,
         max_blocks, _dtype_id(k_pool), _stream())

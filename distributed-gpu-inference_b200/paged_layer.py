@@ -265,12 +265,11 @@ class PagedLlamaDecoderLayer(nn.Module):
                         st.max_context_len, num_splits=st.num_splits, workspace=st.workspace, flags=st.attn_flags,
                     ).view(B, 1, Hq * D)
         else:
-            # prompt pass: the rotated k is also needed densely for the causal attention among the new tokens
-            cos4, sin4 = cos.unsqueeze(2), sin.unsqueeze(2)  # broadcast over heads: [B, T, 1, D]
-            q = q * cos4 + _rotate_half(q) * sin4
-            k = k * cos4 + _rotate_half(k) * sin4
-            ops.kv_append(k.reshape(B * T, Hkv, D), v.reshape(B * T, Hkv, D), past_key_value.k_pool,
-                          past_key_value.v_pool, st.slot_mapping)
+            # prompt pass: RoPE on q and k in place + the append of k / v in one launch; the rotated k stays dense
+            # for the causal attention among the new tokens
+            ops.rope_kv_append(q.flatten(0, 1), k.flatten(0, 1), v.flatten(0, 1), cos.reshape(B * T, D),
+                               sin.reshape(B * T, D), past_key_value.k_pool, past_key_value.v_pool, st.slot_mapping,
+                               rotate_k_in_place=True)
             if st.past_len > 0:
                 # prompt pass that continues a cached prefix: the new tokens also attend to the `past_len` tokens
                 # already sitting in the (shared) blocks, read back densely through the block table

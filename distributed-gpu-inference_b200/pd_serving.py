@@ -72,19 +72,26 @@ class PDPairWorker:
         peer_mail = self._mail_handle.get_buffer(self.peer, (words,), torch.int32)
         self._peer_tokens = peer_mail[n_tab:].view(torch.int64).view(slot_sets, max_batch)
         self._side = torch.cuda.Stream(device=dev)
+        # Both roles take their blocks ONCE: `slot_sets` sets of max_batch sequences, reused wave after wave (no
+        # per-wave allocator traffic — 16 sequences x 4k tokens x 32 layers are 131k block objects).
         self._slot_blocks: List[List] = []
+        self._my_tables = torch.empty((slot_sets, max_batch, self.n_blk), dtype=torch.int32, device=dev)
+        pool: KVCachePool = self.endpoint.pool
+        for s in range(slot_sets):
+            seqs = [[pool.allocate_sequence(total)] for _ in range(max_batch)]
+            for per_shard in seqs:
+                rows0 = KVCachePool.block_table(per_shard[0][0])
+                for li, layer_blocks in enumerate(per_shard[0]):
+                    if KVCachePool.block_table(layer_blocks) != rows0:
+                        raise RuntimeError("layers disagree on block slots")
+                    pool.layer(li).pin(b.block_id for b in layer_blocks)  # never an eviction candidate
+            self._slot_blocks.append(seqs)
+            rows = [KVCachePool.block_table(per_shard[0][0]) for per_shard in seqs]
+            self._my_tables[s].copy_(torch.tensor(rows, dtype=torch.int32))
+        self._set_pushed: List[Optional[torch.cuda.Event]] = [None] * slot_sets
         if not self.is_prefill:
-            pool: KVCachePool = self.endpoint.pool
-            for s in range(slot_sets):
-                seqs = [[pool.allocate_sequence(total)] for _ in range(max_batch)]
-                for per_shard in seqs:
-                    for li, layer_blocks in enumerate(per_shard[0]):
-                        pool.layer(li).pin(b.block_id for b in layer_blocks)  # never an eviction candidate
-                self._slot_blocks.append(seqs)
-                rows = [KVCachePool.block_table(per_shard[0][0]) for per_shard in seqs]
-                self._tables[s].copy_(torch.tensor(rows, dtype=torch.int32))
             peer_tables = peer_mail[:n_used].view(slot_sets, max_batch, self.n_blk)
-            peer_tables.copy_(self._tables)  # publish where each slot set's blocks are
+            peer_tables.copy_(self._my_tables)  # publish where each slot set's blocks are
         torch.cuda.synchronize()
         self.handle.barrier()
         torch.cuda.synchronize()
@@ -98,9 +105,10 @@ class PDPairWorker:
         n, P = prompt_ids.shape
         if n > self.B or P != self.P:
             raise ValueError("wave does not match the pair's shape")
-        self._side.synchronize()  # the previous wave's pushes read blocks that allocate() is about to free
-        eng.allocate(n, P)
         cur = torch.cuda.current_stream()
+        if self._set_pushed[s] is not None:
+            cur.wait_event(self._set_pushed[s])  # the pushes of wave - slot_sets still read these blocks
+        eng.adopt_sequences(self._slot_blocks[s][:n], [0] * n, table_rows=self._my_tables[s, :n])
         if wave >= self.sets:
             with torch.cuda.stream(self._side):
                 self.handle.wait_signal(self.peer, FREE)  # the decode rank is done with this slot set
@@ -126,6 +134,8 @@ class PDPairWorker:
                     events.setdefault("prefill_end", []).append((wave, lo, hi, done))
                     events.setdefault("push", []).append((wave, lo, hi, p0, p1))
         with torch.cuda.stream(self._side):
+            self._set_pushed[s] = torch.cuda.Event()
+            self._set_pushed[s].record(self._side)
             self.handle.put_signal(self.peer, READY)
 
     # ---- decode side --------------------------------------------------------------------------------------
@@ -139,7 +149,7 @@ class PDPairWorker:
         if events is not None:
             e0 = torch.cuda.Event(enable_timing=True)
             e0.record()
-        eng.adopt_sequences(self._slot_blocks[s][:n], [self.P] * n)
+        eng.adopt_sequences(self._slot_blocks[s][:n], [self.P] * n, table_rows=self._my_tables[s, :n])
         out = torch.empty((n, self.n_new), dtype=torch.int64, device=eng.device)
         out[:, 0] = self._tokens[s, :n]
         eng.ids_buf[:n, 0].copy_(out[:, 0])

@@ -200,6 +200,12 @@ int b200_rope_kv_append(void* q, int64_t q_row_stride, const void* k, int64_t k_
                         const void* v, int64_t v_row_stride, const void* cos_table, const void* sin_table,
                         void* k_pool, void* v_pool, const int64_t* slot_mapping, int n_tok,
                         int Hq, int Hkv, int D, int block_size, int64_t max_blocks, int dtype, void* stream);
+/* Prompt-pass form of b200_rope_kv_append: k is rotated IN PLACE as well (the causal attention among the new
+ * tokens needs the rotated k densely), besides being scattered into the pool.  Same arithmetic, same arguments. */
+int b200_rope_kv_append_prompt(void* q, int64_t q_row_stride, void* k, int64_t k_row_stride,
+                               const void* v, int64_t v_row_stride, const void* cos_table, const void* sin_table,
+                               void* k_pool, void* v_pool, const int64_t* slot_mapping, int n_tok,
+                               int Hq, int Hkv, int D, int block_size, int64_t max_blocks, int dtype, void* stream);
 int b200_silu_mul(void* out, const void* gate, const void* up, int64_t rows, int cols,
                   int64_t gate_row_stride, int64_t up_row_stride, int dtype, void* stream);
 

@@ -269,9 +269,22 @@ def test_rope_kv_append_bit_exact_vs_torch_recipe(dtype, Hq, Hkv, D):
     k_pool, v_pool = _pools(max_blocks, Hkv, bs, D, dtype, zero=True)
     k_ref, v_ref = k_pool.clone(), v_pool.clone()
     R.append_ref(k_want, v.clone(), k_ref, v_ref, slots)
+    k_before = k.clone()
     ops.rope_kv_append(q, k, v, cos, sin, k_pool, v_pool, slots)
     assert torch.equal(_bits(q), _bits(q_want))
     assert torch.equal(_bits(k_pool), _bits(k_ref)) and torch.equal(_bits(v_pool), _bits(v_ref))
+    assert torch.equal(_bits(k), _bits(k_before))  # decode form leaves k alone
+    # prompt form: the same, and k is rotated in place too (also for the token whose slot is skipped)
+    q2 = qkv2 = None
+    qkv2 = torch.randn((n, (Hq + 2 * Hkv) * D), generator=torch.Generator(device=DEV).manual_seed(21), device=DEV).to(dtype)
+    q2 = qkv2[:, :Hq * D].view(n, Hq, D)
+    k2 = qkv2[:, Hq * D:(Hq + Hkv) * D].view(n, Hkv, D)
+    v2 = qkv2[:, (Hq + Hkv) * D:].view(n, Hkv, D)
+    k_pool2, v_pool2 = _pools(max_blocks, Hkv, bs, D, dtype, zero=True)
+    ops.rope_kv_append(q2, k2, v2, cos, sin, k_pool2, v_pool2, slots, rotate_k_in_place=True)
+    assert torch.equal(_bits(q2), _bits(q_want)) and torch.equal(_bits(k2), _bits(k_want))
+    assert torch.equal(_bits(k_pool2), _bits(k_ref)) and torch.equal(_bits(v_pool2), _bits(v_ref))
+    assert torch.equal(_bits(v2), _bits(v))
 
 
 @pytest.mark.parametrize("dtype", [torch.bfloat16, torch.float16, torch.float32])

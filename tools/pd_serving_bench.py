@@ -90,10 +90,8 @@ def main():
         mine = [i for i in range(W) if i % 2 == w.me]
         marks = []
         for i in mine:
-            if w.is_prefill:
-                eng.allocate(B, P + n_new)
-            else:  # this rank's blocks are all in its slot sets: serve the wave out of one of them
-                eng.adopt_sequences(w._slot_blocks[i % w.sets], [0] * B)
+            # this rank's blocks are all in its slot sets: serve the wave out of one of them
+            eng.adopt_sequences(w._slot_blocks[i % w.sets], [0] * B, table_rows=w._my_tables[i % w.sets, :B])
             first = torch.empty((B,), dtype=torch.int64, device=dev)
             for lo in range(0, B, a.prefill_chunk):
                 hi = min(B, lo + a.prefill_chunk)
