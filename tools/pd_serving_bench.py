@@ -88,7 +88,7 @@ def main():
     def hybrid_round(record):
         t0 = start()
         mine = [i for i in range(W) if i % 2 == w.me]
-        marks = []
+        marks, sums = [], []
         for i in mine:
             # this rank's blocks are all in its slot sets: serve the wave out of one of them
             eng.adopt_sequences(w._slot_blocks[i % w.sets], [0] * B, table_rows=w._my_tables[i % w.sets, :B])
@@ -102,8 +102,11 @@ def main():
             eng.ids_buf[:B, 0].copy_(first)
             d0 = torch.cuda.Event(enable_timing=True)
             d0.record()
+            csum = first.sum()
             for _ in range(1, n_new):
                 eng.decode_step_device()
+                csum = csum + eng.next_tokens[:B].sum()
+            sums.append(csum)
             d1 = torch.cuda.Event(enable_timing=True)
             d1.record()
             marks.append(("d", d0, d1))
@@ -114,6 +117,7 @@ def main():
             out["tpot_ms"] = [m[1].elapsed_time(m[2]) / (n_new - 1) for m in marks if m[0] == "d"]
             out["e2e_ms"] = [t0.elapsed_time(m[2]) for m in marks if m[0] == "d" for _ in range(B)]
             out["end_ms"] = max(t0.elapsed_time(m[2]) for m in marks if m[0] == "d")
+            out["checksum"] = int(sum(int(c) for c in sums))
         return out
 
     results = {}
@@ -140,7 +144,7 @@ def main():
                 nbytes = max(g.get("migration_bytes", 0) for g in gathered)
                 res["avg_migration_ms"] = statistics.mean(mig)
                 res["migration_GBps_per_pair"] = nbytes / (statistics.mean(mig) * 1e-3) / 1e9
-                res["checksum"] = sum(g.get("checksum", 0) for g in gathered)
+            res["checksum"] = sum(g.get("checksum", 0) for g in gathered)  # sum of all generated token ids
             results[mode] = res
             print(json.dumps(res), flush=True)
     dist.barrier()
