@@ -182,7 +182,7 @@ def run_reference(args, workload, rank, world):
     shape, batch, ctx = workload["shape"], workload["batch"], workload["context"]
     big = shape == "70b"
     res = cpu_reference_tokens_per_s(shape, batch, ctx, args.steps, args.warmup, sample_layers=1 if big else 2,
-                                     sample_batch=16 if big else 0)
+                                     sample_batch=16 if big else min(batch, 64))
     line = {
         "impl": "reference",
         "metric": "decode_tokens_per_s",
@@ -212,10 +212,13 @@ def workload_for(args):
     if args.workload:
         name = args.workload
     else:
-        name = "cfg2" if args.gpus == 1 else "cfg4"
+        name = "cfg2" if args.gpus == 1 else "cfg2pp"
     table = {
         "cfg2": dict(shape="8b", batch=64, context=2048, scaling="weak",
                      name="configs[1]: Llama-3-8B-shape random-init bf16, 1xB200, block 16, batch 64, context 2k, decode"),
+        "cfg2pp": dict(shape="8b", batch=64 * args.gpus, context=2048, scaling="weak",
+                       name=f"configs[1] weak-scaled: Llama-3-8B-shape random-init bf16, layer ranges over {args.gpus} "
+                            f"B200, block 16, batch 64 per GPU = {64 * args.gpus}, context 2k, decode"),
         "cfg4": dict(shape="70b", batch=128, context=4096, scaling="strong",
                      name=f"configs[3]: Llama-3-70B-shape layer-sharded over {args.gpus} B200, batch 128, context 4k, decode"),
         "cfg5": dict(shape="8b", batch=8, context=32768, scaling="weak",
@@ -469,6 +472,8 @@ def main():
                     help="keep q/k/v and gate/up as separate GEMMs (the reference's GEMM shapes)")
     ap.add_argument("--micro-batches", type=int, default=0, help="pipeline micro-batches (default: one per rank)")
     ap.add_argument("--real-prefill", action="store_true", help="multi-GPU: run a real prompt pass instead of synthetic KV")
+    ap.add_argument("--no-cfg4", action="store_true",
+                    help="multi-GPU default run: skip the 70B-shape (configs[3]) leg that is appended to the line")
     args = ap.parse_args()
     if args.warmup < 3:
         args.warmup = 3
@@ -483,8 +488,13 @@ def main():
     else:
         from dgi_b200.bench_pipeline import run_pipeline  # multi-GPU layer-sharded decode
 
+        extra = None
+        if not args.workload and not args.no_cfg4 and not args.batch and not args.context:
+            args.workload = "cfg4"  # the north-star multi-GPU configuration rides along in the same line
+            extra = workload_for(args)
+            args.workload = ""
         run_pipeline(args, workload, SHAPES, ShapeConfig, ClockSampler, measured_peaks, cpu_reference_tokens_per_s,
-                     cpu_handoff=cpu_handoff_reference)
+                     cpu_handoff=cpu_handoff_reference, extra_workload=extra)
 
 
 if __name__ == "__main__":

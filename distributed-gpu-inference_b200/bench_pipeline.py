@@ -21,7 +21,8 @@ from .pipeline import LayerPipeline, make_pipeline_groups
 from .worker.distributed.model_shard import ModelShard, get_layer_range_for_worker
 
 
-def run_pipeline(args, workload, SHAPES, ShapeConfig, ClockSampler, measured_peaks, cpu_reference, cpu_handoff=None):
+def run_pipeline(args, workload, SHAPES, ShapeConfig, ClockSampler, measured_peaks, cpu_reference, cpu_handoff=None,
+                 extra_workload=None):
     rank = int(os.environ.get("RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))
     local = int(os.environ.get("LOCAL_RANK", str(rank)))
@@ -36,6 +37,19 @@ def run_pipeline(args, workload, SHAPES, ShapeConfig, ClockSampler, measured_pea
     dist.init_process_group("nccl", device_id=torch.device(dev))
     try:
         line = _run(args, workload, SHAPES, ShapeConfig, ClockSampler, measured_peaks, rank, world, local, dev)
+        if extra_workload is not None:
+            import gc
+
+            gc.collect()
+            torch.cuda.empty_cache()
+            more = _run(args, extra_workload, SHAPES, ShapeConfig, ClockSampler, measured_peaks, rank, world, local,
+                        dev, with_pd=False)
+            if line is not None and more is not None:
+                keep = ("value", "unit", "ms_per_step", "scaling", "e2e", "gpu_launches", "roofline", "clocks")
+                line["north_star_cfg4"] = {"workload": more["config"]["workload"],
+                                           "parallelism": more["config"]["parallelism"],
+                                           "bound_tokens_per_s": more["config"].get("bound_tokens_per_s"),
+                                           **{k: more[k] for k in keep}}
         if line is not None and cpu_handoff is not None and isinstance(line.get("pd_transfer"), dict):
             line["pd_transfer"]["cpu_reference_handoff"] = cpu_handoff()  # bench.py's host-side baseline leg
         if line is not None:
@@ -95,7 +109,7 @@ def _measure_pd_handoff(rank, world, dev):
         return {"unavailable": repr(exc)}
 
 
-def _run(args, workload, SHAPES, ShapeConfig, ClockSampler, measured_peaks, rank, world, local, dev):
+def _run(args, workload, SHAPES, ShapeConfig, ClockSampler, measured_peaks, rank, world, local, dev, with_pd=True):
     cfg = ShapeConfig(**SHAPES[workload["shape"]])
     B, ctx = workload["batch"], workload["context"]
     K, W = args.steps, args.warmup
@@ -164,12 +178,19 @@ def _run(args, workload, SHAPES, ShapeConfig, ClockSampler, measured_peaks, rank
     attn_ms = statistics.mean(a.elapsed_time(b) for a, b in ev)
     ctx_now = P + 2 * (K + W) + 1
     algo = mb * ctx_now * 2 * eng.Hkv * eng.D * 2 + 2 * mb * eng.Hq * eng.D * 2
-    pd = _measure_pd_handoff(rank, world, dev)
+    pd = _measure_pd_handoff(rank, world, dev) if with_pd else None
     if rank != 0:
         return None
     peaks, kind = measured_peaks()
     achieved = algo / (attn_ms * 1e-3) / 1e9
     layers_here = end - start
+    # HBM bound of layer-range decode: every micro-batch re-streams the stage's weights, the KV is read once per step
+    es = 2
+    per_layer_w = (cfg.hidden_size * (eng.Hq + 2 * eng.Hkv) * eng.D + cfg.hidden_size * eng.Hq * eng.D
+                   + 3 * cfg.hidden_size * cfg.intermediate_size) * es
+    w_total = per_layer_w * cfg.num_hidden_layers + cfg.vocab_size * cfg.hidden_size * es
+    kv_total = B * ctx_now * 2 * eng.Hkv * eng.D * es * cfg.num_hidden_layers
+    bound = B * world * peaks["hbm_gbs"] * 1e9 / (M * w_total + kv_total)
     per_step = M * layers_here * (4 + (1 if eng.num_splits > 1 else 0))  # rank 0's kernels from this repo
     line = {
         "metric": "decode_tokens_per_s",
@@ -194,9 +215,12 @@ def _run(args, workload, SHAPES, ShapeConfig, ClockSampler, measured_peaks, rank
             "l2": "inputs larger than L2 (each rank streams its weights once per micro-batch plus its KV per step)",
             "attn_splits": eng.num_splits,
             "setup_s": round(setup_s, 1),
-            "note": ("the 70B shape (141 GB of bf16 weights + 172 GB of KV at this batch and context) does not fit one "
-                     "GPU, so --gpus 1 runs config 2 (8B shape); compare the N = 2 / 4 / 8 lines among themselves. "
-                     "Bound for layer-range decode: B*N*BW / (M*W + KV) with M = N micro-batches"),
+            "bound_tokens_per_s": bound,
+            "frac_of_bound": (B * K / (dev_ms * 1e-3)) / bound,
+            "note": ("bound for layer-range decode = B*N*BW / (M*W + KV) with M micro-batches, BW the measured HBM "
+                     "copy peak.  The N = 1 line (config 2) and the weak-scaled N > 1 lines run the same model and "
+                     "the same per-GPU batch, so they compare directly; the 70B shape of configs[3] (141 GB of "
+                     "weights + 172 GB of KV, does not fit one GPU) is under north_star_cfg4"),
         },
         "clocks": clocks,
         "e2e": {"value": B * K / (e2e_ms * 1e-3), "unit": "tokens/s", "h2d_bytes_per_step": B * 8,

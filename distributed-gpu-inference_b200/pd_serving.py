@@ -123,7 +123,9 @@ class PDPairWorker:
                 p0 = torch.cuda.Event(enable_timing=True) if events is not None else None
                 if p0 is not None:
                     p0.record(self._side)
-                src = eng.block_tables[lo:hi, :self.n_blk_prompt].reshape(-1).contiguous()
+                # the set's own static table, NOT eng.block_tables: the main stream may already be adopting the
+                # next wave (and rewriting the engine's table) when this runs
+                src = self._my_tables[s, lo:hi, :self.n_blk_prompt].reshape(-1).contiguous()
                 dst = dst_tables[lo:hi, :self.n_blk_prompt].reshape(-1).contiguous()
                 self.endpoint.push(src, dst, self.peer)
                 self._peer_tokens[s, lo:hi].copy_(first)

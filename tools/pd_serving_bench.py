@@ -146,6 +146,8 @@ def main():
                 res["migration_GBps_per_pair"] = nbytes / (statistics.mean(mig) * 1e-3) / 1e9
             res["checksum"] = sum(g.get("checksum", 0) for g in gathered)  # sum of all generated token ids
             results[mode] = res
+            if mode == "hybrid":  # same prompts, same kernels: the two modes must generate the same tokens
+                res["tokens_match_pd_mode"] = res["checksum"] == results["pd"]["checksum"]
             print(json.dumps(res), flush=True)
     dist.barrier()
     dist.destroy_process_group()
