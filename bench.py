@@ -260,7 +260,20 @@ def cpu_handoff_reference(layers: int = 2, n_blocks: int = 256):
     t0 = time.perf_counter()
     moved = H.handoff_sequence(src_k, src_v, st, dst_k, dst_v, dt)
     sec = time.perf_counter() - t0
+    # the device ops' own definition on the host: index_select (pack) and index_copy_ (unpack), oracle/paged_ref.py
+    from oracle import paged_ref as R
+
+    tbl = torch.tensor(st, dtype=torch.int64)
+    t0 = time.perf_counter()
+    packed = [R.pack_ref(k, v, tbl) for k, v in zip(src_k, src_v)]
+    t1 = time.perf_counter()
+    for pk, k, v in zip(packed, dst_k, dst_v):
+        R.unpack_ref(pk, k, v, tbl)
+    t2 = time.perf_counter()
+    nbytes = 2 * sum(p.numel() * p.element_size() for p in packed)  # read + written, as for the GPU figures
     return {"GBps": moved / sec / 1e9, "kind": "port", "cores": 1,
+            "cpu_pack_GBps": nbytes / (t1 - t0) / 1e9, "cpu_unpack_GBps": nbytes / (t2 - t1) / 1e9,
+            "cpu_pack_threads": torch.get_num_threads(),
             "sample": f"{layers} of 32 layers x {n_blocks} blocks x 64 KiB = {moved / 2**20:.0f} MiB on the wire "
                       f"(fp16 bytes), host serializer per block, {sec:.2f} s"}
 

@@ -162,6 +162,59 @@ def attn_workspace_bytes(B: int, Hq: int, D: int, num_splits: int) -> int:
     return _lib.load().b200_paged_decode_attn_workspace(B, Hq, D, num_splits)
 
 
+def _attn_args(q, k_pool, v_pool, block_tables, context_lens, out):
+    """Shared checks of the attention entry points; returns ``(dims, q_stride, table_stride, out)``."""
+    _need_cuda(q, k_pool, v_pool, block_tables, context_lens)
+    max_blocks, Hkv, bs, D = _pool_dims(k_pool)
+    if v_pool.shape != k_pool.shape or v_pool.dtype != k_pool.dtype or not v_pool.is_contiguous():
+        raise ValueError("k_pool and v_pool must match")
+    if q.dtype != k_pool.dtype:
+        raise TypeError("q dtype must equal the pool dtype")
+    B, Hq = q.shape[0], q.shape[1]
+    q_stride = _row_stride(q, Hq, D)
+    if block_tables.dtype != torch.int32 or block_tables.dim() != 2 or block_tables.shape[0] != B:
+        raise ValueError("block_tables must be int32 [B, n]")
+    if block_tables.stride(1) != 1 and block_tables.shape[1] > 1:
+        raise ValueError("block_tables rows must be contiguous")
+    if context_lens.dtype != torch.int32 or context_lens.shape != (B,) or not context_lens.is_contiguous():
+        raise ValueError("context_lens must be a contiguous int32 [B]")
+    if out is None:
+        out = torch.empty((B, Hq, D), dtype=q.dtype, device=q.device)
+    elif tuple(out.shape) != (B, Hq, D) or not out.is_contiguous() or out.dtype != q.dtype or not out.is_cuda:
+        raise ValueError("out must be a contiguous CUDA [B, Hq, D] tensor of q's dtype")
+    table_stride = block_tables.stride(0) if B > 1 else block_tables.shape[1]
+    return (B, Hq, Hkv, D, bs, max_blocks), q_stride, table_stride, out
+
+
+def _split_workspace(lib, B, Hq, D, n_splits, workspace, device, always=False):
+    """``(ptr, bytes, tensor)`` of the split-K scratch: the caller's, or one from torch's caching allocator."""
+    if n_splits <= 1 and not always:
+        return 0, 0, None
+    need = max(16, lib.b200_paged_decode_attn_workspace(B, Hq, D, n_splits))
+    if workspace is None:
+        workspace = torch.empty(need, dtype=torch.uint8, device=device)
+    elif not workspace.is_cuda:
+        raise _lib.B200LibraryError("workspace must be a CUDA tensor")
+    return workspace.data_ptr(), workspace.numel() * workspace.element_size(), workspace
+
+
+class _timed:
+    """Brackets a launch with CUDA events when ``ATTN_EVENTS`` is a list (bench instrumentation), else does nothing."""
+
+    def __enter__(self):
+        self.events = ATTN_EVENTS
+        if self.events is not None:
+            self.ev0, self.ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            self.ev0.record()
+        return self
+
+    def __exit__(self, *exc):
+        if self.events is not None:
+            self.ev1.record()
+            self.events.append((self.ev0, self.ev1))
+        return False
+
+
 def paged_decode_attention(
     q: torch.Tensor,
     k_pool: torch.Tensor,
@@ -182,49 +235,20 @@ def paged_decode_attention(
     ``workspace`` (any dtype, CUDA) is needed when more than one split is used; when it is ``None`` and
     ``num_splits`` is 0 a workspace is taken from torch's caching allocator.
     """
-    _need_cuda(q, k_pool, v_pool, block_tables, context_lens)
-    max_blocks, Hkv, bs, D = _pool_dims(k_pool)
-    if v_pool.shape != k_pool.shape or v_pool.dtype != k_pool.dtype or not v_pool.is_contiguous():
-        raise ValueError("k_pool and v_pool must match")
-    if q.dtype != k_pool.dtype:
-        raise TypeError("q dtype must equal the pool dtype")
-    B, Hq = q.shape[0], q.shape[1]
-    q_stride = _row_stride(q, Hq, D)
-    if block_tables.dtype != torch.int32 or block_tables.dim() != 2 or block_tables.shape[0] != B:
-        raise ValueError("block_tables must be int32 [B, n]")
-    if block_tables.stride(1) != 1 and block_tables.shape[1] > 1:
-        raise ValueError("block_tables rows must be contiguous")
-    if context_lens.dtype != torch.int32 or context_lens.shape != (B,) or not context_lens.is_contiguous():
-        raise ValueError("context_lens must be a contiguous int32 [B]")
-    if out is None:
-        out = torch.empty((B, Hq, D), dtype=q.dtype, device=q.device)
-    elif out.shape != (B, Hq, D) or not out.is_contiguous() or out.dtype != q.dtype:
-        raise ValueError("out must be a contiguous [B, Hq, D] tensor of q's dtype")
-    if scale is None:
-        scale = float(D) ** -0.5
+    (B, Hq, Hkv, D, bs, max_blocks), q_stride, table_stride, out = _attn_args(q, k_pool, v_pool, block_tables,
+                                                                               context_lens, out)
     lib = _lib.load()
     dt = _dtype_id(k_pool)
     if num_splits == 0:
         num_splits = lib.b200_paged_decode_attn_plan(B, Hq, Hkv, D, bs, max_context_len, dt)
-    ws_ptr, ws_bytes = 0, 0
-    if num_splits > 1:
-        need = lib.b200_paged_decode_attn_workspace(B, Hq, D, num_splits)
-        if workspace is None:
-            workspace = torch.empty(need, dtype=torch.uint8, device=q.device)
-        ws_ptr, ws_bytes = workspace.data_ptr(), workspace.numel() * workspace.element_size()
-    table_stride = block_tables.stride(0) if B > 1 else block_tables.shape[1]
-    events = ATTN_EVENTS
-    if events is not None:
-        ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-        ev0.record()
-    rc = lib.b200_paged_decode_attn(
-        out.data_ptr(), q.data_ptr(), q_stride, k_pool.data_ptr(), v_pool.data_ptr(), block_tables.data_ptr(),
-        table_stride, context_lens.data_ptr(), B, Hq, Hkv, D, bs, max_blocks, float(scale), int(max_context_len),
-        int(num_splits), ws_ptr, ws_bytes, dt, int(flags), _stream(),
-    )
-    if events is not None:
-        ev1.record()
-        events.append((ev0, ev1))
+    ws_ptr, ws_bytes, _ws = _split_workspace(lib, B, Hq, D, num_splits, workspace, q.device)
+    with _timed():
+        rc = lib.b200_paged_decode_attn(
+            out.data_ptr(), q.data_ptr(), q_stride, k_pool.data_ptr(), v_pool.data_ptr(), block_tables.data_ptr(),
+            table_stride, context_lens.data_ptr(), B, Hq, Hkv, D, bs, max_blocks,
+            float(D) ** -0.5 if scale is None else float(scale), int(max_context_len), int(num_splits), ws_ptr, ws_bytes,
+            dt, int(flags), _stream(),
+        )
     _lib.check(rc, "b200_paged_decode_attn")
     return out
 
@@ -257,39 +281,27 @@ def rope_append_decode_attention(
     ``q [B, Hq, D]`` un-rotated (left untouched), ``k_new / v_new [B, Hkv, D]``, ``cos / sin [B, D]``;
     ``context_lens`` already counts the new token.
     """
-    _need_cuda(q, k_new, v_new, cos, sin, k_pool, v_pool, block_tables, context_lens)
-    max_blocks, Hkv, bs, D = _pool_dims(k_pool)
-    B, Hq = q.shape[0], q.shape[1]
+    _need_cuda(k_new, v_new, cos, sin)
+    (B, Hq, Hkv, D, bs, max_blocks), q_stride, table_stride, out = _attn_args(q, k_pool, v_pool, block_tables,
+                                                                               context_lens, out)
     if cos.shape != (B, D) or sin.shape != (B, D) or not cos.is_contiguous() or not sin.is_contiguous():
         raise ValueError("cos / sin must be contiguous [B, D]")
-    if block_tables.dtype != torch.int32 or context_lens.dtype != torch.int32:
-        raise ValueError("block_tables and context_lens must be int32")
-    if out is None:
-        out = torch.empty((B, Hq, D), dtype=q.dtype, device=q.device)
+    if not (k_new.dtype == v_new.dtype == cos.dtype == sin.dtype == q.dtype):
+        raise TypeError("q, k_new, v_new, cos and sin must share the pool dtype")
+    if k_new.shape[0] != B or v_new.shape[0] != B:
+        raise ValueError("k_new / v_new must hold one token per sequence")
     lib = _lib.load()
     dt = _dtype_id(k_pool)
     if num_splits == 0:
         num_splits = lib.b200_paged_decode_attn_plan(B, Hq, Hkv, D, bs, max_context_len, dt)
-    ws_ptr, ws_bytes = 0, 0
-    if num_splits > 1:
-        need = lib.b200_paged_decode_attn_workspace(B, Hq, D, num_splits)
-        if workspace is None:
-            workspace = torch.empty(need, dtype=torch.uint8, device=q.device)
-        ws_ptr, ws_bytes = workspace.data_ptr(), workspace.numel() * workspace.element_size()
-    table_stride = block_tables.stride(0) if B > 1 else block_tables.shape[1]
-    events = ATTN_EVENTS
-    if events is not None:
-        ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-        ev0.record()
-    rc = lib.b200_rope_append_decode_attn(
-        out.data_ptr(), q.data_ptr(), _row_stride(q, Hq, D), k_new.data_ptr(), _row_stride(k_new, Hkv, D),
-        v_new.data_ptr(), _row_stride(v_new, Hkv, D), cos.data_ptr(), sin.data_ptr(), k_pool.data_ptr(),
-        v_pool.data_ptr(), block_tables.data_ptr(), table_stride, context_lens.data_ptr(), B, Hq, Hkv, D, bs, max_blocks,
-        float(D) ** -0.5 if scale is None else float(scale), int(max_context_len), int(num_splits), ws_ptr, ws_bytes, dt,
-        int(flags), _stream())
-    if events is not None:
-        ev1.record()
-        events.append((ev0, ev1))
+    ws_ptr, ws_bytes, _ws = _split_workspace(lib, B, Hq, D, num_splits, workspace, q.device)
+    with _timed():
+        rc = lib.b200_rope_append_decode_attn(
+            out.data_ptr(), q.data_ptr(), q_stride, k_new.data_ptr(), _row_stride(k_new, Hkv, D),
+            v_new.data_ptr(), _row_stride(v_new, Hkv, D), cos.data_ptr(), sin.data_ptr(), k_pool.data_ptr(),
+            v_pool.data_ptr(), block_tables.data_ptr(), table_stride, context_lens.data_ptr(), B, Hq, Hkv, D, bs,
+            max_blocks, float(D) ** -0.5 if scale is None else float(scale), int(max_context_len), int(num_splits),
+            ws_ptr, ws_bytes, dt, int(flags), _stream())
     _lib.check(rc, "b200_rope_append_decode_attn")
     return out
 
@@ -323,39 +335,22 @@ def paged_decode_attention_prefix(
 ) -> torch.Tensor:
     """``paged_decode_attention`` for a batch whose first ``prefix_blocks`` table entries are shared by all
     sequences: the shared blocks are read from HBM once for the whole batch."""
-    _need_cuda(q, k_pool, v_pool, block_tables, context_lens)
-    max_blocks, Hkv, bs, D = _pool_dims(k_pool)
-    B, Hq = q.shape[0], q.shape[1]
-    q_stride = _row_stride(q, Hq, D)
-    if block_tables.dtype != torch.int32 or block_tables.dim() != 2 or block_tables.shape[0] != B:
-        raise ValueError("block_tables must be int32 [B, n]")
-    if context_lens.dtype != torch.int32 or context_lens.shape != (B,) or not context_lens.is_contiguous():
-        raise ValueError("context_lens must be a contiguous int32 [B]")
-    if out is None:
-        out = torch.empty((B, Hq, D), dtype=q.dtype, device=q.device)
+    (B, Hq, Hkv, D, bs, max_blocks), q_stride, table_stride, out = _attn_args(q, k_pool, v_pool, block_tables,
+                                                                               context_lens, out)
     dt = _dtype_id(k_pool)
     if prefix_splits == 0 or suffix_splits == 0:
         ps, ss = attn_prefix_plan(B, Hq, Hkv, D, bs, prefix_blocks, max_context_len, q.dtype)
         prefix_splits = prefix_splits or ps
         suffix_splits = suffix_splits or ss
     lib = _lib.load()
-    need = max(16, lib.b200_paged_decode_attn_workspace(B, Hq, D, prefix_splits + suffix_splits))
-    if workspace is None:
-        workspace = torch.empty(need, dtype=torch.uint8, device=q.device)
-    table_stride = block_tables.stride(0) if B > 1 else block_tables.shape[1]
-    events = ATTN_EVENTS
-    if events is not None:
-        ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-        ev0.record()
-    rc = lib.b200_paged_decode_attn_prefix(
-        out.data_ptr(), q.data_ptr(), q_stride, k_pool.data_ptr(), v_pool.data_ptr(), block_tables.data_ptr(),
-        table_stride, context_lens.data_ptr(), B, Hq, Hkv, D, bs, max_blocks,
-        float(D) ** -0.5 if scale is None else float(scale), int(max_context_len), int(prefix_blocks),
-        int(prefix_splits), int(suffix_splits), workspace.data_ptr(), workspace.numel() * workspace.element_size(), dt,
-        int(flags), _stream())
-    if events is not None:
-        ev1.record()
-        events.append((ev0, ev1))
+    ws_ptr, ws_bytes, _ws = _split_workspace(lib, B, Hq, D, prefix_splits + suffix_splits, workspace, q.device,
+                                             always=True)
+    with _timed():
+        rc = lib.b200_paged_decode_attn_prefix(
+            out.data_ptr(), q.data_ptr(), q_stride, k_pool.data_ptr(), v_pool.data_ptr(), block_tables.data_ptr(),
+            table_stride, context_lens.data_ptr(), B, Hq, Hkv, D, bs, max_blocks,
+            float(D) ** -0.5 if scale is None else float(scale), int(max_context_len), int(prefix_blocks),
+            int(prefix_splits), int(suffix_splits), ws_ptr, ws_bytes, dt, int(flags), _stream())
     _lib.check(rc, "b200_paged_decode_attn_prefix")
     return out
 
