@@ -77,6 +77,107 @@ class KVTransferEndpoint:
             ops.kv_unpack_layers(buf, okp, ovp, other.pool_shape, dst_table)
 
 
+class WireHandoff:
+    """Cross-box form of the hand-off (no NVLink between sender and receiver): the messages of the reference's
+    ``TransferKVCache`` RPC, produced and consumed on the GPU.
+
+    Reference: ``KVCacheRequest{prefix_key, start_layer, end_layer, layers[]}`` with ``KVCacheLayer{layer_idx, keys,
+    values, shape, dtype}`` (proto/inference.proto:110-127), where ``keys`` / ``values`` are
+    ``TensorSerializer.serialize`` bytes (common/serialization.py:55-104: bfloat16 travels as float16) and the
+    receiver deserializes per layer and copies into a pool slot (worker/distributed/grpc_server.py:190-235).
+
+    Here the sender makes the bytes of ALL layers and blocks with one launch (b200_kv_pack_layers_wire for bfloat16
+    pools — the narrowing runs on the GPU; b200_kv_pack_layers for float16 / float32 pools, whose wire bytes are
+    their own) and one device→host copy into pinned memory; the receiver does one host→device copy and one launch
+    that widens and scatters into the slots of its own allocator.  The message dictionaries are field-for-field
+    the proto's, so they can be handed to a gRPC / JSON layer unchanged; ``per_block=True`` emits one request per
+    block with ``shape = [heads, block_size, head_dim]`` — the unit a stock reference receiver stores.
+    """
+
+    def __init__(self, pool: KVCachePool, start_layer: int = 0):
+        self.ep = KVTransferEndpoint(pool, chunks=1)
+        self.start_layer = start_layer
+        self.num_layers = pool.num_layers
+        self.dtype = self.ep.dtype
+        self.wire_dtype = torch.float16 if self.dtype == torch.bfloat16 else self.dtype
+        self.dtype_str = {torch.bfloat16: "bfloat16", torch.float16: "float16", torch.float32: "float32"}[self.dtype]
+
+    def _wire_tensor(self, block_table: torch.Tensor) -> torch.Tensor:
+        kp, vp = self.ep._k_ptrs[0], self.ep._v_ptrs[0]
+        if self.dtype == torch.bfloat16:
+            return ops.kv_pack_layers_wire(kp, vp, self.ep.pool_shape, block_table)
+        return ops.kv_pack_layers(kp, vp, self.ep.pool_shape, self.dtype, block_table)
+
+    def export(self, prefix_key: str, block_table: torch.Tensor, per_block: bool = False) -> List[dict]:
+        """``KVCacheRequest`` dictionaries for the blocks in ``block_table`` (int32, device).  One request holding
+        ``[n_blocks, heads, block_size, head_dim]`` per layer, or (``per_block``) one request per block keyed
+        ``"{prefix_key}:{j}"`` with the reference's one-block shape."""
+        n = block_table.shape[0]
+        wire = self._wire_tensor(block_table)                      # [L, 2, n, Hkv, bs, D] on the device
+        host = torch.empty(wire.shape, dtype=wire.dtype, pin_memory=True)
+        host.copy_(wire, non_blocking=True)
+        torch.cuda.current_stream().synchronize()
+        raw = host.view(torch.uint8).numpy()                        # zero-copy view of the pinned buffer
+        _, Hkv, bs, D = self.ep.pool_shape
+
+        def layer_msgs(j0: int, j1: int, shape: List[int]) -> List[dict]:
+            return [{"layer_idx": self.start_layer + l, "keys": raw[l, 0, j0:j1].tobytes(),
+                     "values": raw[l, 1, j0:j1].tobytes(), "shape": shape, "dtype": self.dtype_str}
+                    for l in range(self.num_layers)]
+
+        head = {"start_layer": self.start_layer, "end_layer": self.start_layer + self.num_layers}
+        if per_block:
+            return [{"prefix_key": f"{prefix_key}:{j}", **head, "layers": layer_msgs(j, j + 1, [Hkv, bs, D])}
+                    for j in range(n)]
+        return [{"prefix_key": prefix_key, **head, "layers": layer_msgs(0, n, [n, Hkv, bs, D])}]
+
+    def import_(self, requests: List[dict], block_table: torch.Tensor) -> dict:
+        """Store the blocks carried by ``requests`` (as produced by ``export``, either form, in order) into the
+        slots of ``block_table``; returns the reference's ``KVCacheResponse`` fields."""
+        import time
+
+        import numpy as np
+
+        t0 = time.time()
+        n = block_table.shape[0]
+        _, Hkv, bs, D = self.ep.pool_shape
+        es = torch.empty((), dtype=self.wire_dtype).element_size()
+        blk = Hkv * bs * D * es
+        host = torch.empty((self.num_layers, 2, n, Hkv, bs, D), dtype=self.wire_dtype, pin_memory=True)
+        raw = host.view(torch.uint8).numpy().reshape(self.num_layers, 2, n * blk)
+        total, j = 0, 0
+        try:
+            for req in requests:
+                cnt = None
+                for msg in req["layers"]:
+                    if msg["dtype"] != self.dtype_str:
+                        raise TypeError(f"request carries {msg['dtype']}, the pool holds {self.dtype_str}")
+                    l = msg["layer_idx"] - self.start_layer
+                    if not 0 <= l < self.num_layers:
+                        raise ValueError(f"layer {msg['layer_idx']} is not owned here")
+                    for kv, key in ((0, "keys"), (1, "values")):
+                        data = np.frombuffer(msg[key], dtype=np.uint8)
+                        if data.size % blk or j * blk + data.size > n * blk:
+                            raise ValueError("payload does not match the block geometry / block table")
+                        raw[l, kv, j * blk:j * blk + data.size] = data
+                        total += data.size
+                    cnt = data.size // blk
+                j += cnt or 0
+            if j != n:
+                raise ValueError(f"requests carry {j} blocks, the block table has {n}")
+            dev = host.to(block_table.device, non_blocking=True)
+            kp, vp = self.ep._k_ptrs[0], self.ep._v_ptrs[0]
+            if self.dtype == torch.bfloat16:
+                ops.kv_unpack_layers_wire(dev, kp, vp, self.ep.pool_shape, block_table)
+            else:
+                ops.kv_unpack_layers(dev, kp, vp, self.ep.pool_shape, block_table)
+            torch.cuda.current_stream().synchronize()  # the pinned staging buffer is released on return
+        except Exception as exc:  # noqa: BLE001 - the RPC reports failure in its response
+            return {"success": False, "error_message": str(exc)}
+        return {"success": True, "error_message": "", "bytes_transferred": total,
+                "latency_ms": int((time.time() - t0) * 1000)}
+
+
 class PeerPushEndpoint:
     """Hand-off without staging: the prefill GPU writes a sequence's blocks straight into the decode GPU's pools.
 

@@ -395,6 +395,53 @@ def test_wire_pack_emits_the_reference_serializer_bytes_and_unpack_inverts_it():
     assert torch.isinf(got[0, 0, 0, 0, 0, 1]) and got[0, 0, 0, 0, 0, 0] == 0  # the reference's lossy cases, reproduced
 
 
+@pytest.mark.parametrize("dtype", [torch.bfloat16, torch.float16, torch.float32])
+@pytest.mark.parametrize("per_block", [False, True])
+def test_wire_handoff_messages_are_the_references_rpc_and_land_in_the_receivers_slots(dtype, per_block):
+    """Cross-box hand-off: KVCacheRequest dictionaries (proto/inference.proto:110-127) made on the GPU; each layer's
+    bytes equal TensorSerializer.serialize of that layer's blocks, the oracle's host-side receiver decodes them to
+    the same values the GPU receiver stores, and a stock per-block receiver could take the per_block form."""
+    from dgi_b200.common.serialization import TensorSerializer
+    from dgi_b200.kv_transfer import WireHandoff
+    from dgi_b200.worker.distributed.kv_cache import KVCachePool
+    from oracle import handoff_ref as H
+
+    L_, Hkv, D, bs = 3, 2, 64, 16
+    src = KVCachePool(L_, Hkv, D, bs, 12, device=DEV, dtype=dtype)
+    dst = KVCachePool(L_, Hkv, D, bs, 9, device=DEV, dtype=dtype)
+    src.backing.copy_(torch.randn(src.backing.shape, device=DEV, generator=torch.Generator(device=DEV).manual_seed(5)))
+    dst.allocate_sequence(20)  # the receiver's allocator is elsewhere
+    sblocks, dblocks = src.allocate_sequence(70), dst.allocate_sequence(70)
+    st = torch.tensor(KVCachePool.block_table(sblocks[0]), dtype=torch.int32, device=DEV)
+    dt_ = torch.tensor(KVCachePool.block_table(dblocks[0]), dtype=torch.int32, device=DEV)
+    tx, rx = WireHandoff(src, start_layer=4), WireHandoff(dst, start_layer=4)
+    reqs = tx.export("seq-9", st, per_block=per_block)
+    assert len(reqs) == (5 if per_block else 1)
+    assert all(r["start_layer"] == 4 and r["end_layer"] == 7 and len(r["layers"]) == L_ for r in reqs)
+    for j, r in enumerate(reqs):
+        assert r["prefix_key"] == (f"seq-9:{j}" if per_block else "seq-9")
+        for msg in r["layers"]:
+            l = msg["layer_idx"] - 4
+            for key, pool in (("keys", src.layer(l).key_pool), ("values", src.layer(l).value_pool)):
+                ref_t = pool[int(st[j])] if per_block else pool.index_select(0, st.long())
+                data, shape, name = TensorSerializer.serialize(ref_t)
+                assert msg[key] == data and msg["shape"] == list(shape) and msg["dtype"] == name
+                # the reference's receiver, restated on the host, rebuilds exactly what we are about to store
+                assert torch.equal(H.from_wire(msg[key], tuple(msg["shape"]), msg["dtype"]),
+                                   ref_t.to(torch.float16).to(dtype).cpu() if dtype == torch.bfloat16 else ref_t.cpu())
+    before = dst.backing.clone()
+    resp = rx.import_(reqs, dt_)
+    assert resp["success"] and resp["bytes_transferred"] == sum(len(m["keys"]) + len(m["values"]) for r in reqs for m in r["layers"])
+    want = src.backing[:, :, st.long()]
+    if dtype == torch.bfloat16:
+        want = want.to(torch.float16).to(torch.bfloat16)
+    assert torch.equal(_bits(dst.backing[:, :, dt_.long()]), _bits(want))
+    untouched = [i for i in range(9) if i not in dt_.tolist()]
+    assert torch.equal(dst.backing[:, :, untouched], before[:, :, untouched])
+    bad = rx.import_(reqs[:-1] if per_block else [{**reqs[0], "layers": reqs[0]["layers"][:1]}], dt_[:-1] if not per_block else dt_)
+    assert bad["success"] is False and bad["error_message"]
+
+
 # ---- randomised sweep: many small ragged configurations against the oracle ---------------------------------------
 def test_attention_random_configurations_against_oracle():
     import random

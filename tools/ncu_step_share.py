@@ -30,6 +30,8 @@ def main():
     names = [r[idx["Kernel Name"]] for r in rows]
     durs = [float(r[idx["Metric Value"]].replace(",", "")) for r in rows]
     pos = [i for i, n in enumerate(names) if "rope_append" in n]
+    if len(pos) < 64:  # RoPE + append are fused into the attention kernel: anchor on that one instead
+        pos = [i for i, n in enumerate(names) if "paged_attn_tma" in n]
     per_step = 32
     # a step starts a few launches (slot mapping, RoPE tables, first norm) before its first rope_append
     first = pos[per_step * step]
