@@ -39,7 +39,7 @@ def timed(fn, n, warm=3):
 
 
 def attn_case(name, B, Hq, Hkv, D, ctx_lens, layers, splits, flags=0, share_prefix=0, iters=64, dtype=torch.bfloat16,
-              cascade=False):
+              cascade=False, fused=False):
     bs = 16
     nblk = [(c + bs - 1) // bs for c in ctx_lens]
     uniq_blocks = share_prefix + sum(max(0, n - share_prefix) for n in nblk)
@@ -73,9 +73,20 @@ def attn_case(name, B, Hq, Hkv, D, ctx_lens, layers, splits, flags=0, share_pref
         splits = f"{ps}+{ss}"
         ws = torch.empty(max(16, ops.attn_workspace_bytes(B, Hq, D, ps + ss)), dtype=torch.uint8, device=DEV)
 
+    if fused:  # the launch the decode step actually uses: RoPE(q, k_new) + append + attention
+        kv_new = torch.randn((B, (Hq + 2 * Hkv) * D), device=DEV, dtype=dtype)
+        q = kv_new[:, :Hq * D].view(B, Hq, D)  # strided rows, as slices of the fused q|k|v projection
+        k_new = kv_new[:, Hq * D:(Hq + Hkv) * D].view(B, Hkv, D)
+        v_new = kv_new[:, (Hq + Hkv) * D:].view(B, Hkv, D)
+        cs = torch.randn((B, D), device=DEV, dtype=dtype)
+        sn = torch.randn((B, D), device=DEV, dtype=dtype)
+
     def run(i):
         k, v = pools[i % layers]
-        if cascade:
+        if fused:
+            ops.rope_append_decode_attention(q, k_new, v_new, cs, sn, k, v, tables, lens, max_ctx, out=out,
+                                             num_splits=splits, workspace=ws, flags=flags)
+        elif cascade:
             ops.paged_decode_attention_prefix(q, k, v, tables, lens, max_ctx, share_prefix, out=out, workspace=ws, flags=flags,
                                               prefix_splits=ps, suffix_splits=ss)
         else:
@@ -137,6 +148,9 @@ if __name__ == "__main__":
     for c in a.cases.split(","):
         if c == "cfg2":
             attn_case("cfg2 8B B64 ctx2k", 64, 32, 8, 128, [2048] * 64, a.layers, a.splits, fl, iters=a.iters)
+        elif c == "cfg2f":
+            attn_case("cfg2 8B B64 ctx2k, fused RoPE + append + attention", 64, 32, 8, 128, [2048] * 64, a.layers, a.splits,
+                      fl, iters=a.iters, fused=True)
         elif c == "cfg4":
             attn_case("cfg4 70B B128 ctx4k (per layer)", 128, 64, 8, 128, [4096] * 128, min(a.layers, 4), a.splits, fl, iters=a.iters)
         elif c == "cfg4mb":
