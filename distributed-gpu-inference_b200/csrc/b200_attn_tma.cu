@@ -20,6 +20,7 @@
 //   O^T[d, g]   += V^T[d, tok] P^T[tok, g]    A = V tile (ldmatrix.trans), B = P (movmatrix.trans of S^T frags)
 // Partials (m, l, O) of the 4 warps are merged through shared memory; with num_splits > 1 the CTA stores its
 // partial to the workspace for attn_combine_kernel.
+#include <type_traits>
 #include <cuda.h>
 
 #include <cstdlib>
@@ -243,6 +244,27 @@ paged_attn_tma_kernel(const __grid_constant__ CUtensorMap k_map, const __grid_co
   const int last_blk = n_blocks - 1;
   const bool append_here = FUSED && ctx > 0 && last_blk >= blk_begin && last_blk < blk_end &&
                            ((last_blk - blk_begin) % kWarps) == warp;
+  // The new token's k / v / cos / sin rows and its pool slot are fetched NOW, while the first KV tiles are in
+  // flight, so that the patch of the last tile (end of this warp's loop) does not wait on global memory.
+  constexpr int CH = D / 8;  // 16-byte chunks per row
+  int4 ap_x = make_int4(0, 0, 0, 0), ap_p = ap_x, ap_c = ap_x, ap_s = ap_x;
+  int64_t ap_slot = 0;
+  if constexpr (FUSED) {
+    if (append_here) {
+      ap_slot = block_tables[static_cast<int64_t>(b) * table_stride + last_blk];
+      if (lane < CH) {
+        const int c = lane, pc = (c + CH / 2) % CH;
+        const T* kr = fa.k_new + static_cast<int64_t>(b) * fa.k_stride + static_cast<int64_t>(kvh) * D;
+        ap_x = *reinterpret_cast<const int4*>(kr + 8 * c);
+        ap_p = *reinterpret_cast<const int4*>(kr + 8 * pc);
+        ap_c = *reinterpret_cast<const int4*>(fa.cos_t + static_cast<int64_t>(b) * D + 8 * c);
+        ap_s = *reinterpret_cast<const int4*>(fa.sin_t + static_cast<int64_t>(b) * D + 8 * c);
+      } else if (lane >= 16 && lane < 16 + CH) {
+        const T* vr = fa.v_new + static_cast<int64_t>(b) * fa.v_stride + static_cast<int64_t>(kvh) * D;
+        ap_x = *reinterpret_cast<const int4*>(vr + 8 * (lane - 16));
+      }
+    }
+  }
 
   // per-lane state for the two q heads g = 2 tq, 2 tq + 1: running max (scaled log2 domain), partial sum, O^T
   const float sl2 = scale * 1.4426950408889634f;
@@ -259,29 +281,28 @@ paged_attn_tma_kernel(const __grid_constant__ CUtensorMap k_map, const __grid_co
   const int v_row = (lm_mat >> 1) * 8 + lm_row;  // V: matrices 0/1 -> tok 0-7, 2/3 -> tok 8-15
   const int v_chunk = lm_mat & 1;                //    matrices 0/2 -> chunk 2mt, 1/3 -> chunk 2mt+1
 
-  for (int i = 0; i < n_mine; ++i) {
+  // One KV tile of this warp.  `patch` (compile-time) = this is the sequence's last tile and this warp appends the
+  // new token into it; kept out of the steady-state loop so that loop is the same code as the attention-only kernel.
+  auto tile = [&](const int i, auto patch) {
     const int st = i % STAGES;
     const uint32_t k_tile = ring + st * S::kStageBytes;
     const uint32_t v_tile = k_tile + S::kTileBytes;
     mbar_wait(bars + st * 8, (i / STAGES) & 1);
 
-    if constexpr (FUSED) {
-      if (append_here && i == n_mine - 1) {
+    if constexpr (FUSED && decltype(patch)::value) {
+      {
         // Row r of this tile is the new token.  Lanes 0..D/8-1 rotate one 16-byte chunk of k each, lanes 16.. copy
         // one chunk of v; both go to the pool (for later steps) and into the staged tile (for this step), after the
         // TMA copy of the tile has completed, so nothing is written concurrently with the async proxy.
-        constexpr int CH = D / 8;  // 16-byte chunks per row
         const int r = (ctx - 1) & (kTok - 1);
-        const int64_t slot = block_tables[static_cast<int64_t>(b) * table_stride + last_blk];
-        const int64_t row_elems = ((slot * Hkv + kvh) * kTok + r) * static_cast<int64_t>(D);
+        const int64_t row_elems = ((ap_slot * Hkv + kvh) * kTok + r) * static_cast<int64_t>(D);
         if (lane < CH) {
-          const int c = lane, pc = (c + CH / 2) % CH;
-          const T* kr = fa.k_new + static_cast<int64_t>(b) * fa.k_stride + static_cast<int64_t>(kvh) * D;
+          const int c = lane;
           union { int4 raw; T e[8]; } x, xp, cv, sv, o;
-          x.raw = *reinterpret_cast<const int4*>(kr + 8 * c);
-          xp.raw = *reinterpret_cast<const int4*>(kr + 8 * pc);
-          cv.raw = *reinterpret_cast<const int4*>(fa.cos_t + static_cast<int64_t>(b) * D + 8 * c);
-          sv.raw = *reinterpret_cast<const int4*>(fa.sin_t + static_cast<int64_t>(b) * D + 8 * c);
+          x.raw = ap_x;
+          xp.raw = ap_p;
+          cv.raw = ap_c;
+          sv.raw = ap_s;
           const bool first_half = c < CH / 2;
 #pragma unroll
           for (int e = 0; e < 8; ++e) {
@@ -297,8 +318,7 @@ paged_attn_tma_kernel(const __grid_constant__ CUtensorMap k_map, const __grid_co
                        : "memory");
         } else if (lane >= 16 && lane < 16 + CH) {
           const int c = lane - 16;
-          const T* vr = fa.v_new + static_cast<int64_t>(b) * fa.v_stride + static_cast<int64_t>(kvh) * D;
-          const int4 raw = *reinterpret_cast<const int4*>(vr + 8 * c);
+          const int4 raw = ap_x;
           *reinterpret_cast<int4*>(fa.v_pool + row_elems + 8 * c) = raw;
           asm volatile("st.shared.v4.b32 [%0], {%1,%2,%3,%4};" ::"r"(v_tile + tile_off(r, c)), "r"(raw.x), "r"(raw.y),
                        "r"(raw.z), "r"(raw.w)
@@ -363,6 +383,11 @@ paged_attn_tma_kernel(const __grid_constant__ CUtensorMap k_map, const __grid_co
 
     __syncwarp();  // every lane's reads of this stage are done before lane 0 hands it back to TMA
     if (i + STAGES < n_mine) issue(i + STAGES);
+  };
+  const int n_plain = append_here ? n_mine - 1 : n_mine;
+  for (int i = 0; i < n_plain; ++i) tile(i, std::false_type{});
+  if constexpr (FUSED) {
+    if (append_here) tile(n_mine - 1, std::true_type{});
   }
 
   // ---- merge the 4 warps (buffers alias the ring; all TMA traffic of this CTA has landed and been consumed) ----
