@@ -291,8 +291,65 @@ def gen_tiny_decode() -> None:
     })
 
 
+# ---------------------------------------------------------------------------------------------------------
+# paged device ops: attention pinned to transformers' own eager_attention_forward, pack pinned to index_select
+# ---------------------------------------------------------------------------------------------------------
+def gen_paged_ops() -> None:
+    import hashlib
+
+    from transformers.models.llama import modeling_llama as hf
+
+    from oracle import paged_ref as R
+
+    out = {"note": "inputs are regenerated from seeds by oracle.paged_ref.golden_case_inputs; *_sha256 detects RNG drift"}
+    for name, dtype in (("float32", torch.float32), ("bfloat16", torch.bfloat16), ("float16", torch.float16)):
+        q, k_pool, v_pool, tables, lens = R.golden_case_inputs(dtype)
+        B, Hq, D = q.shape
+        Hkv = k_pool.shape[1]
+        stub = mock.Mock()
+        stub.num_key_value_groups = Hq // Hkv
+        stub.training = False
+        rows = []
+        for b in range(B):
+            ctx = int(lens[b])
+            if ctx == 0:
+                rows.append(torch.zeros((Hq, D), dtype=dtype))
+                continue
+            # the dense [1, Hkv, ctx, D] cache the reference's HF layer would hold for this sequence
+            k = R.gather_dense(k_pool, tables[b], ctx)[None]
+            v = R.gather_dense(v_pool, tables[b], ctx)[None]
+            o, _ = hf.eager_attention_forward(stub, q[b][None, :, None, :], k, v, None, scaling=D ** -0.5)
+            rows.append(o.reshape(Hq, D))
+        want = torch.stack(rows)                                   # transformers' own arithmetic, storage dtype
+        mine = R.paged_attention_ref(q, k_pool, v_pool, tables, lens, mode="eager")
+        assert torch.equal(mine, want), f"oracle eager recipe differs from transformers ({name})"
+        exact = R.paged_attention_ref(q, k_pool, v_pool, tables, lens, mode="fp32")
+        if dtype == torch.float32:
+            assert (exact - want).abs().max() < 2e-6
+        t = tables[4, :6].to(torch.int64)
+        packed = torch.stack((k_pool.index_select(0, t), v_pool.index_select(0, t)))
+        assert torch.equal(R.pack_ref(k_pool, v_pool, tables[4, :6]), packed)
+        as_bytes = lambda x: x.contiguous().view(torch.uint8).numpy().tobytes()  # noqa: E731
+        out[name] = {
+            "q_sha256": hashlib.sha256(as_bytes(q)).hexdigest(),
+            "k_pool_sha256": hashlib.sha256(as_bytes(k_pool)).hexdigest(),
+            "block_tables": tables.tolist(),
+            "context_lens": lens.tolist(),
+            "hf_eager_out_hex": as_bytes(want).hex(),
+            "exact_fp32_out_hex": as_bytes(exact).hex(),
+            "packed_seq4_sha256": hashlib.sha256(as_bytes(packed)).hexdigest(),
+            "packed_seq4_table": tables[4, :6].tolist(),
+        }
+    out["transformers_version"] = __import__("transformers").__version__
+    dump("paged_ops.json", out)
+
+
 if __name__ == "__main__":
+    if "--only-paged" in sys.argv:
+        gen_paged_ops()
+        sys.exit(0)
     gen_host_logic()
     gen_allocator()
     gen_serializer()
     gen_tiny_decode()
+    gen_paged_ops()

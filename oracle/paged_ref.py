@@ -105,3 +105,16 @@ def build_block_tables(n_blocks_per_seq: List[int], max_blocks: int, seed: int, 
             raise ValueError("pool too small for the requested tables")
         rows.append(row + [0] * (width - len(row)))
     return torch.tensor(rows, dtype=torch.int32).reshape(len(rows), width), cursor
+
+
+def golden_case_inputs(dtype: torch.dtype):
+    """The seeded case behind tests/golden/paged_ops.json (CPU RNG, shared by oracle/make_golden.py and the tests):
+    ragged contexts incl. an empty sequence, a single token and an exact block multiple; scattered block tables."""
+    B, Hq, Hkv, D, bs, max_blocks = 5, 8, 2, 64, 16, 24
+    ctx = [37, 0, 1, 48, 90]
+    g = torch.Generator().manual_seed(20240607)
+    k_pool = torch.randn((max_blocks, Hkv, bs, D), generator=g).to(dtype)
+    v_pool = torch.randn((max_blocks, Hkv, bs, D), generator=g).to(dtype)
+    q = torch.randn((B, Hq, D), generator=g).to(dtype)
+    tables, _ = build_block_tables([(c + bs - 1) // bs for c in ctx], max_blocks, seed=11)
+    return q, k_pool, v_pool, tables, torch.tensor(ctx, dtype=torch.int32)

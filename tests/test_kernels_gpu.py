@@ -177,6 +177,32 @@ def test_attention_matches_oracle(case, dtype, tol, splits, flags):
             assert out[b].eq(0).all()
 
 
+@pytest.mark.parametrize("name,tol", [("bfloat16", 1e-2), ("float16", 2e-3), ("float32", 2e-5)])
+@pytest.mark.parametrize("flags", [0, ops.ATTN_FORCE_GENERIC])
+def test_attention_and_pack_against_committed_golden(golden, name, tol, flags):
+    """tests/golden/paged_ops.json: outputs of transformers' own eager_attention_forward (what the reference's HF
+    layer computes) on a seeded ragged case, and the bytes of index_select-packed blocks."""
+    import hashlib
+
+    g = golden("paged_ops.json")[name]
+    dtype = getattr(torch, name)
+    q, k_pool, v_pool, tables, lens = (t.to(DEV) for t in R.golden_case_inputs(dtype))
+    assert tables.tolist() == g["block_tables"]
+    out = ops.paged_decode_attention(q, k_pool, v_pool, tables, lens, 90, flags=flags)
+    exact = torch.frombuffer(bytearray.fromhex(g["exact_fp32_out_hex"]), dtype=torch.float32).view(5, 8, 64).to(DEV)
+    hf = torch.frombuffer(bytearray.fromhex(g["hf_eager_out_hex"]), dtype=dtype).view(5, 8, 64).to(DEV)
+    assert _rel_err(out, exact) <= tol
+    # against the HF recipe in the storage dtype: within the north-star 1e-2 (relative L2), and no further from it on the
+    # strict per-row metric than the two distances to the exact value allow
+    live = [0, 2, 3, 4]  # sequence 1 is empty: zeros on both sides
+    assert ((out[live].float() - hf[live].float()).norm() / hf[live].float().norm()).item() <= 1e-2
+    assert _rel_err(out, hf) <= _rel_err(hf, exact) + tol
+    assert out[1].eq(0).all() and hf[1].eq(0).all()
+    table = torch.tensor(g["packed_seq4_table"], dtype=torch.int32, device=DEV)
+    packed = ops.kv_pack(k_pool, v_pool, table)
+    assert hashlib.sha256(packed.cpu().contiguous().view(torch.uint8).numpy().tobytes()).hexdigest() == g["packed_seq4_sha256"]
+
+
 def test_attention_vs_reference_eager_recipe_bf16():
     """Against the HF eager recipe evaluated in bf16 — what the reference's layer computes on the same inputs.
 
