@@ -16,7 +16,10 @@ Pinning (oracle/make_golden.py, run in the build container where /root/reference
     against outputs of the reference's own code (imported unmodified) and the reference's own test vectors;
   * the decoder-layer restatement is pinned by driving the reference's unmodified ``ModelShard.forward`` /
     ``get_logits`` with it and checking greedy tokens against ``transformers`` ``generate()``;
-  * attention numerics have no golden vector in the reference's tests (its layers are MagicMocks):
-    *parity unpinned* for that piece beyond the token-exact check above.
+  * attention numerics have no golden vector in the reference's own tests (its layers are MagicMocks), so they are
+    pinned on the third-party function the reference's HF layer runs: ``paged_ref.paged_attention_ref(mode="eager")``
+    is asserted bit-identical to ``transformers``' ``eager_attention_forward`` on a seeded ragged paged case (fp32,
+    bf16, fp16) and those outputs are committed (tests/golden/paged_ops.json), together with the digest of
+    ``index_select``-packed blocks.
 Fixtures live in tests/golden/.
 """
