@@ -254,19 +254,25 @@ class PagedKVCache:
         """``free_block`` for many ids with the same observable result, but the pool rows that reach ref-count 0
         are zeroed with one ``index_fill_`` per pool instead of two launches per block (SURVEY.md §9 #10)."""
         dead: List[int] = []
+        blocks, slots, lru, pinned, free = self._blocks, self._block_to_slot, self._lru_queue, self._pinned, self._free_blocks
+        on_free = self._on_free
         for block_id in block_ids:
-            blk = self._blocks.get(block_id)
-            if blk is None or blk.remove_ref() != 0:
+            blk = blocks.get(block_id)
+            if blk is None:
                 continue
-            slot = self._block_to_slot.pop(block_id, None)
+            if blk.ref_count > 1:  # still shared: only drop this holder's reference
+                blk.ref_count -= 1
+                continue
+            blk.ref_count = 0
+            slot = slots.pop(block_id, None)
             if slot is not None:
                 dead.append(slot)
-            del self._blocks[block_id]
-            self._lru_queue.pop(block_id, None)
-            self._pinned.discard(block_id)
-            self._free_blocks.append(block_id)
-            if self._on_free is not None:
-                self._on_free(block_id)
+            del blocks[block_id]
+            lru.pop(block_id, None)
+            pinned.discard(block_id)
+            free.append(block_id)
+            if on_free is not None:
+                on_free(block_id)
         if dead:
             idx = torch.tensor(dead, dtype=torch.int64, device=self._key_pool.device)
             self._key_pool.index_fill_(0, idx, 0)
