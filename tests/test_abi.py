@@ -62,3 +62,18 @@ def test_ops_refuse_cpu_tensors():
         ops.kv_append(torch.zeros(1, 2, 8), torch.zeros(1, 2, 8), k, k.clone(), torch.zeros(1, dtype=torch.int64))
     with pytest.raises(_lib.B200LibraryError):
         ops.kv_pack(k, k.clone(), torch.zeros(1, dtype=torch.int32))
+
+
+def test_integration_doc_stub_binds_the_real_library():
+    """The ctypes stub printed in INTEGRATION.md is executed against the built library: it must load, and the
+    argument lists it declares must be the ones the package itself uses (guards the document against rot)."""
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    text = open(os.path.join(root, "INTEGRATION.md")).read()
+    code = re.search(r"```python\n(.*?)```", text, re.S).group(1)
+    assert "/path/to/libb200_kv.so" in code
+    ns = {}
+    exec(code.replace("/path/to/libb200_kv.so", _lib.LIB_PATH), ns)  # noqa: S102 - our own document
+    for name in ("b200_kv_append", "b200_paged_decode_attn"):
+        assert list(getattr(ns["_lib"], name).argtypes) == list(_lib.SIGNATURES[name][1]), name
+    assert ns["_lib"].b200_paged_decode_attn_workspace.restype is ctypes.c_size_t
+    assert ns["_DT"] == ops.DTYPE_ID and callable(ns["kv_append"])
