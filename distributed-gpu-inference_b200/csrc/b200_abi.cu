@@ -331,6 +331,11 @@ int b200_rope_kv_append_prompt(void* q, int64_t q_row_stride, void* k, int64_t k
                         static_cast<cudaStream_t>(stream));
 }
 
+int b200_argmax_rows(int64_t* out, const void* x, int64_t rows, int64_t cols, int64_t row_stride, int dtype,
+                     void* stream) {
+  return argmax_rows(out, x, rows, cols, row_stride, dtype, static_cast<cudaStream_t>(stream));
+}
+
 int b200_silu_mul(void* out, const void* gate, const void* up, int64_t rows, int cols, int64_t gate_row_stride,
                   int64_t up_row_stride, int dtype, void* stream) {
   return silu_mul(out, gate, up, rows, cols, gate_row_stride, up_row_stride, dtype, static_cast<cudaStream_t>(stream));

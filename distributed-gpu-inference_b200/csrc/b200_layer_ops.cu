@@ -198,6 +198,70 @@ silu_mul_kernel(T* __restrict__ out, const T* __restrict__ gate, const T* __rest
   }
 }
 
+// ---- greedy token: row-wise argmax of the logits --------------------------------------------------------------
+// One CTA per row, 16-byte loads.  Same answer as torch.argmax: the largest value, the smallest index among equal
+// values, NaN counts as larger than everything (first NaN wins).
+struct Best {
+  float v;
+  int i;
+};
+__device__ __forceinline__ bool better(float v, int i, const Best& b) {
+  const bool vn = v != v, bn = b.v != b.v;
+  if (bn) return vn && i < b.i;
+  return vn || v > b.v || (v == b.v && i < b.i);
+}
+constexpr int kArgmaxThreads = 1024;
+
+template <typename T>
+__global__ void __launch_bounds__(kArgmaxThreads)
+argmax_rows_kernel(int64_t* __restrict__ out, const T* __restrict__ x, int cols, int64_t row_stride, bool vec_ok) {
+  constexpr int VN = Vec16<T>::N;
+  const T* row = x + static_cast<int64_t>(blockIdx.x) * row_stride;
+  Best best{-INFINITY, 0x7fffffff};
+  int done = 0;
+  if (vec_ok) {
+    const int nvec = cols / VN;
+    for (int v = threadIdx.x; v < nvec; v += kArgmaxThreads) {
+      Vec16<T> a;
+      a.raw = *reinterpret_cast<const int4*>(row + static_cast<int64_t>(v) * VN);
+#pragma unroll
+      for (int e = 0; e < VN; ++e) {
+        const float f = Cvt<T>::to_f32(a.e[e]);
+        if (better(f, v * VN + e, best)) best = Best{f, v * VN + e};
+      }
+    }
+    done = nvec * VN;
+  }
+  for (int c = done + threadIdx.x; c < cols; c += kArgmaxThreads) {
+    const float f = Cvt<T>::to_f32(row[c]);
+    if (better(f, c, best)) best = Best{f, c};
+  }
+#pragma unroll
+  for (int off = 16; off > 0; off >>= 1) {
+    const float ov = __shfl_xor_sync(0xffffffffu, best.v, off);
+    const int oi = __shfl_xor_sync(0xffffffffu, best.i, off);
+    if (better(ov, oi, best)) best = Best{ov, oi};
+  }
+  __shared__ float sv[kArgmaxThreads / 32];
+  __shared__ int si[kArgmaxThreads / 32];
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  if (lane == 0) {
+    sv[warp] = best.v;
+    si[warp] = best.i;
+  }
+  __syncthreads();
+  if (warp == 0) {
+    best = Best{sv[lane], si[lane]};
+#pragma unroll
+    for (int off = 16; off > 0; off >>= 1) {
+      const float ov = __shfl_xor_sync(0xffffffffu, best.v, off);
+      const int oi = __shfl_xor_sync(0xffffffffu, best.i, off);
+      if (better(ov, oi, best)) best = Best{ov, oi};
+    }
+    if (lane == 0) out[blockIdx.x] = best.i;
+  }
+}
+
 template <typename F>
 int by_dtype(int dtype, const char* name, F&& f) {
   switch (dtype) {
@@ -279,6 +343,22 @@ int silu_mul(void* out, const void* gate, const void* up, int64_t rows, int cols
     silu_mul_kernel<T><<<grid, 256, 0, s>>>(static_cast<T*>(out), static_cast<const T*>(gate),
                                             static_cast<const T*>(up), rows, cols, g_stride, u_stride);
     return check_launch("b200_silu_mul");
+  });
+}
+
+int argmax_rows(int64_t* out, const void* x, int64_t rows, int64_t cols, int64_t row_stride, int dtype, cudaStream_t s) {
+  const int es = dtype_size(dtype);
+  if (es == 0) return fail(B200_EINVAL, "b200_argmax_rows: unsupported dtype %d", dtype);
+  if (rows < 0 || cols <= 0 || cols > 0x7fffffff || rows > 0x7fffffff || row_stride < cols)
+    return fail(B200_EINVAL, "b200_argmax_rows: bad sizes");
+  if (rows == 0) return 0;
+  if (!out || !x) return fail(B200_EINVAL, "b200_argmax_rows: null pointer");
+  const bool vec_ok = aligned16(x) && (row_stride * es) % 16 == 0;
+  return by_dtype(dtype, "b200_argmax_rows", [&](auto* tag) {
+    using T = std::remove_pointer_t<decltype(tag)>;
+    argmax_rows_kernel<T><<<static_cast<unsigned>(rows), kArgmaxThreads, 0, s>>>(out, static_cast<const T*>(x),
+                                                                                  static_cast<int>(cols), row_stride, vec_ok);
+    return check_launch("b200_argmax_rows");
   });
 }
 

@@ -153,6 +153,23 @@ def silu_mul(gate: torch.Tensor, up: torch.Tensor) -> torch.Tensor:
     return out.view(gate.shape)
 
 
+def argmax_rows(x: torch.Tensor, out: Optional[torch.Tensor] = None) -> torch.Tensor:
+    """``torch.argmax(x, dim=-1)`` for a 2-D ``[rows, cols]`` tensor with a contiguous last dim (the greedy token of
+    a decode step); ``out``: int64 ``[rows]``."""
+    _need_cuda(x)
+    if x.dim() != 2 or x.stride(1) != 1:
+        raise ValueError("x must be [rows, cols] with a contiguous last dimension")
+    rows, cols = x.shape
+    if out is None:
+        out = torch.empty((rows,), dtype=torch.int64, device=x.device)
+    elif out.dtype != torch.int64 or out.shape != (rows,) or not out.is_contiguous() or not out.is_cuda:
+        raise ValueError("out must be a contiguous CUDA int64 [rows]")
+    rc = _lib.load().b200_argmax_rows(out.data_ptr(), x.data_ptr(), rows, cols, x.stride(0) if rows > 1 else cols,
+                                     _dtype_id(x), _stream())
+    _lib.check(rc, "b200_argmax_rows")
+    return out
+
+
 def attn_plan(B: int, Hq: int, Hkv: int, D: int, block_size: int, max_context_len: int, dtype: torch.dtype) -> int:
     """Number of context partitions the library would pick for this shape."""
     return _lib.load().b200_paged_decode_attn_plan(B, Hq, Hkv, D, block_size, max_context_len, DTYPE_ID[dtype])

@@ -208,6 +208,11 @@ int b200_rope_kv_append_prompt(void* q, int64_t q_row_stride, void* k, int64_t k
                                int Hq, int Hkv, int D, int block_size, int64_t max_blocks, int dtype, void* stream);
 int b200_silu_mul(void* out, const void* gate, const void* up, int64_t rows, int cols,
                   int64_t gate_row_stride, int64_t up_row_stride, int dtype, void* stream);
+/* Greedy token: out[r] = argmax over x[r, 0..cols) — largest value, smallest index among equals, NaN largest, i.e.
+ * torch.argmax(logits, dim=-1) of the sampling step (the reference: worker/engines/speculative.py:449).  x rows are
+ * row_stride elements apart; out is int64[rows]. */
+int b200_argmax_rows(int64_t* out, const void* x, int64_t rows, int64_t cols, int64_t row_stride, int dtype,
+                     void* stream);
 
 /*
  * KV block pack / unpack for the prefill -> decode hand-off.  Replaces the per-block, per-layer

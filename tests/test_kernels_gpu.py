@@ -547,3 +547,40 @@ def test_fused_decode_entry_rejects_other_shapes():
     assert not ops.fused_decode_supported(k_pool, 8)
     with pytest.raises(B200LibraryError, match="f16/bf16"):
         ops.rope_append_decode_attention(q, z, z, cs, cs, k_pool, v_pool, tables, lens, 40)
+
+
+# ---- greedy token: argmax over the logits ---------------------------------------------------------------------------
+@pytest.mark.parametrize("dtype", [torch.bfloat16, torch.float16, torch.float32])
+@pytest.mark.parametrize("rows,cols", [(64, 128256), (4, 1024), (3, 1001), (1, 7), (16, 32000)])
+def test_argmax_rows_equals_torch_argmax_including_ties(dtype, rows, cols):
+    g = torch.Generator(device=DEV).manual_seed(rows * 31 + cols)
+    x = torch.randn((rows, cols), generator=g, device=DEV).to(dtype)
+    if dtype != torch.float32:
+        assert (x == x.max(dim=-1, keepdim=True).values).sum() >= rows  # low precision: ties do occur at this width
+    want = torch.argmax(x, dim=-1)
+    assert torch.equal(ops.argmax_rows(x), want)
+    # forced ties: the maximum repeated at several positions -> the first one wins, as in torch
+    y = x.clone()
+    top = y.max(dim=-1).values
+    for r in range(rows):
+        for c in (cols - 1, cols // 2, min(5, cols - 1)):
+            y[r, c] = top[r]
+    assert torch.equal(ops.argmax_rows(y), torch.argmax(y, dim=-1))
+    # strided rows (a slice of a wider buffer) and an odd starting column (unaligned rows -> scalar path)
+    wide = torch.randn((rows, cols + 9), generator=g, device=DEV).to(dtype)
+    for view in (wide[:, :cols], wide[:, 1:cols + 1]):
+        assert torch.equal(ops.argmax_rows(view), torch.argmax(view, dim=-1))
+    out = torch.empty((rows,), dtype=torch.int64, device=DEV)
+    assert ops.argmax_rows(x, out=out) is out and torch.equal(out, want)
+
+
+def test_argmax_rows_nan_and_inf_follow_torch():
+    x = torch.randn((4, 4096), device=DEV, generator=torch.Generator(device=DEV).manual_seed(3))
+    x[0, 100] = float("inf")
+    x[1, 7] = float("nan")
+    x[1, 9] = float("nan")
+    x[2, :] = float("-inf")
+    x[3, 4000] = float("nan")
+    x[3, 10] = float("inf")
+    assert torch.equal(ops.argmax_rows(x), torch.argmax(x, dim=-1))
+    assert ops.argmax_rows(x).tolist() == [100, 7, 0, 4000]
