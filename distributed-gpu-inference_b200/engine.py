@@ -18,7 +18,7 @@ from typing import Any, Dict, List, Optional, Sequence
 import torch
 
 from .paged_layer import PagedBatchState, PagedLayerKV, rope_tables
-from .worker.distributed.kv_cache import CacheBlock, KVCachePool
+from .worker.distributed.kv_cache import CacheBlock, KVCachePool, RadixPrefixIndex
 from .worker.distributed.model_shard import ModelShard
 from . import ops
 
@@ -39,6 +39,7 @@ class PagedDecodeEngine:
         spare_blocks: int = 0,
         fuse_projections: bool = False,
         kv_pools: Optional[Sequence[KVCachePool]] = None,
+        prefix_cache: bool = False,
     ):
         if not shards:
             raise ValueError("need at least one shard")
@@ -128,25 +129,45 @@ class PagedDecodeEngine:
         self._pin_out = torch.zeros((max_batch,), dtype=torch.int64).pin_memory()
         self.batch = 0
         self._borrowed = False
+        # prefix cache across requests: one index per shard pool, holding its own reference on the cached blocks
+        self.prefix_index: Optional[List[RadixPrefixIndex]] = (
+            [RadixPrefixIndex(pool, hold=True) for pool in self.pools] if prefix_cache else None)
+        self.cached_blocks = 0
         if len(self.pools) != len(self.shards) or any(
                 p.num_layers != s.get_layer_count() for p, s in zip(self.pools, self.shards)):
             raise ValueError("kv_pools must hold one pool per shard with that shard's layer count")
 
     # ---- allocation ----------------------------------------------------------------------------------
-    def allocate(self, batch: int, total_len: int, shared_prefix_len: int = 0) -> None:
+    def allocate(self, batch: int, total_len: int, shared_prefix_len: int = 0,
+                 prefix_tokens: Optional[Sequence[int]] = None) -> None:
         """Hand every sequence blocks for ``total_len`` tokens (prompt + tokens to generate).
 
         With ``shared_prefix_len`` > 0 all sequences start with the same ``shared_prefix_len`` tokens: sequence 0
         owns the blocks that hold them, the others take references to those blocks (``ref_count`` sharing) and
         allocate only the rest.  Only whole blocks are shared.  Decode then uses the cascade attention kernel.
+
+        ``prefix_tokens`` (the shared tokens themselves; needs ``prefix_cache=True``): the leading blocks that an
+        earlier request already computed are looked up in the prefix cache and reused by EVERY sequence, sequence 0
+        included; ``self.cached_blocks`` says how many, and ``prefill`` skips those tokens.
         """
         if batch > self.max_batch or total_len > self.max_seq_len:
             raise ValueError("batch / length beyond the engine's capacity")
         self.release()
-        n_shared = (shared_prefix_len // self.block_size) if batch > 1 else 0
+        n_shared = shared_prefix_len // self.block_size
+        cached: Optional[List[List[List[CacheBlock]]]] = None
+        n_cached = 0
+        if self.prefix_index is not None and prefix_tokens is not None and n_shared > 0:
+            hits = [idx.match(list(prefix_tokens)[: n_shared * self.block_size]) for idx in self.prefix_index]
+            n_cached = min(h[0] for h in hits)
+            if n_cached > 0:
+                cached = [[lb[:n_cached] for lb in h[1]] for h in hits]
+        self._prefix_tokens = list(prefix_tokens)[: n_shared * self.block_size] if prefix_tokens is not None else None
         rows = []
         for b in range(batch):
-            if b == 0 or n_shared == 0:
+            if b == 0:
+                per_shard = [pool.allocate_sequence(total_len, shared_prefix=cached[si] if cached else None)
+                             for si, pool in enumerate(self.pools)]
+            elif n_shared == 0:
                 per_shard = [pool.allocate_sequence(total_len) for pool in self.pools]
             else:
                 per_shard = [
@@ -168,9 +189,11 @@ class PagedDecodeEngine:
         self.context_lens.zero_()
         self._host_lens = [0] * self.max_batch
         self.batch = batch
+        self.cached_blocks = n_cached
         self._graph = None
         self._graph_chained = None
-        self._set_prefix(n_shared)
+        self._set_prefix(n_shared if batch > 1 else 0)
+        self._shared_blocks = n_shared
 
     def _set_prefix(self, n_shared: int) -> None:
         """Configure decode attention for ``n_shared`` leading blocks common to all sequences (0 = none)."""
@@ -291,13 +314,21 @@ class PagedDecodeEngine:
         prompt_ids = prompt_ids.to(self.device)
         out_tokens = torch.empty((B,), dtype=torch.int64, device=self.device)
         start = 0
-        shared = getattr(self, "prefix_blocks", 0) * self.block_size
+        bs = self.block_size
+        shared = getattr(self, "_shared_blocks", 0) * bs   # tokens whose blocks all sequences have in common
+        cached = self.cached_blocks * bs                    # the part of those an earlier request already computed
         if shared > 0:
-            # sequence 0 computes the shared blocks once; the others only run their own tokens over them
             if not bool((prompt_ids[:, :shared] == prompt_ids[0, :shared]).all()):
                 raise ValueError("sequences do not share the declared prefix")
-            out_tokens[0:1] = self.prefill_chunk(0, 1, prompt_ids[0:1])
+            if self._prefix_tokens is not None and prompt_ids[0, :shared].tolist() != self._prefix_tokens:
+                raise ValueError("prompts do not start with the prefix the blocks were allocated for")
+            # sequence 0 computes what is left of the shared blocks (everything, without a cache hit) plus its own
+            # tokens; the others only run their own tokens over the shared blocks
+            out_tokens[0:1] = self.prefill_chunk(0, 1, prompt_ids[0:1, cached:], past_len=cached)
             start = 1
+            if self.prefix_index is not None and self._prefix_tokens is not None:
+                for si, idx in enumerate(self.prefix_index):  # from now on these blocks serve later requests too
+                    idx.insert(self._prefix_tokens, [lb[:shared // bs] for lb in self._seq_blocks[0][si]])
         for lo in range(start, B, self.prefill_chunk_size):
             hi = min(B, lo + self.prefill_chunk_size)
             out_tokens[lo:hi] = self.prefill_chunk(lo, hi, prompt_ids[lo:hi, shared:], past_len=shared)
@@ -408,9 +439,12 @@ class PagedDecodeEngine:
     @torch.no_grad()
     def generate(self, prompt_ids: torch.Tensor, max_new_tokens: int, shared_prefix_len: int = 0) -> torch.Tensor:
         """Greedy generation: tokens [B, max_new_tokens] on the host.  ``shared_prefix_len``: leading tokens that are
-        identical in every prompt and whose KV blocks should be shared (computed once, reference-counted)."""
+        identical in every prompt and whose KV blocks should be shared (computed once, reference-counted); with
+        ``prefix_cache=True`` they are also kept for later calls, which then skip recomputing them."""
         B, P = prompt_ids.shape
-        self.allocate(B, P + max_new_tokens, shared_prefix_len=min(shared_prefix_len, P - 1))
+        n_pre = min(shared_prefix_len, P - 1)
+        self.allocate(B, P + max_new_tokens, shared_prefix_len=n_pre,
+                      prefix_tokens=prompt_ids[0, :n_pre].tolist() if self.prefix_index is not None and n_pre else None)
         nxt = self.prefill(prompt_ids).cpu()
         out = [nxt]
         for _ in range(max_new_tokens - 1):

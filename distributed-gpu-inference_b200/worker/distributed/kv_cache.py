@@ -583,33 +583,65 @@ class RadixPrefixIndex:
 
     ``match(token_ids)`` returns how many leading full blocks are already cached and the per-layer block lists to
     pass as ``KVCachePool.allocate_sequence(shared_prefix=...)``; ``insert`` registers a sequence's full blocks.
-    Entries whose blocks were freed are dropped lazily on lookup.
+    Entries are held by object identity, so a block that was freed and whose id has since been handed out again is
+    never mistaken for the cached one; such entries are dropped lazily on lookup.
+
+    With ``hold=True`` the index is a prefix CACHE that outlives the sequences: it takes its own reference on every
+    block it registers (``CacheBlock.add_ref``, the sharing the reference declared in worker/distributed/kv_cache.py:
+    63-72 and never used).  A block referenced only by the index has ``ref_count == 1`` and is therefore exactly what
+    the allocator's LRU eviction may reclaim when the pool runs dry (reference :225-238); blocks that live sequences
+    still use have ``ref_count > 1`` and stay.  ``match`` touches the blocks it returns (``get_block``), so recently
+    used prefixes are evicted last.
     """
 
-    def __init__(self, pool: "KVCachePool"):
+    def __init__(self, pool: "KVCachePool", hold: bool = False):
         self.pool = pool
-        self._by_hash: Dict[str, List[str]] = {}  # hash -> block id per layer
+        self.hold = hold
+        self._by_hash: Dict[str, List[CacheBlock]] = {}  # hash -> the block of every layer
+        self.stats = {"lookups": 0, "hit_blocks": 0, "inserted_blocks": 0}
+
+    def _alive(self, blks: List[CacheBlock]) -> bool:
+        return all(self.pool.layer(l)._blocks.get(b.block_id) is b for l, b in enumerate(blks))
 
     def insert(self, token_ids: Sequence[int], blocks: List[List[CacheBlock]]) -> int:
         hashes = chained_block_hashes(token_ids, self.pool.block_size)
         for i, h in enumerate(hashes):
-            if i < len(blocks[0]):
-                self._by_hash.setdefault(h, [layer_blocks[i].block_id for layer_blocks in blocks])
+            if i >= len(blocks[0]):
+                break
+            known = self._by_hash.get(h)
+            if known is not None and self._alive(known):
+                continue
+            entry = [layer_blocks[i] for layer_blocks in blocks]
+            self._by_hash[h] = entry
+            self.stats["inserted_blocks"] += 1
+            if self.hold:
+                for b in entry:
+                    b.add_ref()
         return len(hashes)
 
     def match(self, token_ids: Sequence[int]) -> Tuple[int, Optional[List[List[CacheBlock]]]]:
         hashes = chained_block_hashes(token_ids, self.pool.block_size)
         per_layer: List[List[CacheBlock]] = [[] for _ in range(self.pool.num_layers)]
         n = 0
+        self.stats["lookups"] += 1
         for h in hashes:
-            ids = self._by_hash.get(h)
-            if ids is None:
+            blks = self._by_hash.get(h)
+            if blks is None:
                 break
-            blks = [self.pool.layer(l)._blocks.get(bid) for l, bid in enumerate(ids)]
-            if any(b is None for b in blks):
-                del self._by_hash[h]  # freed since it was indexed
+            if not self._alive(blks):
+                del self._by_hash[h]  # freed (or evicted) since it was indexed
                 break
             for l, b in enumerate(blks):
+                self.pool.layer(l).get_block(b.block_id)  # LRU touch + hit statistics, as a reader of the block would
                 per_layer[l].append(b)
             n += 1
+        self.stats["hit_blocks"] += n
         return n, (per_layer if n else None)
+
+    def drop_all(self) -> None:
+        """Forget every entry, giving back the references a holding index took."""
+        for blks in self._by_hash.values():
+            if self.hold and self._alive(blks):
+                for l, b in enumerate(blks):
+                    self.pool.layer(l).free_blocks([b.block_id])
+        self._by_hash.clear()

@@ -68,7 +68,10 @@ class PagedLLMEngine:
         self.engine = PagedDecodeEngine(
             shards, max_batch=cfg.get("max_batch_size", 32), max_seq_len=cfg.get("max_model_len", 2048),
             block_size=cfg.get("block_size", 16), prefill_mode=cfg.get("prefill_mode", "sdpa"),
-            fuse_projections=cfg.get("fuse_projections", True))
+            fuse_projections=cfg.get("fuse_projections", True),
+            # system prompts stay cached between calls (blocks held by the prefix index, evicted LRU when the pool
+            # runs dry); `prefix_cache_blocks` is the room set aside for them on top of the batch's own blocks
+            prefix_cache=cfg.get("enable_prefix_caching", True), spare_blocks=cfg.get("prefix_cache_blocks", 256))
         self.loaded = True
 
     def unload_model(self) -> None:
@@ -159,11 +162,14 @@ class PagedLLMEngine:
                         cached = 0
                     else:
                         ids = torch.tensor([parsed[i][0] for i in part], dtype=torch.int64)
-                        shared = len(sys_ids) if len(part) > 1 else 0
+                        shared = len(sys_ids) if (len(part) > 1 or eng.prefix_index is not None) else 0
                         rows = eng.generate(ids, n_new, shared_prefix_len=shared).tolist()
                         cached = (min(shared, plen - 1) // eng.block_size) * eng.block_size
+                    # tokens whose KV was not computed for this request: row 0 only skips what an EARLIER call left in
+                    # the prefix cache, the other rows also skip what row 0 has just computed
+                    first = eng.cached_blocks * eng.block_size if plen != "ragged" else 0
                     for row, i in enumerate(part):
-                        results[i] = self._result(rows[row][:parsed[i][2]], len(parsed[i][0]), cached if row > 0 else 0)
+                        results[i] = self._result(rows[row][:parsed[i][2]], len(parsed[i][0]), cached if row > 0 else first)
                 except Exception as exc:  # noqa: BLE001
                     for i in part:
                         results[i] = exc

@@ -310,3 +310,54 @@ def test_adopted_blocks_decode_like_own_blocks(golden):
         assert b.pools[0].layer(0).get_stats()["free_blocks"] == free_before
         for per_shard in mine:
             b.pools[0].free_sequence(per_shard[0])
+
+
+def test_prefix_cache_serves_later_requests_and_gives_way_under_pressure(golden):
+    """A system prompt computed by one call stays in the pool (held by the prefix index) and is reused by later calls —
+    by sequence 0 too, which then runs only its own tokens; tokens equal those of a cache-less engine.  Blocks held
+    only by the cache are what LRU eviction reclaims when a later batch needs the room."""
+    g, cfg, sd = _tiny(golden)
+    base = torch.tensor(g["prompt_ids"])
+    sys_len = 80
+
+    def prompts_with(system, tails):
+        p = base[tails, :112].clone()
+        p[:, :sys_len] = system
+        return p
+
+    sys_a, sys_b = base[0, :sys_len], base[1, :sys_len]
+    shards = build_product_shards(cfg, sd, [(0, 2), (2, 4)], DEV, torch.float32)
+    plain = PagedDecodeEngine(shards, 4, 160, prefill_mode="eager")
+    eng = PagedDecodeEngine(shards, 4, 160, prefill_mode="eager", prefix_cache=True, spare_blocks=8)
+    first, second, single = prompts_with(sys_a, [0, 1, 2, 3]), prompts_with(sys_a, [3, 2, 1, 0]), prompts_with(sys_a, [2])
+
+    got1 = eng.generate(first, 12, shared_prefix_len=sys_len)
+    assert eng.cached_blocks == 0 and torch.equal(got1, plain.generate(first, 12))
+    held = [idx.stats["inserted_blocks"] for idx in eng.prefix_index]
+    assert held == [5, 5]
+    eng.release()
+    # 5 blocks per layer stay allocated for the cache, with exactly the cache's reference
+    assert all(c.get_stats()["free_blocks"] == c.max_blocks - 5 for pool in eng.pools for c in pool._layer_caches)
+
+    got2 = eng.generate(second, 12, shared_prefix_len=sys_len)   # same system prompt: every row starts from the cache
+    assert eng.cached_blocks == 5
+    assert torch.equal(got2, plain.generate(second, 12))
+    assert eng._seq_blocks[0][0][0][0].ref_count == 5            # 4 sequences + the cache
+    got3 = eng.generate(single, 12, shared_prefix_len=sys_len)   # a lone request profits too
+    assert eng.cached_blocks == 5 and torch.equal(got3, plain.generate(single, 12))
+    assert [idx.stats["inserted_blocks"] for idx in eng.prefix_index] == held  # nothing new was cached
+
+    other = prompts_with(sys_b, [0, 1, 2, 3])                   # a different system prompt: miss, then cached as well
+    got4 = eng.generate(other, 12, shared_prefix_len=sys_len)
+    assert eng.cached_blocks == 0 and torch.equal(got4, plain.generate(other, 12))
+    eng.release()
+    assert all(c.get_stats()["free_blocks"] == c.max_blocks - 10 for pool in eng.pools for c in pool._layer_caches)
+
+    # pressure: 4 unrelated sequences of 160 tokens need 40 blocks of the 48; the 10 cached ones must give way (LRU)
+    long_prompts = base[:, :128]
+    got5 = eng.generate(long_prompts, 32)
+    assert torch.equal(got5, plain.generate(long_prompts, 32))
+    evicted = sum(c.get_stats()["evictions"] for c in eng.pools[0]._layer_caches)
+    assert evicted >= 2 * 2  # at least two blocks in each of the shard's two layers
+    got6 = eng.generate(second, 12, shared_prefix_len=sys_len)   # whatever survived is used, the rest recomputed
+    assert torch.equal(got6, got2) and eng.cached_blocks < 5
