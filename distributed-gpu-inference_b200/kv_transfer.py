@@ -77,6 +77,48 @@ class KVTransferEndpoint:
             ops.kv_unpack_layers(buf, okp, ovp, other.pool_shape, dst_table)
 
 
+class HostSwap:
+    """Host tier for whole sequences: the L2 ("CPU memory") level of the reference's cache hierarchy
+    (``DistributedKVCacheManager._add_to_cpu_cache`` / ``_promote_to_gpu``, worker/distributed/kv_cache.py:447-504),
+    which moves one block of one layer per ``.cpu()`` / ``copy_`` call.
+
+    Here a sequence's blocks of ALL layers leave the GPU with one pack launch and one device→host copy into pinned
+    memory, and come back — into whatever slots the allocator hands out then — with one host→device copy and one
+    unpack launch.  Bit-exact (no fp16 detour).  ``swap_out`` returns immediately after queueing the copy; the
+    returned handle's ``ready`` event says when the blocks may be freed or overwritten.
+    """
+
+    class Handle:
+        __slots__ = ("host", "n_blocks", "ready", "_staging")
+
+        def __init__(self, host, n_blocks, ready, staging):
+            self.host, self.n_blocks, self.ready, self._staging = host, n_blocks, ready, staging
+
+    def __init__(self, pool: KVCachePool):
+        self.ep = KVTransferEndpoint(pool, chunks=1)
+
+    def nbytes(self, n_blocks: int) -> int:
+        return self.ep.payload_bytes(n_blocks)
+
+    def swap_out(self, block_table: torch.Tensor) -> "HostSwap.Handle":
+        n = block_table.shape[0]
+        buf = self.ep.staging(n)[0]
+        ops.kv_pack_layers(self.ep._k_ptrs[0], self.ep._v_ptrs[0], self.ep.pool_shape, self.ep.dtype, block_table, out=buf)
+        host = torch.empty(buf.shape, dtype=buf.dtype, pin_memory=True)
+        host.copy_(buf, non_blocking=True)
+        ready = torch.cuda.Event()
+        ready.record()
+        return HostSwap.Handle(host, n, ready, buf)  # the staging tensor lives until the copy has been waited for
+
+    def swap_in(self, handle: "HostSwap.Handle", block_table: torch.Tensor) -> None:
+        if block_table.shape[0] != handle.n_blocks:
+            raise ValueError("block table does not match the swapped-out sequence")
+        handle.ready.synchronize()
+        handle._staging = None
+        dev = handle.host.to(block_table.device, non_blocking=True)
+        ops.kv_unpack_layers(dev, self.ep._k_ptrs[0], self.ep._v_ptrs[0], self.ep.pool_shape, block_table)
+
+
 class WireHandoff:
     """Cross-box form of the hand-off (no NVLink between sender and receiver): the messages of the reference's
     ``TransferKVCache`` RPC, produced and consumed on the GPU.

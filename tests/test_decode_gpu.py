@@ -361,3 +361,38 @@ def test_prefix_cache_serves_later_requests_and_gives_way_under_pressure(golden)
     assert evicted >= 2 * 2  # at least two blocks in each of the shard's two layers
     got6 = eng.generate(second, 12, shared_prefix_len=sys_len)   # whatever survived is used, the rest recomputed
     assert torch.equal(got6, got2) and eng.cached_blocks < 5
+
+
+def test_sequences_swapped_to_host_and_back_decode_the_same_tokens(golden):
+    """Host tier for whole sequences (the reference's L2 level, kv_cache.py:447-504): after the prompt pass every
+    sequence's blocks go to pinned host memory and are freed; they come back into different slots and decoding
+    continues with the reference's tokens."""
+    from dgi_b200.kv_transfer import HostSwap
+
+    g, cfg, sd = _tiny(golden)
+    prompts = torch.tensor(g["prompt_ids"])
+    B, P, n_new = prompts.shape[0], prompts.shape[1], 16
+    shards = build_product_shards(cfg, sd, [(0, 4)], DEV, torch.float32)
+    eng = PagedDecodeEngine(shards, B, 192, prefill_mode="eager", spare_blocks=16)
+    swap = HostSwap(eng.pools[0])
+    eng.allocate(B, P + n_new)
+    first = eng.prefill(prompts)
+    n_blk = (P + 15) // 16
+    old_tables = eng.block_tables[:B, :n_blk].clone()
+    handles = [swap.swap_out(old_tables[b].contiguous()) for b in range(B)]
+    assert handles[0].host.is_pinned() and swap.nbytes(n_blk) == handles[0].host.numel() * 4
+    for h in handles:
+        h.ready.synchronize()
+    eng.release()                                   # blocks freed and zeroed
+    assert not eng.pools[0].backing.any()
+    eng.pools[0].allocate_sequence(40)              # somebody else takes slots in between
+    mine = [[eng.pools[0].allocate_sequence(P + n_new)] for _ in range(B)]
+    for b in range(B):
+        t = torch.tensor(eng.pools[0].block_table(mine[b][0][0])[:n_blk], dtype=torch.int32, device=DEV)
+        swap.swap_in(handles[b], t)
+    eng.adopt_sequences(mine, [P] * B)
+    assert not torch.equal(eng.block_tables[:B, :n_blk], old_tables)
+    out = [first.cpu()]
+    for _ in range(n_new - 1):
+        out.append(eng.decode_step(out[-1]))
+    assert torch.stack(out, 1).tolist() == [row[:n_new] for row in g["tokens"]]
