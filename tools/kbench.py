@@ -126,6 +126,21 @@ def copy_cases():
     a, b_ = torch.empty(payload, dtype=torch.uint8, device=DEV), torch.empty(payload, dtype=torch.uint8, device=DEV)
     ms = timed(lambda i: b_.copy_(a), 20)
     print(json.dumps({"kernel": "torch_copy_same_bytes", "ms": round(ms, 4), "GBps_read_plus_write": round(2 * payload / ms / 1e6, 1)}), flush=True)
+    # host tier: the same sequence out to pinned memory and back (pack + D2H, H2D + unpack); bound = the host link
+    host = torch.empty(packed.shape, dtype=packed.dtype, pin_memory=True)
+
+    def out_(i):
+        ops.kv_pack_layers(kp, vp, shape, torch.bfloat16, tables[i % 4], out=packed)
+        host.copy_(packed, non_blocking=True)
+
+    def in_(i):
+        packed.copy_(host, non_blocking=True)
+        ops.kv_unpack_layers(packed, kp, vp, shape, tables[i % 4])
+
+    for name, fn in (("host_swap_out", out_), ("host_swap_in", in_)):
+        ms = timed(fn, 6, warm=2)
+        print(json.dumps({"kernel": name, "payload_MiB": payload / 2 ** 20, "ms": round(ms, 3),
+                          "GBps_payload": round(payload / ms / 1e6, 1)}), flush=True)
     # append at decode (64 tokens) and at prefill (8 x 2048 tokens)
     for n_tok in (64, 16384):
         k_new = torch.randn((n_tok, Hkv, D), device=DEV, dtype=torch.bfloat16)
