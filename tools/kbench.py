@@ -166,6 +166,13 @@ if __name__ == "__main__":
         elif c == "cfg2f":
             attn_case("cfg2 8B B64 ctx2k, fused RoPE + append + attention", 64, 32, 8, 128, [2048] * 64, a.layers, a.splits,
                       fl, iters=a.iters, fused=True)
+        elif c == "b1_32k":
+            attn_case("8B B1 ctx32k (single long sequence)", 1, 32, 8, 128, [32768], a.layers, a.splits, fl, iters=a.iters)
+        elif c == "b1_128k":
+            attn_case("8B B1 ctx128k (single long sequence)", 1, 32, 8, 128, [131072], min(a.layers, 4), a.splits, fl,
+                      iters=a.iters)
+        elif c == "b4_8k":
+            attn_case("8B B4 ctx8k", 4, 32, 8, 128, [8192] * 4, a.layers, a.splits, fl, iters=a.iters)
         elif c == "cfg4":
             attn_case("cfg4 70B B128 ctx4k (per layer)", 128, 64, 8, 128, [4096] * 128, min(a.layers, 4), a.splits, fl, iters=a.iters)
         elif c == "cfg4mb":
