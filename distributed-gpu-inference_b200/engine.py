@@ -5,8 +5,14 @@ What it owns
     turned into an int32 block table per sequence;
   * the per-step device state (``PagedBatchState``) shared by all layers: slot mapping, context lengths,
     RoPE tables, split-K workspace;
-  * a CUDA graph of one decode step (all layers, lm_head, argmax) so the ~20 launches per layer cost one
-    graph launch per token.
+  * a CUDA graph of one decode step (all layers, lm_head, argmax) so the 8-9 launches per layer cost one
+    graph launch per token;
+  * optionally a prefix cache (``prefix_cache=True``): blocks of a shared leading token run stay referenced after
+    a call and are reused — not recomputed — by later calls, until LRU eviction reclaims them.
+
+Besides ``allocate`` (the engine takes blocks from its pools) there is ``adopt_sequences`` (the caller hands over
+blocks that somebody else filled: the receiving side of a prefill→decode hand-off, or sequences swapped back in
+from the host tier).
 
 What it calls: only ``ModelShard.forward`` / ``get_logits`` (the reference surface) and, through the layers,
 the C-ABI kernels.  Greedy (argmax) sampling, which is what the parity contract is defined on.
