@@ -409,9 +409,10 @@ def run_single(args, workload):
         except Exception:  # noqa: BLE001
             traffic = None
     # this repo's kernels per step: per layer add_rmsnorm x2, the one-launch RoPE + append + attention (+ combine when
-    # split), silu_mul; + the final norm.  With a shared prefix: rope_kv_append + cascade + combine instead.
+    # split), silu_mul; + the final norm and the argmax over the logits.  With a shared prefix: rope_kv_append +
+    # cascade + combine instead.
     per_layer = 6 if eng.state.prefix_blocks else 4 + (1 if eng.num_splits > 1 else 0)
-    launches_per_step = cfg.num_hidden_layers * per_layer + 1
+    launches_per_step = cfg.num_hidden_layers * per_layer + 2
 
     line = {
         "metric": "decode_tokens_per_s",
