@@ -37,6 +37,12 @@ SIGNATURES = {
         [c_void_p, c_void_p, c_int64, c_void_p, c_void_p, c_void_p, c_int, c_void_p, c_int, c_int, c_int, c_int, c_int,
          c_int64, c_float, c_int, c_int, c_int, c_int, c_void_p, c_size_t, c_int, c_uint, c_void_p],
     ),
+    "b200_rope_append_decode_attn_prefix": (
+        c_int,
+        [c_void_p, c_void_p, c_int64, c_void_p, c_int64, c_void_p, c_int64, c_void_p, c_void_p, c_void_p, c_void_p,
+         c_void_p, c_int, c_void_p, c_int, c_int, c_int, c_int, c_int, c_int64, c_float, c_int, c_int, c_int, c_int,
+         c_void_p, c_size_t, c_int, c_uint, c_void_p],
+    ),
     "b200_paged_decode_attn_prefix_plan": (
         c_int, [c_int, c_int, c_int, c_int, c_int, c_int, c_int, c_int, ctypes.POINTER(c_int), ctypes.POINTER(c_int)]),
     "b200_paged_decode_attn_static": (

@@ -198,18 +198,21 @@ int b200_paged_decode_attn_prefix_plan(int B, int Hq, int Hkv, int D, int block_
   return 0;
 }
 
-int b200_paged_decode_attn_prefix(void* out, const void* q, int64_t q_row_stride, const void* k_pool,
-                                  const void* v_pool, const int32_t* block_tables, int table_stride,
-                                  const int32_t* context_lens, int B, int Hq, int Hkv, int D, int block_size,
-                                  int64_t max_blocks, float scale, int max_context_len, int prefix_blocks,
-                                  int prefix_splits, int suffix_splits, void* workspace, size_t workspace_bytes,
-                                  int dtype, unsigned flags, void* stream) {
-  const char* name = "b200_paged_decode_attn_prefix";
-  if (prefix_blocks < 0 || prefix_splits < 0 || suffix_splits < 0) return fail(B200_EINVAL, "%s: negative count", name);
-  if (prefix_blocks == 0)
-    return b200_paged_decode_attn(out, q, q_row_stride, k_pool, v_pool, block_tables, table_stride, context_lens, B, Hq,
-                                  Hkv, D, block_size, max_blocks, scale, max_context_len, suffix_splits, workspace,
-                                  workspace_bytes, dtype, flags, stream);
+namespace {
+struct NewToken {  // operands of the fused decode step; all null = attention only
+  const void* k_new = nullptr;
+  int64_t k_stride = 0;
+  const void* v_new = nullptr;
+  int64_t v_stride = 0;
+  const void* cos_t = nullptr;
+  const void* sin_t = nullptr;
+};
+
+int attn_prefix_entry(const char* name, const NewToken& nt, void* out, const void* q, int64_t q_row_stride,
+                      const void* k_pool, const void* v_pool, const int32_t* block_tables, int table_stride,
+                      const int32_t* context_lens, int B, int Hq, int Hkv, int D, int block_size, int64_t max_blocks,
+                      float scale, int max_context_len, int prefix_blocks, int prefix_splits, int suffix_splits,
+                      void* workspace, size_t workspace_bytes, int dtype, unsigned flags, void* stream) {
   if (dtype_size(dtype) == 0) return fail(B200_EINVAL, "%s: unsupported dtype %d", name, dtype);
   if (B <= 0 || Hq <= 0 || Hkv <= 0 || D <= 0 || block_size <= 0 || max_blocks <= 0 || Hq % Hkv != 0)
     return fail(B200_EINVAL, "%s: bad sizes", name);
@@ -253,9 +256,62 @@ int b200_paged_decode_attn_prefix(void* out, const void* q, int64_t q_row_stride
   a.round_scores = (flags & B200_ATTN_ROUND_SCORES) ? 1 : 0;
   a.ws_acc = static_cast<float*>(workspace);
   a.ws_ml = a.ws_acc + static_cast<size_t>(B) * Hq * total * D;
+  a.k_new = nt.k_new;
+  a.k_new_stride = nt.k_stride;
+  a.v_new = nt.v_new;
+  a.v_new_stride = nt.v_stride;
+  a.cos_t = nt.cos_t;
+  a.sin_t = nt.sin_t;
   if (!attn_prefix_supported(a, dtype))
     return fail(B200_ESHAPE, "%s: needs f16/bf16, block_size 16, head_dim 64/128, group <= 8", name);
   return attn_prefix(a, dtype, prefix_blocks, ps, ss, static_cast<cudaStream_t>(stream));
+}
+}  // namespace
+
+int b200_paged_decode_attn_prefix(void* out, const void* q, int64_t q_row_stride, const void* k_pool,
+                                  const void* v_pool, const int32_t* block_tables, int table_stride,
+                                  const int32_t* context_lens, int B, int Hq, int Hkv, int D, int block_size,
+                                  int64_t max_blocks, float scale, int max_context_len, int prefix_blocks,
+                                  int prefix_splits, int suffix_splits, void* workspace, size_t workspace_bytes,
+                                  int dtype, unsigned flags, void* stream) {
+  const char* name = "b200_paged_decode_attn_prefix";
+  if (prefix_blocks < 0 || prefix_splits < 0 || suffix_splits < 0) return fail(B200_EINVAL, "%s: negative count", name);
+  if (prefix_blocks == 0)
+    return b200_paged_decode_attn(out, q, q_row_stride, k_pool, v_pool, block_tables, table_stride, context_lens, B, Hq,
+                                  Hkv, D, block_size, max_blocks, scale, max_context_len, suffix_splits, workspace,
+                                  workspace_bytes, dtype, flags, stream);
+  return attn_prefix_entry(name, NewToken{}, out, q, q_row_stride, k_pool, v_pool, block_tables, table_stride,
+                           context_lens, B, Hq, Hkv, D, block_size, max_blocks, scale, max_context_len, prefix_blocks,
+                           prefix_splits, suffix_splits, workspace, workspace_bytes, dtype, flags, stream);
+}
+
+int b200_rope_append_decode_attn_prefix(void* out, const void* q, int64_t q_row_stride, const void* k_new,
+                                        int64_t k_row_stride, const void* v_new, int64_t v_row_stride,
+                                        const void* cos_table, const void* sin_table, void* k_pool, void* v_pool,
+                                        const int32_t* block_tables, int table_stride, const int32_t* context_lens, int B,
+                                        int Hq, int Hkv, int D, int block_size, int64_t max_blocks, float scale,
+                                        int max_context_len, int prefix_blocks, int prefix_splits, int suffix_splits,
+                                        void* workspace, size_t workspace_bytes, int dtype, unsigned flags, void* stream) {
+  const char* name = "b200_rope_append_decode_attn_prefix";
+  if (prefix_blocks < 0 || prefix_splits < 0 || suffix_splits < 0) return fail(B200_EINVAL, "%s: negative count", name);
+  if (prefix_blocks == 0)
+    return b200_rope_append_decode_attn(out, q, q_row_stride, k_new, k_row_stride, v_new, v_row_stride, cos_table,
+                                        sin_table, k_pool, v_pool, block_tables, table_stride, context_lens, B, Hq, Hkv, D,
+                                        block_size, max_blocks, scale, max_context_len, suffix_splits, workspace,
+                                        workspace_bytes, dtype, flags, stream);
+  if (!k_new || !v_new || !cos_table || !sin_table) return fail(B200_EINVAL, "%s: null pointer", name);
+  if (Hkv > 0 && D > 0 && (k_row_stride < static_cast<int64_t>(Hkv) * D || v_row_stride < static_cast<int64_t>(Hkv) * D))
+    return fail(B200_EINVAL, "%s: row stride smaller than heads * D", name);
+  NewToken nt;
+  nt.k_new = k_new;
+  nt.k_stride = k_row_stride;
+  nt.v_new = v_new;
+  nt.v_stride = v_row_stride;
+  nt.cos_t = cos_table;
+  nt.sin_t = sin_table;
+  return attn_prefix_entry(name, nt, out, q, q_row_stride, k_pool, v_pool, block_tables, table_stride, context_lens, B,
+                           Hq, Hkv, D, block_size, max_blocks, scale, max_context_len, prefix_blocks, prefix_splits,
+                           suffix_splits, workspace, workspace_bytes, dtype, flags, stream);
 }
 
 int b200_kv_pack(void* packed, const void* k_pool, const void* v_pool, const int32_t* block_table, int n_blocks,

@@ -44,11 +44,22 @@ struct CascadeParams {
   float* ws_acc;
   float* ws_ml;
   int round_scores;
+  // fused decode step (FUSED kernels only): un-rotated q, the new token's rows, RoPE tables, writable pools
+  const void* k_new;
+  int64_t k_new_stride;
+  const void* v_new;
+  int64_t v_new_stride;
+  const void* cos_t;
+  const void* sin_t;
+  void* k_pool;
+  void* v_pool;
 };
 
 // One CTA's work in either role.  SUFFIX = false: prefix role, columns are (sequence, head) pairs of q-group `zi`.
 // SUFFIX = true (NT = 1): columns are the q heads of sequence `zi`; tiles past the context are masked.
-template <typename T, int D, int STAGES, int NT, bool SUFFIX>
+// FUSED: q arrives un-rotated and is rotated in registers (both roles); the suffix warp that owns a sequence's last
+// tile appends the new token's rotated k and its v, exactly as paged_attn_tma_kernel<.., FUSED> does.
+template <typename T, int D, int STAGES, int NT, bool SUFFIX, bool FUSED>
 __device__ __forceinline__ void cascade_role(const CUtensorMap& k_map, const CUtensorMap& v_map, const CascadeParams& p,
                                              int split, int kvh, int zi) {
   using S = Smem<D, STAGES>;
@@ -144,6 +155,36 @@ __device__ __forceinline__ void cascade_role(const CUtensorMap& k_map, const CUt
       qf[kk][nt][0] = ok ? *reinterpret_cast<const uint32_t*>(qrow + kk * 16 + 2 * tq) : 0u;
       qf[kk][nt][1] = ok ? *reinterpret_cast<const uint32_t*>(qrow + kk * 16 + 8 + 2 * tq) : 0u;
     }
+    if constexpr (FUSED) {
+      if (ok) {
+        const T* cs = static_cast<const T*>(p.cos_t) + static_cast<int64_t>(bq) * D;
+        const T* sn = static_cast<const T*>(p.sin_t) + static_cast<int64_t>(bq) * D;
+#pragma unroll
+        for (int kk = 0; kk < KSTEPS / 2; ++kk) {
+#pragma unroll
+          for (int j = 0; j < 2; ++j)
+            rope_q_regs<T, D>(qf[kk][nt][j], qf[kk + KSTEPS / 2][nt][j], cs, sn, kk * 16 + 8 * j + 2 * tq);
+        }
+      }
+    }
+  }
+
+  // suffix role: the warp that owns the sequence's last KV tile appends the new token into it
+  bool append_here = false;
+  AppendRows ap{};
+  FusedAppend<T> fa{};
+  if constexpr (FUSED && SUFFIX) {
+    const int last_blk = (ctx + kTok - 1) / kTok - 1;
+    append_here = ctx > 0 && last_blk >= blk_begin && last_blk < blk_end && ((last_blk - blk_begin) % kWarps) == warp;
+    fa.k_new = static_cast<const T*>(p.k_new);
+    fa.k_stride = p.k_new_stride;
+    fa.v_new = static_cast<const T*>(p.v_new);
+    fa.v_stride = p.v_new_stride;
+    fa.cos_t = static_cast<const T*>(p.cos_t);
+    fa.sin_t = static_cast<const T*>(p.sin_t);
+    fa.k_pool = static_cast<T*>(p.k_pool);
+    fa.v_pool = static_cast<T*>(p.v_pool);
+    if (append_here) ap = append_fetch<T, D>(fa, zi, kvh, lane, table_row[last_blk]);
   }
 
   const float sl2 = scale * 1.4426950408889634f;
@@ -165,6 +206,9 @@ __device__ __forceinline__ void cascade_role(const CUtensorMap& k_map, const CUt
     const uint32_t k_tile = ring + st * S::kStageBytes;
     const uint32_t v_tile = k_tile + S::kTileBytes;
     mbar_wait(bars + st * 8, (i / STAGES) & 1);
+    if constexpr (FUSED && SUFFIX) {
+      if (append_here && i == n_mine - 1) append_patch<T, D>(ap, fa, Hkv, kvh, (ctx - 1) & (kTok - 1), lane, k_tile, v_tile);
+    }
 
     float s[NT][4];
 #pragma unroll
@@ -291,7 +335,7 @@ __device__ __forceinline__ void cascade_role(const CUtensorMap& k_map, const CUt
   }
 }
 
-template <typename T, int D, int STAGES, int NT>
+template <typename T, int D, int STAGES, int NT, bool FUSED>
 __global__ void __launch_bounds__(kWarps * 32, (NT <= 2 ? 2 : 1))
 paged_attn_cascade_kernel(const __grid_constant__ CUtensorMap k_map, const __grid_constant__ CUtensorMap v_map,
                           const __grid_constant__ CascadeParams p) {
@@ -299,12 +343,12 @@ paged_attn_cascade_kernel(const __grid_constant__ CUtensorMap k_map, const __gri
   if (id < p.n_prefix_ctas) {  // heavier CTAs first
     const int split = id % p.prefix_splits;
     const int rest = id / p.prefix_splits;
-    cascade_role<T, D, STAGES, NT, false>(k_map, v_map, p, split, rest % p.Hkv, rest / p.Hkv);
+    cascade_role<T, D, STAGES, NT, false, FUSED>(k_map, v_map, p, split, rest % p.Hkv, rest / p.Hkv);
   } else {
     const int j = id - p.n_prefix_ctas;
     const int split = j % p.suffix_splits;
     const int rest = j / p.suffix_splits;
-    cascade_role<T, D, STAGES, 1, true>(k_map, v_map, p, split, rest % p.Hkv, rest / p.Hkv);
+    cascade_role<T, D, STAGES, 1, true, FUSED>(k_map, v_map, p, split, rest % p.Hkv, rest / p.Hkv);
   }
 }
 
@@ -325,9 +369,9 @@ int prefix_nt() {
   return nt;
 }
 
-template <typename T, int D, int NT>
-int launch_cascade(const AttnArgs& a, int dtype, int prefix_blocks, int prefix_splits, int suffix_splits,
-                   cudaStream_t stream) {
+template <typename T, int D, int NT, bool FUSED>
+int launch_cascade_impl(const AttnArgs& a, int dtype, int prefix_blocks, int prefix_splits, int suffix_splits,
+                        cudaStream_t stream) {
   using S = Smem<D, prefix_stages<NT>()>;
   const uint64_t rows = static_cast<uint64_t>(a.max_blocks) * a.Hkv * kTok;
   CUtensorMap km, vm;
@@ -335,7 +379,7 @@ int launch_cascade(const AttnArgs& a, int dtype, int prefix_blocks, int prefix_s
   if (rc) return rc;
   rc = get_tensor_map(a.v_pool, rows, D, dtype, &vm);
   if (rc) return rc;
-  auto kern = paged_attn_cascade_kernel<T, D, prefix_stages<NT>(), NT>;
+  auto kern = paged_attn_cascade_kernel<T, D, prefix_stages<NT>(), NT, FUSED>;
   cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, S::kTotal);
   if (e != cudaSuccess) return fail(static_cast<int>(e), "cudaFuncSetAttribute: %s", cudaGetErrorString(e));
   CascadeParams p{};
@@ -359,9 +403,27 @@ int launch_cascade(const AttnArgs& a, int dtype, int prefix_blocks, int prefix_s
   p.ws_acc = a.ws_acc;
   p.ws_ml = a.ws_ml;
   p.round_scores = a.round_scores;
+  if (FUSED) {
+    p.k_new = a.k_new;
+    p.k_new_stride = a.k_new_stride;
+    p.v_new = a.v_new;
+    p.v_new_stride = a.v_new_stride;
+    p.cos_t = a.cos_t;
+    p.sin_t = a.sin_t;
+    p.k_pool = const_cast<void*>(a.k_pool);
+    p.v_pool = const_cast<void*>(a.v_pool);
+  }
   const int grid = p.n_prefix_ctas + suffix_splits * a.Hkv * a.B;
   kern<<<grid, kWarps * 32, S::kTotal, stream>>>(km, vm, p);
   return check_launch("b200_paged_decode_attn_prefix(cascade)");
+}
+
+template <typename T, int D, int NT>
+int launch_cascade(const AttnArgs& a, int dtype, int prefix_blocks, int prefix_splits, int suffix_splits,
+                   cudaStream_t stream) {
+  return a.k_new != nullptr
+             ? launch_cascade_impl<T, D, NT, true>(a, dtype, prefix_blocks, prefix_splits, suffix_splits, stream)
+             : launch_cascade_impl<T, D, NT, false>(a, dtype, prefix_blocks, prefix_splits, suffix_splits, stream);
 }
 
 }  // namespace

@@ -111,34 +111,6 @@ using namespace tma;
 
 namespace {
 
-// Operands of the fused variant (FUSED = true): this step's un-rotated q, the new token's k and v rows and the RoPE
-// tables.  The kernel then rotates q in registers, and the one warp that owns a sequence's last KV tile rotates the
-// new k row, writes it and the v row into the pool AND into its staged tile — so RoPE, the KV append and the
-// attention of a decode step are one launch instead of two.
-template <typename T>
-struct FusedAppend {
-  const T* k_new;       // [B, Hkv, D], row stride k_stride
-  int64_t k_stride;
-  const T* v_new;
-  int64_t v_stride;
-  const T* cos_t;       // [B, D]
-  const T* sin_t;
-  T* k_pool;            // writable views of the pools behind k_map / v_map
-  T* v_pool;
-};
-
-// rotate-half RoPE on one element pair with torch's rounding points (see b200_layer_ops.cu)
-template <typename T>
-__device__ __forceinline__ void rope_pair(T x_lo, T x_hi, T c_lo, T s_lo, T c_hi, T s_hi, T& o_lo, T& o_hi) {
-  const float xl = Cvt<T>::to_f32(x_lo), xh = Cvt<T>::to_f32(x_hi);
-  const T a = Cvt<T>::from_f32(__fmul_rn(xl, Cvt<T>::to_f32(c_lo)));
-  const T b = Cvt<T>::from_f32(__fmul_rn(-xh, Cvt<T>::to_f32(s_lo)));
-  o_lo = Cvt<T>::from_f32(__fadd_rn(Cvt<T>::to_f32(a), Cvt<T>::to_f32(b)));
-  const T c = Cvt<T>::from_f32(__fmul_rn(xh, Cvt<T>::to_f32(c_hi)));
-  const T d = Cvt<T>::from_f32(__fmul_rn(xl, Cvt<T>::to_f32(s_hi)));
-  o_hi = Cvt<T>::from_f32(__fadd_rn(Cvt<T>::to_f32(c), Cvt<T>::to_f32(d)));
-}
-
 template <typename T, int D, int STAGES, bool FUSED>
 __global__ void __launch_bounds__(kWarps * 32, (STAGES <= 3 ? 2 : 1))
 paged_attn_tma_kernel(const __grid_constant__ CUtensorMap k_map, const __grid_constant__ CUtensorMap v_map,
@@ -224,20 +196,7 @@ paged_attn_tma_kernel(const __grid_constant__ CUtensorMap k_map, const __grid_co
 #pragma unroll
     for (int kk = 0; kk < KSTEPS / 2; ++kk) {
 #pragma unroll
-      for (int j = 0; j < 2; ++j) {
-        const int d = kk * 16 + 8 * j + 2 * tq;
-        union { uint32_t u; T e[2]; } lo, hi, c_lo, s_lo, c_hi, s_hi, o_lo, o_hi;
-        lo.u = qf[kk][j];
-        hi.u = qf[kk + KSTEPS / 2][j];
-        c_lo.u = *reinterpret_cast<const uint32_t*>(cs + d);
-        s_lo.u = *reinterpret_cast<const uint32_t*>(sn + d);
-        c_hi.u = *reinterpret_cast<const uint32_t*>(cs + D / 2 + d);
-        s_hi.u = *reinterpret_cast<const uint32_t*>(sn + D / 2 + d);
-        rope_pair<T>(lo.e[0], hi.e[0], c_lo.e[0], s_lo.e[0], c_hi.e[0], s_hi.e[0], o_lo.e[0], o_hi.e[0]);
-        rope_pair<T>(lo.e[1], hi.e[1], c_lo.e[1], s_lo.e[1], c_hi.e[1], s_hi.e[1], o_lo.e[1], o_hi.e[1]);
-        qf[kk][j] = o_lo.u;
-        qf[kk + KSTEPS / 2][j] = o_hi.u;
-      }
+      for (int j = 0; j < 2; ++j) rope_q_regs<T, D>(qf[kk][j], qf[kk + KSTEPS / 2][j], cs, sn, kk * 16 + 8 * j + 2 * tq);
     }
   }
   // the warp that owns the sequence's last KV tile (the one the new token lands in) does the append
@@ -246,24 +205,10 @@ paged_attn_tma_kernel(const __grid_constant__ CUtensorMap k_map, const __grid_co
                            ((last_blk - blk_begin) % kWarps) == warp;
   // The new token's k / v / cos / sin rows and its pool slot are fetched NOW, while the first KV tiles are in
   // flight, so that the patch of the last tile (end of this warp's loop) does not wait on global memory.
-  constexpr int CH = D / 8;  // 16-byte chunks per row
-  int4 ap_x = make_int4(0, 0, 0, 0), ap_p = ap_x, ap_c = ap_x, ap_s = ap_x;
-  int64_t ap_slot = 0;
+  AppendRows ap{};
   if constexpr (FUSED) {
-    if (append_here) {
-      ap_slot = block_tables[static_cast<int64_t>(b) * table_stride + last_blk];
-      if (lane < CH) {
-        const int c = lane, pc = (c + CH / 2) % CH;
-        const T* kr = fa.k_new + static_cast<int64_t>(b) * fa.k_stride + static_cast<int64_t>(kvh) * D;
-        ap_x = *reinterpret_cast<const int4*>(kr + 8 * c);
-        ap_p = *reinterpret_cast<const int4*>(kr + 8 * pc);
-        ap_c = *reinterpret_cast<const int4*>(fa.cos_t + static_cast<int64_t>(b) * D + 8 * c);
-        ap_s = *reinterpret_cast<const int4*>(fa.sin_t + static_cast<int64_t>(b) * D + 8 * c);
-      } else if (lane >= 16 && lane < 16 + CH) {
-        const T* vr = fa.v_new + static_cast<int64_t>(b) * fa.v_stride + static_cast<int64_t>(kvh) * D;
-        ap_x = *reinterpret_cast<const int4*>(vr + 8 * (lane - 16));
-      }
-    }
+    if (append_here)
+      ap = append_fetch<T, D>(fa, b, kvh, lane, block_tables[static_cast<int64_t>(b) * table_stride + last_blk]);
   }
 
   // per-lane state for the two q heads g = 2 tq, 2 tq + 1: running max (scaled log2 domain), partial sum, O^T
@@ -289,44 +234,8 @@ paged_attn_tma_kernel(const __grid_constant__ CUtensorMap k_map, const __grid_co
     const uint32_t v_tile = k_tile + S::kTileBytes;
     mbar_wait(bars + st * 8, (i / STAGES) & 1);
 
-    if constexpr (FUSED && decltype(patch)::value) {
-      {
-        // Row r of this tile is the new token.  Lanes 0..D/8-1 rotate one 16-byte chunk of k each, lanes 16.. copy
-        // one chunk of v; both go to the pool (for later steps) and into the staged tile (for this step), after the
-        // TMA copy of the tile has completed, so nothing is written concurrently with the async proxy.
-        const int r = (ctx - 1) & (kTok - 1);
-        const int64_t row_elems = ((ap_slot * Hkv + kvh) * kTok + r) * static_cast<int64_t>(D);
-        if (lane < CH) {
-          const int c = lane;
-          union { int4 raw; T e[8]; } x, xp, cv, sv, o;
-          x.raw = ap_x;
-          xp.raw = ap_p;
-          cv.raw = ap_c;
-          sv.raw = ap_s;
-          const bool first_half = c < CH / 2;
-#pragma unroll
-          for (int e = 0; e < 8; ++e) {
-            const float xf = Cvt<T>::to_f32(x.e[e]);
-            const float pf = first_half ? -Cvt<T>::to_f32(xp.e[e]) : Cvt<T>::to_f32(xp.e[e]);
-            const T a = Cvt<T>::from_f32(__fmul_rn(xf, Cvt<T>::to_f32(cv.e[e])));
-            const T bb = Cvt<T>::from_f32(__fmul_rn(pf, Cvt<T>::to_f32(sv.e[e])));
-            o.e[e] = Cvt<T>::from_f32(__fadd_rn(Cvt<T>::to_f32(a), Cvt<T>::to_f32(bb)));
-          }
-          *reinterpret_cast<int4*>(fa.k_pool + row_elems + 8 * c) = o.raw;
-          asm volatile("st.shared.v4.b32 [%0], {%1,%2,%3,%4};" ::"r"(k_tile + tile_off(r, c)), "r"(o.raw.x), "r"(o.raw.y),
-                       "r"(o.raw.z), "r"(o.raw.w)
-                       : "memory");
-        } else if (lane >= 16 && lane < 16 + CH) {
-          const int c = lane - 16;
-          const int4 raw = ap_x;
-          *reinterpret_cast<int4*>(fa.v_pool + row_elems + 8 * c) = raw;
-          asm volatile("st.shared.v4.b32 [%0], {%1,%2,%3,%4};" ::"r"(v_tile + tile_off(r, c)), "r"(raw.x), "r"(raw.y),
-                       "r"(raw.z), "r"(raw.w)
-                       : "memory");
-        }
-        __syncwarp();
-      }
-    }
+    if constexpr (FUSED && decltype(patch)::value)
+      append_patch<T, D>(ap, fa, Hkv, kvh, (ctx - 1) & (kTok - 1), lane, k_tile, v_tile);
 
     // S^T = K Q^T
     float s[4] = {0.f, 0.f, 0.f, 0.f};

@@ -104,6 +104,120 @@ struct Smem {
 };
 
 
+// ---- fused decode step: RoPE + append inside the attention launch ----------------------------------------------
+// Operands of the fused variants: this step's un-rotated q, the new token's k and v rows and the RoPE tables.  The
+// kernel rotates q in registers, and the one warp that owns a sequence's last KV tile rotates the new k row, writes
+// it and the v row into the pool AND into its staged tile — so RoPE, the KV append and the attention of a decode step
+// are one launch.
+template <typename T>
+struct FusedAppend {
+  const T* k_new;       // [B, Hkv, D], row stride k_stride
+  int64_t k_stride;
+  const T* v_new;
+  int64_t v_stride;
+  const T* cos_t;       // [B, D]
+  const T* sin_t;
+  T* k_pool;            // writable views of the pools behind k_map / v_map
+  T* v_pool;
+};
+
+// rotate-half RoPE on one element pair with torch's rounding points (see b200_layer_ops.cu)
+template <typename T>
+static __device__ __forceinline__ void rope_pair(T x_lo, T x_hi, T c_lo, T s_lo, T c_hi, T s_hi, T& o_lo, T& o_hi) {
+  const float xl = Cvt<T>::to_f32(x_lo), xh = Cvt<T>::to_f32(x_hi);
+  const T a = Cvt<T>::from_f32(__fmul_rn(xl, Cvt<T>::to_f32(c_lo)));
+  const T b = Cvt<T>::from_f32(__fmul_rn(-xh, Cvt<T>::to_f32(s_lo)));
+  o_lo = Cvt<T>::from_f32(__fadd_rn(Cvt<T>::to_f32(a), Cvt<T>::to_f32(b)));
+  const T c = Cvt<T>::from_f32(__fmul_rn(xh, Cvt<T>::to_f32(c_hi)));
+  const T d = Cvt<T>::from_f32(__fmul_rn(xl, Cvt<T>::to_f32(s_hi)));
+  o_hi = Cvt<T>::from_f32(__fadd_rn(Cvt<T>::to_f32(c), Cvt<T>::to_f32(d)));
+}
+
+// RoPE on one query row held as MMA B-operand fragments: `lo` is the register of k-step kk (elements d, d + 1 with
+// d = 16 kk + 8 j + 2 tq), `hi` the same register of k-step kk + D/32 — the rotate-half partners d + D/2 sit in the
+// same lane, so the rotation needs no shuffles.  cs / sn: this sequence's [D] cos / sin rows.
+template <typename T, int D>
+static __device__ __forceinline__ void rope_q_regs(uint32_t& lo_reg, uint32_t& hi_reg, const T* cs, const T* sn, int d) {
+  union { uint32_t u; T e[2]; } lo, hi, c_lo, s_lo, c_hi, s_hi, o_lo, o_hi;
+  lo.u = lo_reg;
+  hi.u = hi_reg;
+  c_lo.u = *reinterpret_cast<const uint32_t*>(cs + d);
+  s_lo.u = *reinterpret_cast<const uint32_t*>(sn + d);
+  c_hi.u = *reinterpret_cast<const uint32_t*>(cs + D / 2 + d);
+  s_hi.u = *reinterpret_cast<const uint32_t*>(sn + D / 2 + d);
+  rope_pair<T>(lo.e[0], hi.e[0], c_lo.e[0], s_lo.e[0], c_hi.e[0], s_hi.e[0], o_lo.e[0], o_hi.e[0]);
+  rope_pair<T>(lo.e[1], hi.e[1], c_lo.e[1], s_lo.e[1], c_hi.e[1], s_hi.e[1], o_lo.e[1], o_hi.e[1]);
+  lo_reg = o_lo.u;
+  hi_reg = o_hi.u;
+}
+
+// The new token's rows, fetched by the appending warp while its first KV tiles are in flight: lanes 0..D/8-1 hold
+// one 16-byte chunk of k (x), its rotate-half partner (p) and the cos / sin chunks; lanes 16.. hold a chunk of v (x).
+struct AppendRows {
+  int4 x, p, c, s;
+  int64_t slot;
+};
+
+template <typename T, int D>
+static __device__ __forceinline__ AppendRows append_fetch(const FusedAppend<T>& fa, int b, int kvh, int lane, int64_t slot) {
+  constexpr int CH = D / 8;  // 16-byte chunks per row
+  AppendRows r;
+  r.x = r.p = r.c = r.s = make_int4(0, 0, 0, 0);
+  r.slot = slot;
+  if (lane < CH) {
+    const int c = lane, pc = (c + CH / 2) % CH;
+    const T* kr = fa.k_new + static_cast<int64_t>(b) * fa.k_stride + static_cast<int64_t>(kvh) * D;
+    r.x = *reinterpret_cast<const int4*>(kr + 8 * c);
+    r.p = *reinterpret_cast<const int4*>(kr + 8 * pc);
+    r.c = *reinterpret_cast<const int4*>(fa.cos_t + static_cast<int64_t>(b) * D + 8 * c);
+    r.s = *reinterpret_cast<const int4*>(fa.sin_t + static_cast<int64_t>(b) * D + 8 * c);
+  } else if (lane >= 16 && lane < 16 + CH) {
+    const T* vr = fa.v_new + static_cast<int64_t>(b) * fa.v_stride + static_cast<int64_t>(kvh) * D;
+    r.x = *reinterpret_cast<const int4*>(vr + 8 * (lane - 16));
+  }
+  return r;
+}
+
+// Row `row` of the staged tile is the new token: rotate k, then write k and v to the pool (for later steps) and into
+// the staged tile (for this step).  Call after the tile's TMA copy has completed, so nothing is written concurrently
+// with the async proxy; ends with __syncwarp().
+template <typename T, int D>
+static __device__ __forceinline__ void append_patch(const AppendRows& pre, const FusedAppend<T>& fa, int Hkv, int kvh,
+                                                    int row, int lane, uint32_t k_tile, uint32_t v_tile) {
+  constexpr int CH = D / 8;
+  const int64_t row_elems = ((pre.slot * Hkv + kvh) * kTok + row) * static_cast<int64_t>(D);
+  if (lane < CH) {
+    const int c = lane;
+    union { int4 raw; T e[8]; } x, xp, cv, sv, o;
+    x.raw = pre.x;
+    xp.raw = pre.p;
+    cv.raw = pre.c;
+    sv.raw = pre.s;
+    const bool first_half = c < CH / 2;
+#pragma unroll
+    for (int e = 0; e < 8; ++e) {
+      const float xf = Cvt<T>::to_f32(x.e[e]);
+      const float pf = first_half ? -Cvt<T>::to_f32(xp.e[e]) : Cvt<T>::to_f32(xp.e[e]);
+      const T a = Cvt<T>::from_f32(__fmul_rn(xf, Cvt<T>::to_f32(cv.e[e])));
+      const T bb = Cvt<T>::from_f32(__fmul_rn(pf, Cvt<T>::to_f32(sv.e[e])));
+      o.e[e] = Cvt<T>::from_f32(__fadd_rn(Cvt<T>::to_f32(a), Cvt<T>::to_f32(bb)));
+    }
+    *reinterpret_cast<int4*>(fa.k_pool + row_elems + 8 * c) = o.raw;
+    asm volatile("st.shared.v4.b32 [%0], {%1,%2,%3,%4};" ::"r"(k_tile + tile_off(row, c)), "r"(o.raw.x), "r"(o.raw.y),
+                 "r"(o.raw.z), "r"(o.raw.w)
+                 : "memory");
+  } else if (lane >= 16 && lane < 16 + CH) {
+    const int c = lane - 16;
+    const int4 raw = pre.x;
+    *reinterpret_cast<int4*>(fa.v_pool + row_elems + 8 * c) = raw;
+    asm volatile("st.shared.v4.b32 [%0], {%1,%2,%3,%4};" ::"r"(v_tile + tile_off(row, c)), "r"(raw.x), "r"(raw.y),
+                 "r"(raw.z), "r"(raw.w)
+                 : "memory");
+  }
+  __syncwarp();
+}
+
+
 // 2D tensor map over a pool viewed as [max_blocks * Hkv * 16 rows, D] with a 64 x 16 box and 128-byte swizzle;
 // cached per (pointer, rows, D, dtype).  Defined in b200_attn_tma.cu.
 int get_tensor_map(const void* pool, uint64_t rows, int D, int dtype, CUtensorMap* out);

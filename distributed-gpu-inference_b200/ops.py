@@ -372,6 +372,56 @@ def paged_decode_attention_prefix(
     return out
 
 
+def rope_append_decode_attention_prefix(
+    q: torch.Tensor,
+    k_new: torch.Tensor,
+    v_new: torch.Tensor,
+    cos: torch.Tensor,
+    sin: torch.Tensor,
+    k_pool: torch.Tensor,
+    v_pool: torch.Tensor,
+    block_tables: torch.Tensor,
+    context_lens: torch.Tensor,
+    max_context_len: int,
+    prefix_blocks: int,
+    scale: Optional[float] = None,
+    out: Optional[torch.Tensor] = None,
+    prefix_splits: int = 0,
+    suffix_splits: int = 0,
+    workspace: Optional[torch.Tensor] = None,
+    flags: int = 0,
+) -> torch.Tensor:
+    """``rope_append_decode_attention`` for a batch that shares its first ``prefix_blocks`` blocks: RoPE, the append
+    of the new token and the cascade attention in one launch (+ the combine).  Every sequence must already be past
+    the shared prefix (shared blocks are never written)."""
+    _need_cuda(k_new, v_new, cos, sin)
+    (B, Hq, Hkv, D, bs, max_blocks), q_stride, table_stride, out = _attn_args(q, k_pool, v_pool, block_tables,
+                                                                               context_lens, out)
+    if cos.shape != (B, D) or sin.shape != (B, D) or not cos.is_contiguous() or not sin.is_contiguous():
+        raise ValueError("cos / sin must be contiguous [B, D]")
+    if not (k_new.dtype == v_new.dtype == cos.dtype == sin.dtype == q.dtype):
+        raise TypeError("q, k_new, v_new, cos and sin must share the pool dtype")
+    if k_new.shape[0] != B or v_new.shape[0] != B:
+        raise ValueError("k_new / v_new must hold one token per sequence")
+    dt = _dtype_id(k_pool)
+    if prefix_splits == 0 or suffix_splits == 0:
+        ps, ss = attn_prefix_plan(B, Hq, Hkv, D, bs, prefix_blocks, max_context_len, q.dtype)
+        prefix_splits = prefix_splits or ps
+        suffix_splits = suffix_splits or ss
+    lib = _lib.load()
+    ws_ptr, ws_bytes, _ws = _split_workspace(lib, B, Hq, D, prefix_splits + suffix_splits, workspace, q.device,
+                                             always=True)
+    with _timed():
+        rc = lib.b200_rope_append_decode_attn_prefix(
+            out.data_ptr(), q.data_ptr(), q_stride, k_new.data_ptr(), _row_stride(k_new, Hkv, D), v_new.data_ptr(),
+            _row_stride(v_new, Hkv, D), cos.data_ptr(), sin.data_ptr(), k_pool.data_ptr(), v_pool.data_ptr(),
+            block_tables.data_ptr(), table_stride, context_lens.data_ptr(), B, Hq, Hkv, D, bs, max_blocks,
+            float(D) ** -0.5 if scale is None else float(scale), int(max_context_len), int(prefix_blocks),
+            int(prefix_splits), int(suffix_splits), ws_ptr, ws_bytes, dt, int(flags), _stream())
+    _lib.check(rc, "b200_rope_append_decode_attn_prefix")
+    return out
+
+
 STATIC_SCRATCH_BYTES = 8 * 1024 * 1024
 
 

@@ -250,6 +250,13 @@ class PagedLlamaDecoderLayer(nn.Module):
                     st.context_lens, st.max_context_len, num_splits=st.num_splits, workspace=st.workspace,
                     flags=st.attn_flags,
                 ).view(B, 1, Hq * D)
+            elif st.prefix_blocks > 0 and ops.fused_decode_supported(past_key_value.k_pool, Hq):
+                # shared prefix: the same one-launch step through the cascade kernel
+                attn = ops.rope_append_decode_attention_prefix(
+                    qf, k[:, 0], v[:, 0], cos2, sin2, past_key_value.k_pool, past_key_value.v_pool, st.block_tables,
+                    st.context_lens, st.max_context_len, st.prefix_blocks, prefix_splits=st.prefix_splits,
+                    suffix_splits=st.suffix_splits, workspace=st.workspace, flags=st.attn_flags,
+                ).view(B, 1, Hq * D)
             else:
                 ops.rope_kv_append(qf, k[:, 0], v[:, 0], cos2, sin2, past_key_value.k_pool, past_key_value.v_pool,
                                    st.slot_mapping)

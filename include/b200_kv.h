@@ -127,6 +127,23 @@ int b200_paged_decode_attn_prefix_plan(int B, int Hq, int Hkv, int D, int block_
                                        int max_context_len, int dtype, int* prefix_splits, int* suffix_splits);
 
 /*
+ * b200_paged_decode_attn_prefix with the decode step's RoPE and KV append inside the same launch (what
+ * b200_rope_append_decode_attn is to b200_paged_decode_attn): q arrives un-rotated; the new token's k row is rotated
+ * and written, with its v row, into the sequence's last block before that block is attended to.  Every sequence must
+ * have at least one token after the shared prefix (context_lens[b] > prefix_blocks * block_size): shared blocks are
+ * never written.  Output and pool contents are bit-identical to b200_rope_kv_append followed by
+ * b200_paged_decode_attn_prefix.
+ */
+int b200_rope_append_decode_attn_prefix(void* out, const void* q, int64_t q_row_stride, const void* k_new,
+                                        int64_t k_row_stride, const void* v_new, int64_t v_row_stride,
+                                        const void* cos_table, const void* sin_table, void* k_pool, void* v_pool,
+                                        const int32_t* block_tables, int table_stride, const int32_t* context_lens,
+                                        int B, int Hq, int Hkv, int D, int block_size, int64_t max_blocks, float scale,
+                                        int max_context_len, int prefix_blocks, int prefix_splits, int suffix_splits,
+                                        void* workspace, size_t workspace_bytes, int dtype, unsigned flags,
+                                        void* stream);
+
+/*
  * Paged decode attention for callers that cannot allocate device memory.  No counterpart in the reference: it
  * exists for hosts that are handed pointers and nothing else — a plugin inside another runtime's serving loop
  * where cudaMalloc is off limits because it stalls the whole device, or a binding without an allocator behind it

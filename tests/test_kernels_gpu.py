@@ -538,6 +538,39 @@ def test_fused_rope_append_attention_equals_the_separate_kernels(dtype, B, Hq, H
     assert torch.equal(_bits(q), _bits(q_before))  # q is left un-rotated
 
 
+@pytest.mark.parametrize("dtype", [torch.bfloat16, torch.float16])
+@pytest.mark.parametrize("B,Hq,Hkv,D,prefix,tails", [
+    (4, 32, 8, 128, 640, [33, 1, 16, 250]),      # 8B shape; a tail of one token, an exact block, ragged
+    (3, 8, 2, 64, 160, [17, 160, 5]),            # config-1 shape
+    (8, 64, 8, 128, 2048, [100 + 37 * i for i in range(8)]),  # 70B shape, group 8
+])
+def test_fused_rope_append_cascade_equals_the_separate_kernels(dtype, B, Hq, Hkv, D, prefix, tails):
+    bs = 16
+    ctx = [prefix + t for t in tails]
+    q, k_pool, v_pool, tables, lens = _attn_case(B, Hq, Hkv, D, bs, ctx, dtype, seed=B + D, share_prefix_blocks=prefix // bs,
+                                                 q_strided=True)
+    g = torch.Generator(device=DEV).manual_seed(77)
+    kv_new = torch.randn((B, 2 * Hkv * D), generator=g, device=DEV).to(dtype)
+    k_new, v_new = kv_new[:, :Hkv * D].view(B, Hkv, D), kv_new[:, Hkv * D:].view(B, Hkv, D)
+    pos = (lens - 1).to(torch.int64)
+    inv_freq = 1.0 / (500000.0 ** (torch.arange(0, D, 2, device=DEV).float() / D))
+    emb = torch.cat((pos.float()[:, None] * inv_freq[None],) * 2, -1)
+    cos, sin = emb.cos().to(dtype), emb.sin().to(dtype)
+    slots = tables.long().gather(1, (pos // bs)[:, None]).squeeze(1) * bs + pos % bs
+    k_ref, v_ref, q_ref = k_pool.clone(), v_pool.clone(), q.clone()
+    ops.rope_kv_append(q_ref, k_new, v_new, cos, sin, k_ref, v_ref, slots)
+    want = ops.paged_decode_attention_prefix(q_ref, k_ref, v_ref, tables, lens, max(ctx), prefix // bs)
+    q_before = q.clone()
+    got = ops.rope_append_decode_attention_prefix(q, k_new, v_new, cos, sin, k_pool, v_pool, tables, lens, max(ctx),
+                                                  prefix // bs)
+    assert torch.equal(_bits(got), _bits(want))
+    assert torch.equal(_bits(k_pool), _bits(k_ref)) and torch.equal(_bits(v_pool), _bits(v_ref))
+    assert torch.equal(_bits(q), _bits(q_before))
+    # and against the oracle on the patched pools
+    exact = R.paged_attention_ref(q_ref, k_ref, v_ref, tables, lens, mode="fp32")
+    assert _rel_err(got, exact) <= (1e-2 if dtype == torch.bfloat16 else 2e-3)
+
+
 def test_fused_decode_entry_rejects_other_shapes():
     from dgi_b200._lib import B200LibraryError
 
