@@ -409,9 +409,9 @@ def run_single(args, workload):
         except Exception:  # noqa: BLE001
             traffic = None
     # this repo's kernels per step: per layer add_rmsnorm x2, the one-launch RoPE + append + attention (+ combine when
-    # split), silu_mul; + the final norm and the argmax over the logits.  With a shared prefix: rope_kv_append +
-    # cascade + combine instead.
-    per_layer = 6 if eng.state.prefix_blocks else 4 + (1 if eng.num_splits > 1 else 0)
+    # split), silu_mul; + the final norm and the argmax over the logits.  With a shared prefix the one-launch step goes
+    # through the cascade kernel, which always has a combine.
+    per_layer = 5 if eng.state.prefix_blocks else 4 + (1 if eng.num_splits > 1 else 0)
     launches_per_step = cfg.num_hidden_layers * per_layer + 2
 
     line = {
