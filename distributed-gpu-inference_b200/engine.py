@@ -139,6 +139,8 @@ class PagedDecodeEngine:
         self.prefix_index: Optional[List[RadixPrefixIndex]] = (
             [RadixPrefixIndex(pool, hold=True) for pool in self.pools] if prefix_cache else None)
         self.cached_blocks = 0
+        self._shared_blocks = 0
+        self._prefix_tokens: Optional[List[int]] = None
         if len(self.pools) != len(self.shards) or any(
                 p.num_layers != s.get_layer_count() for p, s in zip(self.pools, self.shards)):
             raise ValueError("kv_pools must hold one pool per shard with that shard's layer count")
@@ -273,6 +275,7 @@ class PagedDecodeEngine:
             self._graph = None
             self._graph_chained = None
         self._set_prefix(0)
+        self._shared_blocks, self.cached_blocks, self._prefix_tokens = 0, 0, None
 
     # ---- prefill -------------------------------------------------------------------------------------
     @torch.no_grad()
@@ -321,7 +324,7 @@ class PagedDecodeEngine:
         out_tokens = torch.empty((B,), dtype=torch.int64, device=self.device)
         start = 0
         bs = self.block_size
-        shared = getattr(self, "_shared_blocks", 0) * bs   # tokens whose blocks all sequences have in common
+        shared = self._shared_blocks * bs   # tokens whose blocks all sequences have in common
         cached = self.cached_blocks * bs                    # the part of those an earlier request already computed
         if shared > 0:
             if not bool((prompt_ids[:, :shared] == prompt_ids[0, :shared]).all()):
