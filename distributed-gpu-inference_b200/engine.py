@@ -462,12 +462,17 @@ class PagedDecodeEngine:
         return torch.stack(out, dim=1)
 
     @torch.no_grad()
-    def generate_ragged(self, prompts: Sequence[Sequence[int]], max_new_tokens: int) -> List[List[int]]:
+    def generate_ragged(self, prompts: Sequence[Sequence[int]], max_new_tokens: int,
+                        shared_prefix_len: int = 0) -> List[List[int]]:
         """Greedy generation for prompts of DIFFERENT lengths as one decode batch.
 
         The prompt pass runs once per distinct length (sequences are ordered by length so that each length is a
         contiguous slice of the batch); the decode steps then run over all sequences together — context lengths,
         positions and slots are per sequence on the device anyway.  Returns the new tokens in the callers' order.
+
+        ``shared_prefix_len``: leading tokens common to ALL prompts (a system prompt in front of user messages of
+        different lengths).  Their blocks are shared as in ``generate`` — computed once by the shortest prompt's
+        sequence, or taken from the prefix cache — and decode runs through the cascade kernel over the ragged tails.
         """
         order = sorted(range(len(prompts)), key=lambda i: len(prompts[i]))
         lens = [len(prompts[i]) for i in order]
@@ -476,17 +481,33 @@ class PagedDecodeEngine:
             return []
         if min(lens) < 1:
             raise ValueError("empty prompt")
-        self.allocate(B, max(lens) + max_new_tokens)
+        n_pre = max(0, min(shared_prefix_len, min(lens) - 1))
+        head = list(prompts[order[0]][:n_pre])
+        if n_pre and any(list(p[:n_pre]) != head for p in prompts):
+            raise ValueError("prompts do not share the declared prefix")
+        self.allocate(B, max(lens) + max_new_tokens, shared_prefix_len=n_pre,
+                      prefix_tokens=head if self.prefix_index is not None and n_pre else None)
+        bs = self.block_size
+        shared, cached = self._shared_blocks * bs, self.cached_blocks * bs
         first = torch.empty((B,), dtype=torch.int64, device=self.device)
         lo = 0
+        if shared > 0:
+            # the shortest prompt's sequence computes what is left of the shared blocks, then its own tokens
+            ids = torch.tensor([list(prompts[order[0]])[cached:]], dtype=torch.int64, device=self.device)
+            first[0:1] = self.prefill_chunk(0, 1, ids, past_len=cached)
+            if self.prefix_index is not None and self._prefix_tokens is not None:
+                for si, idx in enumerate(self.prefix_index):
+                    idx.insert(self._prefix_tokens, [lb[:shared // bs] for lb in self._seq_blocks[0][si]])
+            lo = 1
         while lo < B:
             hi = lo
             while hi < B and lens[hi] == lens[lo]:
                 hi += 1
             for c0 in range(lo, hi, self.prefill_chunk_size):
                 c1 = min(hi, c0 + self.prefill_chunk_size)
-                ids = torch.tensor([list(prompts[order[i]]) for i in range(c0, c1)], dtype=torch.int64, device=self.device)
-                first[c0:c1] = self.prefill_chunk(c0, c1, ids)
+                ids = torch.tensor([list(prompts[order[i]])[shared:] for i in range(c0, c1)], dtype=torch.int64,
+                                   device=self.device)
+                first[c0:c1] = self.prefill_chunk(c0, c1, ids, past_len=shared)
             lo = hi
         out = [first.cpu()]
         nxt = out[0]

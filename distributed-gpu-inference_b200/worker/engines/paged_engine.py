@@ -144,12 +144,13 @@ class PagedLLMEngine:
             except Exception as exc:  # noqa: BLE001
                 results[i] = exc
         eng = self.engine
-        # requests without a system prompt form one ragged batch whatever their lengths; requests that share a system
-        # prompt AND a length are decoded with the prompt's blocks shared
+        # One batch per system prompt, whatever the lengths of the user parts: the system prompt's blocks are shared
+        # (and cached for later calls), the ragged tails decode together.  Requests without a system prompt form one
+        # ragged batch of their own.
         merged: Dict[Any, List[int]] = {}
-        for (plen, sys_ids), idxs in groups.items():
-            merged.setdefault((plen, sys_ids) if sys_ids else ("ragged", ()), []).extend(idxs)
-        for (plen, sys_ids), idxs in merged.items():
+        for (_plen, sys_ids), idxs in groups.items():
+            merged.setdefault(sys_ids, []).extend(idxs)
+        for sys_ids, idxs in merged.items():
             for lo in range(0, len(idxs), eng.max_batch):
                 part = idxs[lo:lo + eng.max_batch]
                 try:
@@ -157,19 +158,17 @@ class PagedLLMEngine:
                     longest = max(len(parsed[i][0]) for i in part)
                     if longest + n_new > eng.max_seq_len:
                         raise ValueError(f"prompt of {longest} tokens + {n_new} new tokens exceeds max_model_len")
-                    if plen == "ragged":
-                        rows = eng.generate_ragged([parsed[i][0] for i in part], n_new)
-                        cached = 0
-                    else:
-                        ids = torch.tensor([parsed[i][0] for i in part], dtype=torch.int64)
-                        shared = len(sys_ids) if (len(part) > 1 or eng.prefix_index is not None) else 0
-                        rows = eng.generate(ids, n_new, shared_prefix_len=shared).tolist()
-                        cached = (min(shared, plen - 1) // eng.block_size) * eng.block_size
-                    # tokens whose KV was not computed for this request: row 0 only skips what an EARLIER call left in
-                    # the prefix cache, the other rows also skip what row 0 has just computed
-                    first = eng.cached_blocks * eng.block_size if plen != "ragged" else 0
+                    share = len(sys_ids) if (len(part) > 1 or eng.prefix_index is not None) else 0
+                    rows = eng.generate_ragged([parsed[i][0] for i in part], n_new, shared_prefix_len=share)
+                    # tokens whose KV was not computed for this request: the sequence that owns the shared blocks
+                    # (the shortest prompt) only skips what an EARLIER call left in the prefix cache, the others also
+                    # skip what that sequence has just computed
+                    shared_tok = eng._shared_blocks * eng.block_size
+                    cached_tok = eng.cached_blocks * eng.block_size
+                    owner = min(range(len(part)), key=lambda r: len(parsed[part[r]][0]))
                     for row, i in enumerate(part):
-                        results[i] = self._result(rows[row][:parsed[i][2]], len(parsed[i][0]), cached if row > 0 else first)
+                        results[i] = self._result(rows[row][:parsed[i][2]], len(parsed[i][0]),
+                                                  cached_tok if row == owner else shared_tok)
                 except Exception as exc:  # noqa: BLE001
                     for i in part:
                         results[i] = exc

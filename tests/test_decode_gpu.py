@@ -227,6 +227,17 @@ def test_batcher_to_engine_adapter_end_to_end(golden):
     assert out[0]["usage"]["cached_tokens"] == 0 and out[1]["usage"]["cached_tokens"] == 80
     assert eng.engine.prefix_blocks == 5
     assert eng.get_backend_info()["supports_batch_inference"] is True
+    # second call: the same system prompt in front of user messages of DIFFERENT lengths -> still one batch (ragged
+    # tails over shared blocks), and the system prompt now comes out of the prefix cache for every row
+    questions2 = ["a", "bbbbbbbbbbbbbbbbbbbbbbbbb", "cc"]
+    reqs2 = [{"messages": [{"role": "system", "content": system}, {"role": "user", "content": qn}], "max_tokens": 5}
+             for qn in questions2]
+    out2 = eng.batch_inference(reqs2)
+    assert eng.engine.batch == 3 and eng.engine.cached_blocks == 5 and eng.engine.prefix_blocks == 5
+    for r, qn in zip(out2, questions2):
+        ids = tok.encode(system) + tok.encode(f"user: {qn}")[1:]
+        want = L.greedy_decode(L.build_shards(cfg, sd, [(0, 4)]), torch.tensor([ids]), 5)[0].tolist()
+        assert r["output_ids"] == want and r["usage"]["cached_tokens"] == 80
     eng.unload_model()
 
 
@@ -396,3 +407,35 @@ def test_sequences_swapped_to_host_and_back_decode_the_same_tokens(golden):
     for _ in range(n_new - 1):
         out.append(eng.decode_step(out[-1]))
     assert torch.stack(out, 1).tolist() == [row[:n_new] for row in g["tokens"]]
+
+
+def test_ragged_prompts_behind_one_system_prompt_share_its_blocks(golden):
+    """generate_ragged(shared_prefix_len=...): prompts of different lengths that start with the same tokens are one
+    batch; the common blocks are computed once (by the shortest prompt's sequence) and decode runs through the
+    cascade kernel over ragged tails.  Tokens equal those of independent sequences."""
+    g, cfg, sd = _tiny(golden)
+    base = torch.tensor(g["prompt_ids"])
+    sys_len = 70  # 4 full blocks shared, 6 tokens of the prefix fall into each sequence's own fifth block
+    lens = [128, 75, 100, 75, 71]
+    prompts = []
+    for i, n in enumerate(lens):
+        row = base[i % 4, :n].clone()
+        row[:sys_len] = base[0, :sys_len]
+        prompts.append(row.tolist())
+    ref_shards = L.build_shards(cfg, sd, [(0, 4)])
+    want = [L.greedy_decode(ref_shards, torch.tensor([p]), 10)[0].tolist() for p in prompts]
+    for dtype in (torch.float32, torch.bfloat16):
+        shards = build_product_shards(cfg, sd, [(0, 2), (2, 4)], DEV, dtype)
+        eng = PagedDecodeEngine(shards, 5, 160, prefill_mode="eager")
+        got = eng.generate_ragged(prompts, 10, shared_prefix_len=sys_len)
+        tables = eng.block_tables[:5].cpu()
+        assert eng._shared_blocks == 4 and (tables[:, :4] == tables[0, :4]).all() and len(set(tables[:, 4].tolist())) == 5
+        assert eng._seq_blocks[0][0][0][0].ref_count == 5
+        if dtype == torch.float32:
+            assert got == want
+        else:
+            assert eng.state.prefix_blocks == 4  # cascade kernel in use
+            agree = sum(a == b for ga, wa in zip(got, want) for a, b in zip(ga, wa)) / 50
+            assert [r[0] for r in got] == [r[0] for r in want] and agree > 0.6
+        with pytest.raises(ValueError, match="do not share"):
+            eng.generate_ragged([prompts[0], [1] + prompts[1][1:]], 4, shared_prefix_len=sys_len)
