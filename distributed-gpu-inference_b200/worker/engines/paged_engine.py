@@ -114,12 +114,19 @@ class PagedLLMEngine:
         return sys_ids + rest_ids, len(sys_ids)
 
     def _result(self, out_ids: List[int], n_prompt: int, cached: int) -> Dict[str, Any]:
+        # a batch decodes to the longest request's budget; a sequence that produced its end-of-sequence token is cut
+        # there (the token itself is not part of the answer), like the reference's engines report "stop" vs "length"
+        finish = "length"
+        eos = getattr(self.tokenizer, "eos_token_id", None)
+        if eos is not None and eos in out_ids:
+            out_ids = out_ids[:out_ids.index(eos)]
+            finish = "stop"
         return {
             "response": self.tokenizer.decode(out_ids),
             "output_ids": out_ids,
             "usage": {"prompt_tokens": n_prompt, "completion_tokens": len(out_ids),
                       "total_tokens": n_prompt + len(out_ids), "cached_tokens": cached},
-            "finish_reason": "length",
+            "finish_reason": finish,
         }
 
     def inference(self, params: Dict[str, Any]) -> Dict[str, Any]:
