@@ -629,19 +629,30 @@ class RadixPrefixIndex:
             if blks is None:
                 break
             if not self._alive(blks):
-                del self._by_hash[h]  # freed (or evicted) since it was indexed
+                # freed (or evicted) since it was indexed.  Hashes are chained, so whatever was registered BEHIND this
+                # block can never be reached again: give those blocks back now instead of waiting for the LRU.
+                for dead in hashes[n:]:
+                    self._forget(dead)
                 break
             for l, b in enumerate(blks):
-                self.pool.layer(l).get_block(b.block_id)  # LRU touch + hit statistics, as a reader of the block would
                 per_layer[l].append(b)
             n += 1
+        # LRU touch (and hit statistics), last block first: the head of a chain ends up most recently used, so under
+        # pressure eviction shortens cached prefixes from the tail and what remains is still a usable prefix
+        for i in range(n - 1, -1, -1):
+            for l in range(self.pool.num_layers):
+                self.pool.layer(l).get_block(per_layer[l][i].block_id)
         self.stats["hit_blocks"] += n
         return n, (per_layer if n else None)
 
+    def _forget(self, h: str) -> None:
+        blks = self._by_hash.pop(h, None)
+        if blks is not None and self.hold:
+            for l, b in enumerate(blks):
+                if self.pool.layer(l)._blocks.get(b.block_id) is b:
+                    self.pool.layer(l).free_blocks([b.block_id])
+
     def drop_all(self) -> None:
         """Forget every entry, giving back the references a holding index took."""
-        for blks in self._by_hash.values():
-            if self.hold and self._alive(blks):
-                for l, b in enumerate(blks):
-                    self.pool.layer(l).free_blocks([b.block_id])
-        self._by_hash.clear()
+        for h in list(self._by_hash):
+            self._forget(h)

@@ -138,3 +138,40 @@ def test_batched_free_equals_block_by_block_free():
     assert torch.equal(a.key_pool, b.key_pool) and b.key_pool[5].eq(1).all() and b.key_pool[6].eq(0).all()
     assert a.get_stats() == b.get_stats()
     assert ids_a == ids_b
+
+
+def test_holding_prefix_index_is_a_cache_that_eviction_trims_from_the_tail():
+    pool = kv.KVCachePool(2, 2, 8, 4, 8, device="cpu")
+    idx = kv.RadixPrefixIndex(pool, hold=True)
+    toks = list(range(1000, 1016))                      # 4 full blocks
+    seq = pool.allocate_sequence(18)                    # 5 blocks per layer
+    assert idx.insert(toks, seq) == 4 and [b.ref_count for b in seq[0]] == [2, 2, 2, 2, 1]
+    pool.free_sequence(seq)                             # the sequence goes, the cache keeps its four blocks
+    assert all(c.get_stats()["free_blocks"] == 4 for c in pool._layer_caches)
+    n, blocks = idx.match(toks)
+    assert n == 4 and [b.ref_count for b in blocks[0]] == [1, 1, 1, 1]
+    other = pool.allocate_sequence(6 * 4)               # needs 6 of 8 blocks: two cached ones must be evicted ...
+    n2, blocks2 = idx.match(toks)
+    assert n2 == 2                                      # ... and they are the TAIL of the chain: the head still serves
+    assert [b.block_id for b in blocks2[0]] == [b.block_id for b in blocks[0][:2]]
+    assert sum(c.get_stats()["evictions"] for c in pool._layer_caches) == 4
+    # an id that was evicted and handed out again is not mistaken for the cached block
+    assert all(pool.layer(0)._blocks[b.block_id] is b for b in blocks2[0])
+    reused = {b.block_id for b in other[0]} & {b.block_id for b in blocks[0][2:]}
+    assert reused and idx.match(toks)[0] == 2
+    pool.free_sequence(other)
+    idx.drop_all()
+    assert all(c.get_stats()["free_blocks"] == 8 for c in pool._layer_caches)
+
+
+def test_unreachable_tail_of_a_broken_chain_is_released_on_lookup():
+    pool = kv.KVCachePool(1, 2, 8, 4, 8, device="cpu")
+    idx = kv.RadixPrefixIndex(pool, hold=True)
+    toks = list(range(500, 512))                        # 3 full blocks
+    seq = pool.allocate_sequence(12)
+    idx.insert(toks, seq)
+    pool.free_sequence(seq)
+    pool.layer(0).free_blocks([seq[0][1].block_id])     # the middle block disappears (say, evicted)
+    assert pool.layer(0).get_stats()["free_blocks"] == 6
+    assert idx.match(toks)[0] == 1                      # only the head is usable ...
+    assert pool.layer(0).get_stats()["free_blocks"] == 7  # ... and the block behind the gap was given back

@@ -83,7 +83,10 @@ def attn_case(name, B, Hq, Hkv, D, ctx_lens, layers, splits, flags=0, share_pref
 
     def run(i):
         k, v = pools[i % layers]
-        if fused:
+        if fused and cascade:
+            ops.rope_append_decode_attention_prefix(q, k_new, v_new, cs, sn, k, v, tables, lens, max_ctx, share_prefix,
+                                                    out=out, workspace=ws, flags=flags, prefix_splits=ps, suffix_splits=ss)
+        elif fused:
             ops.rope_append_decode_attention(q, k_new, v_new, cs, sn, k, v, tables, lens, max_ctx, out=out,
                                              num_splits=splits, workspace=ws, flags=flags)
         elif cascade:
@@ -188,6 +191,10 @@ if __name__ == "__main__":
             lens = [24576 + 8192 - 512 * i for i in range(8)]
             attn_case("cfg5 cascade", 8, 32, 8, 128, lens, a.layers, a.splits, fl, share_prefix=24576 // 16, iters=a.iters,
                       cascade=True)
+        elif c == "cfg5cf":
+            lens = [24576 + 8192 - 512 * i for i in range(8)]
+            attn_case("cfg5 cascade, fused RoPE + append", 8, 32, 8, 128, lens, a.layers, a.splits, fl,
+                      share_prefix=24576 // 16, iters=a.iters, cascade=True, fused=True)
         elif c == "prefix64":
             lens64 = [2048 + 64 + 16 * (i % 8) for i in range(64)]
             attn_case("8B B64, shared 2048-token system prompt + short tails, plain", 64, 32, 8, 128, lens64, a.layers,
