@@ -82,7 +82,7 @@ def main():
             sys.modules[alias] = importlib.import_module(real)
     files = [os.path.join(REF, f) for f in FILES if os.path.exists(os.path.join(REF, f))]
     args = ["-q", "-p", "no:cacheprovider", "--rootdir", "/tmp/reftests", "-c", "/dev/null", "--noconftest",
-            "-W", "ignore", "--continue-on-collection-errors"] + files + sys.argv[1:]
+            "-W", "ignore", "--continue-on-collection-errors", "--timeout", "120"] + files + sys.argv[1:]
     return pytest.main(args, plugins=[AsyncRunner()])
 
 
