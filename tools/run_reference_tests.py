@@ -80,6 +80,7 @@ def main():
 
         for alias, real in ALIASES.items():
             sys.modules[alias] = importlib.import_module(real)
+    os.makedirs("/tmp/reftests", exist_ok=True)  # pytest's rootdir: anywhere but the read-only reference checkout
     files = [os.path.join(REF, f) for f in FILES if os.path.exists(os.path.join(REF, f))]
     args = ["-q", "-p", "no:cacheprovider", "--rootdir", "/tmp/reftests", "-c", "/dev/null", "--noconftest",
             "-W", "ignore", "--continue-on-collection-errors", "--timeout", "120"] + files + sys.argv[1:]
