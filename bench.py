@@ -464,7 +464,7 @@ def run_single(args, workload):
     }
     line["kv_pack"] = measure_pack_unpack(dev)
     if not args.no_cpu_baseline:
-        res = cpu_reference_tokens_per_s(workload["shape"], B, ctx, steps=2, warmup=1)
+        res = cpu_reference_tokens_per_s(workload["shape"], B, ctx, steps=10, warmup=2)  # about 10 s of host work
         line["cpu_baseline"] = {k: res[k] for k in ("value", "unit", "cores", "kind", "sample")}
         line["kv_pack"]["cpu_reference_handoff"] = cpu_handoff_reference()
     print(json.dumps(line), flush=True)
