@@ -29,6 +29,10 @@ int plan_splits(int B, int Hkv, int block_size, int max_context_len) {
   const int min_blocks = std::max(1, 256 / block_size);
   const int max_by_len = std::max(1, n_blocks / min_blocks);
   int splits = std::max(1, ceil_div(kNumSMs * 7 / 2, pairs));
+  // One or two long sequences (pairs <= 16): exactly one wave of CTAs (2 per SM) beats 1.75 waves of shorter ones —
+  // batch 1 at 16k / 32k / 64k / 128k context: 37 splits 25.7 / 32.5 / 52.7 / 92.6 us vs 26.7 / 35.7 / 56.6 / 94.5 us;
+  // batch 2 at 32k: 18 splits 54.3 vs 55.3 us.  Not so from 32 pairs up (batch 4 at 8k: 9 splits 35.3 us, 17: 33.2 us).
+  if (pairs <= 16) splits = std::min(splits, std::max(1, 2 * kNumSMs / pairs));
   splits = std::min(splits, max_by_len);
   return std::min(splits, 128);
 }

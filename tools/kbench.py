@@ -171,6 +171,9 @@ if __name__ == "__main__":
                       fl, iters=a.iters, fused=True)
         elif c == "b1_32k":
             attn_case("8B B1 ctx32k (single long sequence)", 1, 32, 8, 128, [32768], a.layers, a.splits, fl, iters=a.iters)
+        elif c in ("b1_16k", "b1_64k", "b2_32k"):
+            nb, nctx = (2, 32768) if c == "b2_32k" else (1, 16384 if c == "b1_16k" else 65536)
+            attn_case(f"8B B{nb} ctx{nctx // 1024}k", nb, 32, 8, 128, [nctx] * nb, a.layers, a.splits, fl, iters=a.iters)
         elif c == "b1_128k":
             attn_case("8B B1 ctx128k (single long sequence)", 1, 32, 8, 128, [131072], min(a.layers, 4), a.splits, fl,
                       iters=a.iters)
