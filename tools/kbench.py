@@ -174,6 +174,9 @@ if __name__ == "__main__":
         elif c in ("b1_16k", "b1_64k", "b2_32k"):
             nb, nctx = (2, 32768) if c == "b2_32k" else (1, 16384 if c == "b1_16k" else 65536)
             attn_case(f"8B B{nb} ctx{nctx // 1024}k", nb, 32, 8, 128, [nctx] * nb, a.layers, a.splits, fl, iters=a.iters)
+        elif c in ("b1_2k", "b1_4k", "b8_2k"):
+            nb, nctx = {"b1_2k": (1, 2048), "b1_4k": (1, 4096), "b8_2k": (8, 2048)}[c]
+            attn_case(f"8B B{nb} ctx{nctx // 1024}k", nb, 32, 8, 128, [nctx] * nb, a.layers, a.splits, fl, iters=a.iters)
         elif c == "b1_128k":
             attn_case("8B B1 ctx128k (single long sequence)", 1, 32, 8, 128, [131072], min(a.layers, 4), a.splits, fl,
                       iters=a.iters)
