@@ -77,3 +77,40 @@ def test_integration_doc_stub_binds_the_real_library():
         assert list(getattr(ns["_lib"], name).argtypes) == list(_lib.SIGNATURES[name][1]), name
     assert ns["_lib"].b200_paged_decode_attn_workspace.restype is ctypes.c_size_t
     assert ns["_DT"] == ops.DTYPE_ID and callable(ns["kv_append"])
+
+
+def test_header_is_plain_c_and_the_library_links_from_c(tmp_path):
+    """The boundary is a C ABI: include/b200_kv.h must compile as C (gcc -std=c99 -pedantic) and a C program must be
+    able to link libb200_kv.so and call it.  Only host-side entry points are exercised (no GPU needed)."""
+    import shutil
+    import subprocess
+
+    if shutil.which("gcc") is None:
+        pytest.skip("gcc not available")
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    src = tmp_path / "probe.c"
+    src.write_text(r'''
+#include <stdio.h>
+#include <string.h>
+#include "b200_kv.h"
+int main(void) {
+  if (b200_abi_version() != B200_ABI_VERSION) return 1;
+  if (b200_paged_decode_attn_workspace(64, 32, 128, 1) != 0) return 2;
+  if (b200_paged_decode_attn_workspace(2, 4, 64, 3) != (size_t)2 * 4 * 3 * (64 + 2) * sizeof(float)) return 3;
+  if (b200_paged_decode_attn_plan(64, 32, 8, 128, 16, 2048, B200_DTYPE_BF16) != 1) return 4;
+  int rc = b200_kv_append(NULL, NULL, 0, 0, NULL, NULL, NULL, 4, 8, 128, 16, 32, B200_DTYPE_BF16, NULL);
+  if (rc != B200_EINVAL || strlen(b200_last_error()) == 0) return 5;
+  rc = b200_kv_append(NULL, NULL, 0, 0, NULL, NULL, NULL, 4, 8, 128, 16, 32, 77, NULL);
+  if (rc != B200_EINVAL) return 6;
+  printf("ok %s\n", b200_last_error());
+  return 0;
+}
+''')
+    exe = tmp_path / "probe"
+    libdir = os.path.dirname(_lib.LIB_PATH)
+    cmd = ["gcc", "-std=c99", "-pedantic", "-Wall", "-Werror", "-I", os.path.join(root, "include"), str(src), "-o", str(exe),
+           "-L", libdir, "-l:libb200_kv.so", f"-Wl,-rpath,{libdir}", "-Wl,--allow-shlib-undefined"]
+    res = subprocess.run(cmd, capture_output=True, text=True)
+    assert res.returncode == 0, res.stderr
+    run = subprocess.run([str(exe)], capture_output=True, text=True)
+    assert run.returncode == 0 and run.stdout.startswith("ok "), (run.returncode, run.stdout, run.stderr)
