@@ -44,7 +44,10 @@ __device__ __forceinline__ float block_sum(float v, float* red) {
 constexpr int kNormThreads = 256;
 constexpr int kNormMaxVec = 8;  // vectors cached in registers per thread: hidden <= 256 * 8 * (16 / sizeof(T))
 
-template <typename T>
+// NV = 16-byte vectors cached per thread (ceil(hidden / VN / 256)): sizing the register cache to the row keeps the
+// kernel at ~40 registers for hidden = 4096 instead of ~90, i.e. 6 instead of 2 CTAs per SM when thousands of rows
+// (a prompt pass) are in flight.  Arithmetic and its order do not depend on NV.
+template <typename T, int NV>
 __global__ void __launch_bounds__(kNormThreads)
 add_rmsnorm_kernel(T* __restrict__ out, T* __restrict__ resid_out, const T* __restrict__ x, const T* __restrict__ delta,
                    const T* __restrict__ weight, float eps, int hidden, int64_t x_stride, int64_t d_stride) {
@@ -54,15 +57,15 @@ add_rmsnorm_kernel(T* __restrict__ out, T* __restrict__ resid_out, const T* __re
   const T* xr = x + row * x_stride;
   const T* dr = delta ? delta + row * d_stride : nullptr;
   const int nvec = hidden / VN;
-  Vec16<T> cache[kNormMaxVec], wcache[kNormMaxVec];
+  Vec16<T> cache[NV], wcache[NV];
   float ss = 0.f;
 #pragma unroll
-  for (int i = 0; i < kNormMaxVec; ++i) {  // weights first: their latency hides behind the row loads + reduction
+  for (int i = 0; i < NV; ++i) {  // weights first: their latency hides behind the row loads + reduction
     const int v = threadIdx.x + i * kNormThreads;
     if (v < nvec) wcache[i].raw = *reinterpret_cast<const int4*>(weight + v * VN);
   }
 #pragma unroll
-  for (int i = 0; i < kNormMaxVec; ++i) {
+  for (int i = 0; i < NV; ++i) {
     const int v = threadIdx.x + i * kNormThreads;
     if (v < nvec) {
       cache[i].raw = *reinterpret_cast<const int4*>(xr + v * VN);
@@ -84,7 +87,7 @@ add_rmsnorm_kernel(T* __restrict__ out, T* __restrict__ resid_out, const T* __re
   const float total = block_sum(ss, red);
   const float inv = rsqrtf(total * (1.0f / static_cast<float>(hidden)) + eps);  // torch's mean multiplies by 1/N
 #pragma unroll
-  for (int i = 0; i < kNormMaxVec; ++i) {
+  for (int i = 0; i < NV; ++i) {
     const int v = threadIdx.x + i * kNormThreads;
     if (v < nvec) {
       Vec16<T> ov;
@@ -292,9 +295,16 @@ int add_rmsnorm(void* out, void* resid_out, const void* x, const void* delta, co
     return fail(B200_ESHAPE, "b200_add_rmsnorm: hidden=%d / alignment not supported", hidden);
   return by_dtype(dtype, "b200_add_rmsnorm", [&](auto* tag) {
     using T = std::remove_pointer_t<decltype(tag)>;
-    add_rmsnorm_kernel<T><<<rows, kNormThreads, 0, s>>>(static_cast<T*>(out), static_cast<T*>(resid_out),
-                                                        static_cast<const T*>(x), static_cast<const T*>(delta),
-                                                        static_cast<const T*>(weight), eps, hidden, x_stride, d_stride);
+    const int nv = (hidden / (16 / static_cast<int>(sizeof(T))) + kNormThreads - 1) / kNormThreads;
+    auto launch = [&](auto kern) {
+      kern<<<rows, kNormThreads, 0, s>>>(static_cast<T*>(out), static_cast<T*>(resid_out), static_cast<const T*>(x),
+                                         static_cast<const T*>(delta), static_cast<const T*>(weight), eps, hidden, x_stride,
+                                         d_stride);
+    };
+    if (nv <= 1) launch(add_rmsnorm_kernel<T, 1>);
+    else if (nv <= 2) launch(add_rmsnorm_kernel<T, 2>);
+    else if (nv <= 4) launch(add_rmsnorm_kernel<T, 4>);
+    else launch(add_rmsnorm_kernel<T, kNormMaxVec>);
     return check_launch("b200_add_rmsnorm");
   });
 }
