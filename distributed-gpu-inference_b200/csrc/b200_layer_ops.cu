@@ -177,17 +177,16 @@ rope_append_kernel(T* __restrict__ q, int64_t q_stride, const T* k, int64_t k_st
 }
 
 // ---- SiLU(gate) * up -------------------------------------------------------------------------------------
+// Grid (column chunks, rows): a thread takes one 16-byte vector of one row, rows beyond gridDim.y are walked with a
+// stride — no per-element index division (the flat-index version spent ~40 % of its instructions on 64-bit div/mod).
 template <typename T>
 __global__ void __launch_bounds__(256)
 silu_mul_kernel(T* __restrict__ out, const T* __restrict__ gate, const T* __restrict__ up, int64_t rows, int cols,
                 int64_t g_stride, int64_t u_stride) {
   constexpr int VN = Vec16<T>::N;
-  const int vec_per_row = cols / VN;
-  const int64_t total = rows * vec_per_row;
-  for (int64_t i = static_cast<int64_t>(blockIdx.x) * blockDim.x + threadIdx.x; i < total;
-       i += static_cast<int64_t>(gridDim.x) * blockDim.x) {
-    const int64_t r = i / vec_per_row;
-    const int c = static_cast<int>(i - r * vec_per_row) * VN;
+  const int c = (blockIdx.x * blockDim.x + threadIdx.x) * VN;
+  if (c >= cols) return;
+  for (int64_t r = blockIdx.y; r < rows; r += gridDim.y) {
     Vec16<T> g, u, o;
     g.raw = *reinterpret_cast<const int4*>(gate + r * g_stride + c);
     u.raw = *reinterpret_cast<const int4*>(up + r * u_stride + c);
@@ -346,8 +345,7 @@ int silu_mul(void* out, const void* gate, const void* up, int64_t rows, int cols
   const int vn = 16 / es;
   if (cols % vn || (g_stride * es) % 16 || (u_stride * es) % 16 || !aligned16(out) || !aligned16(gate) || !aligned16(up))
     return fail(B200_ESHAPE, "b200_silu_mul: cols=%d / alignment not supported", cols);
-  const int64_t total = rows * (cols / vn);
-  const int grid = static_cast<int>(std::min<int64_t>((total + 255) / 256, kNumSMs * 16));
+  const dim3 grid(static_cast<unsigned>((cols / vn + 255) / 256), static_cast<unsigned>(std::min<int64_t>(rows, 32768)));
   return by_dtype(dtype, "b200_silu_mul", [&](auto* tag) {
     using T = std::remove_pointer_t<decltype(tag)>;
     silu_mul_kernel<T><<<grid, 256, 0, s>>>(static_cast<T*>(out), static_cast<const T*>(gate),
