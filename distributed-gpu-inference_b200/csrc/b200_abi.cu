@@ -396,6 +396,15 @@ int b200_argmax_rows(int64_t* out, const void* x, int64_t rows, int64_t cols, in
   return argmax_rows(out, x, rows, cols, row_stride, dtype, static_cast<cudaStream_t>(stream));
 }
 
+int b200_argmax_rows_keys(int64_t* keys, const void* x, int64_t rows, int64_t cols, int64_t row_stride,
+                          int64_t col_offset, int dtype, void* stream) {
+  return argmax_rows_keys(keys, x, rows, cols, row_stride, col_offset, dtype, static_cast<cudaStream_t>(stream));
+}
+
+int b200_argmax_keys_decode(int64_t* out, const int64_t* keys, int64_t rows, void* stream) {
+  return argmax_keys_decode(out, keys, rows, static_cast<cudaStream_t>(stream));
+}
+
 int b200_silu_mul(void* out, const void* gate, const void* up, int64_t rows, int cols, int64_t gate_row_stride,
                   int64_t up_row_stride, int dtype, void* stream) {
   return silu_mul(out, gate, up, rows, cols, gate_row_stride, up_row_stride, dtype, static_cast<cudaStream_t>(stream));

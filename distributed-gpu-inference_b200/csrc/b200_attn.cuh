@@ -79,6 +79,9 @@ int rope_kv_append(void* q, int64_t q_stride, const void* k, int64_t k_stride, v
                    const void* cos_t, const void* sin_t, void* k_pool, void* v_pool, const int64_t* slot_mapping,
                    int n_tok, int Hq, int Hkv, int D, int block_size, int64_t max_blocks, int dtype, cudaStream_t s);
 int argmax_rows(int64_t* out, const void* x, int64_t rows, int64_t cols, int64_t row_stride, int dtype, cudaStream_t s);
+int argmax_rows_keys(int64_t* keys, const void* x, int64_t rows, int64_t cols, int64_t row_stride, int64_t col_offset,
+                     int dtype, cudaStream_t s);
+int argmax_keys_decode(int64_t* out, const int64_t* keys, int64_t rows, cudaStream_t s);
 int silu_mul(void* out, const void* gate, const void* up, int64_t rows, int cols, int64_t g_stride, int64_t u_stride,
              int dtype, cudaStream_t s);
 

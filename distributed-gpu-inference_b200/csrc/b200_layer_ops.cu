@@ -214,9 +214,35 @@ __device__ __forceinline__ bool better(float v, int i, const Best& b) {
 }
 constexpr int kArgmaxThreads = 1024;
 
+// Vocabulary-parallel form: every rank reduces its own column slice of the logits and the N partial answers are
+// merged by ONE max-reduction over int64 keys.  key = (order-preserving image of the value) << 32 | ~(global column),
+// top bit flipped so that signed comparison orders keys like (value, -column): the maximum key is the largest value
+// and, among equal values, the smallest column — the same winner torch.argmax picks on the whole row.
+__device__ __forceinline__ int64_t argmax_key(float v, int64_t col) {
+  uint32_t ord;
+  if (v != v) {
+    ord = 0xffffffffu;  // NaN beats everything
+  } else {
+    if (v == 0.f) v = 0.f;  // -0 and +0 compare equal in torch.argmax
+    const uint32_t b = __float_as_uint(v);
+    ord = (b & 0x80000000u) ? ~b : (b | 0x80000000u);
+  }
+  const uint64_t key = (static_cast<uint64_t>(ord) << 32) | (0xffffffffu - static_cast<uint32_t>(col));
+  return static_cast<int64_t>(key ^ 0x8000000000000000ull);
+}
+
+__global__ void argmax_keys_decode_kernel(int64_t* __restrict__ out, const int64_t* __restrict__ keys, int rows) {
+  const int r = blockIdx.x * blockDim.x + threadIdx.x;
+  if (r < rows) {
+    const uint64_t key = static_cast<uint64_t>(keys[r]) ^ 0x8000000000000000ull;
+    out[r] = static_cast<int64_t>(0xffffffffu - static_cast<uint32_t>(key & 0xffffffffu));
+  }
+}
+
 template <typename T>
 __global__ void __launch_bounds__(kArgmaxThreads)
-argmax_rows_kernel(int64_t* __restrict__ out, const T* __restrict__ x, int cols, int64_t row_stride, bool vec_ok) {
+argmax_rows_kernel(int64_t* __restrict__ out, const T* __restrict__ x, int cols, int64_t row_stride, bool vec_ok,
+                   int64_t col_offset, bool as_key) {
   constexpr int VN = Vec16<T>::N;
   const T* row = x + static_cast<int64_t>(blockIdx.x) * row_stride;
   Best best{-INFINITY, 0x7fffffff};
@@ -260,7 +286,7 @@ argmax_rows_kernel(int64_t* __restrict__ out, const T* __restrict__ x, int cols,
       const int oi = __shfl_xor_sync(0xffffffffu, best.i, off);
       if (better(ov, oi, best)) best = Best{ov, oi};
     }
-    if (lane == 0) out[blockIdx.x] = best.i;
+    if (lane == 0) out[blockIdx.x] = as_key ? argmax_key(best.v, col_offset + best.i) : col_offset + best.i;
   }
 }
 
@@ -364,10 +390,36 @@ int argmax_rows(int64_t* out, const void* x, int64_t rows, int64_t cols, int64_t
   const bool vec_ok = aligned16(x) && (row_stride * es) % 16 == 0;
   return by_dtype(dtype, "b200_argmax_rows", [&](auto* tag) {
     using T = std::remove_pointer_t<decltype(tag)>;
-    argmax_rows_kernel<T><<<static_cast<unsigned>(rows), kArgmaxThreads, 0, s>>>(out, static_cast<const T*>(x),
-                                                                                  static_cast<int>(cols), row_stride, vec_ok);
+    argmax_rows_kernel<T><<<static_cast<unsigned>(rows), kArgmaxThreads, 0, s>>>(
+        out, static_cast<const T*>(x), static_cast<int>(cols), row_stride, vec_ok, 0, false);
     return check_launch("b200_argmax_rows");
   });
+}
+
+int argmax_rows_keys(int64_t* keys, const void* x, int64_t rows, int64_t cols, int64_t row_stride, int64_t col_offset,
+                     int dtype, cudaStream_t s) {
+  const int es = dtype_size(dtype);
+  if (es == 0) return fail(B200_EINVAL, "b200_argmax_rows_keys: unsupported dtype %d", dtype);
+  if (rows < 0 || cols <= 0 || cols > 0x7fffffff || rows > 0x7fffffff || row_stride < cols || col_offset < 0 ||
+      col_offset + cols > 0xffffffffll)
+    return fail(B200_EINVAL, "b200_argmax_rows_keys: bad sizes");
+  if (rows == 0) return 0;
+  if (!keys || !x) return fail(B200_EINVAL, "b200_argmax_rows_keys: null pointer");
+  const bool vec_ok = aligned16(x) && (row_stride * es) % 16 == 0;
+  return by_dtype(dtype, "b200_argmax_rows_keys", [&](auto* tag) {
+    using T = std::remove_pointer_t<decltype(tag)>;
+    argmax_rows_kernel<T><<<static_cast<unsigned>(rows), kArgmaxThreads, 0, s>>>(
+        keys, static_cast<const T*>(x), static_cast<int>(cols), row_stride, vec_ok, col_offset, true);
+    return check_launch("b200_argmax_rows_keys");
+  });
+}
+
+int argmax_keys_decode(int64_t* out, const int64_t* keys, int64_t rows, cudaStream_t s) {
+  if (rows < 0 || rows > 0x7fffffff) return fail(B200_EINVAL, "b200_argmax_keys_decode: bad sizes");
+  if (rows == 0) return 0;
+  if (!out || !keys) return fail(B200_EINVAL, "b200_argmax_keys_decode: null pointer");
+  argmax_keys_decode_kernel<<<static_cast<unsigned>((rows + 127) / 128), 128, 0, s>>>(out, keys, static_cast<int>(rows));
+  return check_launch("b200_argmax_keys_decode");
 }
 
 }  // namespace b200

@@ -46,6 +46,7 @@ class PagedDecodeEngine:
         fuse_projections: bool = False,
         kv_pools: Optional[Sequence[KVCachePool]] = None,
         prefix_cache: bool = False,
+        external_head: bool = False,
     ):
         if not shards:
             raise ValueError("need at least one shard")
@@ -109,6 +110,11 @@ class PagedDecodeEngine:
         # a middle / last stage takes hidden states in, a first / middle stage hands hidden states out
         self.h_in = None if self.is_first else torch.zeros((max_batch, 1, cfg.hidden_size), dtype=self.dtype, device=dev)
         self.h_out = None if self.is_last else torch.zeros((max_batch, 1, cfg.hidden_size), dtype=self.dtype, device=dev)
+        # external_head (last stage of a pipeline with a vocabulary-parallel head): the decode step stops at the
+        # normed hidden rows ``hn_out [max_batch, hidden]``; logits and the token are computed by the pipeline
+        self.external_head = bool(external_head) and self.is_last
+        self.hn_out = (torch.zeros((max_batch, cfg.hidden_size), dtype=self.dtype, device=dev)
+                       if self.external_head else None)
         self.num_splits = ops.attn_plan(max_batch, self.Hq, self.Hkv, self.D, block_size, max_seq_len, self.dtype)
         ws = ops.attn_workspace_bytes(max_batch, self.Hq, self.D, self.num_splits)
         self.workspace = torch.empty(max(ws, 16), dtype=torch.uint8, device=dev)
@@ -359,7 +365,9 @@ class PagedDecodeEngine:
         h = self.ids_buf[:B] if self.is_first else self.h_in[:B]
         for shard, handles in zip(self.shards, self._handles):
             h, _ = shard.forward(h, position_ids=pos2, past_key_values=handles, use_cache=True)
-        if self.is_last:
+        if self.external_head:
+            self.hn_out[:B].copy_(h[:, 0, :])
+        elif self.is_last:
             logits = self.shards[-1].get_logits(h)[:, 0, :]
             ops.argmax_rows(logits, out=self.next_tokens[:B])  # one CTA per row; torch's reduce takes 46 us here
         else:

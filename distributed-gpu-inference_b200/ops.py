@@ -170,6 +170,37 @@ def argmax_rows(x: torch.Tensor, out: Optional[torch.Tensor] = None) -> torch.Te
     return out
 
 
+def argmax_rows_keys(x: torch.Tensor, col_offset: int, out: Optional[torch.Tensor] = None) -> torch.Tensor:
+    """Per-row best (value, ``col_offset`` + column) of a column slice of the logits as an int64 key; the element-wise
+    MAX of the ranks' key vectors (one all-reduce) is the key of ``torch.argmax`` over the whole row."""
+    _need_cuda(x)
+    if x.dim() != 2 or x.stride(1) != 1:
+        raise ValueError("x must be [rows, cols] with a contiguous last dimension")
+    rows, cols = x.shape
+    if out is None:
+        out = torch.empty((rows,), dtype=torch.int64, device=x.device)
+    elif out.dtype != torch.int64 or out.shape != (rows,) or not out.is_contiguous() or not out.is_cuda:
+        raise ValueError("out must be a contiguous CUDA int64 [rows]")
+    rc = _lib.load().b200_argmax_rows_keys(out.data_ptr(), x.data_ptr(), rows, cols, x.stride(0) if rows > 1 else cols,
+                                          int(col_offset), _dtype_id(x), _stream())
+    _lib.check(rc, "b200_argmax_rows_keys")
+    return out
+
+
+def argmax_keys_decode(keys: torch.Tensor, out: Optional[torch.Tensor] = None) -> torch.Tensor:
+    """Token ids of (max-reduced) ``argmax_rows_keys`` keys."""
+    _need_cuda(keys)
+    if keys.dtype != torch.int64 or keys.dim() != 1 or not keys.is_contiguous():
+        raise ValueError("keys must be a contiguous int64 vector")
+    if out is None:
+        out = torch.empty_like(keys)
+    elif out.dtype != torch.int64 or out.shape != keys.shape or not out.is_contiguous() or not out.is_cuda:
+        raise ValueError("out must be a contiguous CUDA int64 vector of the keys' length")
+    rc = _lib.load().b200_argmax_keys_decode(out.data_ptr(), keys.data_ptr(), keys.shape[0], _stream())
+    _lib.check(rc, "b200_argmax_keys_decode")
+    return out
+
+
 def attn_plan(B: int, Hq: int, Hkv: int, D: int, block_size: int, max_context_len: int, dtype: torch.dtype) -> int:
     """Number of context partitions the library would pick for this shape."""
     return _lib.load().b200_paged_decode_attn_plan(B, Hq, Hkv, D, block_size, max_context_len, DTYPE_ID[dtype])

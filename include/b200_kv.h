@@ -230,6 +230,15 @@ int b200_silu_mul(void* out, const void* gate, const void* up, int64_t rows, int
  * row_stride elements apart; out is int64[rows]. */
 int b200_argmax_rows(int64_t* out, const void* x, int64_t rows, int64_t cols, int64_t row_stride, int dtype,
                      void* stream);
+/* Greedy token when the vocabulary projection is split by rows of lm_head across ranks (ModelShard.get_logits,
+ * worker/distributed/model_shard.py:230-246, computed as N column slices of the logits): keys[r] encodes the best
+ * (value, col_offset + column) of this rank's slice x[r, 0..cols) so that the element-wise signed MAX of the N ranks'
+ * key vectors — one int64 all-reduce — is the key of torch.argmax over the whole row (largest value, smallest
+ * global column among equals, NaN largest).  b200_argmax_keys_decode turns reduced keys into token ids.
+ * col_offset + cols must stay below 2^32. */
+int b200_argmax_rows_keys(int64_t* keys, const void* x, int64_t rows, int64_t cols, int64_t row_stride,
+                          int64_t col_offset, int dtype, void* stream);
+int b200_argmax_keys_decode(int64_t* out, const int64_t* keys, int64_t rows, void* stream);
 
 /*
  * KV block pack / unpack for the prefill -> decode hand-off.  Replaces the per-block, per-layer

@@ -617,3 +617,30 @@ def test_argmax_rows_nan_and_inf_follow_torch():
     x[3, 10] = float("inf")
     assert torch.equal(ops.argmax_rows(x), torch.argmax(x, dim=-1))
     assert ops.argmax_rows(x).tolist() == [100, 7, 0, 4000]
+
+
+@pytest.mark.parametrize("dtype", [torch.bfloat16, torch.float32])
+@pytest.mark.parametrize("rows,cols,parts", [(64, 128256, 8), (16, 128256, 2), (4, 1024, 4), (3, 1001, 3), (2, 50, 8)])
+def test_argmax_keys_over_column_slices_equal_torch_argmax(dtype, rows, cols, parts):
+    """Vocabulary-parallel greedy token: per-slice keys, element-wise max (what the all-reduce does), decode."""
+    from dgi_b200.pipeline import VocabParallelHead
+
+    g = torch.Generator(device=DEV).manual_seed(rows + cols + parts)
+    x = torch.randn((rows, cols), generator=g, device=DEV).to(dtype)
+    top = x.max(dim=-1).values
+    for r in range(rows):  # the row maximum repeated in (usually) different slices: the first column must win
+        for c in (cols - 1, cols // 2, min(5, cols - 1)):
+            x[r, c] = top[r]
+    x[0, cols // 3] = float("nan")
+    if rows > 1:
+        x[1] = -1.0
+        x[1, cols - 2] = -0.0
+        x[1, 1] = 0.0  # -0 == +0: the earlier one wins even though its bits are larger
+    keys = None
+    for p in range(parts):
+        lo, hi = VocabParallelHead.partition(cols, parts, p, multiple=8)
+        if hi == lo:
+            continue
+        k = ops.argmax_rows_keys(x[:, lo:hi], lo)
+        keys = k if keys is None else torch.maximum(keys, k)
+    assert torch.equal(ops.argmax_keys_decode(keys), torch.argmax(x, dim=-1))
