@@ -4,9 +4,13 @@
     python bench.py --gpus N --steps K --warmup W            # this repo's CUDA path
     python bench.py --impl reference --gpus N --steps K ...  # the reference's torch CPU path (oracle port)
 
-N = 1 : BASELINE config 2 — Llama-3-8B shape, random-init bf16, block 16, batch 64, context 2k, decode.
-N > 1 : BASELINE config 4 — Llama-3-70B shape layer-sharded over N ranks (torchrun, NCCL send/recv of
-        activations), batch 128, context 4k.
+N = 1 : BASELINE configs[1] — Llama-3-8B shape, random-init bf16, block 16, batch 64, context 2k, decode; the line
+        also carries configs[4] (batch 8, context 32k, shared prefix) as `cfg5` and configs[0] (tiny model, in
+        full, GPU and host side by side) as `cpu_baseline_cfg1`.
+N > 1 : BASELINE configs[3] — Llama-3-70B shape layer-sharded over N ranks (torchrun, NCCL send/recv of
+        activations, vocabulary-parallel head), batch 128, context 4k, strong scaling; the 8B shape weak-scaled over
+        the same ranks rides along as `weak_scaled_8b`, the P/D hand-off as `pd_transfer`, and `parity` holds the
+        token checks of the run (dgi_b200/bench_pipeline.py).
 A "step" is one decode step of the whole batch.  `value` times K chained CUDA-graph steps with inputs resident
 in HBM (CUDA events, max over ranks); `e2e` times the public per-step call with host token ids in and out.
 Prints ONE JSON line on rank 0.
@@ -167,6 +171,9 @@ def cpu_reference_tokens_per_s(shape: str, batch: int, ctx: int, steps: int, war
         "unit": "tokens/s",
         "cores": cores,
         "kind": "port",
+        "extrapolated": True,
+        "factor": total_layers / sample_layers,
+        "ms_per_sampled_step": (sum(t_layers) + sum(t_ends)) / max(1, len(t_layers)) * 1e3,
         "sample": (f"{sample_layers} of {total_layers} layers of the {shape} shape at batch {batch}"
                    f"{'' if batch == full_batch else f' (of {full_batch}; throughput reported at the sampled batch)'}, context "
                    f"{start_ctx + warmup}..{ctx}, fp32, dense (k,v) cache, {steps} decode steps after {warmup} "
@@ -191,14 +198,17 @@ def run_reference(args, workload, rank, world):
         "n_gpus": args.gpus,
         "steps": args.steps,
         "warmup": args.warmup,
-        "ms_per_step": res["ms_per_step_extrapolated"],
+        # what one timed step of this arm really took (a step here is the bounded sample described in
+        # cpu_baseline.sample); the full-depth step it stands for is ms_per_step_extrapolated
+        "ms_per_step": res["ms_per_sampled_step"],
+        "ms_per_step_extrapolated": res["ms_per_step_extrapolated"],
         "higher_is_better": True,
         "scaling": workload["scaling"],
         "vs_baseline": None,
         "dtype": "f32",
         "data": "synthetic",
         "config": {"workload": workload["name"], "l2": "inputs larger than L2"},
-        "cpu_baseline": {k: res[k] for k in ("value", "unit", "cores", "kind", "sample")},
+        "cpu_baseline": {k: res[k] for k in ("value", "unit", "cores", "kind", "sample", "extrapolated", "factor")},
         "e2e": {"value": res["value"], "unit": "tokens/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "gpu_launches": 0,
     }
@@ -212,14 +222,15 @@ def workload_for(args):
     if args.workload:
         name = args.workload
     else:
-        name = "cfg2" if args.gpus == 1 else "cfg2pp"
+        name = "cfg2" if args.gpus == 1 else "cfg4"
     table = {
         "cfg2": dict(shape="8b", batch=64, context=2048, scaling="weak",
                      name="configs[1]: Llama-3-8B-shape random-init bf16, 1xB200, block 16, batch 64, context 2k, decode"),
-        "cfg2pp": dict(shape="8b", batch=64 * args.gpus, context=2048, scaling="weak",
+        "cfg2pp": dict(shape="8b", batch=64 * args.gpus, context=2048, scaling="weak", real_prefill=True,
+                       check_sequences=64,
                        name=f"configs[1] weak-scaled: Llama-3-8B-shape random-init bf16, layer ranges over {args.gpus} "
                             f"B200, block 16, batch 64 per GPU = {64 * args.gpus}, context 2k, decode"),
-        "cfg4": dict(shape="70b", batch=128, context=4096, scaling="strong",
+        "cfg4": dict(shape="70b", batch=128, context=4096, scaling="strong", check_sequences=8,
                      name=f"configs[3]: Llama-3-70B-shape layer-sharded over {args.gpus} B200, batch 128, context 4k, decode"),
         "cfg5": dict(shape="8b", batch=8, context=32768, scaling="weak",
                      name="configs[4]: Llama-3-8B-shape long-context decode, batch 8, context 32k"),
@@ -308,7 +319,8 @@ def measure_pack_unpack(dev):
     return out
 
 
-def run_single(args, workload):
+def _single_leg(args, workload):
+    """One timed single-GPU leg; returns the JSON line as a dict."""
     import dgi_b200  # noqa: F401
     from dgi_b200 import ops
     from dgi_b200.engine import PagedDecodeEngine
@@ -328,17 +340,18 @@ def run_single(args, workload):
     eng = PagedDecodeEngine([shard], max_batch=B, max_seq_len=ctx, block_size=16, prefill_chunk=args.prefill_chunk,
                             fuse_projections=not args.no_fuse_projections)
     ragged = None
+    synthetic_kv = args.synthetic_kv
     if workload["key"] == "cfg5":
         # config 5: one shared prefix of 24576 tokens (1536 blocks, reference-counted) + unique tails of
         # 8192 - 512 i tokens: ragged block tables, cascade attention, synthetic KV
         shared = (ctx * 3 // 4) // 16 * 16
         eng.allocate(B, ctx, shared_prefix_len=shared)
         ragged = [shared + (ctx - shared) - 512 * i * (ctx // 32768 or 1) - total_steps for i in range(B)]
-        args.synthetic_kv = True
+        synthetic_kv = True
     else:
         eng.allocate(B, ctx)
     prompts = torch.randint(0, cfg.vocab_size, (B, P), generator=torch.Generator().manual_seed(1234))
-    if args.synthetic_kv:
+    if synthetic_kv:
         fill_pools_synthetic(eng, B, P)
         if ragged is not None:
             eng.context_lens[:B] = torch.tensor(ragged, dtype=torch.int32)
@@ -401,11 +414,13 @@ def run_single(args, workload):
         algo_bytes = logical - (B - 1) * shared_tok * 2 * eng.Hkv * eng.D * es
     peaks, peak_kind = measured_peaks()
     achieved = algo_bytes / (attn_ms_mean * 1e-3) / 1e9
-    traffic = None
+    traffic, traffic_source = None, None
     tpath = os.path.join(ROOT, "profiles", "attn_traffic.json")
     if os.path.exists(tpath):
         try:
-            traffic = json.load(open(tpath)).get(workload["key"])
+            tj = json.load(open(tpath))
+            traffic = tj.get(workload["key"])
+            traffic_source = tj.get("source") if traffic is not None else None
         except Exception:  # noqa: BLE001
             traffic = None
     # this repo's kernels per step: per layer add_rmsnorm x2, the one-launch RoPE + append + attention (+ combine when
@@ -434,7 +449,7 @@ def run_single(args, workload):
             "context": (f"{P + 1 + W}..{P + W + K} during the timed steps" if ragged is None else
                         f"shared prefix {eng.prefix_blocks * 16} + ragged tails, longest sequence {ragged[0] + 1 + W}.."
                         f"{ragged[0] + W + K}, shortest {ragged[-1] + 1 + W}..{ragged[-1] + W + K} during the timed steps"),
-            "kv_fill": "synthetic normal(0,1)" if args.synthetic_kv else "real prefill of random prompts",
+            "kv_fill": "synthetic normal(0,1)" if synthetic_kv else "real prefill of random prompts",
             "l2": "inputs larger than L2 (all weights and the batch's KV are streamed every step)",
             "attn_splits": (f"cascade {eng.state.prefix_splits}+{eng.state.suffix_splits}, {eng.prefix_blocks} shared blocks"
                             if eng.state.prefix_blocks else eng.num_splits),
@@ -456,17 +471,91 @@ def run_single(args, workload):
             "frac": achieved / peaks["hbm_gbs"],
             "frac_of_nominal_8TBs": achieved / 8000.0,
             "traffic": traffic,
+            "traffic_source": traffic_source,
             "algorithmic_bytes_per_launch": algo_bytes,
             "launch_ms": attn_ms_mean,
             "launches_timed": len(attn_ms),
-            "how": "CUDA events around each attention launch of eagerly launched decode steps (same state as the timed loop)",
+            "how": ("CUDA events around each attention launch of eagerly launched decode steps that continue the "
+                    f"timed loop's state (context {ctx_now - n_inst // 2}..{ctx_now - n_inst // 2 + n_inst - 1}, "
+                    f"{2 * (K + W)} tokens past the start of the device-timed window)"),
         },
     }
+    del eng, shard
+    import gc
+
+    gc.collect()
+    torch.cuda.empty_cache()
+    return line
+
+
+def config1_side_by_side():
+    """BASELINE configs[0] IN FULL, un-extrapolated: tiny 4-layer model in 2 layer-range shards, batch 4, prompt 128,
+    64 greedy tokens, fp32 — the reference's torch CPU path (oracle port: ModelShard.forward restatement + legacy
+    HF layer with dense (k, v) tuples) on the host cores, and this repo's paged CUDA path on the GPU, both timed
+    over the 63 decode steps after the prompt pass, tokens compared."""
+    import dgi_b200  # noqa: F401
+    from dgi_b200.engine import PagedDecodeEngine
+    from dgi_b200.testing import LlamaShapeConfig, build_product_shards, seeded_state_dict
+    from oracle import llama_ref as L
+
+    cores = os.cpu_count() or 1
+    torch.set_num_threads(cores)
+    cfg = L.RefConfig(**L.TINY)
+    sd = L.make_weights(cfg, seed=0)
+    ranges = [(0, 2), (2, 4)]
+    B, P, N = 4, 128, 64
+    prompts = torch.randint(0, cfg.vocab_size, (B, P), generator=torch.Generator().manual_seed(1234))
+    shards = L.build_shards(cfg, sd, ranges)
+    L.greedy_decode(shards, prompts[:, :16], 2)  # warm-up
+    t0 = time.perf_counter()
+    L.greedy_decode(shards, prompts, 1)  # prompt pass + first token
+    t_prompt = time.perf_counter() - t0
+    t0 = time.perf_counter()
+    want = L.greedy_decode(shards, prompts, N)
+    t_all = time.perf_counter() - t0
+    cpu_decode_s = max(t_all - t_prompt, 1e-9)
+    gcfg = LlamaShapeConfig(**L.TINY)
+    gshards = build_product_shards(gcfg, seeded_state_dict(gcfg, 0), ranges, "cuda:0", torch.float32)
+    eng = PagedDecodeEngine(gshards, max_batch=B, max_seq_len=P + N, prefill_mode="eager")
+    eng.generate(prompts, 4)  # warm-up: graph capture
+    eng.allocate(B, P + N)
+    nxt = eng.prefill(prompts).cpu()
+    got = [nxt]
+    torch.cuda.synchronize()
+    t0 = time.perf_counter()
+    for _ in range(N - 1):
+        nxt = eng.decode_step(nxt)  # host ids in and out every step
+        got.append(nxt)
+    torch.cuda.synchronize()
+    gpu_s = time.perf_counter() - t0
+    got = torch.stack(got, dim=1)
+    return {
+        "workload": "configs[0]: tiny 4-layer model (d=512, 8 heads, 2 KV heads), 2 layer-range shards, batch 4, prompt 128, "
+                    "64 greedy tokens, fp32",
+        "value": B * (N - 1) / cpu_decode_s, "unit": "tokens/s", "cores": cores, "kind": "port", "extrapolated": False,
+        "sample": f"the whole configuration: {N - 1} decode steps of batch {B} after the prompt pass, {cpu_decode_s:.2f} s",
+        "gpu_value": B * (N - 1) / gpu_s, "gpu_path": "PagedDecodeEngine.decode_step (host ids in / out per step), 1 GPU",
+        "tokens_identical": bool(torch.equal(got, want)),
+    }
+
+
+def run_single(args, workload):
+    line = _single_leg(args, workload)
+    dev = "cuda:0"
+    if not args.workload and not args.batch and not args.context and not args.no_riders:
+        # configs[4] rides along on the N = 1 line: long-context decode over a shared prefix (cascade kernel)
+        args5 = argparse.Namespace(**vars(args))
+        args5.workload = "cfg5"
+        five = _single_leg(args5, workload_for(args5))
+        line["cfg5"] = {"workload": five["config"]["workload"], "config": five["config"],
+                        **{k: five[k] for k in ("value", "unit", "ms_per_step", "e2e", "gpu_launches", "roofline")}}
     line["kv_pack"] = measure_pack_unpack(dev)
     if not args.no_cpu_baseline:
-        res = cpu_reference_tokens_per_s(workload["shape"], B, ctx, steps=10, warmup=2)  # about 10 s of host work
-        line["cpu_baseline"] = {k: res[k] for k in ("value", "unit", "cores", "kind", "sample")}
+        res = cpu_reference_tokens_per_s(workload["shape"], workload["batch"], workload["context"], steps=10,
+                                         warmup=2)  # about 10 s of host work
+        line["cpu_baseline"] = {k: res[k] for k in ("value", "unit", "cores", "kind", "sample", "extrapolated", "factor")}
         line["kv_pack"]["cpu_reference_handoff"] = cpu_handoff_reference()
+        line["cpu_baseline_cfg1"] = config1_side_by_side()
     print(json.dumps(line), flush=True)
 
 
@@ -486,8 +575,12 @@ def main():
                     help="keep q/k/v and gate/up as separate GEMMs (the reference's GEMM shapes)")
     ap.add_argument("--micro-batches", type=int, default=0, help="pipeline micro-batches (default: one per rank)")
     ap.add_argument("--real-prefill", action="store_true", help="multi-GPU: run a real prompt pass instead of synthetic KV")
-    ap.add_argument("--no-cfg4", action="store_true",
-                    help="multi-GPU default run: skip the 70B-shape (configs[3]) leg that is appended to the line")
+    ap.add_argument("--no-riders", action="store_true",
+                    help="default runs: skip the extra legs appended to the line (N = 1: configs[4]; N > 1: the "
+                         "weak-scaled 8B pipeline)")
+    ap.add_argument("--no-parity", action="store_true", help="multi-GPU: skip the token checks of the run")
+    ap.add_argument("--no-vocab-parallel-head", action="store_true",
+                    help="multi-GPU: keep lm_head + argmax on the last stage (the round-1 arrangement)")
     args = ap.parse_args()
     if args.warmup < 3:
         args.warmup = 3
@@ -503,8 +596,8 @@ def main():
         from dgi_b200.bench_pipeline import run_pipeline  # multi-GPU layer-sharded decode
 
         extra = None
-        if not args.workload and not args.no_cfg4 and not args.batch and not args.context:
-            args.workload = "cfg4"  # the north-star multi-GPU configuration rides along in the same line
+        if not args.workload and not args.no_riders and not args.batch and not args.context:
+            args.workload = "cfg2pp"  # the N = 1 model weak-scaled over the same ranks rides along in the line
             extra = workload_for(args)
             args.workload = ""
         run_pipeline(args, workload, SHAPES, ShapeConfig, ClockSampler, measured_peaks, cpu_reference_tokens_per_s,

@@ -135,6 +135,8 @@ class PagedDecodeEngine:
         ]
         self._seq_blocks: List[Optional[List[List[List[CacheBlock]]]]] = [None] * max_batch  # [seq][shard][layer][blk]
         self._host_lens = [0] * max_batch
+        self.keep_logits = False
+        self.last_logits: Optional[torch.Tensor] = None
         self._graph: Optional[torch.cuda.CUDAGraph] = None
         self._graph_chained: Optional[torch.cuda.CUDAGraph] = None
         self._pin_in = torch.zeros((max_batch,), dtype=torch.int64).pin_memory()
@@ -370,6 +372,8 @@ class PagedDecodeEngine:
         elif self.is_last:
             logits = self.shards[-1].get_logits(h)[:, 0, :]
             ops.argmax_rows(logits, out=self.next_tokens[:B])  # one CTA per row; torch's reduce takes 46 us here
+            if self.keep_logits:  # eager launches only: lets a caller look at the margins behind a token
+                self.last_logits = logits
         else:
             self.h_out[:B].copy_(h)
 

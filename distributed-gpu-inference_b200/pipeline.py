@@ -256,20 +256,24 @@ class LayerPipeline:
         return None
 
     # ---- prompt pass ---------------------------------------------------------------------------------------
-    def prefill(self, prompts: Optional[Sequence[torch.Tensor]], prompt_len: int, chunk: int = 2) -> Optional[List[torch.Tensor]]:
+    def prefill(self, prompts: Optional[Sequence[torch.Tensor]], prompt_len: int, chunk: int = 2,
+                rows: Optional[Sequence[int]] = None) -> Optional[List[torch.Tensor]]:
         """Prompt pass of every micro-batch through the stages, ``chunk`` sequences at a time.
 
         ``prompts[m]`` is ``[mb, P]`` token ids (needed on rank 0 only).  Returns the first generated tokens per
-        micro-batch on rank 0 (shipped back from the last rank), ``None`` elsewhere.
+        micro-batch on rank 0 (shipped back from the last rank), ``None`` elsewhere.  ``rows[m]`` (same on every
+        rank): run only the first ``rows[m]`` sequences of micro-batch m (0 = skip it); the tokens of the others
+        come back as 0.
         """
         N, rank = self.world, self.rank
         g = self.groups
         firsts: List[torch.Tensor] = []
         for m, ex in enumerate(self.ex):
             mb = ex.next_tokens.shape[0]
-            toks = torch.empty((mb,), dtype=torch.int64, device=ex.next_tokens.device)
-            for lo in range(0, mb, chunk):
-                hi = min(mb, lo + chunk)
+            n_run = mb if rows is None else min(mb, int(rows[m]))
+            toks = torch.zeros((mb,), dtype=torch.int64, device=ex.next_tokens.device)
+            for lo in range(0, n_run, chunk):
+                hi = min(n_run, lo + chunk)
                 if self.first:
                     x = prompts[m][lo:hi]
                 else:
@@ -280,7 +284,7 @@ class LayerPipeline:
                     toks[lo:hi] = y
                 else:
                     dist.send(y.contiguous(), dst=rank + 1, group=g.fwd[rank])
-            if N > 1:
+            if N > 1 and n_run > 0:
                 if self.last:
                     dist.send(toks, dst=0, group=g.feedback)
                 elif self.first:

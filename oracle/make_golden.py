@@ -218,15 +218,18 @@ def gen_serializer() -> None:
 
 
 # ---------------------------------------------------------------------------------------------------------
-def gen_tiny_decode() -> None:
-    """BASELINE config 1: tiny 4-layer model, 2 reference ModelShards, batch 4, prompt 128, 64 greedy tokens."""
+def gen_tiny_decode(num_layers: int = 4, n_shards: int = 2, out_name: str = "tiny_decode.json") -> None:
+    """BASELINE config 1: tiny 4-layer model, 2 reference ModelShards, batch 4, prompt 128, 64 greedy tokens.
+    (``num_layers=8, n_shards=8``: the same model twice as deep, one layer per reference ModelShard — the fixture
+    an 8-rank pipeline is checked against.)"""
     torch.manual_seed(0)
     torch.set_num_threads(os.cpu_count() or 1)
-    cfg = L.RefConfig(**L.TINY)
+    shape = dict(L.TINY, num_hidden_layers=num_layers)
+    cfg = L.RefConfig(**shape)
     sd = L.make_weights(cfg, seed=0)
     B, P, N = 4, 128, 64
     prompts = torch.randint(0, cfg.vocab_size, (B, P), generator=torch.Generator().manual_seed(1234))
-    ranges = [ref_ms.get_layer_range_for_worker(cfg.num_hidden_layers, 2, i) for i in range(2)]
+    ranges = [ref_ms.get_layer_range_for_worker(cfg.num_hidden_layers, n_shards, i) for i in range(n_shards)]
 
     # (1) the reference's own ModelShard, assembled the way its tests do (constructor + attribute assignment)
     ref_shards = []
@@ -277,9 +280,9 @@ def gen_tiny_decode() -> None:
 
     top2 = logits_ref.topk(2, dim=-1).values
     margin = (top2[..., 0] - top2[..., 1])
-    dump("tiny_decode.json", {
-        "config": L.TINY,
-        "weights": "oracle.llama_ref.make_weights(RefConfig(**TINY), seed=0) — numpy PCG64 standard_normal * 0.02",
+    dump(out_name, {
+        "config": shape,
+        "weights": "oracle.llama_ref.make_weights(RefConfig(**config), seed=0) — numpy PCG64 standard_normal * 0.02",
         "prompt": "torch.randint(0, vocab, (4, 128), generator=manual_seed(1234))",
         "prompt_ids": prompts.tolist(),
         "shard_ranges": [list(r) for r in ranges],
@@ -348,8 +351,12 @@ if __name__ == "__main__":
     if "--only-paged" in sys.argv:
         gen_paged_ops()
         sys.exit(0)
+    if "--only-tiny8" in sys.argv:
+        gen_tiny_decode(num_layers=8, n_shards=8, out_name="tiny8_decode.json")
+        sys.exit(0)
     gen_host_logic()
     gen_allocator()
     gen_serializer()
     gen_tiny_decode()
+    gen_tiny_decode(num_layers=8, n_shards=8, out_name="tiny8_decode.json")
     gen_paged_ops()
