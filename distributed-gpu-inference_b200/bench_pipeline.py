@@ -167,15 +167,15 @@ def _agreement_vs_single_gpu(cfg, prompts, pipe_tokens, ctx, dev, fuse):
     eng = PagedDecodeEngine([shard], max_batch=n, max_seq_len=ctx, block_size=16, prefill_chunk=2,
                             fuse_projections=fuse, use_cuda_graph=False)
     eng.allocate(n, ctx)
-    eng.keep_logits = True
     first = eng.prefill(prompts.to(dev))
     toks = [first]
     margins = []
     eng.ids_buf[:n, 0].copy_(first)
+    eng.logits_log = []
     for _ in range(steps):
         eng.decode_step_device()
         toks.append(eng.next_tokens[:n].clone())
-        top2 = eng.last_logits.float().topk(2, dim=-1).values
+        top2 = eng.logits_log.pop()[2].topk(2, dim=-1).values
         margins.append(torch.stack((top2[:, 0] - top2[:, 1], top2[:, 0].abs())))
     torch.cuda.synchronize()
     single = torch.stack(toks, dim=1).cpu()

@@ -135,8 +135,9 @@ class PagedDecodeEngine:
         ]
         self._seq_blocks: List[Optional[List[List[List[CacheBlock]]]]] = [None] * max_batch  # [seq][shard][layer][blk]
         self._host_lens = [0] * max_batch
-        self.keep_logits = False
-        self.last_logits: Optional[torch.Tensor] = None
+        # when set to a list (with use_cuda_graph=False): every prompt pass and decode step appends
+        # (first row, last row + 1, fp32 logits of those rows) — for token-divergence reports
+        self.logits_log: Optional[list] = None
         self._graph: Optional[torch.cuda.CUDAGraph] = None
         self._graph_chained: Optional[torch.cuda.CUDAGraph] = None
         self._pin_in = torch.zeros((max_batch,), dtype=torch.int64).pin_memory()
@@ -317,7 +318,10 @@ class PagedDecodeEngine:
         self.context_lens[lo:hi] = past_len + P
         self._host_lens[lo:hi] = [past_len + P] * n
         if self.is_last:
-            return ops.argmax_rows(self.shards[-1].get_logits(h[:, -1:, :])[:, 0, :])
+            logits = self.shards[-1].get_logits(h[:, -1:, :])[:, 0, :]
+            if self.logits_log is not None:
+                self.logits_log.append((lo, hi, logits.float().clone()))
+            return ops.argmax_rows(logits)
         return h
 
     @torch.no_grad()
@@ -372,8 +376,8 @@ class PagedDecodeEngine:
         elif self.is_last:
             logits = self.shards[-1].get_logits(h)[:, 0, :]
             ops.argmax_rows(logits, out=self.next_tokens[:B])  # one CTA per row; torch's reduce takes 46 us here
-            if self.keep_logits:  # eager launches only: lets a caller look at the margins behind a token
-                self.last_logits = logits
+            if self.logits_log is not None:  # eager launches only: the margins behind every token
+                self.logits_log.append((0, B, logits.float().clone()))
         else:
             self.h_out[:B].copy_(h)
 
@@ -387,6 +391,8 @@ class PagedDecodeEngine:
         st.max_context_len = self.max_seq_len
 
     def _capture(self, chained: bool) -> torch.cuda.CUDAGraph:
+        if self.logits_log is not None:
+            raise RuntimeError("logits_log needs eager launches (use_cuda_graph=False)")
         self._view_state()
         self._graph_key = (self.batch, getattr(self, "prefix_blocks", 0))  # what a captured graph is valid for
         saved = self.context_lens.clone()

@@ -156,6 +156,36 @@ def test_8b_shape_bf16_paged_path_vs_reference_dense_path():
         eng.release()
 
 
+def _logged_logits(eng, n_rows, row_of=None):
+    """[rows, tokens, vocab] fp32 logits from an engine's ``logits_log``: the prompt-pass entries (each covering a
+    row range) make token 0, every later entry is one decode step of all rows."""
+    first = torch.empty((n_rows, eng.logits_log[0][2].shape[-1]), device=DEV)
+    steps, seen = [], 0
+    for lo, hi, lg in eng.logits_log:
+        if seen < n_rows:
+            first[lo:hi] = lg
+            seen += hi - lo
+        else:
+            steps.append(lg)
+    return torch.stack([first] + steps, dim=1)
+
+
+def _assert_divergences_only_at_near_ties(got, want, logits, dtype, what):
+    """``got`` may leave ``want`` (the tokens of the path that produced ``logits``) only where that path's own top-2
+    logits are closer than 2 ulp of the storage dtype — the same rule the other half-precision token tests use."""
+    eps = torch.finfo(dtype).eps
+    bad = []
+    for b in range(len(want)):
+        for s, (a, w) in enumerate(zip(got[b], want[b])):
+            if int(a) != int(w):
+                top2 = logits[b, s].topk(2).values
+                margin = float(top2[0] - top2[1])
+                if margin > 2 * eps * float(top2[0].abs()) + 1e-6:
+                    bad.append((b, s, margin, float(top2[0])))
+                break  # after a divergence the sequences are different texts
+    assert not bad, f"{what}: divergence at a decided token: {bad}"
+
+
 @pytest.mark.parametrize("dtype", [torch.float32, torch.bfloat16])
 def test_shared_prefix_blocks_give_the_same_tokens(golden, dtype):
     """Radix-style prefix sharing: 4 prompts with a common 80-token system prompt.  The shared blocks are computed
@@ -166,8 +196,12 @@ def test_shared_prefix_blocks_give_the_same_tokens(golden, dtype):
     prompts = base[:, :112].clone()
     prompts[:, :80] = base[0, :80]
     shards = build_product_shards(cfg, sd, [(0, 2), (2, 4)], DEV, dtype)
+    plain = PagedDecodeEngine(shards, 4, 160, prefill_mode="eager", use_cuda_graph=False)
+    plain.logits_log = []
+    want = plain.generate(prompts, 24)
+    logits = _logged_logits(plain, 4)
+    plain.release()
     eng = PagedDecodeEngine(shards, 4, 160, prefill_mode="eager")
-    want = eng.generate(prompts, 24)
     got = eng.generate(prompts, 24, shared_prefix_len=80)
     assert eng.prefix_blocks == 5
     tables = eng.block_tables[:4].cpu()
@@ -181,9 +215,9 @@ def test_shared_prefix_blocks_give_the_same_tokens(golden, dtype):
         assert torch.equal(got, ref)
     else:
         assert eng.state.prefix_blocks == 5
-        # bf16: same tokens up to near-ties; demand agreement of the first tokens and a high overall rate
-        assert torch.equal(got[:, :4], want[:, :4])
-        assert float((got == want).float().mean()) > 0.6
+        # bf16: the cascade path may leave the plain path's tokens only at a near-tie of the plain path's logits
+        print(f"shared prefix bf16: token agreement {float((got == want).float().mean()):.3f}")
+        _assert_divergences_only_at_near_ties(got.tolist(), want.tolist(), logits, dtype, "shared prefix")
     eng.release()
     assert all(c.get_stats()["free_blocks"] == c.max_blocks for pool in eng.pools for c in pool._layer_caches)
 
@@ -435,7 +469,15 @@ def test_ragged_prompts_behind_one_system_prompt_share_its_blocks(golden):
             assert got == want
         else:
             assert eng.state.prefix_blocks == 4  # cascade kernel in use
-            agree = sum(a == b for ga, wa in zip(got, want) for a, b in zip(ga, wa)) / 50
-            assert [r[0] for r in got] == [r[0] for r in want] and agree > 0.6
+            # the same prompts as independent sequences on the plain bf16 path, logits logged: the shared-prefix
+            # tokens may differ from them only at near-ties of those logits
+            plain = PagedDecodeEngine(shards, 5, 160, prefill_mode="eager", use_cuda_graph=False)
+            plain.logits_log = []
+            base_toks = plain.generate_ragged(prompts, 10)
+            order = sorted(range(5), key=lambda i: len(prompts[i]))  # engine rows are ordered by prompt length
+            lg = _logged_logits(plain, 5)
+            logits = torch.stack([lg[order.index(i)] for i in range(5)])
+            plain.release()
+            _assert_divergences_only_at_near_ties(got, base_toks, logits, dtype, "ragged shared prefix")
         with pytest.raises(ValueError, match="do not share"):
             eng.generate_ragged([prompts[0], [1] + prompts[1][1:]], 4, shared_prefix_len=sys_len)

@@ -52,14 +52,18 @@ def _free_port():
         return s.getsockname()[1]
 
 
-def _pipeline_worker(rank, world, port, q):
+def _pipeline_worker_vp(rank, world, port, q):
+    _pipeline_worker(rank, world, port, q, vp=True)
+
+
+def _pipeline_worker(rank, world, port, q, vp=False):
     import sys
     sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
     import json
 
     import dgi_b200  # noqa: F401
     from dgi_b200.engine import PagedDecodeEngine
-    from dgi_b200.pipeline import LayerPipeline, make_pipeline_groups
+    from dgi_b200.pipeline import LayerPipeline, VocabParallelHead, make_pipeline_groups
     from dgi_b200.testing import build_product_shards
     from dgi_b200.worker.distributed.model_shard import get_layer_range_for_worker
     from oracle import llama_ref as L
@@ -76,11 +80,15 @@ def _pipeline_worker(rank, world, port, q):
         shard = build_product_shards(cfg, sd, [rng], dev, torch.float32)[0]
         prompts = torch.tensor(g["prompt_ids"])
         M, mb, n_new = 2, 2, 24
-        engines = [PagedDecodeEngine([shard], mb, 192, prefill_mode="eager") for _ in range(M)]
+        engines = [PagedDecodeEngine([shard], mb, 192, prefill_mode="eager", external_head=vp) for _ in range(M)]
         for e in engines:
             e.allocate(mb, 192)
         groups = make_pipeline_groups(world, warm_up_device=torch.device(dev))
-        pipe = LayerPipeline(engines, rank, world, groups)
+        head = None
+        if vp:  # every rank takes its rows of lm_head from the last rank; logits are reduced as int64 keys
+            head = VocabParallelHead.scatter_from_last(shard, cfg.vocab_size, cfg.hidden_size, rank, world, groups.head,
+                                                       dev, torch.float32)
+        pipe = LayerPipeline(engines, rank, world, groups, head=head)
         chunks = [prompts[m * mb:(m + 1) * mb].to(dev) for m in range(M)]
         firsts = pipe.prefill(chunks if rank == 0 else None, prompts.shape[1], chunk=1)
         if rank == 0:
@@ -100,6 +108,13 @@ def _pipeline_worker(rank, world, port, q):
 def test_two_rank_pipeline_tokens_identical_to_reference(golden):
     g = golden("tiny_decode.json")
     (got,) = _run_ranks(_pipeline_worker, 2, 1)
+    assert got == [row[:27] for row in g["tokens"]]
+
+
+@pytest.mark.skipif(torch.cuda.device_count() < 2, reason="needs 2 GPUs")
+def test_two_rank_pipeline_with_vocabulary_parallel_head_tokens_identical_to_reference(golden):
+    g = golden("tiny_decode.json")
+    (got,) = _run_ranks(_pipeline_worker_vp, 2, 1)
     assert got == [row[:27] for row in g["tokens"]]
 
 
