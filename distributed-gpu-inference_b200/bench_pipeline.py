@@ -275,7 +275,7 @@ def _measure_pd_handoff(rank, world, dev):
 # -----------------------------------------------------------------------------------------------------------------
 # one timed leg
 # -----------------------------------------------------------------------------------------------------------------
-def _run(workload, args, SHAPES, ShapeConfig, ClockSampler, measured_peaks, rank, world, local, dev, groups):
+def _measure(workload, args, SHAPES, ShapeConfig, ClockSampler, measured_peaks, rank, world, local, dev, groups):
     cfg = ShapeConfig(**SHAPES[workload["shape"]])
     B, ctx = workload["batch"], workload["context"]
     K, W = args.steps, args.warmup
@@ -360,21 +360,32 @@ def _run(workload, args, SHAPES, ShapeConfig, ClockSampler, measured_peaks, rank
     attn_ms = statistics.mean(a.elapsed_time(b) for a, b in ev)
     ctx_now = P + 2 * (K + W) + 1
     algo = mb * ctx_now * 2 * eng.Hkv * eng.D * 2 + 2 * mb * eng.Hq * eng.D * 2
-    num_splits, Hq, Hkv, D = eng.num_splits, eng.Hq, eng.Hkv, eng.D
-    layers_here = end - start
-
-    # ---- agreement of the pipeline's tokens with one GPU running the whole model --------------------------------
-    agreement = None
     n_cmp = mb if real_all else n_check
     pipe_tokens = None
     if rank == 0 and n_cmp > 0:
         pipe_tokens = torch.cat([firsts[0][:n_cmp, None]] + [t[0, :n_cmp] for t in produced], dim=1).cpu()
-    del pipe, engines, eng, shard, head, produced
+    # plain values only: every tensor, engine and graph of this leg dies with this frame
+    return dict(cfg=cfg, B=B, ctx=ctx, K=K, W=W, M=M, mb=mb, P=P, fuse=fuse, vp=vp, real_all=real_all, n_check=n_check,
+                n_cmp=n_cmp, setup_s=setup_s, dev_ms=dev_ms, e2e_ms=e2e_ms, clocks=clocks, attn_ms=attn_ms,
+                n_events=len(ev), ctx_now=ctx_now, algo=algo, num_splits=eng.num_splits, Hq=eng.Hq, Hkv=eng.Hkv, D=eng.D,
+                layers_here=end - start, pipe_tokens=pipe_tokens, check_prompts=prompts[0][:n_cmp] if n_cmp else None)
+
+
+def _run(workload, args, SHAPES, ShapeConfig, ClockSampler, measured_peaks, rank, world, local, dev, groups):
+    r = _measure(workload, args, SHAPES, ShapeConfig, ClockSampler, measured_peaks, rank, world, local, dev, groups)
     _free()
+    cfg, B, ctx, K, W, M, mb, P = (r[k] for k in ("cfg", "B", "ctx", "K", "W", "M", "mb", "P"))
+    fuse, vp, real_all, n_check, n_cmp = (r[k] for k in ("fuse", "vp", "real_all", "n_check", "n_cmp"))
+    setup_s, dev_ms, e2e_ms, clocks, attn_ms = (r[k] for k in ("setup_s", "dev_ms", "e2e_ms", "clocks", "attn_ms"))
+    ctx_now, algo, num_splits, Hq, Hkv, D = (r[k] for k in ("ctx_now", "algo", "num_splits", "Hq", "Hkv", "D"))
+    layers_here, pipe_tokens = r["layers_here"], r["pipe_tokens"]
+
+    # ---- agreement of the pipeline's tokens with one GPU running the whole model --------------------------------
+    agreement = None
     if n_cmp > 0:
         if rank == 0:
             try:
-                agreement = _agreement_vs_single_gpu(cfg, prompts[0][:n_cmp], pipe_tokens, ctx, dev, fuse)
+                agreement = _agreement_vs_single_gpu(cfg, r["check_prompts"], pipe_tokens, ctx, dev, fuse)
             except Exception as exc:  # noqa: BLE001 - e.g. the whole model does not fit beside what is left
                 agreement = {"unavailable": repr(exc)}
             _free()
@@ -443,7 +454,7 @@ def _run(workload, args, SHAPES, ShapeConfig, ClockSampler, measured_peaks, rank
             "traffic": None,
             "algorithmic_bytes_per_launch": algo,
             "launch_ms": attn_ms,
-            "launches_timed": len(ev),
+            "launches_timed": r["n_events"],
         },
     }
     return line
