@@ -173,6 +173,86 @@ class WireHandoff:
                     for j in range(n)]
         return [{"prefix_key": prefix_key, **head, "layers": layer_msgs(0, n, [n, Hkv, bs, D])}]
 
+    # ---- StreamingTensorBuffer framing (reference: common/serialization.py:209-265) --------------------------
+    def export_stream(self, block_table: torch.Tensor, chunk_size: int = 1024 * 1024):
+        """The same payload as ``export`` as ONE chunked tensor stream: first the ``StreamingTensorBuffer`` header
+        (``[ndim u32][dims u64 ...][dtype id u8]`` for shape ``[L, 2, n_blocks, heads, block_size, head_dim]``), then
+        ``chunk_size``-byte frames (1 MiB by default, the reference's chunk size) — what a stock
+        ``StreamingTensorBuffer`` receiver consumes with ``read_header`` / ``write_chunk`` / ``finalize``.
+
+        The wire tensor is made by one launch; the device→host copy runs layer by layer on a side stream and a
+        layer's frames are yielded as soon as its copy has landed in the pinned buffer, so the consumer (a socket
+        writer) overlaps with the remaining copies.  Frames are zero-copy ``memoryview`` slices of that pinned
+        buffer, valid until the generator is closed; a frame never straddles more than the bytes in flight."""
+        from .common.serialization import StreamingTensorBuffer
+
+        wire = self._wire_tensor(block_table)                      # [L, 2, n, Hkv, bs, D] on the device
+        host = torch.empty(wire.shape, dtype=wire.dtype, pin_memory=True)
+        side = torch.cuda.Stream(device=wire.device)
+        side.wait_stream(torch.cuda.current_stream())
+        done = []
+        with torch.cuda.stream(side):
+            for l in range(self.num_layers):
+                host[l].copy_(wire[l], non_blocking=True)
+                ev = torch.cuda.Event()
+                ev.record(side)
+                done.append(ev)
+        wire.record_stream(side)
+        yield StreamingTensorBuffer(chunk_size).write_header(tuple(wire.shape), self.dtype_str)
+        raw = memoryview(host.view(torch.uint8).numpy()).cast("B")
+        per_layer = len(raw) // self.num_layers
+        sent, landed = 0, 0
+        for l in range(self.num_layers):
+            done[l].synchronize()
+            landed += per_layer
+            last = l == self.num_layers - 1
+            while sent + chunk_size <= landed or (last and sent < landed):
+                end = min(sent + chunk_size, landed)
+                yield raw[sent:end]
+                sent = end
+
+    def import_stream(self, frames, block_table: torch.Tensor) -> dict:
+        """Receiver of ``export_stream``: header frame, then data frames of any size, written straight into a pinned
+        buffer; one host→device copy and one launch scatter them into the slots of ``block_table``.  Returns the
+        reference's ``KVCacheResponse`` fields."""
+        import time
+
+        from .common.serialization import StreamingTensorBuffer
+
+        t0 = time.time()
+        try:
+            it = iter(frames)
+            meta = StreamingTensorBuffer().read_header(bytes(next(it)))
+            n = block_table.shape[0]
+            _, Hkv, bs, D = self.ep.pool_shape
+            want = (self.num_layers, 2, n, Hkv, bs, D)
+            if tuple(meta["shape"]) != want:
+                raise ValueError(f"stream carries shape {tuple(meta['shape'])}, expected {want}")
+            if meta["dtype"] != self.dtype_str:
+                raise TypeError(f"stream carries {meta['dtype']}, the pool holds {self.dtype_str}")
+            host = torch.empty(want, dtype=self.wire_dtype, pin_memory=True)
+            raw = memoryview(host.view(torch.uint8).numpy()).cast("B")
+            off = 0
+            for frame in it:
+                size = len(frame)
+                if off + size > len(raw):
+                    raise ValueError("stream is longer than its header says")
+                raw[off:off + size] = frame
+                off += size
+            if off != len(raw):
+                raise ValueError(f"stream ended after {off} of {len(raw)} bytes")
+            dev = host.to(block_table.device, non_blocking=True)
+            kp, vp = self.ep._k_ptrs[0], self.ep._v_ptrs[0]
+            if self.dtype == torch.bfloat16:
+                ops.kv_unpack_layers_wire(dev, kp, vp, self.ep.pool_shape, block_table)
+            else:
+                ops.kv_unpack_layers(dev, kp, vp, self.ep.pool_shape, block_table)
+            torch.cuda.current_stream().synchronize()
+        except Exception as exc:  # noqa: BLE001 - the RPC reports failure in its response
+            return {"success": False, "error_message": str(exc)}
+        return {"success": True, "error_message": "", "bytes_transferred": off,
+                "latency_ms": int((time.time() - t0) * 1000)}
+
     def import_(self, requests: List[dict], block_table: torch.Tensor) -> dict:
         """Store the blocks carried by ``requests`` (as produced by ``export``, either form, in order) into the
         slots of ``block_table``; returns the reference's ``KVCacheResponse`` fields."""

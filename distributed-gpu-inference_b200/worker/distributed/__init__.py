@@ -1,6 +1,7 @@
 """Layer-range inference components (reference: worker/distributed/__init__.py)."""
 from .kv_cache import CacheBlock, DistributedKVCacheManager, KVCachePool, PagedKVCache
 from .model_shard import ModelShard, ShardedModelLoader, get_layer_range_for_worker
+from .servicer import InferenceServicer
 
 __all__ = [
     "ModelShard",
@@ -10,4 +11,5 @@ __all__ = [
     "PagedKVCache",
     "KVCachePool",
     "CacheBlock",
+    "InferenceServicer",
 ]

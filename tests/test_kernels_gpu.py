@@ -468,6 +468,56 @@ def test_wire_handoff_messages_are_the_references_rpc_and_land_in_the_receivers_
     assert bad["success"] is False and bad["error_message"]
 
 
+@pytest.mark.parametrize("dtype", [torch.bfloat16, torch.float16])
+def test_wire_handoff_stream_is_a_streaming_tensor_buffer_stream(dtype):
+    """export_stream: StreamingTensorBuffer framing (reference common/serialization.py:209-265) of the wire tensor —
+    header + 1 MiB chunks.  The host class consumes the frames (read_header / write_chunk / finalize) and rebuilds the
+    tensor the per-layer messages carry; import_stream scatters the same frames into the receiver's slots."""
+    from dgi_b200.common.serialization import StreamingTensorBuffer, TensorSerializer
+    from dgi_b200.kv_transfer import WireHandoff
+    from dgi_b200.worker.distributed.kv_cache import KVCachePool
+
+    L_, Hkv, D, bs, n_tok = 5, 8, 128, 16, 400     # 25 blocks x 32 KiB x 2 x 5 layers = 8000 KiB: 7 full frames + a tail
+    src = KVCachePool(L_, Hkv, D, bs, 40, device=DEV, dtype=dtype)
+    dst = KVCachePool(L_, Hkv, D, bs, 31, device=DEV, dtype=dtype)
+    src.backing.copy_(torch.randn(src.backing.shape, device=DEV, generator=torch.Generator(device=DEV).manual_seed(9)))
+    dst.allocate_sequence(50)
+    st = torch.tensor(KVCachePool.block_table(src.allocate_sequence(n_tok)[0]), dtype=torch.int32, device=DEV)
+    dt_ = torch.tensor(KVCachePool.block_table(dst.allocate_sequence(n_tok)[0]), dtype=torch.int32, device=DEV)
+    tx, rx = WireHandoff(src), WireHandoff(dst)
+    frames = [bytes(f) for f in tx.export_stream(st)]
+    n = st.shape[0]
+    shape = (L_, 2, n, Hkv, bs, D)
+    name = "bfloat16" if dtype == torch.bfloat16 else "float16"
+    assert frames[0] == StreamingTensorBuffer().write_header(shape, name)   # the golden header layout
+    payload = L_ * 2 * n * Hkv * bs * D * 2
+    assert [len(f) for f in frames[1:]] == [1 << 20] * (payload >> 20) + ([payload % (1 << 20)] if payload % (1 << 20) else [])
+    # a stock receiver: the host class rebuilds the tensor; it equals TensorSerializer's view of the same blocks
+    buf = StreamingTensorBuffer()
+    buf.metadata = buf.read_header(frames[0])
+    for f in frames[1:]:
+        buf.write_chunk(f)
+    rebuilt = buf.finalize()
+    want = src.backing[:, :, st.long()]
+    data, _, _ = TensorSerializer.serialize(want)
+    assert b"".join(frames[1:]) == data
+    assert torch.equal(_bits(rebuilt), _bits(TensorSerializer.deserialize(data, shape, name)))
+    # the GPU receiver
+    before = dst.backing.clone()
+    resp = rx.import_stream(frames, dt_)
+    assert resp["success"] and resp["bytes_transferred"] == payload
+    if dtype == torch.bfloat16:
+        want = want.to(torch.float16).to(torch.bfloat16)
+    assert torch.equal(_bits(dst.backing[:, :, dt_.long()]), _bits(want))
+    untouched = [i for i in range(31) if i not in dt_.tolist()]
+    assert torch.equal(dst.backing[:, :, untouched], before[:, :, untouched])
+    # small chunks and damaged streams
+    small = [bytes(f) for f in tx.export_stream(st, chunk_size=100_000)]
+    assert b"".join(small[1:]) == data and max(len(f) for f in small[1:]) == 100_000
+    assert rx.import_stream(frames[:-1], dt_)["success"] is False
+    assert rx.import_stream(frames, dt_[:-1])["success"] is False
+
+
 # ---- randomised sweep: many small ragged configurations against the oracle ---------------------------------------
 def test_attention_random_configurations_against_oracle():
     import random
