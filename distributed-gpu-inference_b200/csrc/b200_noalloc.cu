@@ -48,6 +48,10 @@ extern "C" int b200_paged_decode_attn_static(void* out, const void* q, int64_t q
                                              int num_splits, int dtype, unsigned flags, void* stream) {
   if (num_splits < 0) return b200::fail(B200_EINVAL, "b200_paged_decode_attn_static: negative num_splits");
   if (num_splits == 0) num_splits = b200_paged_decode_attn_plan(B, Hq, Hkv, D, block_size, max_context_len, dtype);
+  if (block_size > 0) {  // the regular entry point never uses more partitions than the context has blocks
+    const int n_blocks = (max_context_len > 1 ? max_context_len - 1 : 0) / block_size + 1;
+    if (num_splits > n_blocks) num_splits = n_blocks;
+  }
   const size_t need = b200_paged_decode_attn_workspace(B, Hq, D, num_splits);
   if (need > static_cast<size_t>(B200_STATIC_SCRATCH_BYTES))
     return b200::fail(B200_ENOSPC,

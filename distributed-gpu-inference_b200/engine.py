@@ -118,7 +118,9 @@ class PagedDecodeEngine:
         self.num_splits = ops.attn_plan(max_batch, self.Hq, self.Hkv, self.D, block_size, max_seq_len, self.dtype)
         ws = ops.attn_workspace_bytes(max_batch, self.Hq, self.D, self.num_splits)
         self.workspace = torch.empty(max(ws, 16), dtype=torch.uint8, device=dev)
-        self.inv_freq = self.shards[0].layers[0].inv_freq.to(dev) if len(self.shards[0].layers) else None
+        layer0 = self.shards[0].layers[0] if len(self.shards[0].layers) else None
+        self.inv_freq = layer0.inv_freq.to(dev) if layer0 is not None else None
+        self.rope_scaling = float(getattr(layer0, "rope_attention_scaling", 1.0))
         self.state = PagedBatchState(
             block_tables=self.block_tables,
             context_lens=self.context_lens,
@@ -310,7 +312,7 @@ class PagedDecodeEngine:
             prefill_mode=self.prefill_mode,
             past_len=past_len,
         )
-        chunk_state.cos, chunk_state.sin = rope_tables(pos, self.inv_freq, self.dtype)
+        chunk_state.cos, chunk_state.sin = rope_tables(pos, self.inv_freq, self.dtype, self.rope_scaling)
         h = inputs.to(self.device)
         for shard, handles in zip(self.shards, self._handles):
             hs = [PagedLayerKV(hd.k_pool, hd.v_pool, chunk_state) for hd in handles]
@@ -367,7 +369,7 @@ class PagedDecodeEngine:
         st.slot_mapping[:B].copy_(slot)
         self.context_lens[:B].add_(1)
         pos2 = pos[:, None]
-        st.cos, st.sin = rope_tables(pos2, self.inv_freq, self.dtype)
+        st.cos, st.sin = rope_tables(pos2, self.inv_freq, self.dtype, self.rope_scaling)
         h = self.ids_buf[:B] if self.is_first else self.h_in[:B]
         for shard, handles in zip(self.shards, self._handles):
             h, _ = shard.forward(h, position_ids=pos2, past_key_values=handles, use_cache=True)
@@ -400,6 +402,9 @@ class PagedDecodeEngine:
         side.wait_stream(torch.cuda.current_stream())
         with torch.cuda.stream(side):  # warm-up outside capture: cuBLAS handles, lazy module loads
             for _ in range(2):
+                # both warm-up steps run at the CURRENT position (the slot the first real step overwrites anyway):
+                # a second step one token further could index past a sequence's last block
+                self.context_lens.copy_(saved)
                 self._step_body()
         torch.cuda.current_stream().wait_stream(side)
         torch.cuda.synchronize()

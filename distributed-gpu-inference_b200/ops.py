@@ -476,15 +476,11 @@ def paged_decode_attention_static(
     partials exceed that raise; the first call per device performs a one-time address look-up, so issue it before
     any stream capture; calls that overlap on the GPU (different streams) race on the shared array.
     """
-    _need_cuda(q, k_pool, v_pool, block_tables, context_lens, out)
-    max_blocks, Hkv, bs, D = _pool_dims(k_pool)
-    B, Hq = q.shape[0], q.shape[1]
-    if tuple(out.shape) != (B, Hq, D) or not out.is_contiguous() or out.dtype != q.dtype:
-        raise ValueError("out must be a contiguous [B, Hq, D] tensor of q's dtype")
-    if block_tables.dtype != torch.int32 or context_lens.dtype != torch.int32:
-        raise ValueError("block_tables and context_lens must be int32")
-    q_stride = _row_stride(q, Hq, D)
-    table_stride = block_tables.stride(0) if B > 1 else block_tables.shape[1]
+    if out is None:
+        raise ValueError("out must be supplied: this entry point allocates nothing")
+    # the same argument checks as every other attention wrapper; with `out` given they allocate nothing
+    (B, Hq, Hkv, D, bs, max_blocks), q_stride, table_stride, out = _attn_args(q, k_pool, v_pool, block_tables,
+                                                                               context_lens, out)
     rc = _lib.load().b200_paged_decode_attn_static(
         out.data_ptr(), q.data_ptr(), q_stride, k_pool.data_ptr(), v_pool.data_ptr(), block_tables.data_ptr(),
         table_stride, context_lens.data_ptr(), B, Hq, Hkv, D, bs, max_blocks,

@@ -61,11 +61,64 @@ class RMSNorm(nn.Module):
         return ops.add_rmsnorm(x, self.weight, self.variance_epsilon)
 
 
-def rope_tables(position_ids: torch.Tensor, inv_freq: torch.Tensor, dtype: torch.dtype):
-    """``position_ids [B, T]`` → ``cos, sin [B, T, D]`` (fp32 math, cast to ``dtype``)."""
+def rope_tables(position_ids: torch.Tensor, inv_freq: torch.Tensor, dtype: torch.dtype, scaling: float = 1.0):
+    """``position_ids [B, T]`` → ``cos, sin [B, T, D]`` (fp32 math, times the RoPE variant's attention factor, cast to
+    ``dtype`` — transformers' ``LlamaRotaryEmbedding.forward``)."""
     freqs = position_ids.to(torch.float32)[:, :, None] * inv_freq[None, None, :]
     emb = torch.cat((freqs, freqs), dim=-1)
+    if scaling != 1.0:
+        return (emb.cos() * scaling).to(dtype), (emb.sin() * scaling).to(dtype)
     return emb.cos().to(dtype), emb.sin().to(dtype)
+
+
+def rope_init(config, head_dim: int, device=None):
+    """``(inv_freq [head_dim / 2] fp32, attention_scaling)`` for the RoPE variant a config names.
+
+    The reference runs the HuggingFace layers themselves (worker/distributed/model_shard.py:205-215), so whatever
+    ``config.rope_scaling`` / ``config.rope_parameters`` says is applied there by ``LlamaRotaryEmbedding``; a paged
+    layer that ignored it would load a Llama-3.1-style checkpoint without complaint and decode different tokens.
+    Supported: ``default``, ``linear``, ``llama3`` (formulas below), ``yarn`` (through transformers' own initialiser
+    when ``config`` is an HF config).  Variants whose frequencies change with the running sequence length
+    (``dynamic``, ``longrope``) and partial rotary dims are refused."""
+    import math
+
+    params = getattr(config, "rope_parameters", None) or getattr(config, "rope_scaling", None) or {}
+    params = dict(params)
+    kind = params.get("rope_type", params.get("type")) or "default"
+    theta = float(params.get("rope_theta", getattr(config, "rope_theta", None) or 10000.0))
+    if float(params.get("partial_rotary_factor", getattr(config, "partial_rotary_factor", 1.0) or 1.0)) != 1.0:
+        raise NotImplementedError("partial rotary embeddings are not supported by the paged layer")
+    inv_freq = 1.0 / (theta ** (torch.arange(0, head_dim, 2, dtype=torch.int64).to(torch.float32) / head_dim))
+    scaling = 1.0
+    if kind == "default":
+        pass
+    elif kind == "linear":
+        inv_freq = inv_freq / float(params["factor"])
+    elif kind == "llama3":
+        factor, lo, hi = float(params["factor"]), float(params["low_freq_factor"]), float(params["high_freq_factor"])
+        old_len = float(params["original_max_position_embeddings"])
+        wavelen = 2 * math.pi / inv_freq
+        scaled = torch.where(wavelen > old_len / lo, inv_freq / factor, inv_freq)   # long waves: slowed down
+        smooth = (old_len / wavelen - lo) / (hi - lo)                               # in between: blended
+        mid = ~(wavelen < old_len / hi) & ~(wavelen > old_len / lo)
+        inv_freq = torch.where(mid, (1 - smooth) * scaled / factor + smooth * scaled, scaled)
+    elif kind == "yarn" and hasattr(config, "standardize_rope_params"):
+        from transformers.modeling_rope_utils import ROPE_INIT_FUNCTIONS
+
+        inv_freq, scaling = ROPE_INIT_FUNCTIONS["yarn"](config, "cpu")
+        inv_freq, scaling = inv_freq.to(torch.float32), float(scaling)
+    else:
+        raise NotImplementedError(f"rope_type {kind!r} is not supported by the paged layer")
+    return (inv_freq.to(device) if device is not None else inv_freq), scaling
+
+
+def check_supported_config(config) -> None:
+    """Refuse Llama-family options the paged layer does not implement instead of silently ignoring them."""
+    for name in ("attention_bias", "mlp_bias"):
+        if getattr(config, name, False):
+            raise NotImplementedError(f"config.{name}=True is not supported by the paged layer (bias-free projections only)")
+    if getattr(config, "sliding_window", None):
+        raise NotImplementedError("sliding-window attention is not supported by the paged layer")
 
 
 def _rotate_half(x: torch.Tensor) -> torch.Tensor:
@@ -125,7 +178,7 @@ class PagedLlamaDecoderLayer(nn.Module):
         self.num_kv_heads = getattr(config, "num_key_value_heads", self.num_heads) or self.num_heads
         self.head_dim = getattr(config, "head_dim", None) or self.hidden_size // self.num_heads
         self.eps = getattr(config, "rms_norm_eps", 1e-5)
-        self.rope_theta = float(getattr(config, "rope_theta", 10000.0))
+        check_supported_config(config)
         kw = dict(bias=False, device=device, dtype=dtype)
         H, D = self.hidden_size, self.head_dim
         self.self_attn = nn.Module()
@@ -139,8 +192,8 @@ class PagedLlamaDecoderLayer(nn.Module):
         self.mlp.down_proj = nn.Linear(config.intermediate_size, H, **kw)
         self.input_layernorm = RMSNorm(H, self.eps, device, dtype)
         self.post_attention_layernorm = RMSNorm(H, self.eps, device, dtype)
-        inv_freq = 1.0 / (self.rope_theta ** (torch.arange(0, D, 2, dtype=torch.int64).to(torch.float32) / D))
-        self.register_buffer("inv_freq", inv_freq.to(device) if device is not None else inv_freq, persistent=False)
+        inv_freq, self.rope_attention_scaling = rope_init(config, D, device)
+        self.register_buffer("inv_freq", inv_freq, persistent=False)
 
     # ---- construction helpers ----------------------------------------------------------------------
     _LINEARS = (
@@ -237,7 +290,7 @@ class PagedLlamaDecoderLayer(nn.Module):
         else:
             if position_ids is None:
                 raise ValueError("position_ids (or precomputed RoPE tables in the batch state) are required")
-            cos, sin = rope_tables(position_ids, self.inv_freq, x.dtype)
+            cos, sin = rope_tables(position_ids, self.inv_freq, x.dtype, self.rope_attention_scaling)
 
         if T == 1:
             # decode: RoPE on q (in place) and k, append of k / v, all in one launch; then paged attention

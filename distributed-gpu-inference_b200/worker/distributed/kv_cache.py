@@ -375,6 +375,7 @@ class KVCachePool:
         bs = self._layer_caches[0].block_size
         n_blocks = (seq_len + bs - 1) // bs
         out: List[List[CacheBlock]] = []
+        held: List[List[str]] = []  # per layer: ids pinned by THIS call (never a shared block its owner pinned)
         for layer_idx, cache in enumerate(self._layer_caches):
             mine: List[CacheBlock] = []
             if shared_prefix is not None:
@@ -382,6 +383,7 @@ class KVCachePool:
                     blk.add_ref()
                     mine.append(blk)
             fresh = cache.allocate_blocks(layer_idx, n_blocks - len(mine), prefix_hash)
+            held.append([])
             if fresh is not None:  # enough free ids: no eviction can happen, so nothing needs protecting either
                 mine.extend(fresh)
                 out.append(mine)
@@ -389,20 +391,25 @@ class KVCachePool:
             for _ in range(n_blocks - len(mine)):
                 blk = cache.allocate_block(layer_idx, prefix_hash)
                 if blk is None:
-                    cache.unpin(b.block_id for b in mine)
+                    for li, ids in enumerate(held):
+                        self._layer_caches[li].unpin(ids)
                     self._free_sequence_blocks(out + [mine])
                     raise RuntimeError(f"Failed to allocate KV-Cache for layer {layer_idx}")
-                cache._pinned.add(blk.block_id)  # not evictable by the rest of this call
+                if blk.block_id not in cache._pinned:
+                    cache._pinned.add(blk.block_id)  # not evictable by the rest of this call
+                    held[layer_idx].append(blk.block_id)
                 mine.append(blk)
             out.append(mine)
-        for layer_idx, mine in enumerate(out):
-            self._layer_caches[layer_idx].unpin(b.block_id for b in mine)
+        for layer_idx, ids in enumerate(held):
+            self._layer_caches[layer_idx].unpin(ids)
         return out
 
     def _free_sequence_blocks(self, blocks: List[List[CacheBlock]]) -> None:
         for layer_idx, layer_blocks in enumerate(blocks):
             cache = self._layer_caches[layer_idx]
-            cache.unpin(b.block_id for b in layer_blocks)
+            # a block another sequence still references keeps its owner's pin: only blocks this free releases for
+            # good (last reference) stop being protected
+            cache.unpin(b.block_id for b in layer_blocks if b.ref_count <= 1)
             cache.free_blocks([blk.block_id for blk in layer_blocks])
 
     def free_sequence(self, blocks: List[List[CacheBlock]]) -> None:

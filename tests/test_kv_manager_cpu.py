@@ -122,6 +122,28 @@ def test_chained_block_hashes_and_radix_index():
     assert idx.match(toks)[0] == 0 and all(c.get_stats()["free_blocks"] == 16 for c in pool._layer_caches)
 
 
+def test_a_borrower_of_shared_blocks_never_lifts_the_owners_pins():
+    """A live owner pins its blocks; a second sequence borrows the leading ones (shared_prefix) and goes away again.
+    The owner's blocks must stay pinned throughout — otherwise they fall back to ref_count == 1, become LRU eviction
+    candidates while the owner is still decoding, and free_block zeroes them."""
+    pool = kv.KVCachePool(1, 2, 8, 4, 6, device="cpu", dtype=torch.float32)
+    cache = pool.layer(0)
+    owner = pool.allocate_sequence(12)                      # 3 blocks
+    cache.pin(b.block_id for b in owner[0])
+    owner[0][0].keys.fill_(7.0)
+    borrower = pool.allocate_sequence(16, shared_prefix=[owner[0][:2]])   # 2 shared + 2 fresh
+    assert all(b.block_id in cache._pinned for b in owner[0])            # allocation did not unpin what it borrowed
+    pool.free_sequence(borrower)
+    assert [b.ref_count for b in owner[0]] == [1, 1, 1]
+    assert all(b.block_id in cache._pinned for b in owner[0])            # nor did the borrower's departure
+    # pressure: 3 free blocks, ask for 5 -> eviction must not take the owner's pinned blocks, so this fails cleanly
+    with pytest.raises(RuntimeError, match="Failed to allocate"):
+        pool.allocate_sequence(20)
+    assert owner[0][0].keys.eq(7.0).all() and cache.get_stats()["evictions"] == 0
+    pool.free_sequence(owner)                                            # the owner's own free lifts its pins
+    assert not cache._pinned and cache.get_stats()["free_blocks"] == 6
+
+
 def test_batched_free_equals_block_by_block_free():
     a = kv.PagedKVCache(1, 2, 8, block_size=4, max_blocks=8, device="cpu", dtype=torch.float32)
     b = kv.PagedKVCache(1, 2, 8, block_size=4, max_blocks=8, device="cpu", dtype=torch.float32)

@@ -101,3 +101,55 @@ def test_from_config_checks_the_range_and_loader_rejects_too_little_memory():
     assert shard.is_last_shard and not shard.is_first_shard and shard.get_layer_count() == 2 and shard.lm_head is not None
     again = ModelShard.from_config(cfg, 0, 4, device="cpu", dtype=torch.float32, seed=0)
     assert torch.equal(again.layers[2].mlp.up_proj.weight, shard.layers[0].mlp.up_proj.weight)  # same weights in any partition
+
+
+# ---- RoPE variants: the paged layer must rotate like the HF layers the reference runs ------------------------------
+@pytest.mark.parametrize("scaling", [
+    None,
+    {"rope_type": "linear", "factor": 4.0},
+    {"rope_type": "llama3", "factor": 8.0, "low_freq_factor": 1.0, "high_freq_factor": 4.0,
+     "original_max_position_embeddings": 1024},
+    {"rope_type": "yarn", "factor": 4.0, "original_max_position_embeddings": 1024},
+])
+def test_paged_layer_rope_tables_equal_transformers_rotary_embedding(scaling):
+    from transformers import LlamaConfig
+    from transformers.models.llama.modeling_llama import LlamaRotaryEmbedding
+
+    from dgi_b200.paged_layer import PagedLlamaDecoderLayer, rope_tables
+
+    cfg = LlamaConfig(hidden_size=256, num_attention_heads=4, num_key_value_heads=2, intermediate_size=512, vocab_size=128,
+                      num_hidden_layers=1, rope_theta=500000.0, max_position_embeddings=8192, rope_scaling=scaling)
+    hf = LlamaRotaryEmbedding(cfg)
+    layer = PagedLlamaDecoderLayer(cfg, 0, device="cpu", dtype=torch.float32)
+    assert torch.equal(layer.inv_freq, hf.inv_freq)
+    assert layer.rope_attention_scaling == pytest.approx(float(hf.attention_scaling))
+    pos = torch.tensor([[0, 1, 17, 4095, 8000]])
+    for dtype in (torch.float32, torch.bfloat16):
+        want_cos, want_sin = hf(torch.zeros(1, 5, 256, dtype=dtype), pos)
+        cos, sin = rope_tables(pos, layer.inv_freq, dtype, layer.rope_attention_scaling)
+        assert torch.equal(cos, want_cos) and torch.equal(sin, want_sin)
+    if scaling is not None:
+        plain = PagedLlamaDecoderLayer(LlamaConfig(hidden_size=256, num_attention_heads=4, rope_theta=500000.0), 0,
+                                       device="cpu", dtype=torch.float32)
+        assert not torch.equal(plain.inv_freq, layer.inv_freq)  # the scaling is really applied
+
+
+def test_paged_layer_refuses_what_it_does_not_implement():
+    from transformers import LlamaConfig
+
+    from dgi_b200.paged_layer import PagedLlamaDecoderLayer
+
+    base = dict(hidden_size=256, num_attention_heads=4, num_key_value_heads=2, intermediate_size=512, vocab_size=128,
+                num_hidden_layers=1)
+    with pytest.raises(NotImplementedError, match="dynamic"):
+        PagedLlamaDecoderLayer(LlamaConfig(**base, rope_scaling={"rope_type": "dynamic", "factor": 2.0}), 0, "cpu", torch.float32)
+    with pytest.raises(NotImplementedError, match="attention_bias"):
+        PagedLlamaDecoderLayer(LlamaConfig(**base, attention_bias=True), 0, "cpu", torch.float32)
+    with pytest.raises(NotImplementedError, match="mlp_bias"):
+        PagedLlamaDecoderLayer(LlamaConfig(**base, mlp_bias=True), 0, "cpu", torch.float32)
+    # attribute-bag configs (bench.py's shapes) keep working: rope_theta as a plain attribute, no scaling
+    from dgi_b200.testing import LlamaShapeConfig
+
+    layer = PagedLlamaDecoderLayer(LlamaShapeConfig(**base), 0, "cpu", torch.float32)
+    want = 1.0 / (500000.0 ** (torch.arange(0, 64, 2, dtype=torch.int64).float() / 64))
+    assert torch.equal(layer.inv_freq, want) and layer.rope_attention_scaling == 1.0

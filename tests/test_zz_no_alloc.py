@@ -87,3 +87,21 @@ def test_static_scratch_entry_rejects_oversized_requests():
     torch.cuda.synchronize()
     want = ops.paged_decode_attention(q, k_pool, v_pool, tables, lens, 256, num_splits=1)
     assert torch.equal(out.view(torch.int16), want.view(torch.int16))
+
+
+def test_static_scratch_entry_sizes_its_check_like_the_regular_entry_and_validates_arguments():
+    # a generous split count on a short context is clamped to the number of blocks (3) before the size check, exactly
+    # as the regular entry point does — 64 splits of this shape would not fit the array, 3 do
+    q, k_pool, v_pool, tables, lens = _case(64, 64, 8, 128, [48] * 64, seed=404)
+    out = torch.empty_like(q)
+    assert _call_static_raw(q, k_pool, v_pool, tables, lens, 48, out, splits=64) == 0, _lib.load().b200_last_error()
+    torch.cuda.synchronize()
+    want = ops.paged_decode_attention(q, k_pool, v_pool, tables, lens, 48, num_splits=64)
+    assert torch.equal(out.view(torch.int16), want.view(torch.int16))
+    # the wrapper refuses mismatched arguments instead of reinterpreting them
+    with pytest.raises(TypeError, match="dtype"):
+        ops.paged_decode_attention_static(q.to(torch.float16), k_pool, v_pool, tables, lens, 48, out.to(torch.float16))
+    with pytest.raises(ValueError, match="block_tables"):
+        ops.paged_decode_attention_static(q, k_pool, v_pool, tables.t().contiguous().t(), lens, 48, out)
+    with pytest.raises(ValueError, match="out must be supplied"):
+        ops.paged_decode_attention_static(q, k_pool, v_pool, tables, lens, 48, None)
