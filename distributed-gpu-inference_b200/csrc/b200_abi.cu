@@ -55,9 +55,14 @@ int b200_kv_append(const void* k_new, const void* v_new, int64_t k_row_stride, i
                    max_blocks, dtype, static_cast<cudaStream_t>(stream));
 }
 
+namespace {
+// bytes in front of the partials that hold one arrival counter per (sequence, q head) row
+size_t counter_bytes(int B, int Hq) { return (static_cast<size_t>(B) * Hq * sizeof(int) + 255) / 256 * 256; }
+}  // namespace
+
 size_t b200_paged_decode_attn_workspace(int B, int Hq, int D, int num_splits) {
   if (B <= 0 || Hq <= 0 || D <= 0 || num_splits <= 1) return 0;
-  return static_cast<size_t>(B) * Hq * num_splits * (static_cast<size_t>(D) + 2) * sizeof(float);
+  return counter_bytes(B, Hq) + static_cast<size_t>(B) * Hq * num_splits * (static_cast<size_t>(D) + 2) * sizeof(float);
 }
 
 int b200_paged_decode_attn_plan(int B, int Hq, int Hkv, int D, int block_size, int max_context_len, int dtype) {
@@ -258,7 +263,9 @@ int attn_prefix_entry(const char* name, const NewToken& nt, void* out, const voi
   a.num_splits = ss;
   a.blocks_per_split = ceil_div(suffix_blocks, ss);
   a.round_scores = (flags & B200_ATTN_ROUND_SCORES) ? 1 : 0;
-  a.ws_acc = static_cast<float*>(workspace);
+  a.ws_counters = static_cast<int*>(workspace);
+  a.ws_counters_zero = (flags & B200_ATTN_WS_COUNTERS_ZERO) != 0;
+  a.ws_acc = reinterpret_cast<float*>(static_cast<unsigned char*>(workspace) + counter_bytes(B, Hq));
   a.ws_ml = a.ws_acc + static_cast<size_t>(B) * Hq * total * D;
   a.k_new = nt.k_new;
   a.k_new_stride = nt.k_stride;

@@ -23,6 +23,8 @@ struct AttnArgs {
   float* ws_acc;                // [B, Hq, num_splits, D] un-normalised partial outputs
   float* ws_ml;                 // [B, Hq, num_splits, 2] running max and sum
   int round_scores;
+  int* ws_counters;             // [B * Hq] arrival counters in front of the partials (shared-prefix entry points)
+  bool ws_counters_zero;        // the caller vouches that they read zero (B200_ATTN_WS_COUNTERS_ZERO)
   // fused RoPE + KV append (b200_rope_append_decode_attn); all null / zero for the plain entry points
   const void* k_new;   // [B, Hkv, D] un-rotated k of the new token, row stride k_new_stride
   int64_t k_new_stride;

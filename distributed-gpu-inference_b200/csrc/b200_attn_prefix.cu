@@ -13,7 +13,10 @@
 //       suffix CTAs  (suffix_splits x Hkv x B): a sequence's own blocks after the prefix, one kv head, its group
 //                    of q heads — the plain kernel's work item.
 //                    Every CTA files a partial (m, l, O) in the split-K workspace.
-//   launch 2               attn_combine_kernel over prefix_splits + suffix_splits partials per (sequence, q head).
+//   merge                  every CTA counts its arrival per (sequence, q head) row in a counter that lives in front of
+//                          the workspace; the CTA that brings a row's count to prefix_splits + suffix_splits merges that
+//                          row's partials into `out` and puts the counter back to zero — no second launch.
+//                          Long prefix runs per CTA keep the two-launch form (attn_combine_kernel), see attn_prefix().
 //
 // The caller guarantees: block_tables[b][0:prefix_blocks] are identical for all b, and every context_lens[b] >=
 // prefix_blocks * 16 (the prefix blocks are full for everybody, so launch 1 needs no masking).
@@ -43,7 +46,8 @@ struct CascadeParams {
   int n_prefix_ctas;               // CTAs [0, n_prefix_ctas) run the prefix role
   float* ws_acc;
   float* ws_ml;
-  int round_scores;
+  int* counters;                   // [B * Hq] arrival counters, zero before and after the launch; null: separate combine
+  void* out;                       // [B, Hq, D] (written by the merging CTAs)
   // fused decode step (FUSED kernels only): un-rotated q, the new token's rows, RoPE tables, writable pools
   const void* k_new;
   int64_t k_new_stride;
@@ -59,7 +63,9 @@ struct CascadeParams {
 // SUFFIX = true (NT = 1): columns are the q heads of sequence `zi`; tiles past the context are masked.
 // FUSED: q arrives un-rotated and is rotated in registers (both roles); the suffix warp that owns a sequence's last
 // tile appends the new token's rotated k and its v, exactly as paged_attn_tma_kernel<.., FUSED> does.
-template <typename T, int D, int STAGES, int NT, bool SUFFIX, bool FUSED>
+constexpr int kMaxMergeSplits = 256;  // as attn_combine_kernel
+
+template <typename T, int D, int STAGES, int NT, bool SUFFIX, bool FUSED, bool ROUND>
 __device__ __forceinline__ void cascade_role(const CUtensorMap& k_map, const CUtensorMap& v_map, const CascadeParams& p,
                                              int split, int kvh, int zi) {
   using S = Smem<D, STAGES>;
@@ -72,9 +78,8 @@ __device__ __forceinline__ void cascade_role(const CUtensorMap& k_map, const CUt
   const int64_t q_row_stride = p.q_row_stride;
   const int B = p.B, Hq = p.Hq, Hkv = p.Hkv, G = p.G;
   const float scale = p.scale;
-  const int round_scores = p.round_scores;
-  float* __restrict__ ws_acc = p.ws_acc;
-  float* __restrict__ ws_ml = p.ws_ml;
+  float* ws_acc = p.ws_acc;
+  float* ws_ml = p.ws_ml;
   const int splits_total = p.prefix_splits + p.suffix_splits;
   const int qgroup = zi;
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
@@ -210,20 +215,28 @@ __device__ __forceinline__ void cascade_role(const CUtensorMap& k_map, const CUt
       if (append_here && i == n_mine - 1) append_patch<T, D>(ap, fa, Hkv, kvh, (ctx - 1) & (kTok - 1), lane, k_tile, v_tile);
     }
 
-    float s[NT][4];
+    // S^T = K Q^T.  Two accumulators per column group (even / odd k-steps) halve the dependent-MMA chain.
+    float s[NT][4], s2[NT][4];
 #pragma unroll
-    for (int nt = 0; nt < NT; ++nt) s[nt][0] = s[nt][1] = s[nt][2] = s[nt][3] = 0.f;
+    for (int nt = 0; nt < NT; ++nt) {
+      s[nt][0] = s[nt][1] = s[nt][2] = s[nt][3] = 0.f;
+      s2[nt][0] = s2[nt][1] = s2[nt][2] = s2[nt][3] = 0.f;
+    }
 #pragma unroll
-    for (int kk = 0; kk < KSTEPS; ++kk) {
-      uint32_t a[4];
+    for (int kk = 0; kk < KSTEPS; kk += 2) {
+      uint32_t a[4], a2[4];
       ldmatrix_x4(a, k_tile + tile_off(k_row, 2 * kk + k_chunk));
+      ldmatrix_x4(a2, k_tile + tile_off(k_row, 2 * kk + 2 + k_chunk));
 #pragma unroll
-      for (int nt = 0; nt < NT; ++nt) Mma<T>::run(s[nt], a, qf[kk][nt][0], qf[kk][nt][1]);
+      for (int nt = 0; nt < NT; ++nt) {
+        Mma<T>::run(s[nt], a, qf[kk][nt][0], qf[kk][nt][1]);
+        Mma<T>::run(s2[nt], a2, qf[kk + 1][nt][0], qf[kk + 1][nt][1]);
+      }
     }
 
     float corr[NT][2];
     uint32_t pb[NT][2];
-#pragma unroll
+    bool rescale = false;
     const int tok0 = (blk_begin + warp + i * kWarps) * kTok + quad;
     const bool ok_lo = !SUFFIX || tok0 < ctx, ok_hi = !SUFFIX || tok0 + 8 < ctx;
 #pragma unroll
@@ -231,7 +244,8 @@ __device__ __forceinline__ void cascade_role(const CUtensorMap& k_map, const CUt
       float x[4];
 #pragma unroll
       for (int e = 0; e < 4; ++e) {
-        const float v = round_scores ? Mma<T>::round(Mma<T>::round(s[nt][e]) * scale) * 1.4426950408889634f : s[nt][e] * sl2;
+        const float sv = s[nt][e] + s2[nt][e];
+        const float v = ROUND ? Mma<T>::round(Mma<T>::round(sv) * scale) * 1.4426950408889634f : sv * sl2;
         x[e] = ((e < 2) ? ok_lo : ok_hi) ? v : -INFINITY;
       }
 #pragma unroll
@@ -240,29 +254,37 @@ __device__ __forceinline__ void cascade_role(const CUtensorMap& k_map, const CUt
         mx = fmaxf(mx, __shfl_xor_sync(0xffffffffu, mx, 4));
         mx = fmaxf(mx, __shfl_xor_sync(0xffffffffu, mx, 8));
         mx = fmaxf(mx, __shfl_xor_sync(0xffffffffu, mx, 16));
-        const float m_new = fmaxf(m_run[nt][c], mx);
-        corr[nt][c] = exp2f(m_run[nt][c] - m_new);
+        const float m_new = fmaxf(m_run[nt][c], mx);  // finite: every tile holds at least one valid token
+        rescale |= m_new != m_run[nt][c];
+        corr[nt][c] = fast_exp2(m_run[nt][c] - m_new);  // 2^-inf = 0 on the first tile
         m_run[nt][c] = m_new;
-        x[c] = exp2f(x[c] - m_new);
-        x[c + 2] = exp2f(x[c + 2] - m_new);
+        x[c] = fast_exp2(x[c] - m_new);
+        x[c + 2] = fast_exp2(x[c + 2] - m_new);
         l_run[nt][c] = l_run[nt][c] * corr[nt][c] + x[c] + x[c + 2];
       }
       pb[nt][0] = movmatrix_trans(Mma<T>::pack(x[0], x[1]));
       pb[nt][1] = movmatrix_trans(Mma<T>::pack(x[2], x[3]));
     }
 
+    // O^T = O^T * corr + V^T P^T.  Once the running maxima have settled (after the first few tiles of a run) every
+    // corr is exactly 1 and the 4 * NT * MTILES multiplies are skipped for the whole warp.
+    if (__any_sync(0xffffffffu, rescale)) {
+#pragma unroll
+      for (int mt = 0; mt < MTILES; ++mt)
+#pragma unroll
+        for (int nt = 0; nt < NT; ++nt) {
+          o[mt][nt][0] *= corr[nt][0];
+          o[mt][nt][1] *= corr[nt][1];
+          o[mt][nt][2] *= corr[nt][0];
+          o[mt][nt][3] *= corr[nt][1];
+        }
+    }
 #pragma unroll
     for (int mt = 0; mt < MTILES; ++mt) {
       uint32_t a[4];
       ldmatrix_x4_trans(a, v_tile + tile_off(v_row, 2 * mt + v_chunk));
 #pragma unroll
-      for (int nt = 0; nt < NT; ++nt) {
-        o[mt][nt][0] *= corr[nt][0];
-        o[mt][nt][1] *= corr[nt][1];
-        o[mt][nt][2] *= corr[nt][0];
-        o[mt][nt][3] *= corr[nt][1];
-        Mma<T>::run(o[mt][nt], a, pb[nt][0], pb[nt][1]);
-      }
+      for (int nt = 0; nt < NT; ++nt) Mma<T>::run(o[mt][nt], a, pb[nt][0], pb[nt][1]);
     }
     __syncwarp();
     if (i + STAGES < n_mine) issue(i + STAGES);
@@ -302,19 +324,22 @@ __device__ __forceinline__ void cascade_role(const CUtensorMap& k_map, const CUt
   }
   __syncthreads();
   const float ln2 = 0.6931471805599453f;
-  for (int idx = threadIdx.x; idx < COLS * D; idx += kWarps * 32) {
-    const int c = idx / D, d = idx - c * D;
-    int bq, g;
+  auto row_of = [&](int c, int& bq, int& g) -> bool {  // column c of this CTA -> (sequence, head of the group)
     if constexpr (SUFFIX) {
       bq = zi;
       g = c;
-      if (c >= G) continue;
+      return c < G;
     } else {
       const int r = qgroup * COLS + c;
       bq = r / G;
       g = r - bq * G;
-      if (bq >= B) continue;
+      return bq < B;
     }
+  };
+  for (int idx = threadIdx.x; idx < COLS * D; idx += kWarps * 32) {
+    const int c = idx / D, d = idx - c * D;
+    int bq, g;
+    if (!row_of(c, bq, g)) continue;
     float M = -INFINITY;
 #pragma unroll
     for (int w = 0; w < kWarps; ++w) M = fmaxf(M, m_s[w * COLS + c]);
@@ -322,7 +347,7 @@ __device__ __forceinline__ void cascade_role(const CUtensorMap& k_map, const CUt
 #pragma unroll
     for (int w = 0; w < kWarps; ++w) {
       const float mw = m_s[w * COLS + c];
-      const float wgt = (mw == -INFINITY) ? 0.f : exp2f(mw - M);
+      const float wgt = (mw == -INFINITY) ? 0.f : fast_exp2(mw - M);
       acc = fmaf(wgt, o_s[(w * COLS + c) * D + d], acc);
       L = fmaf(wgt, l_s[w * COLS + c], L);
     }
@@ -333,9 +358,78 @@ __device__ __forceinline__ void cascade_role(const CUtensorMap& k_map, const CUt
       ws_ml[pidx * 2 + 1] = L;
     }
   }
+  if (p.counters == nullptr) return;  // two-launch form: attn_combine_kernel merges
+
+  // ---- merge by the last-arriving CTA of each row ------------------------------------------------------------------
+  // One warp per row (the CTA's rows are dealt round-robin to its 4 warps): lanes stride over the partials for the
+  // weights, then every lane owns D / 32 consecutive output elements and streams the partial rows with independent
+  // 8- or 16-byte loads, so a row costs about two global round trips.
+  constexpr int VPL = D / 32;  // output elements per lane: 4 (float4) or 2 (float2)
+  __shared__ int last_s[COLS];
+  __shared__ float w_s[kWarps][kMaxMergeSplits];
+  __threadfence();  // this CTA's partials are visible device-wide before its arrival is counted
+  __syncthreads();
+  if (threadIdx.x < COLS) {
+    int bq, g, last = 0;
+    if (row_of(threadIdx.x, bq, g)) {
+      int* cnt = p.counters + static_cast<int64_t>(bq) * Hq + kvh * G + g;
+      last = atomicAdd(cnt, 1) == splits_total - 1;
+      if (last) *cnt = 0;  // everybody has arrived: leave the counter as the next launch expects it
+    }
+    last_s[threadIdx.x] = last;
+  }
+  __syncthreads();
+  T* __restrict__ out = static_cast<T*>(p.out);
+  float* wv = w_s[warp];
+  for (int c = warp; c < COLS; c += kWarps) {
+    if (!last_s[c]) continue;  // warp-uniform
+    int bq, g;
+    row_of(c, bq, g);
+    const int64_t row = static_cast<int64_t>(bq) * Hq + kvh * G + g;
+    __threadfence();
+    const float2* ml = reinterpret_cast<const float2*>(ws_ml) + row * splits_total;
+    float M = -INFINITY;
+    for (int sp = lane; sp < splits_total; sp += 32) M = fmaxf(M, __ldcg(ml + sp).x);
+#pragma unroll
+    for (int off = 16; off > 0; off >>= 1) M = fmaxf(M, __shfl_xor_sync(0xffffffffu, M, off));
+    float L = 0.f;
+    for (int sp = lane; sp < splits_total; sp += 32) {
+      const float2 v = __ldcg(ml + sp);
+      const float w = (v.x == -INFINITY) ? 0.f : __expf(v.x - M);
+      wv[sp] = w;
+      L = fmaf(w, v.y, L);
+    }
+#pragma unroll
+    for (int off = 16; off > 0; off >>= 1) L += __shfl_xor_sync(0xffffffffu, L, off);
+    const float inv = L > 0.f ? 1.f / L : 0.f;
+    __syncwarp();
+    const float* acc = ws_acc + row * splits_total * D + lane * VPL;
+    float o[VPL];
+#pragma unroll
+    for (int e = 0; e < VPL; ++e) o[e] = 0.f;
+#pragma unroll 8
+    for (int sp = 0; sp < splits_total; ++sp) {
+      const float w = wv[sp];
+      if constexpr (VPL == 4) {
+        const float4 v = __ldcg(reinterpret_cast<const float4*>(acc + static_cast<int64_t>(sp) * D));
+        o[0] = fmaf(w, v.x, o[0]);
+        o[1] = fmaf(w, v.y, o[1]);
+        o[2] = fmaf(w, v.z, o[2]);
+        o[3] = fmaf(w, v.w, o[3]);
+      } else {
+        const float2 v = __ldcg(reinterpret_cast<const float2*>(acc + static_cast<int64_t>(sp) * D));
+        o[0] = fmaf(w, v.x, o[0]);
+        o[1] = fmaf(w, v.y, o[1]);
+      }
+    }
+    T* orow = out + row * D + lane * VPL;
+#pragma unroll
+    for (int e = 0; e < VPL; ++e) orow[e] = Cvt<T>::from_f32(o[e] * inv);
+    __syncwarp();  // wv is reused by this warp's next row
+  }
 }
 
-template <typename T, int D, int STAGES, int NT, bool FUSED>
+template <typename T, int D, int STAGES, int NT, bool FUSED, bool ROUND>
 __global__ void __launch_bounds__(kWarps * 32, (NT <= 2 ? 2 : 1))
 paged_attn_cascade_kernel(const __grid_constant__ CUtensorMap k_map, const __grid_constant__ CUtensorMap v_map,
                           const __grid_constant__ CascadeParams p) {
@@ -343,43 +437,40 @@ paged_attn_cascade_kernel(const __grid_constant__ CUtensorMap k_map, const __gri
   if (id < p.n_prefix_ctas) {  // heavier CTAs first
     const int split = id % p.prefix_splits;
     const int rest = id / p.prefix_splits;
-    cascade_role<T, D, STAGES, NT, false, FUSED>(k_map, v_map, p, split, rest % p.Hkv, rest / p.Hkv);
+    cascade_role<T, D, STAGES, NT, false, FUSED, ROUND>(k_map, v_map, p, split, rest % p.Hkv, rest / p.Hkv);
   } else {
     const int j = id - p.n_prefix_ctas;
     const int split = j % p.suffix_splits;
     const int rest = j / p.suffix_splits;
-    cascade_role<T, D, STAGES, 1, true, FUSED>(k_map, v_map, p, split, rest % p.Hkv, rest / p.Hkv);
+    cascade_role<T, D, STAGES, 1, true, FUSED, ROUND>(k_map, v_map, p, split, rest % p.Hkv, rest / p.Hkv);
   }
 }
 
 inline int ceil_div(int a, int b) { return (a + b - 1) / b; }
 
-// ring depth: 3 stages at 2 CTAs per SM (NT <= 2); the 32-row variant (NT = 4) needs the whole register file of an SM
-// for one CTA, so it gets a 6-stage ring to keep the same number of bytes in flight
-template <int NT>
-constexpr int prefix_stages() { return NT <= 2 ? 3 : 6; }
+constexpr int kPrefixNT = 2;       // 16 query rows ((sequence, head) pairs) per prefix CTA
+constexpr int kPrefixStages = 3;   // ring depth at 2 CTAs per SM
 
-// Query rows per CTA = 8 * NT.  NT = 2 by default; B200_PREFIX_NT=1|2|4 overrides (tools/kbench.py sweeps).
-int prefix_nt() {
-  static const int nt = [] {
-    const char* e = getenv("B200_PREFIX_NT");
-    const int v = e ? atoi(e) : 2;
-    return (v == 1 || v == 2 || v == 4) ? v : 2;
+int separate_combine() {  // -1: library's choice, 0 / 1: forced by B200_PREFIX_SEPARATE_COMBINE
+  static const int v = [] {
+    const char* e = getenv("B200_PREFIX_SEPARATE_COMBINE");
+    return e ? (atoi(e) != 0 ? 1 : 0) : -1;
   }();
-  return nt;
+  return v;
 }
 
-template <typename T, int D, int NT, bool FUSED>
+template <typename T, int D, bool FUSED, bool ROUND>
 int launch_cascade_impl(const AttnArgs& a, int dtype, int prefix_blocks, int prefix_splits, int suffix_splits,
-                        cudaStream_t stream) {
-  using S = Smem<D, prefix_stages<NT>()>;
+                        int* counters, cudaStream_t stream) {
+  constexpr int NT = kPrefixNT;
+  using S = Smem<D, kPrefixStages>;
   const uint64_t rows = static_cast<uint64_t>(a.max_blocks) * a.Hkv * kTok;
   CUtensorMap km, vm;
   int rc = get_tensor_map(a.k_pool, rows, D, dtype, &km);
   if (rc) return rc;
   rc = get_tensor_map(a.v_pool, rows, D, dtype, &vm);
   if (rc) return rc;
-  auto kern = paged_attn_cascade_kernel<T, D, prefix_stages<NT>(), NT, FUSED>;
+  auto kern = paged_attn_cascade_kernel<T, D, kPrefixStages, NT, FUSED, ROUND>;
   cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, S::kTotal);
   if (e != cudaSuccess) return fail(static_cast<int>(e), "cudaFuncSetAttribute: %s", cudaGetErrorString(e));
   CascadeParams p{};
@@ -402,7 +493,8 @@ int launch_cascade_impl(const AttnArgs& a, int dtype, int prefix_blocks, int pre
   p.n_prefix_ctas = prefix_splits * a.Hkv * qgroups;
   p.ws_acc = a.ws_acc;
   p.ws_ml = a.ws_ml;
-  p.round_scores = a.round_scores;
+  p.counters = counters;
+  p.out = a.out;
   if (FUSED) {
     p.k_new = a.k_new;
     p.k_new_stride = a.k_new_stride;
@@ -418,12 +510,15 @@ int launch_cascade_impl(const AttnArgs& a, int dtype, int prefix_blocks, int pre
   return check_launch("b200_paged_decode_attn_prefix(cascade)");
 }
 
-template <typename T, int D, int NT>
-int launch_cascade(const AttnArgs& a, int dtype, int prefix_blocks, int prefix_splits, int suffix_splits,
+template <typename T, int D>
+int launch_cascade(const AttnArgs& a, int dtype, int prefix_blocks, int prefix_splits, int suffix_splits, int* counters,
                    cudaStream_t stream) {
-  return a.k_new != nullptr
-             ? launch_cascade_impl<T, D, NT, true>(a, dtype, prefix_blocks, prefix_splits, suffix_splits, stream)
-             : launch_cascade_impl<T, D, NT, false>(a, dtype, prefix_blocks, prefix_splits, suffix_splits, stream);
+  const bool fused = a.k_new != nullptr, round = a.round_scores != 0;
+#define B200_CASCADE_GO(F, R) \
+  launch_cascade_impl<T, D, F, R>(a, dtype, prefix_blocks, prefix_splits, suffix_splits, counters, stream)
+  if (fused) return round ? B200_CASCADE_GO(true, true) : B200_CASCADE_GO(true, false);
+  return round ? B200_CASCADE_GO(false, true) : B200_CASCADE_GO(false, false);
+#undef B200_CASCADE_GO
 }
 
 }  // namespace
@@ -437,7 +532,7 @@ bool attn_prefix_supported(const AttnArgs& a, int dtype) { return attn_tma_suppo
 void attn_prefix_plan(int B, int Hq, int Hkv, int block_size, int prefix_blocks, int max_context_len,
                       int* prefix_splits, int* suffix_splits) {
   const int G = std::max(1, Hq / std::max(1, Hkv));
-  const int qgroups = std::max(1, ceil_div(B * G, 8 * prefix_nt()));
+  const int qgroups = std::max(1, ceil_div(B * G, 8 * kPrefixNT));
   const int min_blocks = std::max(1, 256 / block_size);
   int ps = ceil_div(kNumSMs, std::max(1, Hkv * qgroups));
   ps = std::max(1, std::min(ps, std::max(1, prefix_blocks / min_blocks)));
@@ -452,25 +547,31 @@ void attn_prefix_plan(int B, int Hq, int Hkv, int block_size, int prefix_blocks,
 
 int attn_prefix(const AttnArgs& a, int dtype, int prefix_blocks, int prefix_splits, int suffix_splits, cudaStream_t s) {
   const int total = prefix_splits + suffix_splits;
-  int rc;
-#define B200_CASCADE_DISPATCH(NT)                                                                                       \
-  (dtype == B200_DTYPE_BF16                                                                                             \
-       ? (a.D == 128 ? launch_cascade<__nv_bfloat16, 128, NT>(a, dtype, prefix_blocks, prefix_splits, suffix_splits, s) \
-                     : launch_cascade<__nv_bfloat16, 64, NT>(a, dtype, prefix_blocks, prefix_splits, suffix_splits, s)) \
-       : (a.D == 128 ? launch_cascade<__half, 128, NT>(a, dtype, prefix_blocks, prefix_splits, suffix_splits, s)        \
-                     : launch_cascade<__half, 64, NT>(a, dtype, prefix_blocks, prefix_splits, suffix_splits, s)))
-  switch (prefix_nt()) {
-    case 1:
-      rc = B200_CASCADE_DISPATCH(1);
-      break;
-    case 4:
-      rc = B200_CASCADE_DISPATCH(4);
-      break;
-    default:
-      rc = B200_CASCADE_DISPATCH(2);
+  if (total > kMaxMergeSplits)
+    return fail(B200_ESHAPE, "b200_paged_decode_attn_prefix: more than %d splits cannot be merged", kMaxMergeSplits);
+  // Arrival counters in front of the partials.  They must read zero when the kernel starts; the merging CTAs put
+  // them back to zero, so a caller that owns the workspace exclusively can promise that (B200_ATTN_WS_COUNTERS_ZERO)
+  // and save the memset node.
+  // Who merges: the last CTA to arrive when launches are short (the second launch would be a visible share of the
+  // step), a separate combine launch when each prefix CTA streams a long run of blocks — there the prefix CTAs are the
+  // last to finish, each would merge its 16 rows on its own at the very end, and that tail costs more than the launch
+  // (measured on B200, config 5: 68.5 us merged in-kernel vs 62.7 us with the combine launch; 64 sequences behind a
+  // 2048-token prompt: 37 us vs 42 us).  B200_PREFIX_SEPARATE_COMBINE=0|1 overrides.
+  const int force = separate_combine();
+  const bool in_kernel = force >= 0 ? force == 0 : ceil_div(prefix_blocks, prefix_splits) < 96;
+  int* counters = in_kernel ? a.ws_counters : nullptr;
+  if (counters != nullptr && !a.ws_counters_zero) {
+    cudaError_t e = cudaMemsetAsync(counters, 0, sizeof(int) * static_cast<size_t>(a.B) * a.Hq, s);
+    if (e != cudaSuccess) return fail(static_cast<int>(e), "cudaMemsetAsync(counters): %s", cudaGetErrorString(e));
   }
-#undef B200_CASCADE_DISPATCH
-  if (rc) return rc;
+  int rc;
+  if (dtype == B200_DTYPE_BF16)
+    rc = a.D == 128 ? launch_cascade<__nv_bfloat16, 128>(a, dtype, prefix_blocks, prefix_splits, suffix_splits, counters, s)
+                    : launch_cascade<__nv_bfloat16, 64>(a, dtype, prefix_blocks, prefix_splits, suffix_splits, counters, s);
+  else
+    rc = a.D == 128 ? launch_cascade<__half, 128>(a, dtype, prefix_blocks, prefix_splits, suffix_splits, counters, s)
+                    : launch_cascade<__half, 64>(a, dtype, prefix_blocks, prefix_splits, suffix_splits, counters, s);
+  if (rc || counters != nullptr) return rc;
   return attn_combine(a.out, a.ws_acc, a.ws_ml, a.B * a.Hq, a.D, total, dtype, s);
 }
 

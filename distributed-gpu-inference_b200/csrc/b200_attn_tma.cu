@@ -261,6 +261,7 @@ paged_attn_tma_kernel(const __grid_constant__ CUtensorMap k_map, const __grid_co
       x[e] = ((e < 2) ? ok_lo : ok_hi) ? v : -INFINITY;
     }
     float corr[2];
+    bool rescale = false;
 #pragma unroll
     for (int c = 0; c < 2; ++c) {
       float mx = fmaxf(x[c], x[c + 2]);
@@ -268,25 +269,32 @@ paged_attn_tma_kernel(const __grid_constant__ CUtensorMap k_map, const __grid_co
       mx = fmaxf(mx, __shfl_xor_sync(0xffffffffu, mx, 8));
       mx = fmaxf(mx, __shfl_xor_sync(0xffffffffu, mx, 16));
       const float m_new = fmaxf(m_run[c], mx);  // finite: every tile holds at least one valid token
-      corr[c] = exp2f(m_run[c] - m_new);        // exp2(-inf) = 0 on the first tile
+      rescale |= m_new != m_run[c];
+      corr[c] = fast_exp2(m_run[c] - m_new);    // 2^-inf = 0 on the first tile
       m_run[c] = m_new;
-      x[c] = exp2f(x[c] - m_new);
-      x[c + 2] = exp2f(x[c + 2] - m_new);
+      x[c] = fast_exp2(x[c] - m_new);
+      x[c + 2] = fast_exp2(x[c + 2] - m_new);
       l_run[c] = l_run[c] * corr[c] + x[c] + x[c + 2];
     }
     // P^T as the B operand: transpose the two 8x8 (tok x g) fragments into (g x tok) register layout
     const uint32_t pb0 = movmatrix_trans(Mma<T>::pack(x[0], x[1]));
     const uint32_t pb1 = movmatrix_trans(Mma<T>::pack(x[2], x[3]));
 
-    // O^T = O^T * corr + V^T P^T
+    // O^T = O^T * corr + V^T P^T; once the running maxima have settled every corr is exactly 1 and the multiplies
+    // are skipped for the whole warp
+    if (__any_sync(0xffffffffu, rescale)) {
+#pragma unroll
+      for (int mt = 0; mt < MTILES; ++mt) {
+        o[mt][0] *= corr[0];
+        o[mt][1] *= corr[1];
+        o[mt][2] *= corr[0];
+        o[mt][3] *= corr[1];
+      }
+    }
 #pragma unroll
     for (int mt = 0; mt < MTILES; ++mt) {
       uint32_t a[4];
       ldmatrix_x4_trans(a, v_tile + tile_off(v_row, 2 * mt + v_chunk));
-      o[mt][0] *= corr[0];
-      o[mt][1] *= corr[1];
-      o[mt][2] *= corr[0];
-      o[mt][3] *= corr[1];
       Mma<T>::run(o[mt], a, pb0, pb1);
     }
 
@@ -337,7 +345,7 @@ paged_attn_tma_kernel(const __grid_constant__ CUtensorMap k_map, const __grid_co
 #pragma unroll
     for (int w = 0; w < kWarps; ++w) {
       const float mw = m_s[w * 8 + g];
-      const float wgt = (mw == -INFINITY) ? 0.f : exp2f(mw - M);
+      const float wgt = (mw == -INFINITY) ? 0.f : fast_exp2(mw - M);
       acc = fmaf(wgt, o_s[(w * 8 + g) * D + d], acc);
       L = fmaf(wgt, l_s[w * 8 + g], L);
     }

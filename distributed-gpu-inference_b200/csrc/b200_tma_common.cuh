@@ -55,6 +55,14 @@ static __device__ __forceinline__ uint32_t movmatrix_trans(uint32_t a) {
   return d;
 }
 
+// 2^x in one MUFU instruction (exp2f() wraps the same instruction in range scaling for denormal results, four more
+// instructions per call).  ex2.approx(-inf) = +0, which the online softmax relies on.
+static __device__ __forceinline__ float fast_exp2(float x) {
+  float y;
+  asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
+  return y;
+}
+
 template <typename T>
 struct Mma;
 template <>

@@ -117,7 +117,7 @@ class PagedDecodeEngine:
                        if self.external_head else None)
         self.num_splits = ops.attn_plan(max_batch, self.Hq, self.Hkv, self.D, block_size, max_seq_len, self.dtype)
         ws = ops.attn_workspace_bytes(max_batch, self.Hq, self.D, self.num_splits)
-        self.workspace = torch.empty(max(ws, 16), dtype=torch.uint8, device=dev)
+        self.workspace = torch.zeros(max(ws, 16), dtype=torch.uint8, device=dev)
         layer0 = self.shards[0].layers[0] if len(self.shards[0].layers) else None
         self.inv_freq = layer0.inv_freq.to(dev) if layer0 is not None else None
         self.rope_scaling = float(getattr(layer0, "rope_attention_scaling", 1.0))
@@ -218,6 +218,7 @@ class PagedDecodeEngine:
         """Configure decode attention for ``n_shared`` leading blocks common to all sequences (0 = none)."""
         st = self.state
         st.prefix_blocks = 0
+        st.attn_flags &= ~ops.ATTN_WS_COUNTERS_ZERO
         self.prefix_blocks = n_shared
         if n_shared > 0 and self.dtype in (torch.bfloat16, torch.float16) and self.block_size == 16 \
                 and self.D in (64, 128) and self.Hq // self.Hkv <= 8:
@@ -225,8 +226,13 @@ class PagedDecodeEngine:
                                           self.max_seq_len, self.dtype)
             need = ops.attn_workspace_bytes(self.batch, self.Hq, self.D, ps + ss)
             if self.workspace.numel() < need:
-                self.workspace = torch.empty(need, dtype=torch.uint8, device=self.device)
+                self.workspace = torch.zeros(need, dtype=torch.uint8, device=self.device)
                 st.workspace = self.workspace
+            else:
+                self.workspace.zero_()
+            # the workspace is this engine's alone and starts out zero: the cascade kernel's arrival counters (its
+            # first bytes) need no clearing per step
+            st.attn_flags |= ops.ATTN_WS_COUNTERS_ZERO
             st.prefix_blocks, st.prefix_splits, st.suffix_splits = n_shared, ps, ss
 
     def release(self) -> None:
@@ -235,6 +241,8 @@ class PagedDecodeEngine:
                 continue
             if not self._borrowed:
                 for pool, shard_blocks in zip(self.pools, per_shard):
+                    for li, layer_blocks in enumerate(shard_blocks):  # the pins allocate() set for this sequence
+                        pool.layer(li).unpin(blk.block_id for blk in layer_blocks)
                     pool.free_sequence(shard_blocks)
             self._seq_blocks[b] = None
         self.batch = 0

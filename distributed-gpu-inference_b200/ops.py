@@ -16,6 +16,7 @@ DTYPE_ID = {torch.float16: 0, torch.float32: 1, torch.bfloat16: 2}
 
 ATTN_FORCE_GENERIC = 1
 ATTN_ROUND_SCORES = 2
+ATTN_WS_COUNTERS_ZERO = 4  # shared-prefix calls: the caller vouches for the zeroed counter header of its workspace
 
 # bench.py instrumentation: when set to a list, every attention call appends a (start, end) CUDA-event pair
 # recorded on the launching stream around the C-ABI call.

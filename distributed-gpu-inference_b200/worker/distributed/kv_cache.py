@@ -158,7 +158,7 @@ class PagedKVCache:
         self._value_pool: Optional[torch.Tensor] = None
         self._block_to_slot: Dict[str, int] = {}
         self._lru_queue: "OrderedDict[str, float]" = OrderedDict()
-        self._pinned: Set[str] = set()
+        self._pinned: Dict[str, int] = {}  # block id -> number of pins (live sequences that use the block)
         self._stats = {"allocations": 0, "evictions": 0, "hits": 0, "misses": 0}
         self._on_free = None  # optional callback(block_id), used by the tier manager to drop index entries
 
@@ -245,7 +245,7 @@ class PagedKVCache:
         del self._blocks[block_id]
         self._block_to_slot.pop(block_id, None)
         self._lru_queue.pop(block_id, None)
-        self._pinned.discard(block_id)
+        self._pinned.pop(block_id, None)
         self._free_blocks.append(block_id)
         if self._on_free is not None:
             self._on_free(block_id)
@@ -269,7 +269,7 @@ class PagedKVCache:
                 dead.append(slot)
             del blocks[block_id]
             lru.pop(block_id, None)
-            pinned.discard(block_id)
+            pinned.pop(block_id, None)
             free.append(block_id)
             if on_free is not None:
                 on_free(block_id)
@@ -302,11 +302,22 @@ class PagedKVCache:
         return self._block_to_slot[block_id]
 
     def pin(self, block_ids: Iterable[str]) -> None:
-        """Protect blocks of a live sequence from LRU eviction (SURVEY.md §9 #8)."""
-        self._pinned.update(b for b in block_ids if b in self._blocks)
+        """Protect blocks of a live sequence from LRU eviction.  Pins are counted: a block shared
+        by several live sequences is pinned once per sequence and stays protected until each has called ``unpin``.
+        Freeing a sequence lifts no pin of a block that survives the free — whoever pinned must unpin."""
+        pinned = self._pinned
+        for b in block_ids:
+            if b in self._blocks:
+                pinned[b] = pinned.get(b, 0) + 1
 
     def unpin(self, block_ids: Iterable[str]) -> None:
-        self._pinned.difference_update(block_ids)
+        pinned = self._pinned
+        for b in block_ids:
+            n = pinned.get(b, 0)
+            if n > 1:
+                pinned[b] = n - 1
+            elif n == 1:
+                del pinned[b]
 
     def get_stats(self) -> Dict[str, Any]:
         return {
@@ -395,9 +406,8 @@ class KVCachePool:
                         self._layer_caches[li].unpin(ids)
                     self._free_sequence_blocks(out + [mine])
                     raise RuntimeError(f"Failed to allocate KV-Cache for layer {layer_idx}")
-                if blk.block_id not in cache._pinned:
-                    cache._pinned.add(blk.block_id)  # not evictable by the rest of this call
-                    held[layer_idx].append(blk.block_id)
+                cache.pin((blk.block_id,))  # not evictable by the rest of this call
+                held[layer_idx].append(blk.block_id)
                 mine.append(blk)
             out.append(mine)
         for layer_idx, ids in enumerate(held):
@@ -407,9 +417,8 @@ class KVCachePool:
     def _free_sequence_blocks(self, blocks: List[List[CacheBlock]]) -> None:
         for layer_idx, layer_blocks in enumerate(blocks):
             cache = self._layer_caches[layer_idx]
-            # a block another sequence still references keeps its owner's pin: only blocks this free releases for
-            # good (last reference) stop being protected
-            cache.unpin(b.block_id for b in layer_blocks if b.ref_count <= 1)
+            # pins belong to whoever set them (a block that another holder still references keeps them); a block
+            # this call releases for good loses its pin entry together with everything else (free_blocks)
             cache.free_blocks([blk.block_id for blk in layer_blocks])
 
     def free_sequence(self, blocks: List[List[CacheBlock]]) -> None:

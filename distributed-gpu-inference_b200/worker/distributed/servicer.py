@@ -59,6 +59,7 @@ class _SessionKV:
         self.batch = batch
         self.max_length = max_length
         self.blocks = []
+        self.pinned = False
         try:
             for _ in range(batch):
                 self.blocks.append(pool.allocate_sequence(max_length))
@@ -68,6 +69,7 @@ class _SessionKV:
         for per_layer in self.blocks:
             for li, layer_blocks in enumerate(per_layer):
                 pool.layer(li).pin(b.block_id for b in layer_blocks)
+        self.pinned = True
         rows = []
         for per_layer in self.blocks:
             row = KVCachePool.block_table(per_layer[0])
@@ -79,8 +81,12 @@ class _SessionKV:
 
     def free(self) -> None:
         for per_layer in self.blocks:
+            if self.pinned:
+                for li, layer_blocks in enumerate(per_layer):
+                    self.pool.layer(li).unpin(b.block_id for b in layer_blocks)
             self.pool.free_sequence(per_layer)
         self.blocks = []
+        self.pinned = False
 
 
 class InferenceServicer:

@@ -71,7 +71,9 @@ def attn_case(name, B, Hq, Hkv, D, ctx_lens, layers, splits, flags=0, share_pref
         ps = int(os.environ.get("KBENCH_PSPLITS", ps))
         ss = int(os.environ.get("KBENCH_SSPLITS", ss))
         splits = f"{ps}+{ss}"
-        ws = torch.empty(max(16, ops.attn_workspace_bytes(B, Hq, D, ps + ss)), dtype=torch.uint8, device=DEV)
+        ws = torch.zeros(max(16, ops.attn_workspace_bytes(B, Hq, D, ps + ss)), dtype=torch.uint8, device=DEV)
+        if not os.environ.get("KBENCH_NO_WSFLAG"):
+            flags |= ops.ATTN_WS_COUNTERS_ZERO  # zero-filled workspace of our own: no per-call clearing of the counters
 
     if fused:  # the launch the decode step actually uses: RoPE(q, k_new) + append + attention
         kv_new = torch.randn((B, (Hq + 2 * Hkv) * D), device=DEV, dtype=dtype)
@@ -193,6 +195,12 @@ if __name__ == "__main__":
             attn_case("cfg5 8B B8 ctx32k ragged, shared 24576 prefix, CASCADE kernel", 8, 32, 8, 128, lens, a.layers,
                       a.splits, fl, share_prefix=24576 // 16, iters=a.iters, cascade=True)
             attn_case("cfg5 8B B8 ctx32k ragged, unshared", 8, 32, 8, 128, lens, min(a.layers, 4), a.splits, fl, iters=a.iters)
+        elif c == "cfg5_prefix_only":   # diagnostic: the prefix role alone (every context ends with the shared blocks)
+            attn_case("cfg5 cascade, prefix role only", 8, 32, 8, 128, [24576] * 8, a.layers, a.splits, fl,
+                      share_prefix=24576 // 16, iters=a.iters, cascade=True)
+        elif c == "cfg5_tails_plain":   # diagnostic: the tails as an unshared batch through the plain kernel
+            attn_case("cfg5 tails only, plain kernel", 8, 32, 8, 128, [8192 - 512 * i for i in range(8)], a.layers,
+                      a.splits, fl, iters=a.iters)
         elif c == "cfg5c":
             lens = [24576 + 8192 - 512 * i for i in range(8)]
             attn_case("cfg5 cascade", 8, 32, 8, 128, lens, a.layers, a.splits, fl, share_prefix=24576 // 16, iters=a.iters,
