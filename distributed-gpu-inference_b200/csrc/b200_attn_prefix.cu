@@ -175,12 +175,16 @@ __device__ __forceinline__ void cascade_role(const CUtensorMap& k_map, const CUt
   }
 
   // suffix role: the warp that owns the sequence's last KV tile appends the new token into it
-  bool append_here = false;
+  bool append_here = false, owns_last = false;
   AppendRows ap{};
   FusedAppend<T> fa{};
+  if constexpr (SUFFIX) {
+    const int last_blk = (ctx + kTok - 1) / kTok - 1;
+    owns_last = ctx > 0 && last_blk >= blk_begin && last_blk < blk_end && ((last_blk - blk_begin) % kWarps) == warp;
+  }
   if constexpr (FUSED && SUFFIX) {
     const int last_blk = (ctx + kTok - 1) / kTok - 1;
-    append_here = ctx > 0 && last_blk >= blk_begin && last_blk < blk_end && ((last_blk - blk_begin) % kWarps) == warp;
+    append_here = owns_last;
     fa.k_new = static_cast<const T*>(p.k_new);
     fa.k_stride = p.k_new_stride;
     fa.v_new = static_cast<const T*>(p.v_new);
@@ -211,8 +215,11 @@ __device__ __forceinline__ void cascade_role(const CUtensorMap& k_map, const CUt
     const uint32_t k_tile = ring + st * S::kStageBytes;
     const uint32_t v_tile = k_tile + S::kTileBytes;
     mbar_wait(bars + st * 8, (i / STAGES) & 1);
-    if constexpr (FUSED && SUFFIX) {
-      if (append_here && i == n_mine - 1) append_patch<T, D>(ap, fa, Hkv, kvh, (ctx - 1) & (kTok - 1), lane, k_tile, v_tile);
+    if constexpr (SUFFIX) {
+      if (owns_last && i == n_mine - 1) {  // the sequence's last, partly filled tile
+        if constexpr (FUSED) append_patch<T, D>(ap, fa, Hkv, kvh, (ctx - 1) & (kTok - 1), lane, k_tile, v_tile);
+        zero_v_tail<D>(v_tile, ((ctx - 1) & (kTok - 1)) + 1, lane);  // rows past the context: 0 x NaN must stay 0
+      }
     }
 
     // S^T = K Q^T.  Two accumulators per column group (even / odd k-steps) halve the dependent-MMA chain.
@@ -430,7 +437,7 @@ __device__ __forceinline__ void cascade_role(const CUtensorMap& k_map, const CUt
 }
 
 template <typename T, int D, int STAGES, int NT, bool FUSED, bool ROUND>
-__global__ void __launch_bounds__(kWarps * 32, (NT <= 2 ? 2 : 1))
+__global__ void __launch_bounds__(kWarps * 32, (STAGES <= 2 ? 3 : 2))
 paged_attn_cascade_kernel(const __grid_constant__ CUtensorMap k_map, const __grid_constant__ CUtensorMap v_map,
                           const __grid_constant__ CascadeParams p) {
   const int id = blockIdx.x;
@@ -449,7 +456,7 @@ paged_attn_cascade_kernel(const __grid_constant__ CUtensorMap k_map, const __gri
 inline int ceil_div(int a, int b) { return (a + b - 1) / b; }
 
 constexpr int kPrefixNT = 2;       // 16 query rows ((sequence, head) pairs) per prefix CTA
-constexpr int kPrefixStages = 3;   // ring depth at 2 CTAs per SM
+constexpr int kPrefixStages = 3;   // ring depth at 2 CTAs per SM (2 stages x 3 CTAs measured the same: 63.2 vs 63.5 us on config 5)
 
 int separate_combine() {  // -1: library's choice, 0 / 1: forced by B200_PREFIX_SEPARATE_COMBINE
   static const int v = [] {

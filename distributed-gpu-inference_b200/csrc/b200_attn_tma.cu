@@ -201,8 +201,8 @@ paged_attn_tma_kernel(const __grid_constant__ CUtensorMap k_map, const __grid_co
   }
   // the warp that owns the sequence's last KV tile (the one the new token lands in) does the append
   const int last_blk = n_blocks - 1;
-  const bool append_here = FUSED && ctx > 0 && last_blk >= blk_begin && last_blk < blk_end &&
-                           ((last_blk - blk_begin) % kWarps) == warp;
+  const bool owns_last = ctx > 0 && last_blk >= blk_begin && last_blk < blk_end && ((last_blk - blk_begin) % kWarps) == warp;
+  const bool append_here = FUSED && owns_last;
   // The new token's k / v / cos / sin rows and its pool slot are fetched NOW, while the first KV tiles are in
   // flight, so that the patch of the last tile (end of this warp's loop) does not wait on global memory.
   AppendRows ap{};
@@ -226,16 +226,19 @@ paged_attn_tma_kernel(const __grid_constant__ CUtensorMap k_map, const __grid_co
   const int v_row = (lm_mat >> 1) * 8 + lm_row;  // V: matrices 0/1 -> tok 0-7, 2/3 -> tok 8-15
   const int v_chunk = lm_mat & 1;                //    matrices 0/2 -> chunk 2mt, 1/3 -> chunk 2mt+1
 
-  // One KV tile of this warp.  `patch` (compile-time) = this is the sequence's last tile and this warp appends the
-  // new token into it; kept out of the steady-state loop so that loop is the same code as the attention-only kernel.
+  // One KV tile of this warp.  `patch` (compile-time) = this is the sequence's last, partly filled tile: the fused
+  // variant appends the new token into it, and its V rows past the context are cleared; kept out of the steady-state
+  // loop.
   auto tile = [&](const int i, auto patch) {
     const int st = i % STAGES;
     const uint32_t k_tile = ring + st * S::kStageBytes;
     const uint32_t v_tile = k_tile + S::kTileBytes;
     mbar_wait(bars + st * 8, (i / STAGES) & 1);
 
-    if constexpr (FUSED && decltype(patch)::value)
-      append_patch<T, D>(ap, fa, Hkv, kvh, (ctx - 1) & (kTok - 1), lane, k_tile, v_tile);
+    if constexpr (decltype(patch)::value) {
+      if constexpr (FUSED) append_patch<T, D>(ap, fa, Hkv, kvh, (ctx - 1) & (kTok - 1), lane, k_tile, v_tile);
+      zero_v_tail<D>(v_tile, ((ctx - 1) & (kTok - 1)) + 1, lane);
+    }
 
     // S^T = K Q^T
     float s[4] = {0.f, 0.f, 0.f, 0.f};
@@ -301,11 +304,10 @@ paged_attn_tma_kernel(const __grid_constant__ CUtensorMap k_map, const __grid_co
     __syncwarp();  // every lane's reads of this stage are done before lane 0 hands it back to TMA
     if (i + STAGES < n_mine) issue(i + STAGES);
   };
-  const int n_plain = append_here ? n_mine - 1 : n_mine;
+  const bool tail_tile = owns_last && (FUSED || (ctx & (kTok - 1)) != 0);
+  const int n_plain = tail_tile ? n_mine - 1 : n_mine;
   for (int i = 0; i < n_plain; ++i) tile(i, std::false_type{});
-  if constexpr (FUSED) {
-    if (append_here) tile(n_mine - 1, std::true_type{});
-  }
+  if (tail_tile) tile(n_mine - 1, std::true_type{});
 
   // ---- merge the 4 warps (buffers alias the ring; all TMA traffic of this CTA has landed and been consumed) ----
 #pragma unroll

@@ -226,6 +226,19 @@ static __device__ __forceinline__ void append_patch(const AppendRows& pre, const
 }
 
 
+// Rows `first_row`..15 of a staged V tile <- 0.  The last tile of a sequence is staged whole, but its rows past the
+// context length belong to nobody: their probabilities are exactly 0, and 0 x (whatever the pool holds there, possibly
+// NaN / Inf in a pool that was never zero-filled) must stay 0 in the P V product.  Ends with __syncwarp().
+template <int D>
+static __device__ __forceinline__ void zero_v_tail(uint32_t v_tile, int first_row, int lane) {
+  constexpr int CH = D / 8;  // 16-byte chunks per row
+  for (int idx = first_row * CH + lane; idx < kTok * CH; idx += 32) {
+    const int row = idx / CH, c = idx - row * CH;
+    asm volatile("st.shared.v4.b32 [%0], {%1,%1,%1,%1};" ::"r"(v_tile + tile_off(row, c)), "r"(0) : "memory");
+  }
+  __syncwarp();
+}
+
 // 2D tensor map over a pool viewed as [max_blocks * Hkv * 16 rows, D] with a 64 x 16 box and 128-byte swizzle;
 // cached per (pointer, rows, D, dtype).  Defined in b200_attn_tma.cu.
 int get_tensor_map(const void* pool, uint64_t rows, int D, int dtype, CUtensorMap* out);

@@ -694,3 +694,42 @@ def test_argmax_keys_over_column_slices_equal_torch_argmax(dtype, rows, cols, pa
         k = ops.argmax_rows_keys(x[:, lo:hi], lo)
         keys = k if keys is None else torch.maximum(keys, k)
     assert torch.equal(ops.argmax_keys_decode(keys), torch.argmax(x, dim=-1))
+
+
+@pytest.mark.parametrize("dtype", [torch.bfloat16, torch.float16])
+def test_rows_past_the_context_may_hold_nan(dtype):
+    """A pool that was never zero-filled (cudaMalloc / torch.empty from a C-ABI caller) can hold NaN or Inf in the rows
+    of a sequence's last block that lie past its context.  Those tokens have probability 0; every attention entry
+    point must give the same answer as with clean rows (0 x NaN must not reach the output)."""
+    B, Hq, Hkv, D, bs = 4, 32, 8, 128, 16
+    ctx = [100, 33, 257, 16 * 9 + 1]
+    q, k_pool, v_pool, tables, lens = _attn_case(B, Hq, Hkv, D, bs, ctx, dtype, seed=41, share_prefix_blocks=2)
+    want = R.paged_attention_ref(q, k_pool, v_pool, tables, lens, mode="fp32")
+    kp, vp = k_pool.clone(), v_pool.clone()
+    for b, c in enumerate(ctx):
+        blk = int(tables[b, (c - 1) // bs])
+        kp[blk, :, c % bs:, :] = float("nan")
+        vp[blk, :, c % bs:, :] = float("nan")
+        vp[blk, 0, bs - 1, 0] = float("inf")
+    outs = {
+        "tma": ops.paged_decode_attention(q, kp, vp, tables, lens, max(ctx), num_splits=1),
+        "tma split": ops.paged_decode_attention(q, kp, vp, tables, lens, max(ctx), num_splits=3),
+        "generic": ops.paged_decode_attention(q, kp, vp, tables, lens, max(ctx), flags=ops.ATTN_FORCE_GENERIC),
+        "cascade": ops.paged_decode_attention_prefix(q, kp, vp, tables, lens, max(ctx), 2),
+    }
+    for name, out in outs.items():
+        assert torch.isfinite(out.float()).all(), name
+        assert _rel_err(out, want) <= 1e-2, name
+    # the fused step: the new token lands in row (ctx - 1) % 16 of the poisoned block, rows after it stay poisoned
+    g = torch.Generator(device=DEV).manual_seed(3)
+    k_new = torch.randn((B, Hkv, D), generator=g, device=DEV).to(dtype)
+    v_new = torch.randn((B, Hkv, D), generator=g, device=DEV).to(dtype)
+    cos = torch.ones((B, D), device=DEV, dtype=dtype)
+    sin = torch.zeros((B, D), device=DEV, dtype=dtype)
+    for fused in (ops.rope_append_decode_attention,
+                  lambda *a, **k: ops.rope_append_decode_attention_prefix(*a, 2, **k)):
+        kc, vc, kn, vn = k_pool.clone(), v_pool.clone(), kp.clone(), vp.clone()
+        clean = fused(q, k_new, v_new, cos, sin, kc, vc, tables, lens, max(ctx))
+        dirty = fused(q, k_new, v_new, cos, sin, kn, vn, tables, lens, max(ctx))
+        assert torch.isfinite(dirty.float()).all()
+        assert torch.equal(_bits(clean), _bits(dirty))
