@@ -28,6 +28,7 @@ def main():
     ap.add_argument("--prompt", type=int, default=4096)
     ap.add_argument("--layers", type=int, default=32)
     ap.add_argument("--skip-push", action="store_true")
+    ap.add_argument("--quick", action="store_true", help="NCCL path with one layer group only")
     a = ap.parse_args()
     rank, world = int(os.environ["RANK"]), int(os.environ["WORLD_SIZE"])
     local = int(os.environ.get("LOCAL_RANK", rank))
@@ -72,7 +73,24 @@ def main():
         pool.backing.normal_()
     gen = torch.Generator().manual_seed(rank)
     tables = [torch.randperm(max_blocks, generator=gen)[:n_blocks].to(torch.int32).to(dev) for _ in range(a.seqs)]
-    for chunks in (1, 2, 4, 8):
+    # bare wire rate: the same bytes as ready-made contiguous buffers, no pack / unpack — what NCCL's send/recv itself
+    # sustains between the two GPUs (the ceiling of the packed path)
+    ep = KVTransferEndpoint(pool, chunks=1)
+    flat = [ep.staging(n_blocks)[0] for _ in range(2)]
+
+    def bare():
+        works = []
+        for i in range(a.seqs):
+            if sender:
+                works.append(dist.isend(flat[i % 2], dst=peer, group=pair_group))
+            else:
+                works.append(dist.irecv(flat[i % 2], src=peer, group=pair_group))
+        for w in works:
+            w.wait()
+
+    run("bare nccl send/recv of the packed bytes (no pack / unpack)", bare, ep.payload_bytes(n_blocks) * a.seqs)
+    del flat
+    for chunks in ((1,) if a.quick else (1, 2, 4, 8)):
         ep = KVTransferEndpoint(pool, chunks=chunks)
         bufs = [ep.staging(n_blocks) for _ in range(2)]
         payload = ep.payload_bytes(n_blocks) * a.seqs
@@ -113,7 +131,10 @@ def main():
 
         run("peer push (b200_kv_move_blocks_layers into symmetric-memory pools)", push_path, payload)
     if rank == 0:
+        env = {k: v for k, v in os.environ.items() if k.startswith("NCCL_") and k != "NCCL_DEBUG"}
         for r in results:
+            if env:
+                r["nccl_env"] = env
             print(json.dumps(r), flush=True)
     dist.destroy_process_group()
 
