@@ -156,6 +156,32 @@ def copy_cases():
         print(json.dumps({"kernel": "kv_append", "n_tok": n_tok, "ms": round(ms, 5), "GBps": round(byt / ms / 1e6, 1)}), flush=True)
 
 
+def append_cases(iters):
+    """k1 alone: the paged KV append of a 16k-token prompt chunk (8B shape), and the prompt-pass launch that does RoPE
+    on q and k plus that append (b200_rope_kv_append_prompt)."""
+    Hq, Hkv, D, bs, max_blocks, n_tok, L_ = 32, 8, 128, 16, 4096, 16384, 4
+    pools = [(torch.zeros((max_blocks, Hkv, bs, D), device=DEV, dtype=torch.bfloat16),
+              torch.zeros((max_blocks, Hkv, bs, D), device=DEV, dtype=torch.bfloat16)) for _ in range(L_)]
+    qkv = torch.randn((n_tok, (Hq + 2 * Hkv) * D), device=DEV, dtype=torch.bfloat16)  # strided rows, as in the layer
+    q = qkv[:, :Hq * D].view(n_tok, Hq, D)
+    k_new = qkv[:, Hq * D:(Hq + Hkv) * D].view(n_tok, Hkv, D)
+    v_new = qkv[:, (Hq + Hkv) * D:].view(n_tok, Hkv, D)
+    slots = torch.randperm(max_blocks * bs, device=DEV)[:n_tok].to(torch.int64)
+    cos = torch.randn((n_tok, D), device=DEV, dtype=torch.bfloat16)
+    sin = torch.randn((n_tok, D), device=DEV, dtype=torch.bfloat16)
+    es = 2
+    ms = timed(lambda i: ops.kv_append(k_new, v_new, pools[i % L_][0], pools[i % L_][1], slots), iters)
+    byt = 2 * (2 * n_tok * Hkv * D * es) + 8 * n_tok  # K and V rows read + written, + the slot mapping
+    print(json.dumps({"kernel": "kv_append", "n_tok": n_tok, "ms": round(ms, 5), "algorithmic_bytes": byt,
+                      "GBps": round(byt / ms / 1e6, 1), "frac_of_measured_peak": round(byt / ms / 1e6 / PEAK, 4)}), flush=True)
+    ms = timed(lambda i: ops.rope_kv_append(q, k_new, v_new, cos, sin, pools[i % L_][0], pools[i % L_][1], slots,
+                                            rotate_k_in_place=True), iters)
+    # q read + written, k read + written in place + written to the pool, v read + written to the pool, cos / sin, slots
+    byt = (2 * n_tok * Hq * D + 3 * n_tok * Hkv * D + 2 * n_tok * Hkv * D + 2 * n_tok * D) * es + 8 * n_tok
+    print(json.dumps({"kernel": "rope_kv_append_prompt", "n_tok": n_tok, "ms": round(ms, 5), "algorithmic_bytes": byt,
+                      "GBps": round(byt / ms / 1e6, 1), "frac_of_measured_peak": round(byt / ms / 1e6 / PEAK, 4)}), flush=True)
+
+
 if __name__ == "__main__":
     ap = argparse.ArgumentParser()
     ap.add_argument("--cases", default="cfg2,cfg4,cfg5,copy")
@@ -217,3 +243,5 @@ if __name__ == "__main__":
                       a.splits, fl, share_prefix=128, iters=a.iters, cascade=True)
         elif c == "copy":
             copy_cases()
+        elif c == "append":
+            append_cases(a.iters)
