@@ -13,8 +13,12 @@ namespace b200 {
 // ---------------------------------------------------------------------------------------------------------
 // append
 // ---------------------------------------------------------------------------------------------------------
-// One thread per 16-byte vector of the new K and V rows.  vec index -> (which, token, head, v).
-template <int UNROLL>
+// A CTA takes TOKS consecutive tokens.  The first TOKS threads turn the tokens' slots into pool row offsets once (the
+// only divisions of the kernel; the flat-index version of round 1 spent two 64-bit divisions per 16-byte vector and
+// was issue-bound at 62 % of the copy peak, profiles/r02_ncu_append.md); after that thread x owns 16-byte vector x of
+// the K|V row pair of every token of the CTA — TOKS independent loads in flight before the first store, consecutive
+// threads on consecutive vectors of one contiguous head row.
+template <int TOKS>
 __global__ void __launch_bounds__(256)
 kv_append_vec16_kernel(const char* __restrict__ k_new, const char* __restrict__ v_new,
                        int64_t k_row_bytes, int64_t v_row_bytes,
@@ -22,40 +26,40 @@ kv_append_vec16_kernel(const char* __restrict__ k_new, const char* __restrict__ 
                        const int64_t* __restrict__ slot_mapping,
                        int n_tok, int Hkv, int block_size, int64_t max_blocks,
                        int vec_per_head /* D * elem_size / 16 */) {
-  const int64_t vec_per_tok = static_cast<int64_t>(Hkv) * vec_per_head;
-  const int64_t per_tensor = static_cast<int64_t>(n_tok) * vec_per_tok;
-  const int64_t total = 2 * per_tensor;
-  const int64_t head_bytes = static_cast<int64_t>(vec_per_head) * 16;
-  const int64_t base = (static_cast<int64_t>(blockIdx.x) * UNROLL) * blockDim.x + threadIdx.x;
-
-  int4 val[UNROLL];
-  char* dst[UNROLL];
-#pragma unroll
-  for (int u = 0; u < UNROLL; ++u) {
-    const int64_t i = base + static_cast<int64_t>(u) * blockDim.x;
-    dst[u] = nullptr;
-    if (i < total) {
-      const bool is_v = i >= per_tensor;
-      const int64_t j = is_v ? i - per_tensor : i;
-      const int tok = static_cast<int>(j / vec_per_tok);
-      const int rem = static_cast<int>(j - static_cast<int64_t>(tok) * vec_per_tok);
-      const int h = rem / vec_per_head;
-      const int v = rem - h * vec_per_head;
+  __shared__ int64_t row0_s[TOKS];  // (block * Hkv * block_size + offset in block) of the token, -1 = skip
+  const int tok0 = blockIdx.x * TOKS;
+  if (threadIdx.x < TOKS) {
+    const int tok = tok0 + threadIdx.x;
+    int64_t row0 = -1;
+    if (tok < n_tok) {
       const int64_t slot = slot_mapping[tok];
       if (slot >= 0) {
         const int64_t blk = slot / block_size;
-        const int64_t off = slot - blk * block_size;
-        if (blk < max_blocks) {
-          const char* src = (is_v ? v_new + tok * v_row_bytes : k_new + tok * k_row_bytes) + h * head_bytes + v * 16;
-          val[u] = ld_stream16(src);
-          dst[u] = (is_v ? v_pool : k_pool) + ((blk * Hkv + h) * block_size + off) * head_bytes + v * 16;
-        }
+        if (blk < max_blocks) row0 = blk * Hkv * block_size + (slot - blk * block_size);
       }
     }
+    row0_s[threadIdx.x] = row0;
   }
+  __syncthreads();
+  const int vec_per_tok = Hkv * vec_per_head;  // vectors of one K (or V) row
+  const int head_bytes = vec_per_head * 16;
+  for (int x = threadIdx.x; x < 2 * vec_per_tok; x += blockDim.x) {
+    const bool is_v = x >= vec_per_tok;
+    const int r = is_v ? x - vec_per_tok : x;
+    const int h = r / vec_per_head;
+    const int col = (r - h * vec_per_head) * 16;  // byte offset inside the head row
+    const char* src = (is_v ? v_new : k_new) + h * head_bytes + col;
+    const int64_t src_row = is_v ? v_row_bytes : k_row_bytes;
+    char* pool = (is_v ? v_pool : k_pool) + col;
+    int4 val[TOKS];
 #pragma unroll
-  for (int u = 0; u < UNROLL; ++u)
-    if (dst[u] != nullptr) *reinterpret_cast<int4*>(dst[u]) = val[u];
+    for (int u = 0; u < TOKS; ++u)
+      if (row0_s[u] >= 0) val[u] = ld_stream16(src + (tok0 + u) * src_row);
+#pragma unroll
+    for (int u = 0; u < TOKS; ++u)
+      if (row0_s[u] >= 0)
+        *reinterpret_cast<int4*>(pool + (row0_s[u] + static_cast<int64_t>(h) * block_size) * head_bytes) = val[u];
+  }
 }
 
 // Fallback for rows that are not 16-byte aligned (odd head_dim, fp32 with D % 4 != 0, unaligned views).
@@ -103,13 +107,11 @@ int kv_append(const void* k_new, const void* v_new, int64_t k_row_stride, int64_
   const bool vec_ok = (D * es) % 16 == 0 && (k_row_stride * es) % 16 == 0 && (v_row_stride * es) % 16 == 0 &&
                       aligned16(k_new) && aligned16(v_new) && aligned16(k_pool) && aligned16(v_pool);
   if (vec_ok) {
-    constexpr int UNROLL = 4;
+    constexpr int TOKS = 8;
     const int vec_per_head = D * es / 16;
-    const int64_t total = 2ll * n_tok * Hkv * vec_per_head;
-    const int threads = 256;
-    const int64_t per_cta = static_cast<int64_t>(threads) * UNROLL;
-    const int64_t grid = (total + per_cta - 1) / per_cta;
-    kv_append_vec16_kernel<UNROLL><<<static_cast<unsigned>(grid), threads, 0, stream>>>(
+    const int threads = std::min(256, std::max(32, (2 * Hkv * vec_per_head + 31) / 32 * 32));
+    const int grid = (n_tok + TOKS - 1) / TOKS;
+    kv_append_vec16_kernel<TOKS><<<static_cast<unsigned>(grid), threads, 0, stream>>>(
         static_cast<const char*>(k_new), static_cast<const char*>(v_new), k_row_stride * es, v_row_stride * es,
         static_cast<char*>(k_pool), static_cast<char*>(v_pool), slot_mapping, n_tok, Hkv, block_size, max_blocks,
         vec_per_head);
