@@ -230,7 +230,10 @@ def workload_for(args):
                        check_sequences=64,
                        name=f"configs[1] weak-scaled: Llama-3-8B-shape random-init bf16, layer ranges over {args.gpus} "
                             f"B200, block 16, batch 64 per GPU = {64 * args.gpus}, context 2k, decode"),
-        "cfg4": dict(shape="70b", batch=128, context=4096, scaling="strong", check_sequences=8,
+        # sequences of micro-batch 0 re-run on one GPU for the token check: the whole micro-batch when it fits beside the
+        # 141 GB of weights (16 sequences at N = 8: same GEMM row counts in both runs), else the first 8
+        "cfg4": dict(shape="70b", batch=128, context=4096, scaling="strong",
+                     check_sequences=16 if 128 // max(1, args.gpus) <= 16 else 8,
                      name=f"configs[3]: Llama-3-70B-shape layer-sharded over {args.gpus} B200, batch 128, context 4k, decode"),
         "cfg5": dict(shape="8b", batch=8, context=32768, scaling="weak",
                      name="configs[4]: Llama-3-8B-shape long-context decode, batch 8, context 32k"),
