@@ -35,10 +35,17 @@ class CachedSequence:
 
 
 class SequenceDirectory:
-    """kv_cache_key -> CachedSequence; the data-plane companion of the scheduler's ``_kv_cache_locations``."""
+    """kv_cache_key -> CachedSequence; the data-plane companion of the scheduler's ``_kv_cache_locations``.
 
-    def __init__(self):
+    With a ``scheduler`` (the reference's ``PrefillDecodeScheduler`` or anything with ``_kv_cache_locations``) the
+    directory feeds that index: the first worker a sequence is registered on becomes its location (what
+    ``transition_to_decode`` would record, server/app/services/pd_scheduler.py:231), and dropping the copy the index
+    points at moves the index to a remaining copy or removes the entry — so ``_assign_decode`` (:274-323) always
+    sees where the blocks really are."""
+
+    def __init__(self, scheduler=None):
         self._seqs: Dict[str, CachedSequence] = {}
+        self.scheduler = scheduler
 
     def put(self, key: str, worker: str, n_tokens: int, blocks) -> CachedSequence:
         from .worker.distributed.kv_cache import KVCachePool
@@ -47,6 +54,8 @@ class SequenceDirectory:
         seq.n_tokens = n_tokens
         seq.tables[worker] = KVCachePool.block_table(blocks[0])
         seq.blocks[worker] = blocks
+        if self.scheduler is not None:
+            self.scheduler._kv_cache_locations.setdefault(key, worker)
         return seq
 
     def get(self, key: str) -> Optional[CachedSequence]:
@@ -57,6 +66,13 @@ class SequenceDirectory:
         if seq is not None:
             seq.tables.pop(worker, None)
             seq.blocks.pop(worker, None)
+            if self.scheduler is not None and self.scheduler._kv_cache_locations.get(key) == worker:
+                if seq.tables:
+                    self.scheduler._kv_cache_locations[key] = next(iter(seq.tables))
+                else:
+                    del self.scheduler._kv_cache_locations[key]
+            if not seq.tables:
+                del self._seqs[key]
 
 
 class KVCacheMigrator:

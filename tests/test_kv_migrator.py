@@ -42,6 +42,85 @@ def test_migrate_updates_index_dedups_and_reports_failure():
     asyncio.run(run())
 
 
+def _reference_pd_scheduler():
+    """The reference's own scheduler module, loaded the way its test does (tests/test_server_pd_scheduler.py:26-32).
+    Only the build container has /root/reference; elsewhere the test is skipped."""
+    import importlib.util
+    import os
+    import sys
+
+    path = "/root/reference/server/app/services/pd_scheduler.py"
+    if not os.path.exists(path):
+        pytest.skip("the reference checkout is not mounted here")
+    spec = importlib.util.spec_from_file_location("pd_scheduler", path)
+    module = importlib.util.module_from_spec(spec)
+    sys.modules["pd_scheduler"] = module
+    spec.loader.exec_module(module)
+    return module
+
+
+def test_the_references_scheduler_drives_a_real_migration():
+    """f1 end to end with the reference's PrefillDecodeScheduler object (server/app/services/pd_scheduler.py:207-323):
+    role-aware worker choice, `_kv_cache_locations` fed by SequenceDirectory, `kv_migration_needed` honoured by this
+    package's KVCacheMigrator with a mover that really copies the blocks, and the next decode assignment finding the
+    sequence where it now is."""
+    from dgi_b200.worker.distributed.kv_cache import KVCachePool
+
+    ref = _reference_pd_scheduler()
+    sch = ref.PrefillDecodeScheduler(enable_migration=True)
+    sch.register_worker("prefill0", ref.WorkerCapability("prefill0", role=ref.WorkerRole.PREFILL, compute_flops=2000.0,
+                                                         memory_bandwidth_gbps=6500.0, gpu_memory_gb=180.0,
+                                                         kv_cache_tokens_total=1 << 20))
+    sch.register_worker("decode0", ref.WorkerCapability("decode0", role=ref.WorkerRole.DECODE, compute_flops=2000.0,
+                                                        memory_bandwidth_gbps=6500.0, gpu_memory_gb=180.0,
+                                                        kv_cache_tokens_total=1 << 20))
+    pools = {w: KVCachePool(2, 2, 8, 4, 16, device="cpu", dtype=torch.float32) for w in ("prefill0", "decode0")}
+    pools["decode0"].allocate_sequence(9)  # so the two workers hand out different slots
+    directory = SequenceDirectory(scheduler=sch)
+
+    def mover(key, src, dst):  # host stand-in for the CUDA movers: same contract, torch indexing on CPU pools
+        seq = directory.get(key)
+        dst_blocks = pools[dst].allocate_sequence(seq.n_tokens)
+        directory.put(key, dst, seq.n_tokens, dst_blocks)
+        s, d = torch.tensor(seq.tables[src]), torch.tensor(seq.tables[dst])
+        pools[dst].backing[:, :, d] = pools[src].backing[:, :, s]
+        return pools[src].backing[:, :, s].numel() * 4
+
+    async def run():
+        job = ref.PendingJob(priority=-1.0, created_at=0.0, job_id="j1", phase=ref.JobPhase.PREFILL, prompt_tokens=14)
+        a = await sch.assign_job(job)
+        assert a.worker_id == "prefill0" and a.phase == ref.JobPhase.PREFILL
+        blocks = pools[a.worker_id].allocate_sequence(14)       # the prompt pass fills these
+        for layer in blocks:
+            for blk in layer:
+                blk.keys.normal_()
+                blk.values.normal_()
+        directory.put("kv-j1", a.worker_id, 14, blocks)
+        assert sch._kv_cache_locations["kv-j1"] == "prefill0"   # fed by the directory
+        await sch.transition_to_decode("j1", "kv-j1", a.worker_id)
+        d = await sch.assign_job(sch._decode_queue[0])
+        assert d.worker_id == "decode0" and d.kv_migration_needed and d.migration_source == "prefill0"
+        mig = KVCacheMigrator(sch, mover)
+        assert await mig.migrate("kv-j1", d.migration_source, d.worker_id) is True
+        assert sch._kv_cache_locations["kv-j1"] == "decode0" and sch.get_stats()["migrations"] == 1
+        seq = directory.get("kv-j1")
+        s, t = torch.tensor(seq.tables["prefill0"]), torch.tensor(seq.tables["decode0"])
+        assert seq.tables["prefill0"] != seq.tables["decode0"]
+        assert torch.equal(pools["decode0"].backing[:, :, t], pools["prefill0"].backing[:, :, s])
+        # a later decode job for the same cache entry (the queued one carries its stale holder by value, reference
+        # :277) is resolved through the index: the holder is now a decode worker, so nothing has to move
+        later = ref.PendingJob(priority=0, created_at=0.0, job_id="j1-next", phase=ref.JobPhase.DECODE, kv_cache_key="kv-j1")
+        again = await sch.assign_job(later)
+        assert again.worker_id == "decode0" and not again.kv_migration_needed
+        pools["prefill0"].free_sequence(seq.blocks["prefill0"])
+        directory.drop("kv-j1", "prefill0")
+        assert sch._kv_cache_locations["kv-j1"] == "decode0"
+        directory.drop("kv-j1", "decode0")
+        assert "kv-j1" not in sch._kv_cache_locations and directory.get("kv-j1") is None
+
+    asyncio.run(run())
+
+
 @pytest.mark.gpu
 def test_migration_moves_the_blocks_bit_exactly_on_one_gpu():
     from dgi_b200.worker.distributed.kv_cache import KVCachePool
