@@ -440,6 +440,9 @@ template <typename T, int D, int STAGES, int NT, bool FUSED, bool ROUND>
 __global__ void __launch_bounds__(kWarps * 32, (STAGES <= 2 ? 3 : 2))
 paged_attn_cascade_kernel(const __grid_constant__ CUtensorMap k_map, const __grid_constant__ CUtensorMap v_map,
                           const __grid_constant__ CascadeParams p) {
+  // lets the combine grid (a programmatic dependent, see attn_combine) be scheduled once every CTA of this grid has
+  // started; it still waits for this grid to complete before it reads a partial
+  asm volatile("griddepcontrol.launch_dependents;");
   const int id = blockIdx.x;
   if (id < p.n_prefix_ctas) {  // heavier CTAs first
     const int split = id % p.prefix_splits;

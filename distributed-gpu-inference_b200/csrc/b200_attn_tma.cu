@@ -127,6 +127,9 @@ paged_attn_tma_kernel(const __grid_constant__ CUtensorMap k_map, const __grid_co
   const int split = blockIdx.x, kvh = blockIdx.y, b = blockIdx.z;
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int quad = lane >> 2, tq = lane & 3;
+  // split-K: the combine grid is a programmatic dependent of this one (attn_combine) and may be scheduled as soon as
+  // every CTA here has started; a no-op when nothing depends on this launch
+  asm volatile("griddepcontrol.launch_dependents;");
 
   extern __shared__ unsigned char smem_raw[];
   unsigned char* smem = reinterpret_cast<unsigned char*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
