@@ -423,7 +423,8 @@ def _single_leg(args, workload):
         try:
             tj = json.load(open(tpath))
             traffic = tj.get(workload["key"])
-            traffic_source = tj.get("source") if traffic is not None else None
+            src = tj.get("source")
+            traffic_source = (src.get(workload["key"]) if isinstance(src, dict) else src) if traffic is not None else None
         except Exception:  # noqa: BLE001
             traffic = None
     # this repo's kernels per step: per layer add_rmsnorm x2, the one-launch RoPE + append + attention (+ combine when
