@@ -87,6 +87,10 @@ int b200_paged_decode_attn(void* out, const void* q, int64_t q_row_stride,
                            float scale, int max_context_len, int num_splits,
                            void* workspace, size_t workspace_bytes,
                            int dtype, unsigned flags, void* stream);
+/* Bytes of scratch for `num_splits` partitions (0 for num_splits <= 1): B * Hq * num_splits * (D + 2) floats of
+ * partials (un-normalised outputs, running max and sum) behind a header of 4 * B * Hq bytes rounded up to 256 — the
+ * arrival counters of the shared-prefix entry points (B200_ATTN_WS_COUNTERS_ZERO above); the plain entry point
+ * ignores the header. */
 size_t b200_paged_decode_attn_workspace(int B, int Hq, int D, int num_splits);
 int b200_paged_decode_attn_plan(int B, int Hq, int Hkv, int D, int block_size, int max_context_len, int dtype);
 

@@ -40,7 +40,9 @@ def test_loader_signatures_cover_the_header():
     lib = _lib.load()
     assert lib.b200_abi_version() == 1
     # pure host-side helpers are safe without a GPU
-    assert lib.b200_paged_decode_attn_workspace(64, 32, 128, 4) == 64 * 32 * 4 * 130 * 4
+    # partials + the 256-byte-rounded counter header of the shared-prefix entry points (include/b200_kv.h)
+    assert lib.b200_paged_decode_attn_workspace(64, 32, 128, 4) == 64 * 32 * 4 * 130 * 4 + 64 * 32 * 4
+    assert lib.b200_paged_decode_attn_workspace(3, 8, 64, 2) == 3 * 8 * 2 * 66 * 4 + 256
     assert lib.b200_paged_decode_attn_workspace(64, 32, 128, 1) == 0
     assert lib.b200_paged_decode_attn_plan(64, 32, 8, 128, 16, 2048, 2) >= 1
 
@@ -96,7 +98,7 @@ def test_header_is_plain_c_and_the_library_links_from_c(tmp_path):
 int main(void) {
   if (b200_abi_version() != B200_ABI_VERSION) return 1;
   if (b200_paged_decode_attn_workspace(64, 32, 128, 1) != 0) return 2;
-  if (b200_paged_decode_attn_workspace(2, 4, 64, 3) != (size_t)2 * 4 * 3 * (64 + 2) * sizeof(float)) return 3;
+  if (b200_paged_decode_attn_workspace(2, 4, 64, 3) != 256 + (size_t)2 * 4 * 3 * (64 + 2) * sizeof(float)) return 3;
   if (b200_paged_decode_attn_plan(64, 32, 8, 128, 16, 2048, B200_DTYPE_BF16) != 1) return 4;
   int rc = b200_kv_append(NULL, NULL, 0, 0, NULL, NULL, NULL, 4, 8, 128, 16, 32, B200_DTYPE_BF16, NULL);
   if (rc != B200_EINVAL || strlen(b200_last_error()) == 0) return 5;
