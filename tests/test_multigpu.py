@@ -56,6 +56,84 @@ def _pipeline_worker_vp(rank, world, port, q):
     _pipeline_worker(rank, world, port, q, vp=True)
 
 
+class _Staged:
+    """Work handle of a host-staged transfer: wait() finishes the gloo operation, then lands the bytes on the GPU."""
+
+    def __init__(self, work, host, after=None):
+        self.work, self.host, self.after = work, host, after
+
+    def wait(self):
+        if self.work is not None:
+            self.work.wait()
+        if self.after is not None:
+            self.after()
+            self.after = None
+
+
+def _stage_collectives_through_the_host():
+    """gloo moves host memory only.  For the one-GPU runs the collectives LayerPipeline uses are wrapped so that CUDA
+    tensors travel as host copies (`.cpu()` waits for the producing stream, `copy_` back is ordered on the current
+    stream); shapes, order and semantics of the calls are untouched.  Test-only: the product path is NCCL."""
+    real = {k: getattr(dist, k) for k in ("isend", "irecv", "send", "recv", "broadcast", "all_reduce")}
+
+    def isend(t, dst, group=None):
+        h = t.detach().cpu()
+        return _Staged(real["isend"](h, dst, group=group), h)
+
+    def irecv(t, src, group=None):
+        h = torch.empty(t.shape, dtype=t.dtype)
+        return _Staged(real["irecv"](h, src, group=group), h, lambda: t.copy_(h))
+
+    def send(t, dst, group=None):
+        real["send"](t.detach().cpu(), dst, group=group)
+
+    def recv(t, src, group=None):
+        h = torch.empty(t.shape, dtype=t.dtype)
+        real["recv"](h, src, group=group)
+        t.copy_(h)
+
+    def broadcast(t, src, group=None, async_op=False):
+        h = t.detach().cpu()
+        real["broadcast"](h, src, group=group)
+        t.copy_(h)
+        return _Staged(None, h) if async_op else None
+
+    def all_reduce(t, op=dist.ReduceOp.SUM, group=None, async_op=False):
+        h = t.detach().cpu()
+        real["all_reduce"](h, op=op, group=group)
+        t.copy_(h)
+        return _Staged(None, h) if async_op else None
+
+    for name, fn in (("isend", isend), ("irecv", irecv), ("send", send), ("recv", recv), ("broadcast", broadcast),
+                     ("all_reduce", all_reduce)):
+        setattr(dist, name, fn)
+
+
+def _bring_up(rank, world, port):
+    """Process group + device of a test rank.  Normally rank r owns cuda:r and talks NCCL.  With DGI_TEST_ONE_GPU=1 (set
+    by the one-GPU tests around the spawn) every rank is a process of its own on cuda:0 and the hops go over gloo,
+    staged through the host — nothing on the GPU ever waits for another rank, so the ranks can share the device: the
+    same product code and the same CUDA kernels, runnable where only one GPU is present."""
+    os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port))
+    if os.environ.get("DGI_TEST_ONE_GPU") == "1":
+        torch.cuda.set_device(0)
+        dist.init_process_group("gloo", rank=rank, world_size=world)
+        _stage_collectives_through_the_host()
+        return "cuda:0"
+    torch.cuda.set_device(rank)
+    dev = f"cuda:{rank}"
+    dist.init_process_group("nccl", rank=rank, world_size=world, device_id=torch.device(dev))
+    return dev
+
+
+def _run_ranks_on_one_gpu(target, world, n_items, timeout=150):
+    os.environ["DGI_TEST_ONE_GPU"] = "1"
+    try:
+        return _run_ranks(target, world, n_items, timeout=timeout)
+    finally:
+        del os.environ["DGI_TEST_ONE_GPU"]
+
+
 def _pipeline_worker(rank, world, port, q, vp=False):
     import sys
     sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
@@ -68,10 +146,7 @@ def _pipeline_worker(rank, world, port, q, vp=False):
     from dgi_b200.worker.distributed.model_shard import get_layer_range_for_worker
     from oracle import llama_ref as L
 
-    os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port))
-    torch.cuda.set_device(rank)
-    dev = f"cuda:{rank}"
-    dist.init_process_group("nccl", rank=rank, world_size=world, device_id=torch.device(dev))
+    dev = _bring_up(rank, world, port)
     try:
         g = json.load(open(os.path.join(os.path.dirname(__file__), "golden", "tiny_decode.json")))
         cfg = L.RefConfig(**g["config"])
@@ -111,6 +186,17 @@ def test_two_rank_pipeline_tokens_identical_to_reference(golden):
     assert got == [row[:27] for row in g["tokens"]]
 
 
+@pytest.mark.parametrize("world", [2, 4])
+@pytest.mark.parametrize("vp", [False, True])
+def test_pipeline_ranks_as_processes_on_one_gpu_give_the_reference_tokens(golden, world, vp):
+    """The N-rank layer pipeline where only ONE GPU is present: N processes on cuda:0, hops over gloo.  Same
+    LayerPipeline schedule, same paged CUDA kernels per stage, golden tokens of the reference's ModelShard pair — for
+    2 ranks and for 4 ranks of one layer each, with the head on the last stage and vocabulary-parallel."""
+    g = golden("tiny_decode.json")
+    (got,) = _run_ranks_on_one_gpu(_pipeline_worker_vp if vp else _pipeline_worker, world, 1)
+    assert got == [row[:27] for row in g["tokens"]]
+
+
 @pytest.mark.skipif(torch.cuda.device_count() < 2, reason="needs 2 GPUs")
 def test_two_rank_pipeline_with_vocabulary_parallel_head_tokens_identical_to_reference(golden):
     g = golden("tiny_decode.json")
@@ -125,10 +211,7 @@ def _transfer_worker(rank, world, port, q):
     from dgi_b200.kv_transfer import KVTransferEndpoint
     from dgi_b200.worker.distributed.kv_cache import KVCachePool
 
-    os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port))
-    torch.cuda.set_device(rank)
-    dev = f"cuda:{rank}"
-    dist.init_process_group("nccl", rank=rank, world_size=world, device_id=torch.device(dev))
+    dev = _bring_up(rank, world, port)
     try:
         L_, Hkv, D, bs, max_blocks, seq_len = 6, 8, 128, 16, 40, 300
         pool = KVCachePool(L_, Hkv, D, bs, max_blocks, device=dev, dtype=torch.bfloat16)
@@ -164,6 +247,12 @@ def _transfer_worker(rank, world, port, q):
 @pytest.mark.skipif(torch.cuda.device_count() < 2, reason="needs 2 GPUs")
 def test_pd_handoff_over_nccl_is_bit_exact():
     items = dict(_run_ranks(_transfer_worker, 2, 2))
+    assert items["sent"] == items["received"]
+
+
+def test_pd_handoff_between_two_processes_on_one_gpu_is_bit_exact():
+    """pack -> send / recv -> unpack between two ranks that share one GPU (host-staged gloo hop)."""
+    items = dict(_run_ranks_on_one_gpu(_transfer_worker, 2, 2))
     assert items["sent"] == items["received"]
 
 
@@ -268,10 +357,7 @@ def _pipeline70b_worker(rank, world, port, q):
     from dgi_b200.worker.distributed.model_shard import ModelShard, get_layer_range_for_worker
     from oracle import llama_ref as L
 
-    os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port))
-    torch.cuda.set_device(rank)
-    dev = f"cuda:{rank}"
-    dist.init_process_group("nccl", rank=rank, world_size=world, device_id=torch.device(dev))
+    dev = _bring_up(rank, world, port)
     try:
         shape = dict(L.LLAMA3_70B)
         shape["num_hidden_layers"] = 4
@@ -327,6 +413,13 @@ def test_two_rank_70b_shape_bf16_pipeline_vs_reference_recipe():
     assert not bad, f"divergence at a decided token: {bad}"
 
 
+def test_70b_shape_bf16_pipeline_of_two_processes_on_one_gpu_vs_reference_recipe():
+    (item,) = _run_ranks_on_one_gpu(_pipeline70b_worker, 2, 1, timeout=400)
+    _, agreement, bad = item
+    print(f"70B-shape (4 layers) bf16, 2 ranks on one GPU x 2 micro-batches: token agreement {agreement:.3f}")
+    assert not bad, f"divergence at a decided token: {bad}"
+
+
 def _pd_worker(rank, world, port, q):
     """BASELINE config 3 in miniature: rank 0 runs the prompt pass, ships every sequence's KV blocks to rank 1,
     rank 1 decodes.  Tokens must equal the reference's (golden) tokens for the same prompts."""
@@ -340,10 +433,7 @@ def _pd_worker(rank, world, port, q):
     from dgi_b200.testing import build_product_shards
     from oracle import llama_ref as L
 
-    os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port))
-    torch.cuda.set_device(rank)
-    dev = f"cuda:{rank}"
-    dist.init_process_group("nccl", rank=rank, world_size=world, device_id=torch.device(dev))
+    dev = _bring_up(rank, world, port)
     try:
         g = json.load(open(os.path.join(os.path.dirname(__file__), "golden", "tiny_decode.json")))
         cfg = L.RefConfig(**g["config"])
@@ -393,6 +483,17 @@ def test_prefill_rank_to_decode_rank_handoff_gives_reference_tokens(golden):
     (tables0,) = items["tables0"]
     assert toks == [row[:20] for row in g["tokens"]]
     assert tables0 != tables1  # the decode rank put the blocks where ITS allocator said
+
+
+def test_prefill_process_to_decode_process_on_one_gpu_gives_reference_tokens(golden):
+    """The prefill -> decode hand-off (prompt pass on one rank, pack -> hop -> unpack into the other rank's own blocks,
+    decode there) with both ranks as processes on one GPU: the reference's golden tokens."""
+    g = golden("tiny_decode.json")
+    items = {i[0]: i[1:] for i in _run_ranks_on_one_gpu(_pd_worker, 2, 2)}
+    toks, tables1 = items["tokens"]
+    (tables0,) = items["tables0"]
+    assert toks == [row[:20] for row in g["tokens"]]
+    assert tables0 != tables1
 
 
 def _pd_serving_worker(rank, world, port, q):
