@@ -25,9 +25,20 @@ inline int ceil_div(int a, int b) { return (a + b - 1) / b; }
 int plan_splits(int B, int Hkv, int block_size, int max_context_len) {
   const int n_blocks = std::max(1, ceil_div(std::max(1, max_context_len), block_size));
   const int pairs = std::max(1, B * Hkv);
-  if (pairs >= 120) return 1;
   const int min_blocks = std::max(1, 256 / block_size);
   const int max_by_len = std::max(1, n_blocks / min_blocks);
+  if (pairs >= 120) {
+    // One CTA per pair is right when the pairs put (at most) one CTA on every SM, or so many that the block scheduler
+    // balances them by itself.  In between every CTA is resident from the start, some SMs hold two and the others one,
+    // and the launch takes as long as the doubly loaded SMs: 160 pairs (batch 20, 8 kv heads, context 4k) ran at 0.58
+    // of the copy peak, 192 at 0.68, 320 at 0.82.  Cutting the context so that there are roughly 700 CTAs (a bit over
+    // two waves of the 296 slots) lets the scheduler even them out, and with the combine launched as a programmatic
+    // dependent the second launch costs little: 0.80-0.83 / 0.88 / 0.94 for those three, 256 pairs 0.90 -> 0.92,
+    // 384 pairs 0.94 -> 0.97 (tools/kbench.py --cases grid:BxCTX, profiles/r02_kbench_midsize_grids.txt).
+    if (pairs <= kNumSMs || pairs >= 500) return 1;
+    const int s = std::min(6, std::max(2, ceil_div(700, pairs)));
+    return std::max(1, std::min(s, max_by_len));
+  }
   int splits = std::max(1, ceil_div(kNumSMs * 7 / 2, pairs));
   // One or two long sequences (pairs <= 16): exactly one wave of CTAs (2 per SM) beats 1.75 waves of shorter ones —
   // batch 1 at 16k / 32k / 64k / 128k context: 37 splits 25.7 / 32.5 / 52.7 / 92.6 us vs 26.7 / 35.7 / 56.6 / 94.5 us;

@@ -245,3 +245,7 @@ if __name__ == "__main__":
             copy_cases()
         elif c == "append":
             append_cases(a.iters)
+        elif c.startswith("grid:"):  # e.g. grid:20x4096 or grid:20x4096x64 = batch x context [x q heads], 8 kv heads
+            parts = [int(x) for x in c[5:].split("x")]
+            nb, nctx, hq = parts[0], parts[1], (parts[2] if len(parts) > 2 else 32)
+            attn_case(f"B{nb} ctx{nctx} Hq{hq}", nb, hq, 8, 128, [nctx] * nb, a.layers, a.splits, fl, iters=a.iters)
