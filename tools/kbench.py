@@ -214,6 +214,9 @@ if __name__ == "__main__":
             attn_case("cfg4 70B B128 ctx4k (per layer)", 128, 64, 8, 128, [4096] * 128, min(a.layers, 4), a.splits, fl, iters=a.iters)
         elif c == "cfg4mb":
             attn_case("cfg4 70B micro-batch 16 ctx4k", 16, 64, 8, 128, [4096] * 16, a.layers, a.splits, fl, iters=a.iters)
+        elif c == "cfg4mbf":
+            attn_case("cfg4 70B micro-batch 16 ctx4k, fused RoPE + append + attention", 16, 64, 8, 128, [4096] * 16, a.layers,
+                      a.splits, fl, iters=a.iters, fused=True)
         elif c == "cfg5":
             lens = [24576 + 8192 - 512 * i for i in range(8)]
             attn_case("cfg5 8B B8 ctx32k ragged, shared 24576 prefix", 8, 32, 8, 128, lens, a.layers, a.splits, fl,
