@@ -1,23 +1,25 @@
-"""Prefill/decode-separated serving over one (prefill GPU, decode GPU) pair: the data plane behind the reference's
-P/D scheduler (server/app/services/pd_scheduler.py:207-323) and the workload of its benchmark
-(benchmarks/pd_separation.py: prefill on one worker, KV migration, decode on another).
+"""Prefill/decode-separated serving over a group of K prefill GPUs feeding one decode GPU (K = 1: a pair): the data
+plane behind the reference's P/D scheduler (server/app/services/pd_scheduler.py:207-323) and the workload of its
+benchmark (benchmarks/pd_separation.py: prefill on one worker, KV migration, decode on another).
 
-Both ranks of a pair hold the whole model.  A *wave* is a batch of requests with equal prompt length:
+Every rank of a group holds the whole model.  A *wave* is a batch of requests with equal prompt length on ONE
+prefill rank; the decode rank takes the waves with the same number from all K prefill ranks as one decode batch:
 
-  prefill rank   prompt pass chunk by chunk into its own blocks; after each chunk, on a side stream, ONE kernel
+  prefill rank p prompt pass chunk by chunk into its own blocks; after each chunk, on a side stream, ONE kernel
                  (b200_kv_move_blocks_layers) writes that chunk's blocks of all layers over NVLink straight into the
-                 blocks the DECODE rank's allocator handed out; first tokens follow as a peer copy; then a signal.
-  decode rank    waits for the signal on its stream, adopts the blocks (``PagedDecodeEngine.adopt_sequences``) and
-                 decodes; then signals the slot set free.
+                 blocks the DECODE rank's allocator handed out (rows p*B .. of the slot set); first tokens follow
+                 as a peer copy; then a signal.
+  decode rank    waits for the K signals on its stream, adopts the blocks (``PagedDecodeEngine.adopt_sequences``)
+                 and decodes K*B sequences per step; then signals the slot set free to every prefill rank.
 
-No NCCL call and no host synchronisation sits between the two ranks on the data path: block tables, first tokens and
-the two semaphores ("KV ready", "slot set free") all live in symmetric memory, so the prefill rank never waits for
-the decode rank unless both slot sets are still in use (back-pressure), and prompt passes overlap decode steps of
-the previous wave.
+No NCCL call and no host synchronisation sits between the ranks on the data path: block tables, first tokens and
+the two semaphores per prefill rank ("KV ready", "slot set free") all live in symmetric memory, so a prefill rank
+never waits for the decode rank unless both slot sets are still in use (back-pressure), and prompt passes overlap
+decode steps of the previous wave.
 """
 from __future__ import annotations
 
-from typing import List, Optional, Sequence
+from typing import List, Optional
 
 import torch
 import torch.distributed as dist
@@ -31,54 +33,60 @@ from .worker.distributed.kv_cache import KVCachePool
 READY, FREE = 2, 3
 
 
-class PDPairWorker:
-    """One side of a prefill/decode pair.  ``group`` holds exactly the two ranks; group rank 0 prefills, 1 decodes."""
+class PDGroupWorker:
+    """One rank of a prefill/decode group.  ``group`` holds K + 1 ranks: group ranks 0 .. K-1 prefill waves of up to
+    ``max_batch`` sequences each, group rank K decodes up to ``K * max_batch`` sequences per step."""
 
     def __init__(self, shard, group, max_batch: int, prompt_len: int, max_new_tokens: int, block_size: int = 16,
                  prefill_chunk: int = 4, slot_sets: int = 2, fuse_projections: bool = False,
                  prefill_mode: str = "sdpa", use_cuda_graph: bool = True):
         import torch.distributed._symmetric_memory as symm_mem
 
-        if dist.get_world_size(group) != 2:
-            raise ValueError("a P/D pair is two ranks")
+        size = dist.get_world_size(group)
+        if size < 2:
+            raise ValueError("a P/D group is at least one prefill rank and one decode rank")
         self.group = group
         self.me = dist.get_rank(group)
-        self.is_prefill = self.me == 0
-        self.peer = 1 - self.me
+        self.K = size - 1
+        self.decode_rank = self.K
+        self.is_prefill = self.me < self.K
         self.B, self.P, self.n_new, self.sets = max_batch, prompt_len, max_new_tokens, slot_sets
+        self.rows = self.K * max_batch  # sequences of one slot set (the decode rank's batch)
         cfg = shard.config
         Hq = cfg.num_attention_heads
         Hkv = getattr(cfg, "num_key_value_heads", Hq) or Hq
         D = getattr(cfg, "head_dim", None) or cfg.hidden_size // Hq
         total = prompt_len + max_new_tokens
+        self.total = total
         self.n_blk = (total + block_size - 1) // block_size        # blocks a decode-side sequence owns
         self.n_blk_prompt = (prompt_len + block_size - 1) // block_size  # blocks that travel
         dev = str(shard.device)
+        # symmetric memory: every rank of the group maps the same number of blocks
         self.endpoint = PeerPushEndpoint(shard.get_layer_count(), Hkv, D, block_size,
-                                         slot_sets * max_batch * self.n_blk, dev, shard.dtype, group=group)
+                                         slot_sets * self.rows * self.n_blk, dev, shard.dtype, group=group)
         self.handle = self.endpoint.handle
-        self.engine = PagedDecodeEngine([shard], max_batch, total, block_size=block_size, prefill_chunk=prefill_chunk,
+        self.engine = PagedDecodeEngine([shard], max_batch if self.is_prefill else self.rows, total,
+                                        block_size=block_size, prefill_chunk=prefill_chunk,
                                         prefill_mode=prefill_mode, fuse_projections=fuse_projections,
                                         use_cuda_graph=use_cuda_graph, kv_pools=[self.endpoint.pool])
         # mailbox in symmetric memory: the decode rank's block tables per slot set + the first tokens per slot set
-        n_tab = (slot_sets * max_batch * self.n_blk + 1) // 2 * 2  # even, so the int64 token area is 8-byte aligned
-        words = n_tab + 2 * slot_sets * max_batch
+        n_used = slot_sets * self.rows * self.n_blk
+        n_tab = (n_used + 1) // 2 * 2  # even, so the int64 token area is 8-byte aligned
+        words = n_tab + 2 * slot_sets * self.rows
         self._mail = symm_mem.empty((words,), dtype=torch.int32, device=dev)
         self._mail.zero_()
         self._mail_handle = symm_mem.rendezvous(self._mail, group.group_name)
-        n_used = slot_sets * max_batch * self.n_blk
-        self._tables = self._mail[:n_used].view(slot_sets, max_batch, self.n_blk)
-        self._tokens = self._mail[n_tab:].view(torch.int64).view(slot_sets, max_batch)
-        peer_mail = self._mail_handle.get_buffer(self.peer, (words,), torch.int32)
-        self._peer_tokens = peer_mail[n_tab:].view(torch.int64).view(slot_sets, max_batch)
+        self._tables = self._mail[:n_used].view(slot_sets, self.rows, self.n_blk)
+        self._tokens = self._mail[n_tab:].view(torch.int64).view(slot_sets, self.rows)
         self._side = torch.cuda.Stream(device=dev)
-        # Both roles take their blocks ONCE: `slot_sets` sets of max_batch sequences, reused wave after wave (no
-        # per-wave allocator traffic — 16 sequences x 4k tokens x 32 layers are 131k block objects).
+        # Every rank takes its blocks ONCE: `slot_sets` sets of K * max_batch sequences, reused wave after wave (no
+        # per-wave allocator traffic — 16 sequences x 4k tokens x 32 layers are 131k block objects).  A prefill
+        # rank's waves use the first max_batch rows of a set.
         self._slot_blocks: List[List] = []
-        self._my_tables = torch.empty((slot_sets, max_batch, self.n_blk), dtype=torch.int32, device=dev)
+        self._my_tables = torch.empty((slot_sets, self.rows, self.n_blk), dtype=torch.int32, device=dev)
         pool: KVCachePool = self.endpoint.pool
         for s in range(slot_sets):
-            seqs = [[pool.allocate_sequence(total)] for _ in range(max_batch)]
+            seqs = [[pool.allocate_sequence(total)] for _ in range(self.rows)]
             for per_shard in seqs:
                 rows0 = KVCachePool.block_table(per_shard[0][0])
                 for li, layer_blocks in enumerate(per_shard[0]):
@@ -89,9 +97,13 @@ class PDPairWorker:
             rows = [KVCachePool.block_table(per_shard[0][0]) for per_shard in seqs]
             self._my_tables[s].copy_(torch.tensor(rows, dtype=torch.int32))
         self._set_pushed: List[Optional[torch.cuda.Event]] = [None] * slot_sets
-        if not self.is_prefill:
-            peer_tables = peer_mail[:n_used].view(slot_sets, max_batch, self.n_blk)
-            peer_tables.copy_(self._my_tables)  # publish where each slot set's blocks are
+        if self.is_prefill:
+            peer_mail = self._mail_handle.get_buffer(self.decode_rank, (words,), torch.int32)
+            self._peer_tokens = peer_mail[n_tab:].view(torch.int64).view(slot_sets, self.rows)
+        else:
+            for p in range(self.K):  # publish where each slot set's blocks are
+                peer_mail = self._mail_handle.get_buffer(p, (words,), torch.int32)
+                peer_mail[:n_used].view(slot_sets, self.rows, self.n_blk).copy_(self._my_tables)
         torch.cuda.synchronize()
         self.handle.barrier()
         torch.cuda.synchronize()
@@ -99,19 +111,21 @@ class PDPairWorker:
     # ---- prefill side -------------------------------------------------------------------------------------
     @torch.no_grad()
     def prefill_wave(self, wave: int, prompt_ids: torch.Tensor, events: Optional[dict] = None) -> None:
-        """Prompt pass of ``prompt_ids`` [n, P] and the push of its KV into slot set ``wave % slot_sets`` of the peer."""
+        """Prompt pass of ``prompt_ids`` [n, P] and the push of its KV into this rank's rows of slot set
+        ``wave % slot_sets`` on the decode rank."""
         assert self.is_prefill
         eng, s = self.engine, wave % self.sets
         n, P = prompt_ids.shape
         if n > self.B or P != self.P:
-            raise ValueError("wave does not match the pair's shape")
+            raise ValueError("wave does not match the group's shape")
         cur = torch.cuda.current_stream()
         if self._set_pushed[s] is not None:
             cur.wait_event(self._set_pushed[s])  # the pushes of wave - slot_sets still read these blocks
         eng.adopt_sequences(self._slot_blocks[s][:n], [0] * n, table_rows=self._my_tables[s, :n])
         if wave >= self.sets:
             with torch.cuda.stream(self._side):
-                self.handle.wait_signal(self.peer, FREE)  # the decode rank is done with this slot set
+                self.handle.wait_signal(self.decode_rank, FREE)  # the decode rank is done with this slot set
+        row0 = self.me * self.B  # this rank's rows of the decode batch
         dst_tables = self._tables[s]
         for lo in range(0, n, eng.prefill_chunk_size):
             hi = min(n, lo + eng.prefill_chunk_size)
@@ -126,9 +140,9 @@ class PDPairWorker:
                 # the set's own static table, NOT eng.block_tables: the main stream may already be adopting the
                 # next wave (and rewriting the engine's table) when this runs
                 src = self._my_tables[s, lo:hi, :self.n_blk_prompt].reshape(-1).contiguous()
-                dst = dst_tables[lo:hi, :self.n_blk_prompt].reshape(-1).contiguous()
-                self.endpoint.push(src, dst, self.peer)
-                self._peer_tokens[s, lo:hi].copy_(first)
+                dst = dst_tables[row0 + lo:row0 + hi, :self.n_blk_prompt].reshape(-1).contiguous()
+                self.endpoint.push(src, dst, self.decode_rank)
+                self._peer_tokens[s, row0 + lo:row0 + hi].copy_(first)
                 first.record_stream(self._side)
                 if events is not None:
                     p1 = torch.cuda.Event(enable_timing=True)
@@ -138,33 +152,49 @@ class PDPairWorker:
         with torch.cuda.stream(self._side):
             self._set_pushed[s] = torch.cuda.Event()
             self._set_pushed[s].record(self._side)
-            self.handle.put_signal(self.peer, READY)
+            self.handle.put_signal(self.decode_rank, READY)
 
     # ---- decode side --------------------------------------------------------------------------------------
     @torch.no_grad()
     def decode_wave(self, wave: int, n: int, n_waves: int, events: Optional[dict] = None) -> torch.Tensor:
-        """Decode ``max_new_tokens`` tokens for the ``n`` sequences of ``wave``; returns them [n, max_new_tokens] on
-        the device (column 0 is the token the prompt pass produced)."""
+        """Decode ``max_new_tokens`` tokens for the ``n`` sequences each prefill rank sent as ``wave``; returns them
+        [K * n, max_new_tokens] on the device, prefill rank by prefill rank (column 0 is the token the prompt pass
+        produced)."""
         assert not self.is_prefill
         eng, s = self.engine, wave % self.sets
-        self.handle.wait_signal(self.peer, READY)
+        if n > self.B:
+            raise ValueError("wave does not match the group's shape")
+        for p in range(self.K):
+            self.handle.wait_signal(p, READY)
         if events is not None:
             e0 = torch.cuda.Event(enable_timing=True)
             e0.record()
-        eng.adopt_sequences(self._slot_blocks[s][:n], [self.P] * n, table_rows=self._my_tables[s, :n])
-        out = torch.empty((n, self.n_new), dtype=torch.int64, device=eng.device)
-        out[:, 0] = self._tokens[s, :n]
-        eng.ids_buf[:n, 0].copy_(out[:, 0])
+        if n == self.B:
+            seqs, tables, first = self._slot_blocks[s], self._my_tables[s], self._tokens[s]
+        else:  # partial waves: rows p*B .. p*B + n of every prefill rank
+            idx = [p * self.B + i for p in range(self.K) for i in range(n)]
+            sel = torch.tensor(idx, dtype=torch.int64, device=eng.device)
+            seqs = [self._slot_blocks[s][i] for i in idx]
+            tables, first = self._my_tables[s].index_select(0, sel), self._tokens[s].index_select(0, sel)
+        nb = len(seqs)
+        eng.adopt_sequences(seqs, [self.P] * nb, table_rows=tables)
+        out = torch.empty((nb, self.n_new), dtype=torch.int64, device=eng.device)
+        out[:, 0] = first
+        eng.ids_buf[:nb, 0].copy_(out[:, 0])
         for i in range(1, self.n_new):
             eng.decode_step_device()
-            out[:, i] = eng.next_tokens[:n]
+            out[:, i] = eng.next_tokens[:nb]
         if wave + self.sets < n_waves:
-            self.handle.put_signal(self.peer, FREE)
+            for p in range(self.K):
+                self.handle.put_signal(p, FREE)
         if events is not None:
             e1 = torch.cuda.Event(enable_timing=True)
             e1.record()
             events.setdefault("decode", []).append((wave, e0, e1))
         return out
+
+
+PDPairWorker = PDGroupWorker  # a pair is the K = 1 group
 
 
 def make_pair_groups(world: int):
@@ -175,5 +205,20 @@ def make_pair_groups(world: int):
     for i in range(half):
         g = dist.new_group([i, i + half])
         if rank in (i, i + half):
+            mine = g
+    return mine
+
+
+def make_fanin_groups(world: int, prefill_ranks: int):
+    """Groups of ``prefill_ranks + 1`` consecutive ranks, the last of each decoding; returns this rank's group."""
+    size = prefill_ranks + 1
+    if world % size:
+        raise ValueError(f"{world} ranks do not split into groups of {size}")
+    mine = None
+    rank = dist.get_rank()
+    for g0 in range(0, world, size):
+        members = list(range(g0, g0 + size))
+        g = dist.new_group(members)
+        if rank in members:
             mine = g
     return mine

@@ -541,6 +541,64 @@ def _pd_serving_worker(rank, world, port, q):
         dist.destroy_process_group()
 
 
+def _pd_fanin_worker(rank, world, port, q):
+    """Two prefill ranks feed one decode rank (PDGroupWorker, K = 2): each prefill rank runs waves of two sequences,
+    the decode rank decodes four per step; partial waves included."""
+    import sys
+    sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+    import json
+
+    import dgi_b200  # noqa: F401
+    from dgi_b200.pd_serving import PDGroupWorker, make_fanin_groups
+    from dgi_b200.testing import build_product_shards
+    from oracle import llama_ref as L
+
+    os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port))
+    torch.cuda.set_device(rank)
+    dev = f"cuda:{rank}"
+    dist.init_process_group("nccl", rank=rank, world_size=world, device_id=torch.device(dev))
+    try:
+        g = json.load(open(os.path.join(os.path.dirname(__file__), "golden", "tiny_decode.json")))
+        cfg = L.RefConfig(**g["config"])
+        sd = L.make_weights(cfg, seed=0)
+        shard = build_product_shards(cfg, sd, [(0, 4)], dev, torch.float32)[0]
+        prompts = torch.tensor(g["prompt_ids"]).to(dev)
+        B, P, n_new, waves = 2, prompts.shape[1], 20, 5
+        group = make_fanin_groups(world, 2)
+        w = PDGroupWorker(shard, group, B, P, n_new, prefill_chunk=1, slot_sets=2, prefill_mode="eager")
+        assert w.K == 2 and w.engine.max_batch == (B if w.is_prefill else 2 * B)
+        got = []
+        sizes = [2, 2, 1, 2, 1]
+        for i in range(waves):
+            rows = prompts.roll(i, dims=0)
+            if w.is_prefill:
+                with torch.cuda.stream(w._side):
+                    torch.cuda._sleep(20_000_000 * (1 + w.me))  # the two prefill ranks finish at different times
+                w.prefill_wave(i, rows[w.me * B:w.me * B + sizes[i]])
+            else:
+                got.append(w.decode_wave(i, sizes[i], waves))
+        torch.cuda.synchronize()
+        w._side.synchronize()
+        if not w.is_prefill:
+            q.put(("tokens", [t.cpu().tolist() for t in got]))
+        dist.barrier()
+    finally:
+        dist.destroy_process_group()
+
+
+@pytest.mark.skipif(torch.cuda.device_count() < 3, reason="needs 3 GPUs")
+def test_pd_fan_in_two_prefill_ranks_one_decode_rank(golden):
+    g = golden("tiny_decode.json")
+    ((_, waves),) = _run_ranks(_pd_fanin_worker, 3, 1)
+    want = [row[:20] for row in g["tokens"]]
+    assert len(waves) == 5
+    for i, toks in enumerate(waves):
+        k = i % len(want)
+        rolled = want[-k:] + want[:-k] if k else want
+        n = [2, 2, 1, 2, 1][i]
+        assert toks == rolled[0:n] + rolled[2:2 + n], f"wave {i}"
+
+
 @pytest.mark.skipif(torch.cuda.device_count() < 2, reason="needs 2 GPUs")
 def test_pd_serving_waves_give_reference_tokens(golden):
     g = golden("tiny_decode.json")
