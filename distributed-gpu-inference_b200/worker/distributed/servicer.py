@@ -171,6 +171,11 @@ class InferenceServicer:
             return hidden_states, kv_cache_keys  # reference :359-361: echo
         B, T = hidden_states.shape[0], hidden_states.shape[1]
         dev = hidden_states.device
+        held = int(session.get("position", 0))
+        if position < 0 or position > held:
+            # a retry (position <= what the session holds) rewrites the same slots; a gap would attend over slots
+            # nobody wrote
+            raise ValueError(f"position {position} is beyond the {held} tokens session {session['session_id']} holds")
         kv = self._session_kv(session, B, position + T)
         pool = kv.pool
         bs = pool.block_size
@@ -189,7 +194,7 @@ class InferenceServicer:
         position_ids = t[None, :].expand(B, T)  # reference :365-369: arange(position, position + T)
         output, _ = self.model_shard.forward(hidden_states, position_ids=position_ids, past_key_values=handles,
                                              use_cache=True)
-        session["position"] = position + T
+        session["position"] = max(held, position + T)
         self._stats["total_tokens"] += B * T
         keys = list(kv_cache_keys) if kv_cache_keys else [f"session:{session['session_id']}"]
         return output, keys
@@ -293,7 +298,13 @@ class InferenceServicer:
         seq = int(_get(request, "sequence_index", 0) or 0)
         batch = int(_get(request, "batch", 1) or 1)
         num_tokens = int(_get(request, "num_tokens", 0) or n_blocks * pool.block_size)
+        if num_tokens > n_blocks * pool.block_size:
+            raise ValueError(f"{n_blocks} blocks cannot hold {num_tokens} tokens")
         kv = self._session_kv(session, batch, num_tokens)
+        if not 0 <= seq < kv.batch:
+            raise ValueError(f"sequence_index {seq} outside the session's batch of {kv.batch}")
+        if n_blocks > kv.tables.shape[1]:
+            raise ValueError(f"{n_blocks} blocks do not fit the session's {kv.tables.shape[1]} blocks per sequence")
         start_layer = int(_get(request, "start_layer", 0) or 0)
         wire = session.get("_wire")
         if wire is None or wire.start_layer != start_layer:
@@ -341,9 +352,10 @@ class InferenceServicer:
             response = {"healthy": True, "worker_id": self.worker_id, "status": "online",
                         "active_sessions": len(self._sessions)}
             if _get(request, "include_stats", False):
-                if torch.cuda.is_available():
-                    response["gpu_memory_used_gb"] = torch.cuda.memory_allocated() / (1024 ** 3)
-                    response["gpu_memory_total_gb"] = torch.cuda.get_device_properties(0).total_memory / (1024 ** 3)
+                dev = torch.device(self._device())
+                if dev.type == "cuda" and torch.cuda.is_available():
+                    response["gpu_memory_used_gb"] = torch.cuda.memory_allocated(dev) / (1024 ** 3)
+                    response["gpu_memory_total_gb"] = torch.cuda.get_device_properties(dev).total_memory / (1024 ** 3)
                 pool = getattr(self.kv_cache, "gpu_cache", None)
                 if isinstance(pool, KVCachePool):
                     used = max(pool.layer(li).get_stats()["total_blocks"] for li in range(pool.num_layers))

@@ -86,3 +86,47 @@ def test_stream_inference_yields_one_response_per_request():
 
     out = run(go())
     assert [r["step_id"] for r in out] == [0, 1, 2] and all(r["success"] and r["tokens_processed"] == 1 for r in out)
+
+
+class _PassThroughShard:
+    """Stands in for a ModelShard: two layers, returns its input (the session bookkeeping is what is under test)."""
+    device = "cpu"
+
+    def get_layer_count(self):
+        return 2
+
+    def forward(self, hidden_states, attention_mask=None, position_ids=None, past_key_values=None, use_cache=True):
+        assert len(past_key_values) == 2 and position_ids.shape == hidden_states.shape[:2]
+        return hidden_states, None
+
+
+def test_forward_refuses_a_position_gap_and_accepts_a_retry():
+    sv = InferenceServicer("w0", _PassThroughShard(), _mgr(blocks=16))
+    sid = run(sv.CreateSession({"model_name": "m", "max_length": 16}))["session_id"]
+    x = torch.zeros(1, 3, 8)
+    ok = run(sv.Forward({"session_id": sid, "input": x, "position": 0}))
+    assert ok["success"] and sv._sessions[sid]["position"] == 3
+    gap = run(sv.Forward({"session_id": sid, "input": x[:, :1], "position": 5}))
+    assert not gap["success"] and "beyond the 3 tokens" in gap["error_message"]
+    retry = run(sv.Forward({"session_id": sid, "input": x[:, :1], "position": 2}))  # the client's retry loop
+    assert retry["success"] and sv._sessions[sid]["position"] == 3
+    nxt = run(sv.Forward({"session_id": sid, "input": x[:, :1], "position": 3}))
+    assert nxt["success"] and sv._sessions[sid]["position"] == 4
+    too_long = run(sv.Forward({"session_id": sid, "input": torch.zeros(1, 20, 8), "position": 4}))
+    assert not too_long["success"] and "Maximum length exceeded" in too_long["error_message"]
+    assert run(sv.CloseSession({"session_id": sid}))["success"]
+    assert sv._get_cache_capacity() == 16 * 4  # the session's blocks went back to the pool
+
+
+def test_session_hand_off_checks_its_bounds():
+    sv = InferenceServicer("w0", _PassThroughShard(), _mgr(blocks=16))
+    sid = run(sv.CreateSession({"model_name": "m", "max_length": 8}))["session_id"]  # 2 blocks of 4 tokens
+    blk = torch.zeros(3, 2, 4, 8, dtype=torch.float16)
+    data, shape, dtype = TensorSerializer.serialize(blk)
+    layer = {"layer_idx": 0, "keys": data, "values": data, "shape": list(shape), "dtype": dtype}
+    resp = run(sv.TransferKVCache({"prefix_key": sid, "layers": [layer], "num_tokens": 8}))
+    assert not resp["success"] and "do not fit" in resp["error_message"]
+    resp = run(sv.TransferKVCache({"prefix_key": sid, "layers": [layer], "num_tokens": 13}))
+    assert not resp["success"] and "cannot hold" in resp["error_message"]
+    resp = run(sv.TransferKVCache({"prefix_key": sid, "layers": [layer], "num_tokens": 8, "sequence_index": 1}))
+    assert not resp["success"] and "sequence_index" in resp["error_message"]
