@@ -2,7 +2,7 @@
 """Headline benchmark: greedy decode tokens/s of the layer-range path over paged KV (BASELINE.json).
 
     python bench.py --gpus N --steps K --warmup W            # this repo's CUDA path
-    python bench.py --impl reference --gpus N --steps K ...  # the reference's torch CPU path (oracle port)
+    python bench.py --impl reference --gpus N --steps K ...  # the reference's torch CPU path (oracle/_ref bytecode, else the oracle port)
 
 N = 1 : BASELINE configs[1] — Llama-3-8B shape, random-init bf16, block 16, batch 64, context 2k, decode; the line
         also carries configs[4] (batch 8, context 32k, shared prefix) as `cfg5` and configs[0] (tiny model, in
@@ -117,13 +117,25 @@ class ClockSampler:
 
 
 # ---------------------------------------------------------------------------------------------------------
-# reference CPU path (oracle port) — bounded sample
+# reference CPU path (oracle/_ref bytecode of the reference's ModelShard, else the oracle port) — bounded sample
 # ---------------------------------------------------------------------------------------------------------
+def _reference_modules():
+    """The reference's own ModelShard module from oracle/_ref (bytecode compiled from /root/reference by
+    oracle/build_ref.py; it travels with the snapshot), or None when it was not built."""
+    from oracle import ref_loader
+
+    return ref_loader.load("model_shard")
+
+
 def cpu_reference_tokens_per_s(shape: str, batch: int, ctx: int, steps: int, warmup: int, sample_layers: int = 2,
                                sample_batch: int = 0):
-    """Time the reference's torch path (oracle.llama_ref: ModelShard.forward restatement + legacy HF layer with
-    dense (k, v) tuples, fp32) on the host cores for `sample_layers` layers of the named shape at the full batch
-    and context, plus the embedding / final norm / lm_head once per step, and extrapolate to the full depth."""
+    """Time the reference's torch CPU path on the host cores for `sample_layers` layers of the named shape at the full
+    batch and context, plus the embedding / final norm / lm_head once per step, and extrapolate to the full depth.
+
+    kind "reference": the reference's own ``ModelShard.forward`` / ``get_logits`` (oracle/_ref bytecode) run the step,
+    over the legacy-convention HF layer of oracle/llama_ref.py with dense (k, v) tuples, fp32 (the installed
+    transformers no longer speaks the call convention of model_shard.py:209-215).  kind "port": the same
+    step spelled out here, when oracle/_ref was not built."""
     from oracle import llama_ref as L
 
     cores = os.cpu_count() or 1
@@ -148,10 +160,41 @@ def cpu_reference_tokens_per_s(shape: str, batch: int, ctx: int, steps: int, war
     pasts = [(torch.randn(batch, cfg.num_key_value_heads, start_ctx, cfg.head_dim, generator=g),
               torch.randn(batch, cfg.num_key_value_heads, start_ctx, cfg.head_dim, generator=g)) for _ in layers]
     ids = torch.randint(0, cfg.vocab_size, (batch, 1), generator=g)
-    t_layers, t_ends = [], []
+    ref_ms = _reference_modules()
+    full = ends = None
+    if ref_ms is not None:
+        def assemble(owned):  # one shard that is first and last: embedding, `owned` layers, norm, lm_head
+            sh = ref_ms.ModelShard(shape, 0, len(owned), device="cpu", dtype=torch.float32)
+            for layer in owned:
+                sh.layers.append(layer)
+            sh.is_first_shard = sh.is_last_shard = True
+            sh.total_layers = len(owned)
+            sh.embed_tokens = torch.nn.Embedding.from_pretrained(embed, freeze=True)
+            sh.embed_positions = None
+            sh.norm = L.RefNorm(norm_w, cfg.rms_norm_eps)
+            sh.lm_head = torch.nn.Linear(cfg.hidden_size, cfg.vocab_size, bias=False)
+            sh.lm_head.weight.data = head
+            return sh.eval()
+
+        full, ends = assemble(layers), assemble([])  # `ends`: the per-step work that does not grow with depth
+    t_layers, t_ends, t_extra = [], [], []
     with torch.no_grad():
         for it in range(warmup + steps):
             pos = torch.full((batch, 1), start_ctx + it, dtype=torch.long)
+            if full is not None:
+                t0 = time.perf_counter()
+                h, pasts = full.forward(ids, position_ids=pos, past_key_values=pasts, use_cache=True)
+                nxt = full.get_logits(h)[:, 0].argmax(-1, keepdim=True)
+                t1 = time.perf_counter()
+                h0, _ = ends.forward(ids, position_ids=pos, past_key_values=None, use_cache=True)
+                ends.get_logits(h0)[:, 0].argmax(-1, keepdim=True)
+                t2 = time.perf_counter()
+                ids = nxt
+                if it >= warmup:
+                    t_ends.append(t2 - t1)
+                    t_layers.append(max((t1 - t0) - (t2 - t1), 0.0))
+                    t_extra.append(t2 - t1)  # the ends-only pass is work this step really did, beyond the sample
+                continue
             t0 = time.perf_counter()
             h = torch.nn.functional.embedding(ids, embed)
             t1 = time.perf_counter()
@@ -166,20 +209,23 @@ def cpu_reference_tokens_per_s(shape: str, batch: int, ctx: int, steps: int, war
                 t_ends.append((t1 - t0) + (t3 - t2))
     per_layer = statistics.mean(t_layers) / sample_layers
     step_s = per_layer * total_layers + statistics.mean(t_ends)
+    how = ("the reference's ModelShard.forward + get_logits (oracle/_ref bytecode) over the legacy HF layer"
+           if full is not None else "oracle port of ModelShard.forward + the legacy HF layer")
     return {
         "value": batch / step_s,
         "unit": "tokens/s",
         "cores": cores,
-        "kind": "port",
+        "kind": "reference" if full is not None else "port",
         "extrapolated": True,
         "factor": total_layers / sample_layers,
-        "ms_per_sampled_step": (sum(t_layers) + sum(t_ends)) / max(1, len(t_layers)) * 1e3,
-        "sample": (f"{sample_layers} of {total_layers} layers of the {shape} shape at batch {batch}"
+        "ms_per_sampled_step": (sum(t_layers) + sum(t_ends) + sum(t_extra)) / max(1, len(t_layers)) * 1e3,
+        "sample": (f"{how}: {sample_layers} of {total_layers} layers of the {shape} shape at batch {batch}"
                    f"{'' if batch == full_batch else f' (of {full_batch}; throughput reported at the sampled batch)'}, context "
                    f"{start_ctx + warmup}..{ctx}, fp32, dense (k,v) cache, {steps} decode steps after {warmup} "
-                   f"warm-up; per-layer time x {total_layers} + embed/norm/lm_head per step"),
+                   f"warm-up; per-layer time x {total_layers} + embed/norm/lm_head per step"
+                   f"{' (timed by a second pass through a shard that owns no layer)' if full is not None else ''}"),
         "ms_per_step_extrapolated": step_s * 1e3,
-        "sample_seconds": sum(t_layers) + sum(t_ends),
+        "sample_seconds": sum(t_layers) + sum(t_ends) + sum(t_extra),
     }
 
 
@@ -494,7 +540,7 @@ def _single_leg(args, workload):
 
 def config1_side_by_side():
     """BASELINE configs[0] IN FULL, un-extrapolated: tiny 4-layer model in 2 layer-range shards, batch 4, prompt 128,
-    64 greedy tokens, fp32 — the reference's torch CPU path (oracle port: ModelShard.forward restatement + legacy
+    64 greedy tokens, fp32 — the reference's torch CPU path (its own ModelShard from oracle/_ref, else the oracle port, + legacy
     HF layer with dense (k, v) tuples) on the host cores, and this repo's paged CUDA path on the GPU, both timed
     over the 63 decode steps after the prompt pass, tokens compared."""
     import dgi_b200  # noqa: F401
@@ -509,7 +555,11 @@ def config1_side_by_side():
     ranges = [(0, 2), (2, 4)]
     B, P, N = 4, 128, 64
     prompts = torch.randint(0, cfg.vocab_size, (B, P), generator=torch.Generator().manual_seed(1234))
-    shards = L.build_shards(cfg, sd, ranges)
+    from oracle import ref_loader
+
+    by_reference = ref_loader.available("model_shard")
+    # the reference's own ModelShard objects (oracle/_ref bytecode) when built, else the oracle's restatement of them
+    shards = ref_loader.reference_shards(cfg, sd, ranges, L) if by_reference else L.build_shards(cfg, sd, ranges)
     L.greedy_decode(shards, prompts[:, :16], 2)  # warm-up
     t0 = time.perf_counter()
     L.greedy_decode(shards, prompts, 1)  # prompt pass + first token
@@ -536,7 +586,8 @@ def config1_side_by_side():
     return {
         "workload": "configs[0]: tiny 4-layer model (d=512, 8 heads, 2 KV heads), 2 layer-range shards, batch 4, prompt 128, "
                     "64 greedy tokens, fp32",
-        "value": B * (N - 1) / cpu_decode_s, "unit": "tokens/s", "cores": cores, "kind": "port", "extrapolated": False,
+        "value": B * (N - 1) / cpu_decode_s, "unit": "tokens/s", "cores": cores,
+        "kind": "reference" if by_reference else "port", "extrapolated": False,
         "sample": f"the whole configuration: {N - 1} decode steps of batch {B} after the prompt pass, {cpu_decode_s:.2f} s",
         "gpu_value": B * (N - 1) / gpu_s, "gpu_path": "PagedDecodeEngine.decode_step (host ids in / out per step), 1 GPU",
         "tokens_identical": bool(torch.equal(got, want)),

@@ -22,4 +22,10 @@ Pinning (oracle/make_golden.py, run in the build container where /root/reference
     bf16, fp16) and those outputs are committed (tests/golden/paged_ops.json), together with the digest of
     ``index_select``-packed blocks.
 Fixtures live in tests/golden/.
+
+``oracle/_ref/`` (git-ignored, built by ``oracle/build_ref.py`` / ``__graft_entry__.build()`` where /root/reference is
+mounted, carried to the GPU box with the snapshot) holds the reference's own modules of the path as bytecode compiled
+from the sources where they lie; ``oracle/ref_loader.py`` imports them.  With it the pinning above is re-checked
+against the reference itself wherever the suite runs (tests/test_reference_bytecode.py), and the timed CPU legs run
+the reference's own ``ModelShard.forward`` (``cpu_baseline.kind = "reference"``).
 """
