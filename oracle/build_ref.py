@@ -2,7 +2,8 @@
 """Recipe for ``oracle/_ref/``: the reference's own modules of this path, byte-compiled WHERE THEY LIE.
 
 The reference is pure Python, so "compiling it from its own source files" is ``py_compile``: each module below is
-compiled straight from ``/root/reference/<path>`` into ``oracle/_ref/<name>.pyc``.  Only compiler output lands in
+compiled straight from ``/root/reference/<path>`` into ``oracle/_ref/<name>.bin`` (a .pyc under another suffix: the
+snapshot that carries the tree to the GPU box leaves ``*.pyc`` behind).  Only compiler output lands in
 the repository tree (no source is copied), ``oracle/_ref/`` is git-ignored, and — like the built ``.so`` — it travels
 to the GPU box with the snapshot, where ``/root/reference`` does not exist.  ``oracle/ref_loader.py`` imports the
 bytecode; it is used by
@@ -37,14 +38,14 @@ def build(ref_root: str = REF_ROOT, out_dir: str = OUT_DIR) -> list:
     written = []
     for name, rel in MODULES.items():
         src = os.path.join(ref_root, rel)
-        dst = os.path.join(out_dir, name + ".pyc")
+        dst = os.path.join(out_dir, name + ".bin")
         # dfile: the path recorded in the code objects (tracebacks point at the reference file, not at a copy)
         py_compile.compile(src, cfile=dst, dfile=f"<reference>/{rel}", doraise=True)
         written.append(dst)
     with open(os.path.join(out_dir, "BUILT_FROM.txt"), "w") as fh:
         fh.write(f"python {sys.version.split()[0]}\n")
         for name, rel in MODULES.items():
-            fh.write(f"{name}.pyc <- {rel}\n")
+            fh.write(f"{name}.bin <- {rel}\n")
     return written
 
 

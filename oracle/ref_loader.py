@@ -14,7 +14,7 @@ _PREFIX = "_dgi_reference_"
 
 
 def path_of(name: str) -> str:
-    return os.path.join(_DIR, name + ".pyc")
+    return os.path.join(_DIR, name + ".bin")
 
 
 def available(name: str = "model_shard") -> bool:

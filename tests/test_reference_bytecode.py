@@ -1,4 +1,4 @@
-"""CPU: the reference's OWN code (oracle/_ref/*.pyc, byte-compiled from /root/reference by oracle/build_ref.py and
+"""CPU: the reference's OWN code (oracle/_ref/*.bin, byte-compiled from /root/reference by oracle/build_ref.py and
 carried to the GPU box with the snapshot) against the committed fixtures, the oracle restatements and the product's
 host logic.  Where the fixtures pin the oracle to reference outputs recorded once, these tests re-run the reference
 itself, wherever the suite runs."""
