@@ -29,6 +29,7 @@ MODULES = {
     "kv_cache": "worker/distributed/kv_cache.py",            # PagedKVCache, KVCachePool, DistributedKVCacheManager
     "serialization": "common/serialization.py",              # TensorSerializer, StreamingTensorBuffer
     "data_structures": "common/data_structures.py",          # compute_prefix_hash and the record types
+    "batch_processor": "worker/batch_processor.py",          # ContinuousBatcher (the caller of engine.batch_inference)
 }
 
 

@@ -131,3 +131,36 @@ def test_serializer_bytes_reference_vs_product(ref):
         back_ref = rs.deserialize(*want)
         back = ps.deserialize(*got)
         assert back.dtype == back_ref.dtype and torch.equal(back.float().nan_to_num(), back_ref.float().nan_to_num())
+
+
+def test_reference_batcher_and_product_batcher_treat_an_engine_alike(ref):
+    """The reference's own ContinuousBatcher and the product's mirror of it, same fake engine, same requests: same
+    batches, same per-request results, same stats keys."""
+    import asyncio
+
+    from dgi_b200.worker import batch_processor as prod_bp
+
+    class Engine:
+        def __init__(self):
+            self.calls = []
+
+        def batch_inference(self, params_list):
+            self.calls.append(len(params_list))
+            return [ValueError("bad") if p.get("boom") else {"echo": p["x"]} for p in params_list]
+
+    async def drive(mod):
+        eng = Engine()
+        b = mod.ContinuousBatcher(eng, max_batch_size=3, max_wait_ms=20)
+        await b.start()
+        reqs = [{"x": i} for i in range(5)] + [{"x": 9, "boom": True}]
+        res = await asyncio.gather(*[b.submit(f"j{i}", r) for i, r in enumerate(reqs)], return_exceptions=True)
+        stats = b.get_stats()
+        await b.stop()
+        return eng.calls, [r if isinstance(r, dict) else type(r).__name__ for r in res], stats
+
+    calls_r, res_r, stats_r = asyncio.run(drive(ref["batch_processor"]))
+    calls_p, res_p, stats_p = asyncio.run(drive(prod_bp))
+    assert res_p == res_r == [{"echo": i} for i in range(5)] + ["ValueError"]
+    assert sum(calls_p) == sum(calls_r) == 6 and max(calls_p) <= 3 and max(calls_r) <= 3
+    assert set(stats_p) == set(stats_r)
+    assert stats_p["total_requests"] == stats_r["total_requests"] == 6
