@@ -13,7 +13,9 @@ bytecode; it is used by
   * ``bench.py``'s ``cpu_baseline`` / ``--impl reference`` legs — ``ModelShard.forward`` / ``get_logits`` of the
     reference itself drive the timed CPU path (``kind = "reference"``).
 
-Every module listed is free of package-relative imports (checked at survey time), so each loads on its own.
+Every module listed is free of package-relative imports, so each loads on its own; ``session`` imports
+``common.data_structures`` / ``common.serialization`` by absolute name, which ``ref_loader`` satisfies with the two
+bytecode modules of the same list.
 TEST INFRASTRUCTURE: nothing under ``distributed-gpu-inference_b200/`` may import this.
 """
 import os
@@ -30,6 +32,7 @@ MODULES = {
     "serialization": "common/serialization.py",              # TensorSerializer, StreamingTensorBuffer
     "data_structures": "common/data_structures.py",          # compute_prefix_hash and the record types
     "batch_processor": "worker/batch_processor.py",          # ContinuousBatcher (the caller of engine.batch_inference)
+    "session": "worker/distributed/session.py",              # DistributedInferenceSession.step, WorkerSession (a14)
 }
 
 

@@ -9,8 +9,47 @@ import importlib.util
 import os
 import sys
 
+import contextlib
+import types
+
 _DIR = os.path.join(os.path.dirname(os.path.abspath(__file__)), "_ref")
 _PREFIX = "_dgi_reference_"
+# absolute imports a module of the list performs -> the bytecode module of the same list that satisfies it
+_ABSOLUTE_IMPORTS = {"session": {"common.data_structures": "data_structures", "common.serialization": "serialization"}}
+
+
+@contextlib.contextmanager
+def _absolute_names(name: str):
+    """While ``name`` is executed, make the reference's own ``common.*`` modules importable under the names it uses;
+    whatever sat under those names before (nothing, in this repository) is put back afterwards."""
+    wanted = _ABSOLUTE_IMPORTS.get(name, {})
+    if not wanted:
+        yield
+        return
+    saved = {}
+
+    def put(key, value):
+        if key not in saved:
+            saved[key] = sys.modules.get(key)
+        sys.modules[key] = value
+
+    try:
+        for dotted, dep in wanted.items():
+            mod = load(dep)
+            if mod is None:
+                raise ImportError(f"oracle/_ref/{dep}.bin is missing")
+            pkg_name, attr = dotted.split(".")
+            if pkg_name not in saved:
+                put(pkg_name, types.ModuleType(pkg_name))  # a stand-in package for the duration of the import
+            setattr(sys.modules[pkg_name], attr, mod)
+            put(dotted, mod)
+        yield
+    finally:
+        for key, old in saved.items():
+            if old is None:
+                sys.modules.pop(key, None)
+            else:
+                sys.modules[key] = old
 
 
 def path_of(name: str) -> str:
@@ -32,14 +71,18 @@ def load(name: str):
     spec = importlib.util.spec_from_file_location(full, path, loader=loader)
     module = importlib.util.module_from_spec(spec)
     sys.modules[full] = module  # dataclasses look their module up while the body runs
+    path_before = list(sys.path)
     try:
-        loader.exec_module(module)
+        with _absolute_names(name):
+            loader.exec_module(module)
     except ImportError:  # bad magic number: bytecode of another interpreter version
         del sys.modules[full]
         return None
     except BaseException:
         del sys.modules[full]
         raise
+    finally:
+        sys.path[:] = path_before  # session.py prepends a directory of its own to sys.path when imported
     return module
 
 

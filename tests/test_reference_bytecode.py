@@ -164,3 +164,41 @@ def test_reference_batcher_and_product_batcher_treat_an_engine_alike(ref):
     assert sum(calls_p) == sum(calls_r) == 6 and max(calls_p) <= 3 and max(calls_r) <= 3
     assert set(stats_p) == set(stats_r)
     assert stats_p["total_requests"] == stats_r["total_requests"] == 6
+
+
+def test_reference_session_steps_over_the_product_hop(ref):
+    """The reference's own DistributedInferenceSession (bytecode) with its module-global ``WorkerSession`` swapped for
+    this package's — the seam the reference's tests use (tests/test_worker_distributed_inference_session.py:63) —
+    hops through ServicerTransport into the product's servicer (no shard: echo, reference grpc_server.py:359-361)."""
+    import asyncio
+
+    from dgi_b200.worker.distributed import session as prod_session
+    from dgi_b200.worker.distributed.servicer import InferenceServicer, ServicerTransport
+
+    rs, ds = ref["session"], ref["data_structures"]
+    mgr = prod_kv.DistributedKVCacheManager(num_layers=2, num_heads=2, head_dim=8, gpu_cache_blocks=8,
+                                            cpu_cache_gb=0.001, block_size=4, device="cpu", dtype=torch.float16)
+    sv = InferenceServicer("w-bytecode", None, mgr)
+    sv._device = lambda: "cpu"
+    prod_session.TRANSPORTS["w-bytecode"] = ServicerTransport(sv, max_length=32)
+    stock = rs.WorkerSession
+    rs.WorkerSession = prod_session.WorkerSession
+    try:
+        async def go():
+            route = [ds.WorkerInfo(worker_id="w-bytecode", state=ds.WorkerState.ONLINE)]
+            sess = rs.DistributedInferenceSession(ds.SessionConfig(model_name="m", max_length=32, max_retries=1), route)
+            await sess.setup()
+            x = torch.randn(1, 3, 8)
+            y = await sess.step(x)
+            z = await sess.step(x[:, :1])
+            stats, pos = sess.get_stats(), sess.position
+            await sess.close()
+            return x, y, z, stats, pos
+
+        x, y, z, stats, pos = asyncio.run(go())
+    finally:
+        rs.WorkerSession = stock
+        prod_session.TRANSPORTS.pop("w-bytecode", None)
+    assert torch.equal(x, y) and torch.equal(z, x[:, :1]) and pos == 4
+    assert stats["total_steps"] == 2 and stats["total_tokens"] == 4 and stats["retries"] == 0
+    assert sv.get_stats()["total_requests"] == 2 and not sv._sessions  # close() reached CloseSession

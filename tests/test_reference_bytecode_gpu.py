@@ -140,3 +140,57 @@ def test_the_references_own_model_shard_forward_runs_the_paged_layers(ref, golde
                             use_cuda_graph=graphs)
     got = eng.generate(prompts, n)
     assert got.tolist() == [row[:n] for row in g["tokens"]]
+
+
+def test_the_references_own_session_steps_through_the_paged_servicers(ref, golden):
+    """SURVEY §8b seam 1 + 3, literally: the reference's own ``DistributedInferenceSession.step`` loop
+    (worker/distributed/session.py:271-337, bytecode) with ``WorkerSession`` swapped the way its tests swap it, two
+    hops, each an ``InferenceServicer`` of this package over a layer-range shard and paged per-session KV: the golden
+    tokens of BASELINE config 1, positions and retries counted by the reference's code."""
+    from dgi_b200.worker.distributed import session as prod_session
+    from dgi_b200.worker.distributed.kv_cache import DistributedKVCacheManager
+    from dgi_b200.worker.distributed.servicer import InferenceServicer, ServicerTransport
+
+    rs, ds = ref["session"], ref["data_structures"]
+    g = golden("tiny_decode.json")
+    cfg = L.RefConfig(**g["config"])
+    sd = L.make_weights(cfg, seed=0)
+    ranges = [tuple(r) for r in g["shard_ranges"]]
+    shards = build_product_shards(cfg, sd, ranges, DEV, torch.float32)
+    route, svs = [], []
+    for i, (sh, (lo, hi)) in enumerate(zip(shards, ranges)):
+        mgr = DistributedKVCacheManager(num_layers=hi - lo, num_heads=cfg.num_key_value_heads, head_dim=cfg.head_dim,
+                                        gpu_cache_blocks=64, cpu_cache_gb=0.01, block_size=16, device=DEV,
+                                        dtype=torch.float32)
+        sv = InferenceServicer(f"bc-worker-{i}", sh, mgr, max_sessions=2)
+        sv.prefill_mode = "eager"
+        svs.append(sv)
+        prod_session.TRANSPORTS[f"bc-worker-{i}"] = ServicerTransport(sv, max_length=192)
+        route.append(ds.WorkerInfo(worker_id=f"bc-worker-{i}", state=ds.WorkerState.ONLINE))
+    prompts = torch.tensor(g["prompt_ids"]).to(DEV)
+    n_new = 20
+    stock = rs.WorkerSession
+    rs.WorkerSession = prod_session.WorkerSession
+    try:
+        async def go():
+            sess = rs.DistributedInferenceSession(ds.SessionConfig(model_name="tiny", max_length=192, max_retries=1), route)
+            await sess.setup()
+            h = await sess.step(prompts)
+            toks = []
+            for _ in range(n_new):
+                nxt = shards[-1].get_logits(h[:, -1:, :])[:, 0, :].argmax(-1)
+                toks.append(nxt)
+                if len(toks) < n_new:
+                    h = await sess.step(nxt[:, None])
+            pos, stats = sess.position, sess.get_stats()
+            await sess.close()
+            return torch.stack(toks, dim=1), pos, stats
+
+        toks, pos, stats = asyncio.run(go())
+    finally:
+        rs.WorkerSession = stock
+        for i in range(len(route)):
+            prod_session.TRANSPORTS.pop(f"bc-worker-{i}", None)
+    assert toks.tolist() == [row[:n_new] for row in g["tokens"]]
+    assert pos == 128 + n_new - 1 and stats["total_steps"] == n_new and stats["retries"] == 0
+    assert all(not sv._sessions for sv in svs)
