@@ -33,6 +33,7 @@ MODULES = {
     "data_structures": "common/data_structures.py",          # compute_prefix_hash and the record types
     "batch_processor": "worker/batch_processor.py",          # ContinuousBatcher (the caller of engine.batch_inference)
     "session": "worker/distributed/session.py",              # DistributedInferenceSession.step, WorkerSession (a14)
+    "pd_scheduler": "server/app/services/pd_scheduler.py",   # PrefillDecodeScheduler, KVCacheMigrator (f1)
 }
 
 

@@ -43,19 +43,17 @@ def test_migrate_updates_index_dedups_and_reports_failure():
 
 
 def _reference_pd_scheduler():
-    """The reference's own scheduler module, loaded the way its test does (tests/test_server_pd_scheduler.py:26-32).
-    Only the build container has /root/reference; elsewhere the test is skipped."""
-    import importlib.util
+    """The reference's own scheduler module: bytecode compiled from server/app/services/pd_scheduler.py by
+    oracle/build_ref.py (it travels to the GPU box; built here on first use when /root/reference is mounted)."""
     import os
-    import sys
 
-    path = "/root/reference/server/app/services/pd_scheduler.py"
-    if not os.path.exists(path):
-        pytest.skip("the reference checkout is not mounted here")
-    spec = importlib.util.spec_from_file_location("pd_scheduler", path)
-    module = importlib.util.module_from_spec(spec)
-    sys.modules["pd_scheduler"] = module
-    spec.loader.exec_module(module)
+    from oracle import build_ref, ref_loader
+
+    if not os.path.exists(ref_loader.path_of("pd_scheduler")) and os.path.isdir(build_ref.REF_ROOT):
+        build_ref.build()
+    module = ref_loader.load("pd_scheduler")
+    if module is None:
+        pytest.skip("oracle/_ref is not built here (needs /root/reference once: python oracle/build_ref.py)")
     return module
 
 
@@ -144,3 +142,22 @@ def test_migration_moves_the_blocks_bit_exactly_on_one_gpu():
     s, d = torch.tensor(seq.tables["prefill0"], device=dev), torch.tensor(seq.tables["decode0"], device=dev)
     assert torch.equal(pools["decode0"].backing[:, :, d], pools["prefill0"].backing[:, :, s])
     assert mig.stats["bytes_moved"] == 3 * 2 * 7 * 8 * 16 * 128 * 2
+
+
+def test_index_only_migration_matches_the_references_own_migrator():
+    """The reference's KVCacheMigrator (its ``_do_migrate`` sleeps 50 ms and moves nothing,
+    server/app/services/pd_scheduler.py:452-479) and this package's, with no mover, on the same scheduler object:
+    same return values, same ``_kv_cache_locations``, same ``migrations`` count, concurrent requests de-duplicated."""
+    ref = _reference_pd_scheduler()
+
+    async def drive(migrator_cls):
+        sch = ref.PrefillDecodeScheduler(enable_migration=True)
+        sch._kv_cache_locations["k1"] = "w0"
+        m = migrator_cls(sch)
+        r = await asyncio.gather(m.migrate("k1", "w0", "w1"), m.migrate("k1", "w0", "w1"))
+        r.append(await m.migrate("k1", "w1", "w2"))
+        return r, dict(sch._kv_cache_locations), sch.get_stats()["migrations"]
+
+    theirs = asyncio.run(drive(ref.KVCacheMigrator))
+    ours = asyncio.run(drive(KVCacheMigrator))
+    assert ours == theirs and ours[1] == {"k1": "w2"}
