@@ -306,8 +306,10 @@ def fill_pools_synthetic(engine, batch, ctx_len):
 def cpu_handoff_reference(layers: int = 2, n_blocks: int = 256):
     """The reference's own hand-off (serialize → bytes → deserialize → copy into a pool slot, per block per layer,
     on the host; oracle/handoff_ref.py) timed on a bounded sample of the 512 MiB sequence: ``layers`` of its 32."""
-    from oracle import handoff_ref as H
+    from oracle import handoff_ref as H, ref_loader
 
+    ref_ser = ref_loader.load("serialization")  # the reference's own TensorSerializer when oracle/_ref is built
+    ser = ref_ser.TensorSerializer if ref_ser is not None else None
     Hkv, D, bs, max_blocks = 8, 128, 16, n_blocks + 16
     gen = torch.Generator().manual_seed(7)
     src_k = [torch.randn(max_blocks, Hkv, bs, D, generator=gen).to(torch.bfloat16) for _ in range(layers)]
@@ -316,9 +318,9 @@ def cpu_handoff_reference(layers: int = 2, n_blocks: int = 256):
     dst_v = [torch.zeros_like(t) for t in src_v]
     st = torch.randperm(max_blocks, generator=gen)[:n_blocks].tolist()
     dt = torch.randperm(max_blocks, generator=gen)[:n_blocks].tolist()
-    H.handoff_sequence(src_k[:1], src_v[:1], st[:16], dst_k[:1], dst_v[:1], dt[:16])  # warm-up
+    H.handoff_sequence(src_k[:1], src_v[:1], st[:16], dst_k[:1], dst_v[:1], dt[:16], serializer=ser)  # warm-up
     t0 = time.perf_counter()
-    moved = H.handoff_sequence(src_k, src_v, st, dst_k, dst_v, dt)
+    moved = H.handoff_sequence(src_k, src_v, st, dst_k, dst_v, dt, serializer=ser)
     sec = time.perf_counter() - t0
     # the device ops' own definition on the host: index_select (pack) and index_copy_ (unpack), oracle/paged_ref.py
     from oracle import paged_ref as R
@@ -331,7 +333,7 @@ def cpu_handoff_reference(layers: int = 2, n_blocks: int = 256):
         R.unpack_ref(pk, k, v, tbl)
     t2 = time.perf_counter()
     nbytes = 2 * sum(p.numel() * p.element_size() for p in packed)  # read + written, as for the GPU figures
-    return {"GBps": moved / sec / 1e9, "kind": "port", "cores": 1,
+    return {"GBps": moved / sec / 1e9, "kind": "reference" if ser is not None else "port", "cores": 1,
             "cpu_pack_GBps": nbytes / (t1 - t0) / 1e9, "cpu_unpack_GBps": nbytes / (t2 - t1) / 1e9,
             "cpu_pack_threads": torch.get_num_threads(),
             "sample": f"{layers} of 32 layers x {n_blocks} blocks x 64 KiB = {moved / 2**20:.0f} MiB on the wire "

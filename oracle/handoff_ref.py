@@ -41,15 +41,19 @@ def from_wire(data: bytes, shape: Tuple[int, ...], dtype_str: str) -> torch.Tens
 
 
 def handoff_sequence(src_k: List[torch.Tensor], src_v: List[torch.Tensor], src_table: List[int],
-                     dst_k: List[torch.Tensor], dst_v: List[torch.Tensor], dst_table: List[int]) -> int:
+                     dst_k: List[torch.Tensor], dst_v: List[torch.Tensor], dst_table: List[int], serializer=None) -> int:
     """Move one sequence's blocks, layer by layer and block by block, the way the reference does; pools are per
-    layer ``[max_blocks, heads, block_size, head_dim]``.  Returns the bytes that crossed the wire."""
+    layer ``[max_blocks, heads, block_size, head_dim]``.  Returns the bytes that crossed the wire.
+    ``serializer``: the reference's own ``TensorSerializer`` class (oracle/_ref bytecode) to do the two conversions
+    with instead of the restatements above."""
+    to_wire = serializer.serialize if serializer is not None else wire_bytes
+    back = serializer.deserialize if serializer is not None else from_wire
     total = 0
     for kp, vp, dk, dv in zip(src_k, src_v, dst_k, dst_v):
         for s, d in zip(src_table, dst_table):
-            kb, shape, name = wire_bytes(kp[s])
-            vb, _, _ = wire_bytes(vp[s])
-            dk[d].copy_(from_wire(kb, shape, name))
-            dv[d].copy_(from_wire(vb, shape, name))
+            kb, shape, name = to_wire(kp[s])
+            vb, _, _ = to_wire(vp[s])
+            dk[d].copy_(back(kb, shape, name))
+            dv[d].copy_(back(vb, shape, name))
             total += len(kb) + len(vb)
     return total
