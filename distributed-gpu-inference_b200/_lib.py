@@ -77,6 +77,11 @@ SIGNATURES = {
     "b200_argmax_rows_keys": (c_int, [c_void_p, c_void_p, c_int64, c_int64, c_int64, c_int64, c_int, c_void_p]),
     "b200_argmax_keys_decode": (c_int, [c_void_p, c_void_p, c_int64, c_void_p]),
     "b200_silu_mul": (c_int, [c_void_p, c_void_p, c_void_p, c_int64, c_int, c_int64, c_int64, c_int, c_void_p]),
+    "b200_kv_gather_dense": (
+        c_int,
+        [c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_int, c_int, c_int, c_int, c_int, c_int, c_int64, c_int,
+         c_void_p],
+    ),
     "b200_kv_pack": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_int, c_int, c_int, c_int, c_int64, c_int, c_void_p]),
     "b200_kv_unpack": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_int, c_int, c_int, c_int, c_int64, c_int, c_void_p]),
     "b200_kv_pack_layers": (

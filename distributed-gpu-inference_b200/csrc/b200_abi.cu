@@ -336,6 +336,13 @@ int b200_rope_append_decode_attn_prefix(void* out, const void* q, int64_t q_row_
                            suffix_splits, workspace, workspace_bytes, dtype, flags, stream);
 }
 
+int b200_kv_gather_dense(void* k_out, void* v_out, const void* k_pool, const void* v_pool,
+                         const int32_t* block_tables, int max_blocks_per_seq, int B, int n_tokens, int Hkv, int D,
+                         int block_size, int64_t max_blocks, int dtype, void* stream) {
+  return kv_gather_dense(k_out, v_out, k_pool, v_pool, block_tables, max_blocks_per_seq, B, n_tokens, Hkv, D,
+                         block_size, max_blocks, dtype, static_cast<cudaStream_t>(stream));
+}
+
 int b200_kv_pack(void* packed, const void* k_pool, const void* v_pool, const int32_t* block_table, int n_blocks,
                  int Hkv, int D, int block_size, int64_t max_blocks, int dtype, void* stream) {
   return kv_pack(packed, k_pool, v_pool, block_table, n_blocks, Hkv, D, block_size, max_blocks, dtype,

@@ -52,6 +52,9 @@ int attn_combine(void* out, const float* ws_acc, const float* ws_ml, int rows, i
 int kv_append(const void* k_new, const void* v_new, int64_t k_row_stride, int64_t v_row_stride, void* k_pool,
               void* v_pool, const int64_t* slot_mapping, int n_tok, int Hkv, int D, int block_size,
               int64_t max_blocks, int dtype, cudaStream_t stream);
+int kv_gather_dense(void* k_out, void* v_out, const void* k_pool, const void* v_pool, const int32_t* tables,
+                    int table_stride, int B, int n_tokens, int Hkv, int D, int bs, int64_t max_blocks, int dtype,
+                    cudaStream_t s);
 int kv_pack(void* packed, const void* k_pool, const void* v_pool, const int32_t* table, int n_blocks, int Hkv, int D,
             int bs, int64_t max_blocks, int dtype, cudaStream_t s);
 int kv_unpack(void* k_pool, void* v_pool, const void* packed, const int32_t* table, int n_blocks, int Hkv, int D,

@@ -350,6 +350,69 @@ int kv_unpack_layers_wire(void* const* k_pools, void* const* v_pools, int n_laye
                         "b200_kv_unpack_layers_wire");
 }
 
+// ---------------------------------------------------------------------------------------------------------
+// gather to dense: the first n_tokens tokens of every sequence, read through its block-table row, laid out
+// [B, Hkv, n_tokens, D] — what a prompt pass that continues a cached prefix hands to the dense attention.
+// Work item = (sequence, table entry, K|V): Hkv runs of `rows x D` elements, each contiguous on both sides.
+// ---------------------------------------------------------------------------------------------------------
+template <int HU>
+__global__ void __launch_bounds__(256)
+kv_gather_dense_kernel(char* __restrict__ k_out, char* __restrict__ v_out, const char* __restrict__ k_pool,
+                       const char* __restrict__ v_pool, const int32_t* __restrict__ tables, int table_stride,
+                       int n_blk, int n_tokens, int Hkv, int block_size, int row_bytes, int64_t max_blocks) {
+  const int item = blockIdx.x;  // (b * n_blk + j) * 2 + kv
+  const bool is_v = item & 1;
+  const int bj = item >> 1;
+  const int j = bj % n_blk, b = bj / n_blk;
+  const int32_t slot = tables[static_cast<int64_t>(b) * table_stride + j];
+  if (slot < 0 || slot >= max_blocks) return;
+  const int rows = min(block_size, n_tokens - j * block_size);
+  const int vec_valid = rows * (row_bytes / 16);
+  const int64_t head_bytes = static_cast<int64_t>(block_size) * row_bytes;  // one head of one block in the pool
+  const int64_t seq_bytes = static_cast<int64_t>(n_tokens) * row_bytes;      // one head of one sequence in the output
+  const char* src = (is_v ? v_pool : k_pool) + static_cast<int64_t>(slot) * Hkv * head_bytes;
+  char* dst = (is_v ? v_out : k_out) + static_cast<int64_t>(b) * Hkv * seq_bytes +
+              static_cast<int64_t>(j) * block_size * row_bytes;
+  for (int h0 = 0; h0 < Hkv; h0 += HU) {
+    for (int x = threadIdx.x; x < vec_valid; x += 256) {
+      int4 val[HU];
+#pragma unroll
+      for (int u = 0; u < HU; ++u)
+        if (h0 + u < Hkv) val[u] = ld_stream16(src + (h0 + u) * head_bytes + static_cast<int64_t>(x) * 16);
+#pragma unroll
+      for (int u = 0; u < HU; ++u)
+        if (h0 + u < Hkv) st_stream16(dst + (h0 + u) * seq_bytes + static_cast<int64_t>(x) * 16, val[u]);
+    }
+  }
+}
+
+int kv_gather_dense(void* k_out, void* v_out, const void* k_pool, const void* v_pool, const int32_t* tables,
+                    int table_stride, int B, int n_tokens, int Hkv, int D, int bs, int64_t max_blocks, int dtype,
+                    cudaStream_t s) {
+  const char* name = "b200_kv_gather_dense";
+  const int es = dtype_size(dtype);
+  if (es == 0) return fail(B200_EINVAL, "%s: unsupported dtype %d", name, dtype);
+  if (B < 0 || n_tokens < 0 || Hkv <= 0 || D <= 0 || bs <= 0 || max_blocks <= 0)
+    return fail(B200_EINVAL, "%s: bad sizes", name);
+  if (B == 0 || n_tokens == 0) return 0;
+  if (!k_out || !v_out || !k_pool || !v_pool || !tables) return fail(B200_EINVAL, "%s: null pointer", name);
+  const int n_blk = (n_tokens + bs - 1) / bs;
+  if (table_stride < n_blk) return fail(B200_ESHAPE, "%s: %d tokens need %d table entries per row, rows hold %d", name,
+                                        n_tokens, n_blk, table_stride);
+  const int64_t row_bytes = static_cast<int64_t>(D) * es;
+  if (row_bytes % 16 != 0 || row_bytes > INT32_MAX || !aligned16(k_out) || !aligned16(v_out) || !aligned16(k_pool) ||
+      !aligned16(v_pool))
+    return fail(B200_ESHAPE, "%s: rows of %lld bytes / pointers must be 16-byte aligned", name,
+                static_cast<long long>(row_bytes));
+  const int64_t grid = 2ll * B * n_blk;
+  if (grid > INT32_MAX) return fail(B200_ESHAPE, "%s: too many blocks", name);
+  kv_gather_dense_kernel<8><<<static_cast<unsigned>(grid), 256, 0, s>>>(
+      static_cast<char*>(k_out), static_cast<char*>(v_out), static_cast<const char*>(k_pool),
+      static_cast<const char*>(v_pool), tables, table_stride, n_blk, n_tokens, Hkv, bs, static_cast<int>(row_bytes),
+      max_blocks);
+  return check_launch(name);
+}
+
 int kv_pack(void* packed, const void* k_pool, const void* v_pool, const int32_t* table, int n_blocks, int Hkv, int D,
             int bs, int64_t max_blocks, int dtype, cudaStream_t s) {
   PoolSet p{nullptr, nullptr, k_pool, v_pool};

@@ -498,6 +498,27 @@ def _check_table(block_table: torch.Tensor) -> int:
     return block_table.shape[0]
 
 
+def kv_gather_dense(k_pool: torch.Tensor, v_pool: torch.Tensor, block_tables: torch.Tensor, n_tokens: int):
+    """The first ``n_tokens`` tokens of every row of ``block_tables`` ``[B, >= ceil(n_tokens / bs)]`` as dense
+    ``(k, v)``, each ``[B, Hkv, n_tokens, D]``, in one launch (bit-exact copy out of the pools)."""
+    _need_cuda(k_pool, v_pool, block_tables)
+    max_blocks, Hkv, bs, D = _pool_dims(k_pool)
+    _pool_dims(v_pool)
+    if block_tables.dtype != torch.int32 or block_tables.dim() != 2 or (block_tables.shape[1] > 1 and block_tables.stride(1) != 1):
+        raise ValueError("block_tables must be int32 [B, max_blocks_per_seq] with contiguous rows")
+    B = block_tables.shape[0]
+    if n_tokens < 0 or (n_tokens + bs - 1) // bs > block_tables.shape[1]:
+        raise ValueError(f"{n_tokens} tokens do not fit rows of {block_tables.shape[1]} blocks")
+    k_out = torch.empty((B, Hkv, n_tokens, D), dtype=k_pool.dtype, device=k_pool.device)
+    v_out = torch.empty_like(k_out)
+    stride = block_tables.stride(0) if B > 1 else block_tables.shape[1]
+    rc = _lib.load().b200_kv_gather_dense(k_out.data_ptr(), v_out.data_ptr(), k_pool.data_ptr(), v_pool.data_ptr(),
+                                         block_tables.data_ptr(), stride, B, n_tokens, Hkv, D, bs, max_blocks,
+                                         _dtype_id(k_pool), _stream())
+    _lib.check(rc, "b200_kv_gather_dense")
+    return k_out, v_out
+
+
 def kv_pack(k_pool: torch.Tensor, v_pool: torch.Tensor, block_table: torch.Tensor,
             out: Optional[torch.Tensor] = None) -> torch.Tensor:
     """Gather one layer's blocks: returns ``[2, n_blocks, Hkv, bs, D]`` (K blocks, then V blocks)."""

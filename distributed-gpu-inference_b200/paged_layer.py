@@ -332,7 +332,7 @@ class PagedLlamaDecoderLayer(nn.Module):
                                rotate_k_in_place=True)
             if st.past_len > 0:
                 # prompt pass that continues a cached prefix: the new tokens also attend to the `past_len` tokens
-                # already sitting in the (shared) blocks, read back densely through the block table
+                # already sitting in the (shared) blocks; everything is read back densely through the block table
                 k, v = self._with_cached_prefix(k, v, past_key_value, st)
             attn = self._prefill_attention(q, k, v, attention_mask, st.prefill_mode)
 
@@ -356,17 +356,13 @@ class PagedLlamaDecoderLayer(nn.Module):
         return h, (past_key_value if use_cache else None)
 
     def _with_cached_prefix(self, k, v, handle: PagedLayerKV, st: PagedBatchState):
-        """Prepend the first ``st.past_len`` cached tokens (gathered through the block table) to k and v."""
-        B = k.shape[0]
-        bs = handle.k_pool.shape[2]
-        n_blk = (st.past_len + bs - 1) // bs
-        idx = st.block_tables[:, :n_blk].reshape(-1).to(torch.int64)
-
-        def dense(pool):  # [B * n_blk, Hkv, bs, D] -> [B, past_len, Hkv, D]
-            x = pool.index_select(0, idx).view(B, n_blk, pool.shape[1], bs, pool.shape[3])
-            return x.permute(0, 1, 3, 2, 4).reshape(B, n_blk * bs, pool.shape[1], pool.shape[3])[:, :st.past_len]
-
-        return torch.cat((dense(handle.k_pool), k), dim=1), torch.cat((dense(handle.v_pool), v), dim=1)
+        """Dense k and v ``[B, past_len + T, Hkv, D]`` for a prompt pass that continues ``st.past_len`` cached tokens.
+        The T new tokens were appended to the pools a moment ago, so prefix and new tokens come out of the blocks
+        together: one launch, one pass (b200_kv_gather_dense writes ``[B, Hkv, S, D]``, the layout the attention
+        wants; the returned tensors are transposed views of it)."""
+        B, T = k.shape[0], k.shape[1]
+        kd, vd = ops.kv_gather_dense(handle.k_pool, handle.v_pool, st.block_tables[:B], st.past_len + T)
+        return kd.transpose(1, 2), vd.transpose(1, 2)
 
     def _prefill_attention(self, q, k, v, attention_mask, mode: str) -> torch.Tensor:
         """Causal attention of the T new tokens over the S >= T tokens in k / v (the last T of which are the new

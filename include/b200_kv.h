@@ -251,6 +251,19 @@ int b200_argmax_rows_keys(int64_t* keys, const void* x, int64_t rows, int64_t co
 int b200_argmax_keys_decode(int64_t* out, const int64_t* keys, int64_t rows, void* stream);
 
 /*
+ * Gather to dense: the first n_tokens tokens of B sequences, read through their block-table rows, written as
+ *   k_out, v_out : [B, Hkv, n_tokens, D]
+ * in ONE pass.  Replaces what a dense-cache layer does when a prompt continues after cached tokens — the
+ * torch.cat((past_k, k), dim=2) of the HF layer ModelShard.forward calls (worker/distributed/model_shard.py:209-215) —
+ * for paged pools: the prompt pass appends its new tokens first (b200_rope_kv_append_prompt), then gathers prefix and
+ * new tokens together for the dense causal attention.  Bit-exact copy.
+ *   block_tables : int32[B, max_blocks_per_seq], the first ceil(n_tokens / block_size) entries of each row are read
+ */
+int b200_kv_gather_dense(void* k_out, void* v_out, const void* k_pool, const void* v_pool,
+                         const int32_t* block_tables, int max_blocks_per_seq, int B, int n_tokens, int Hkv, int D,
+                         int block_size, int64_t max_blocks, int dtype, void* stream);
+
+/*
  * KV block pack / unpack for the prefill -> decode hand-off.  Replaces the per-block, per-layer
  * TensorSerializer.serialize -> wire -> deserialize -> block.keys.copy_ round trip of
  * InferenceServicer.TransferKVCache (worker/distributed/grpc_server.py:190-235) and

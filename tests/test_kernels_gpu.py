@@ -96,6 +96,32 @@ def test_pack_unpack_bit_exact(dtype, Hkv, D, bs, n):
     assert torch.equal(k2.index_select(0, dst.long()), k_pool.index_select(0, table.long()))
 
 
+@pytest.mark.parametrize("dtype", [torch.bfloat16, torch.float16, torch.float32])
+@pytest.mark.parametrize("Hkv,D,bs,B,n_tokens", [(8, 128, 16, 3, 200), (2, 64, 16, 4, 129), (1, 32, 4, 1, 3),
+                                                 (11, 64, 16, 2, 16), (8, 128, 16, 2, 4096)])
+def test_gather_dense_bit_exact(dtype, Hkv, D, bs, B, n_tokens):
+    """b200_kv_gather_dense == the dense (k, v) of oracle/paged_ref.gather_dense for every row of the table,
+    including a partly filled last block and rows that are a strided view of a wider table."""
+    n_blk = (n_tokens + bs - 1) // bs
+    max_blocks = B * n_blk + 5
+    k_pool, v_pool = _pools(max_blocks, Hkv, bs, D, dtype)
+    perm = torch.randperm(max_blocks, generator=torch.Generator().manual_seed(9))[:B * n_blk]
+    wide = torch.full((B, n_blk + 7), -1, dtype=torch.int32)  # entries past n_blk must never be read
+    wide[:, :n_blk] = perm.view(B, n_blk).to(torch.int32)
+    wide = wide.to(DEV)
+    for tables in (wide, wide[:, :n_blk]):
+        kd, vd = ops.kv_gather_dense(k_pool, v_pool, tables, n_tokens)
+        assert kd.shape == (B, Hkv, n_tokens, D) and kd.is_contiguous()
+        for b in range(B):
+            want_k = R.gather_dense(k_pool, wide[b, :n_blk], n_tokens)  # [Hkv, n_tokens, D]
+            want_v = R.gather_dense(v_pool, wide[b, :n_blk], n_tokens)
+            assert torch.equal(_bits(kd[b]), _bits(want_k)) and torch.equal(_bits(vd[b]), _bits(want_v))
+    with pytest.raises(ValueError):
+        ops.kv_gather_dense(k_pool, v_pool, wide[:, :max(n_blk - 1, 0)], n_tokens)
+    k0, v0 = ops.kv_gather_dense(k_pool, v_pool, wide, 0)
+    assert k0.shape == (B, Hkv, 0, D) and v0.numel() == 0
+
+
 def test_pack_empty_table():
     k_pool, v_pool = _pools(4, 2, 16, 64, torch.bfloat16)
     out = ops.kv_pack(k_pool, v_pool, torch.zeros((0,), dtype=torch.int32, device=DEV))
