@@ -1,6 +1,7 @@
 #!/usr/bin/env python
 """Randomised bit-exact cross-check of the KV data-movement kernels against torch indexing (the oracle's definitions):
-append, RoPE + append (decode and prompt forms), pack / unpack (one layer and all layers), block move, wire pack / unpack.
+append, RoPE + append (decode and prompt forms), pack / unpack (one layer and all layers), gather to dense, block move,
+wire pack / unpack.
 Odd shapes on purpose (head_dim 16..256 incl. non-multiples of 64, block sizes 4..32, any head count, three dtypes,
 skipped slots, strided source rows).   usage: python tools/fuzz_kv_ops.py [--cases N] [--seed S]
 """
@@ -35,7 +36,7 @@ def main():
     ap.add_argument("--seed", type=int, default=0)
     a = ap.parse_args()
     rng = random.Random(a.seed)
-    counts = {"append": 0, "rope": 0, "pack": 0, "layers": 0, "move": 0, "wire": 0}
+    counts = {"append": 0, "rope": 0, "pack": 0, "gather": 0, "layers": 0, "move": 0, "wire": 0}
     for case in range(a.cases):
         dtype = rng.choice([torch.bfloat16, torch.float16, torch.float32])
         D = rng.choice([16, 32, 64, 80, 96, 128, 256])
@@ -100,6 +101,17 @@ def main():
         R.unpack_ref(packed, rk, rv, dst)
         assert torch.equal(bits(dk), bits(rk)) and torch.equal(bits(dv), bits(rv)), f"{tag}: unpack"
         counts["pack"] += 1
+
+        # gather to dense through a table with several rows (prompt pass continuing cached tokens)
+        rows_b = rng.randint(1, 3)
+        per_row = max(1, min(max_blocks // rows_b, rng.randint(1, 12)))
+        n_dense = rng.randint(1, per_row * bs)
+        tab2 = torch.randperm(max_blocks, generator=g, device=DEV)[:rows_b * per_row].to(torch.int32).view(rows_b, per_row)
+        kd, vd = ops.kv_gather_dense(backing[0, 0], backing[0, 1], tab2, n_dense)
+        for b in range(rows_b):
+            assert torch.equal(bits(kd[b]), bits(R.gather_dense(backing[0, 0], tab2[b], n_dense))), f"{tag}: gather k"
+            assert torch.equal(bits(vd[b]), bits(R.gather_dense(backing[0, 1], tab2[b], n_dense))), f"{tag}: gather v"
+        counts["gather"] += 1
 
         # all layers in one launch, and the block move
         shape = (max_blocks, Hkv, bs, D)
