@@ -16,6 +16,11 @@ What is different, and why:
   (the CUDA kernels behind ``PagedLlamaDecoderLayer``), and ``CloseSession`` frees the blocks (the reference's
   ``TODO``, :277-280).  A repeated call for a position that was already served (the client's retry loop,
   worker/distributed/session.py:303-329) overwrites the same slots, so retries are idempotent.
+* A one-token call replays a CUDA graph of the shard's decode step (``decode_graphs``, on by default): the session's
+  first such call builds a ``PagedDecodeEngine`` that borrows the session's blocks and captures the step; later calls
+  copy the input into the graph's buffer, set the position the request names and replay.  Measured on B200 (8B shape,
+  32 layers, batch 64, context 2k, profiles/r02_servicer_bench.json): 6.40 ms per call against 8.37 ms with eager
+  launches and 6.38 ms for the bare graph.  Multi-token (prompt) calls launch eagerly with one RoPE table per call.
 * ``HealthCheck`` and ``_get_cache_capacity`` use the pool's real block size and free-block count instead of the
   hard-coded 16 and a stats key that does not exist (:311,394); ``total_tokens`` is counted (:61), so
   ``throughput_tokens_per_sec`` is live.
@@ -37,7 +42,7 @@ from typing import Any, AsyncIterator, Dict, List, Optional
 import torch
 
 from ...common.serialization import TensorSerializer
-from ...paged_layer import PagedBatchState, PagedLayerKV
+from ...paged_layer import PagedBatchState, PagedLayerKV, rope_tables
 from .kv_cache import DistributedKVCacheManager, KVCachePool
 
 logger = logging.getLogger(__name__)
@@ -107,6 +112,9 @@ class InferenceServicer:
         self._stats = {"total_requests": 0, "total_tokens": 0, "total_latency_ms": 0, "errors": 0}
         # attention recipe of multi-token (prompt) calls: "sdpa", or "eager" = the reference layer's exact O(T^2) recipe
         self.prefill_mode = "sdpa"
+        # one-token calls replay a CUDA graph of the shard's decode step, captured per session on its first such call
+        # (the ~290 launches of a 32-layer step cost more on the host than on the GPU); False: eager launches
+        self.decode_graphs = True
 
     # ---- helpers ---------------------------------------------------------------------------------------------
     def _device(self) -> str:
@@ -138,9 +146,26 @@ class InferenceServicer:
         return self._sessions[session_id]
 
     def _release_kv(self, session: Dict[str, Any]) -> None:
+        eng = session.pop("_engine", None)
+        if eng is not None:
+            eng.release()  # the blocks are the session's: dropped, not freed
         kv = session.pop("_kv", None)
         if kv is not None:
             kv.free()
+
+    def _decode_engine(self, session: Dict[str, Any], kv: _SessionKV, position: int):
+        """The session's decode-step graph: a ``PagedDecodeEngine`` over this shard that borrows the session's blocks
+        (``adopt_sequences``) and stops at the shard's output — hidden states, or the normed rows on the last shard,
+        which is what ``ModelShard.forward`` returns."""
+        eng = session.get("_engine")
+        if eng is None:
+            from ...engine import PagedDecodeEngine
+
+            eng = PagedDecodeEngine([self.model_shard], kv.batch, kv.max_length, block_size=kv.pool.block_size,
+                                    kv_pools=[kv.pool], external_head=True)
+            eng.adopt_sequences([[per_layer] for per_layer in kv.blocks], [position] * kv.batch, table_rows=kv.tables)
+            session["_engine"] = eng
+        return eng
 
     def _session_kv(self, session: Dict[str, Any], batch: int, need_len: int) -> _SessionKV:
         kv: Optional[_SessionKV] = session.get("_kv")
@@ -179,6 +204,17 @@ class InferenceServicer:
         kv = self._session_kv(session, B, position + T)
         pool = kv.pool
         bs = pool.block_size
+        keys = list(kv_cache_keys) if kv_cache_keys else [f"session:{session['session_id']}"]
+        if T == 1 and self.decode_graphs and hidden_states.is_cuda and hasattr(self.model_shard, "layers"):
+            eng = self._decode_engine(session, kv, position)
+            # the step runs at the position the request names (a retry repeats one, a hand-off may have moved it)
+            eng.context_lens[:B].fill_(position)
+            (eng.ids_buf if eng.is_first else eng.h_in)[:B].copy_(hidden_states)
+            eng.stage_step()
+            output = (eng.hn_out[:B].unsqueeze(1) if eng.is_last else eng.h_out[:B]).clone()
+            session["position"] = max(held, position + 1)
+            self._stats["total_tokens"] += B
+            return output, keys
         t = torch.arange(position, position + T, device=dev)
         slots = kv.tables.to(torch.int64)[:, t // bs] * bs + (t % bs)[None, :]
         state = PagedBatchState(
@@ -192,11 +228,15 @@ class InferenceServicer:
         handles = [PagedLayerKV(pool.layer(li).key_pool, pool.layer(li).value_pool, state)
                    for li in range(self.model_shard.get_layer_count())]
         position_ids = t[None, :].expand(B, T)  # reference :365-369: arange(position, position + T)
+        layers = getattr(self.model_shard, "layers", None)
+        layer0 = layers[0] if layers is not None and len(layers) else None
+        if getattr(layer0, "inv_freq", None) is not None:  # RoPE tables once per call, not once per layer
+            state.cos, state.sin = rope_tables(position_ids, layer0.inv_freq.to(dev), getattr(self.model_shard, "dtype", None)
+                                               or hidden_states.dtype, float(getattr(layer0, "rope_attention_scaling", 1.0)))
         output, _ = self.model_shard.forward(hidden_states, position_ids=position_ids, past_key_values=handles,
                                              use_cache=True)
         session["position"] = max(held, position + T)
         self._stats["total_tokens"] += B * T
-        keys = list(kv_cache_keys) if kv_cache_keys else [f"session:{session['session_id']}"]
         return output, keys
 
     async def _forward(self, session: Dict[str, Any], hidden_states: torch.Tensor, position: int,

@@ -21,7 +21,7 @@ pytestmark = pytest.mark.gpu
 DEV = "cuda:0"
 
 
-def _servicers(golden, dtype=torch.float32, blocks=64, wire=(False, False)):
+def _servicers(golden, dtype=torch.float32, blocks=64, wire=(False, False), decode_graphs=True):
     g = golden("tiny_decode.json")
     cfg = L.RefConfig(**g["config"])
     sd = L.make_weights(cfg, seed=0)
@@ -33,6 +33,7 @@ def _servicers(golden, dtype=torch.float32, blocks=64, wire=(False, False)):
                                         gpu_cache_blocks=blocks, cpu_cache_gb=0.01, block_size=16, device=DEV, dtype=dtype)
         sv = InferenceServicer(f"worker-{i}", sh, mgr, max_sessions=4)  # constructor injection, reference :43-53
         sv.prefill_mode = "eager"
+        sv.decode_graphs = decode_graphs  # one-token calls: the session's CUDA graph, or eager launches
         svs.append(sv)
         S.TRANSPORTS[f"worker-{i}"] = ServicerTransport(sv, max_length=192, wire=wire[i])
         route.append(WorkerInfo(worker_id=f"worker-{i}", state=WorkerState.ONLINE))
@@ -50,9 +51,9 @@ async def _decode(session, shards, prompts, n_new):
     return torch.stack(toks, dim=1)
 
 
-@pytest.mark.parametrize("wire", [(False, False), (True, True)])
-def test_session_step_through_servicers_reproduces_the_golden_tokens(golden, wire):
-    g, cfg, shards, svs, route = _servicers(golden, wire=wire)
+@pytest.mark.parametrize("wire,graphs", [((False, False), True), ((True, True), True), ((False, True), False)])
+def test_session_step_through_servicers_reproduces_the_golden_tokens(golden, wire, graphs):
+    g, cfg, shards, svs, route = _servicers(golden, wire=wire, decode_graphs=graphs)
     prompts = torch.tensor(g["prompt_ids"]).to(DEV)
 
     async def go():
