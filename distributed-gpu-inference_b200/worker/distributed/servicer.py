@@ -19,8 +19,8 @@ What is different, and why:
 * A one-token call replays a CUDA graph of the shard's decode step (``decode_graphs``, on by default): the session's
   first such call builds a ``PagedDecodeEngine`` that borrows the session's blocks and captures the step; later calls
   copy the input into the graph's buffer, set the position the request names and replay.  Measured on B200 (8B shape,
-  32 layers, batch 64, context 2k, profiles/r02_servicer_bench.json): 6.40 ms per call against 8.37 ms with eager
-  launches and 6.38 ms for the bare graph.  Multi-token (prompt) calls launch eagerly with one RoPE table per call.
+  32 layers, batch 64, context 2k, profiles/r02_servicer_bench.json): 6.44 ms per call (5.58 ms with
+  ``fuse_projections``) against 7.97 ms with eager launches and 6.43 ms for the bare graph.  Multi-token (prompt) calls launch eagerly with one RoPE table per call.
 * ``HealthCheck`` and ``_get_cache_capacity`` use the pool's real block size and free-block count instead of the
   hard-coded 16 and a stats key that does not exist (:311,394); ``total_tokens`` is counted (:61), so
   ``throughput_tokens_per_sec`` is live.
@@ -115,6 +115,10 @@ class InferenceServicer:
         # one-token calls replay a CUDA graph of the shard's decode step, captured per session on its first such call
         # (the ~290 launches of a 32-layer step cost more on the host than on the GPU); False: eager launches
         self.decode_graphs = True
+        # True: the decode engine lays q|k|v and gate|up out as one K-major GEMM each and fuses the residual adds into
+        # the norms (PagedDecodeEngine(fuse_projections=True): same dot products, same roundings, fewer launches);
+        # it rewrites the shard's weight storage in place, so it is the owner's choice
+        self.fuse_projections = False
 
     # ---- helpers ---------------------------------------------------------------------------------------------
     def _device(self) -> str:
@@ -162,7 +166,7 @@ class InferenceServicer:
             from ...engine import PagedDecodeEngine
 
             eng = PagedDecodeEngine([self.model_shard], kv.batch, kv.max_length, block_size=kv.pool.block_size,
-                                    kv_pools=[kv.pool], external_head=True)
+                                    kv_pools=[kv.pool], external_head=True, fuse_projections=self.fuse_projections)
             eng.adopt_sequences([[per_layer] for per_layer in kv.blocks], [position] * kv.batch, table_rows=kv.tables)
             session["_engine"] = eng
         return eng

@@ -21,7 +21,7 @@ pytestmark = pytest.mark.gpu
 DEV = "cuda:0"
 
 
-def _servicers(golden, dtype=torch.float32, blocks=64, wire=(False, False), decode_graphs=True):
+def _servicers(golden, dtype=torch.float32, blocks=64, wire=(False, False), decode_graphs=True, fuse=False):
     g = golden("tiny_decode.json")
     cfg = L.RefConfig(**g["config"])
     sd = L.make_weights(cfg, seed=0)
@@ -34,6 +34,7 @@ def _servicers(golden, dtype=torch.float32, blocks=64, wire=(False, False), deco
         sv = InferenceServicer(f"worker-{i}", sh, mgr, max_sessions=4)  # constructor injection, reference :43-53
         sv.prefill_mode = "eager"
         sv.decode_graphs = decode_graphs  # one-token calls: the session's CUDA graph, or eager launches
+        sv.fuse_projections = fuse
         svs.append(sv)
         S.TRANSPORTS[f"worker-{i}"] = ServicerTransport(sv, max_length=192, wire=wire[i])
         route.append(WorkerInfo(worker_id=f"worker-{i}", state=WorkerState.ONLINE))
@@ -51,9 +52,10 @@ async def _decode(session, shards, prompts, n_new):
     return torch.stack(toks, dim=1)
 
 
-@pytest.mark.parametrize("wire,graphs", [((False, False), True), ((True, True), True), ((False, True), False)])
-def test_session_step_through_servicers_reproduces_the_golden_tokens(golden, wire, graphs):
-    g, cfg, shards, svs, route = _servicers(golden, wire=wire, decode_graphs=graphs)
+@pytest.mark.parametrize("wire,graphs,fuse", [((False, False), True, False), ((True, True), True, False),
+                                              ((False, True), False, False), ((False, False), True, True)])
+def test_session_step_through_servicers_reproduces_the_golden_tokens(golden, wire, graphs, fuse):
+    g, cfg, shards, svs, route = _servicers(golden, wire=wire, decode_graphs=graphs, fuse=fuse)
     prompts = torch.tensor(g["prompt_ids"]).to(DEV)
 
     async def go():

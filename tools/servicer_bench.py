@@ -85,9 +85,12 @@ def main():
     e1.record()
     torch.cuda.synchronize()
     ms_engine = e0.elapsed_time(e1) / steps
+    sv.fuse_projections = True  # last: it rewrites the shard's weight storage
+    ms_fused = asyncio.run(run(True))
     print(json.dumps({"shape": a.shape, "layers": a.layers, "batch": B, "context": ctx, "steps": steps,
                       "servicer_forward_ms_per_step": round(ms_servicer, 3),
                       "servicer_forward_eager_launches_ms_per_step": round(ms_eager, 3),
+                      "servicer_forward_fused_projections_ms_per_step": round(ms_fused, 3),
                       "engine_graph_ms_per_step": round(ms_engine, 3),
                       "note": "same shard (embedding + layers + final norm), bf16, synthetic KV; the servicer step is the "
                               "session's decode graph behind the RPC envelope (decode_graphs=False: eager launches), "
