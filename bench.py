@@ -596,6 +596,23 @@ def config1_side_by_side():
     }
 
 
+def reference_api_leg(workload):
+    """configs[1] driven the way a user of the reference drives it (tools/session_bench.py): one hop over all layers,
+    in-process transport, token ids from pinned host memory in and tokens back to the host every step."""
+    import importlib.util
+
+    spec = importlib.util.spec_from_file_location("session_bench", os.path.join(ROOT, "tools", "session_bench.py"))
+    mod = importlib.util.module_from_spec(spec)
+    spec.loader.exec_module(mod)
+    torch.cuda.empty_cache()
+    res = mod.run(workload["shape"], SHAPES[workload["shape"]]["num_hidden_layers"], 1, workload["batch"],
+                  workload["context"], steps=32, fuse=True, host_io=True)
+    torch.cuda.empty_cache()
+    return {"value": res["tokens_per_second"], "unit": "tokens/s", "ms_per_step": res["ms_per_step"],
+            "h2d_bytes_per_step": 8 * workload["batch"], "d2h_bytes_per_step": 8 * workload["batch"],
+            "kv_fill": "synthetic normal(0,1)", "path": res["path"]}
+
+
 def run_single(args, workload):
     line = _single_leg(args, workload)
     dev = "cuda:0"
@@ -607,6 +624,10 @@ def run_single(args, workload):
         line["cfg5"] = {"workload": five["config"]["workload"], "config": five["config"],
                         **{k: five[k] for k in ("value", "unit", "ms_per_step", "e2e", "gpu_launches", "roofline")}}
     line["kv_pack"] = measure_pack_unpack(dev)
+    if not args.workload and not args.batch and not args.context and not args.no_riders:
+        # the same workload through the reference's own call stack (DistributedInferenceSession.step -> WorkerSession ->
+        # InferenceServicer.Forward -> ModelShard.forward; get_logits + argmax by the caller), host ids in and out
+        line["reference_api"] = reference_api_leg(workload)
     if not args.no_cpu_baseline:
         res = cpu_reference_tokens_per_s(workload["shape"], workload["batch"], workload["context"], steps=10,
                                          warmup=2)  # about 10 s of host work

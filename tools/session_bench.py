@@ -24,17 +24,11 @@ from dgi_b200.worker.distributed.model_shard import ModelShard, get_layer_range_
 from dgi_b200.worker.distributed.servicer import InferenceServicer, ServicerTransport  # noqa: E402
 
 
-def main():
-    ap = argparse.ArgumentParser()
-    ap.add_argument("--shape", default="8b")
-    ap.add_argument("--layers", type=int, default=32)
-    ap.add_argument("--hops", type=int, default=2)
-    ap.add_argument("--batch", type=int, default=64)
-    ap.add_argument("--ctx", type=int, default=2048)
-    ap.add_argument("--steps", type=int, default=32)
-    ap.add_argument("--no-fuse", action="store_true")
-    a = ap.parse_args()
-    dev = "cuda:0"
+def run(shape_name="8b", layers=32, hops=2, batch=64, ctx=2048, steps=32, fuse=True, host_io=False, dev="cuda:0"):
+    """One measurement; ``host_io``: the caller's token ids start in pinned host memory and every step's tokens are
+    read back to the host (the end-to-end form of bench.py's ``e2e``)."""
+    a = argparse.Namespace(shape=shape_name, layers=layers, hops=hops, batch=batch, ctx=ctx, steps=steps,
+                           no_fuse=not fuse)
     shape = dict(SHAPES[a.shape])
     shape["num_hidden_layers"] = a.layers
     cfg = ShapeConfig(**shape)
@@ -57,7 +51,7 @@ def main():
         svs.append(sv)
     ids = torch.randint(0, cfg.vocab_size, (B, 1), device=dev)
 
-    async def run():
+    async def drive():
         sess = S.DistributedInferenceSession(SessionConfig(model_name=a.shape, max_length=ctx, max_retries=1), route)
         await sess.setup()
         await sess.step(ids)  # the first call creates the hops' sessions and their blocks
@@ -69,11 +63,19 @@ def main():
         sess.position = start  # fans out to the hop sessions
         nxt = ids
 
+        host_ids = torch.empty((B, 1), dtype=torch.int64).pin_memory() if host_io else None
+        if host_io:
+            host_ids.copy_(ids.cpu())
+
         async def one():
             nonlocal nxt
+            if host_io:
+                nxt = host_ids.to(dev, non_blocking=True)
             h = await sess.step(nxt)
             logits = shards[-1].get_logits(h[:, -1:, :])[:, 0, :]
             nxt = ops.argmax_rows(logits)[:, None]
+            if host_io:
+                host_ids.copy_(nxt)  # device -> pinned host; synchronises the step
 
         for _ in range(5):
             await one()
@@ -89,12 +91,28 @@ def main():
         await sess.close()
         return ms, pos
 
-    ms, pos = asyncio.run(run())
-    print(json.dumps({"shape": a.shape, "layers": a.layers, "hops": a.hops, "batch": B, "context_at_end": pos,
-                      "steps": steps, "fused_projections": not a.no_fuse, "ms_per_step": round(ms, 3),
-                      "tokens_per_second": round(B / ms * 1e3, 1),
-                      "path": "DistributedInferenceSession.step -> WorkerSession.forward -> ServicerTransport -> "
-                              "InferenceServicer.Forward (session decode graph) per hop; get_logits + argmax by the caller"}))
+    ms, pos = asyncio.run(drive())
+    for r in range(a.hops):
+        S.TRANSPORTS.pop(f"sb-worker-{r}", None)
+    return {"shape": a.shape, "layers": a.layers, "hops": a.hops, "batch": B, "context_at_end": pos,
+            "steps": steps, "fused_projections": not a.no_fuse, "host_ids_in_and_out": bool(host_io),
+            "ms_per_step": round(ms, 3), "tokens_per_second": round(B / ms * 1e3, 1),
+            "path": "DistributedInferenceSession.step -> WorkerSession.forward -> ServicerTransport -> "
+                    "InferenceServicer.Forward (session decode graph) per hop; get_logits + argmax by the caller"}
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--shape", default="8b")
+    ap.add_argument("--layers", type=int, default=32)
+    ap.add_argument("--hops", type=int, default=2)
+    ap.add_argument("--batch", type=int, default=64)
+    ap.add_argument("--ctx", type=int, default=2048)
+    ap.add_argument("--steps", type=int, default=32)
+    ap.add_argument("--no-fuse", action="store_true")
+    ap.add_argument("--host-io", action="store_true")
+    a = ap.parse_args()
+    print(json.dumps(run(a.shape, a.layers, a.hops, a.batch, a.ctx, a.steps, not a.no_fuse, a.host_io)))
 
 
 if __name__ == "__main__":
