@@ -6,7 +6,8 @@
 
 N = 1 : BASELINE configs[1] — Llama-3-8B shape, random-init bf16, block 16, batch 64, context 2k, decode; the line
         also carries configs[4] (batch 8, context 32k, shared prefix) as `cfg5` and configs[0] (tiny model, in
-        full, GPU and host side by side) as `cpu_baseline_cfg1`.
+        full, GPU and host side by side) as `cpu_baseline_cfg1`, and configs[1] once more through the reference's own call
+        stack (DistributedInferenceSession.step -> servicer hop, host ids in / out) as `reference_api`.
 N > 1 : BASELINE configs[3] — Llama-3-70B shape layer-sharded over N ranks (torchrun, NCCL send/recv of
         activations, vocabulary-parallel head), batch 128, context 4k, strong scaling; the 8B shape weak-scaled over
         the same ranks rides along as `weak_scaled_8b`, the P/D hand-off as `pd_transfer`, and `parity` holds the
