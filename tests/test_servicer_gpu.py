@@ -104,6 +104,36 @@ def test_a_retried_step_is_idempotent(golden):
     assert asyncio.run(go()).tolist() == [row[:12] for row in g["tokens"]]
 
 
+@pytest.mark.parametrize("cuts", [(48, 128), (16, 17, 100, 128)])
+def test_a_prompt_delivered_in_chunks_gives_the_same_tokens(golden, cuts):
+    """A long prompt may reach the hop in several Forward calls (position = tokens already delivered): every chunk after
+    the first attends to the session's cached tokens through the block table (b200_kv_gather_dense + dense causal
+    attention), chunk boundaries inside a block included.  Tokens afterwards: the golden ones."""
+    g, cfg, shards, svs, route = _servicers(golden)
+    prompts = torch.tensor(g["prompt_ids"]).to(DEV)
+    sv0, sv1 = svs
+
+    async def go():
+        s0 = {"session_id": "c", "position": 0, "max_length": 192}
+        s1 = {"session_id": "c", "position": 0, "max_length": 192}
+        sv0._sessions["c"], sv1._sessions["c"] = s0, s1
+        lo = 0
+        for hi in cuts:
+            h0, _ = await sv0._forward(s0, prompts[:, lo:hi], lo, [])
+            h, _ = await sv1._forward(s1, h0, lo, [])
+            lo = hi
+        assert s0["position"] == s1["position"] == 128
+        toks = []
+        for step in range(10):
+            nxt = shards[-1].get_logits(h[:, -1:, :])[:, 0, :].argmax(-1)
+            toks.append(nxt)
+            h0, _ = await sv0._forward(s0, nxt[:, None], 128 + step, [])
+            h, _ = await sv1._forward(s1, h0, 128 + step, [])
+        return torch.stack(toks, dim=1)
+
+    assert asyncio.run(go()).tolist() == [row[:10] for row in g["tokens"]]
+
+
 def test_transfer_kv_cache_hands_a_prompt_pass_to_a_session(golden):
     """Prefill -> decode hand-off through the RPC: an engine computes the prompt pass, WireHandoff.export turns each
     sequence's blocks into KVCacheRequest messages (proto/inference.proto:110-127), the servicer's TransferKVCache
