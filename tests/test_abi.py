@@ -54,6 +54,11 @@ def test_argument_errors_are_reported_without_a_gpu():
     rc = lib.b200_paged_decode_attn(None, None, 0, None, None, None, 0, None, 2, 6, 4, 128, 16, 10, 1.0, 16, 1, None, 0, 2,
                                     0, None)
     assert rc == -2 and b"multiple" in lib.b200_last_error()
+    rc = lib.b200_kv_gather_dense(None, None, None, None, None, 4, 2, 40, 8, 128, 16, 10, 9, None)  # dtype 9
+    assert rc == -1 and b"unsupported dtype" in lib.b200_last_error()
+    rc = lib.b200_kv_gather_dense(None, None, None, None, None, 4, 2, 40, 8, 128, 16, 10, 2, None)  # null pointers
+    assert rc == -1 and b"null pointer" in lib.b200_last_error()
+    assert lib.b200_kv_gather_dense(None, None, None, None, None, 4, 0, 40, 8, 128, 16, 10, 2, None) == 0  # empty batch
 
 
 def test_ops_refuse_cpu_tensors():
