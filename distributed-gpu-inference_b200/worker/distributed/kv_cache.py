@@ -33,7 +33,7 @@ import time
 from collections import OrderedDict
 from dataclasses import dataclass, field  # noqa: F401
 from enum import Enum
-from typing import Any, Dict, Iterable, List, Optional, Sequence, Set, Tuple
+from typing import Any, Dict, Iterable, List, Optional, Sequence, Tuple
 
 import torch
 
