@@ -586,6 +586,23 @@ def config1_side_by_side():
     torch.cuda.synchronize()
     gpu_s = time.perf_counter() - t0
     got = torch.stack(got, dim=1)
+    # the same 63 steps with the tokens staying on the device (chained CUDA-graph steps, as `value` is measured)
+    eng.allocate(B, P + N)
+    first = eng.prefill(prompts)
+    eng.ids_buf[:B, 0].copy_(first)
+    dev_toks = [first.clone()]
+    eng.decode_step_device()  # captures the chained graph
+    dev_toks.append(eng.next_tokens[:B].clone())
+    torch.cuda.synchronize()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for _ in range(N - 2):
+        eng.decode_step_device()
+        dev_toks.append(eng.next_tokens[:B].clone())
+    e1.record()
+    torch.cuda.synchronize()
+    gpu_dev_s = e0.elapsed_time(e1) / 1e3 * (N - 1) / (N - 2)  # 62 timed steps scaled to the 63 of the other legs
+    got_dev = torch.stack(dev_toks, dim=1).cpu()
     return {
         "workload": "configs[0]: tiny 4-layer model (d=512, 8 heads, 2 KV heads), 2 layer-range shards, batch 4, prompt 128, "
                     "64 greedy tokens, fp32",
@@ -593,7 +610,9 @@ def config1_side_by_side():
         "kind": "reference" if by_reference else "port", "extrapolated": False,
         "sample": f"the whole configuration: {N - 1} decode steps of batch {B} after the prompt pass, {cpu_decode_s:.2f} s",
         "gpu_value": B * (N - 1) / gpu_s, "gpu_path": "PagedDecodeEngine.decode_step (host ids in / out per step), 1 GPU",
-        "tokens_identical": bool(torch.equal(got, want)),
+        "gpu_value_device_resident": B * (N - 1) / gpu_dev_s,
+        "gpu_path_device_resident": "PagedDecodeEngine.decode_step_device (chained CUDA-graph steps, CUDA events)",
+        "tokens_identical": bool(torch.equal(got, want)) and bool(torch.equal(got_dev, want)),
     }
 
 
