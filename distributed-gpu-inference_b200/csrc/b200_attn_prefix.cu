@@ -13,10 +13,11 @@
 //       suffix CTAs  (suffix_splits x Hkv x B): a sequence's own blocks after the prefix, one kv head, its group
 //                    of q heads — the plain kernel's work item.
 //                    Every CTA files a partial (m, l, O) in the split-K workspace.
-//   merge                  every CTA counts its arrival per (sequence, q head) row in a counter that lives in front of
-//                          the workspace; the CTA that brings a row's count to prefix_splits + suffix_splits merges that
-//                          row's partials into `out` and puts the counter back to zero — no second launch.
-//                          Long prefix runs per CTA keep the two-launch form (attn_combine_kernel), see attn_prefix().
+//   launch 2               attn_combine_kernel merges the partials of every (sequence, q head) row; it is a
+//                          programmatic dependent of launch 1, so it is resident by the time the last CTA finishes.
+//   (in-kernel merge)      alternative kept behind B200_PREFIX_SEPARATE_COMBINE=0: every CTA counts its arrival per row
+//                          in a counter in front of the workspace and the CTA that completes a row merges it — no
+//                          second launch, but measured slower than the dependent launch at every shape (attn_prefix()).
 //
 // The caller guarantees: block_tables[b][0:prefix_blocks] are identical for all b, and every context_lens[b] >=
 // prefix_blocks * 16 (the prefix blocks are full for everybody, so launch 1 needs no masking).
@@ -562,13 +563,15 @@ int attn_prefix(const AttnArgs& a, int dtype, int prefix_blocks, int prefix_spli
   // Arrival counters in front of the partials.  They must read zero when the kernel starts; the merging CTAs put
   // them back to zero, so a caller that owns the workspace exclusively can promise that (B200_ATTN_WS_COUNTERS_ZERO)
   // and save the memset node.
-  // Who merges: the last CTA to arrive when launches are short (the second launch would be a visible share of the
-  // step), a separate combine launch when each prefix CTA streams a long run of blocks — there the prefix CTAs are the
-  // last to finish, each would merge its 16 rows on its own at the very end, and that tail costs more than the launch
-  // (measured on B200, config 5: 68.5 us merged in-kernel vs 62.7 us with the combine launch; 64 sequences behind a
-  // 2048-token prompt: 37 us vs 42 us).  B200_PREFIX_SEPARATE_COMBINE=0|1 overrides.
+  // Who merges: a separate combine launch (attn_combine_kernel, a programmatic dependent of this grid, so its launch
+  // latency hides behind the attention CTAs).  Merging inside the kernel by the last-arriving CTA of each row was
+  // the better choice for short prefix runs before the combine became a dependent launch; measured again afterwards
+  // on B200 (tools/prefix_merge_probe.py, profiles/r02_prefix_merge_probe.jsonl, counters vouched for): the separate
+  // launch wins at every shape tried — 8 x (512 + 64): 17.5 vs 24.6 us, 64 x (2048 + 176): 41.0 vs 43.7 us,
+  // config 5: 72.3 vs 80.4 us — because the rows of a CTA are merged by whichever CTA finishes last, at the very end
+  // of the launch, with nothing left to overlap.  B200_PREFIX_SEPARATE_COMBINE=0 still selects the in-kernel merge.
   const int force = separate_combine();
-  const bool in_kernel = force >= 0 ? force == 0 : ceil_div(prefix_blocks, prefix_splits) < 96;
+  const bool in_kernel = force == 0;
   int* counters = in_kernel ? a.ws_counters : nullptr;
   if (counters != nullptr && !a.ws_counters_zero) {
     cudaError_t e = cudaMemsetAsync(counters, 0, sizeof(int) * static_cast<size_t>(a.B) * a.Hq, s);

@@ -42,9 +42,11 @@ extern "C" {
 #define B200_ATTN_FORCE_GENERIC 1u /* skip the TMA + tensor-core variant (used by tests to cross-check) */
 #define B200_ATTN_ROUND_SCORES 2u  /* round q.k and scaled scores to the storage dtype before softmax, the way
                                       the reference's eager HF attention does (bf16/f16 only) */
-#define B200_ATTN_WS_COUNTERS_ZERO 4u /* shared-prefix entry points: the first 4 * B * Hq bytes of the workspace (one
-                                      arrival counter per (sequence, q head); the merge of the partials is done by the
-                                      last CTA to arrive) are known to be zero: the workspace was zero-filled once, is
+#define B200_ATTN_WS_COUNTERS_ZERO 4u /* shared-prefix entry points, only when the partials are merged inside the kernel
+                                      by the last CTA to arrive (B200_PREFIX_SEPARATE_COMBINE=0; the default is a
+                                      dependent combine launch, which needs no counters): the first 4 * B * Hq bytes of
+                                      the workspace (one arrival counter per (sequence, q head)) are known to be zero:
+                                      the workspace was zero-filled once, is
                                       used by nothing but these entry points with the same B and Hq, and no earlier call
                                       on it was aborted.  Every call leaves the counters zero again.  Without the flag
                                       the library clears them itself (one cudaMemsetAsync on the stream per call). */

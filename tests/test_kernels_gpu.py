@@ -759,3 +759,19 @@ def test_rows_past_the_context_may_hold_nan(dtype):
         dirty = fused(q, k_new, v_new, cos, sin, kn, vn, tables, lens, max(ctx))
         assert torch.isfinite(dirty.float()).all()
         assert torch.equal(_bits(clean), _bits(dirty))
+
+
+def test_in_kernel_merge_variant_still_matches_the_oracle():
+    """The shared-prefix entry points merge their partials with a dependent combine launch by default; the merge by
+    the last-arriving CTA stays selectable (B200_PREFIX_SEPARATE_COMBINE=0, read once per process).  The shared-prefix
+    parity tests of this file, re-run in a child process with that variant."""
+    import os
+    import subprocess
+    import sys
+
+    env = dict(os.environ, B200_PREFIX_SEPARATE_COMBINE="0")
+    res = subprocess.run([sys.executable, "-m", "pytest", os.path.abspath(__file__), "-q", "-m", "gpu", "-p", "no:cacheprovider",
+                          "-k", "prefix_attention_matches_oracle or fused_rope_append_cascade or strided_q_and_prefix"],
+                         env=env, capture_output=True, text=True, timeout=600)
+    assert res.returncode == 0, res.stdout[-2000:] + res.stderr[-2000:]
+    assert " passed" in res.stdout and "failed" not in res.stdout
