@@ -546,7 +546,11 @@ void attn_prefix_plan(int B, int Hq, int Hkv, int block_size, int prefix_blocks,
   const int qgroups = std::max(1, ceil_div(B * G, 8 * kPrefixNT));
   const int min_blocks = std::max(1, 256 / block_size);
   int ps = ceil_div(kNumSMs, std::max(1, Hkv * qgroups));
-  ps = std::max(1, std::min(ps, std::max(1, prefix_blocks / min_blocks)));
+  // a grid that nearly fills the machine unsplit (>= 100 prefix CTAs) is split in two only for runs of >= 1024 tokens
+  // per piece (profiles/r02_prefix_split_sweep.jsonl: 64 sequences, 512-token prompt: 24.9 us unsplit vs 27.5 us;
+  // 2048-token prompt: 41.8 us split in two vs 46.2 us)
+  const int min_prefix_blocks = Hkv * qgroups >= 100 ? std::max(min_blocks, 1024 / block_size) : min_blocks;
+  ps = std::max(1, std::min(ps, std::max(1, prefix_blocks / min_prefix_blocks)));
   *prefix_splits = std::min(ps, 96);
   const int suffix_tokens = std::max(0, max_context_len - prefix_blocks * block_size);
   const int suffix_blocks = std::max(1, ceil_div(std::max(1, suffix_tokens), block_size));
