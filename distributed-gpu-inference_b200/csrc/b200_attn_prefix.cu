@@ -45,6 +45,8 @@ struct CascadeParams {
   int prefix_splits, prefix_bps;   // prefix role: splits and blocks per split
   int suffix_splits, suffix_bps;   // suffix role
   int n_prefix_ctas;               // CTAs [0, n_prefix_ctas) run the prefix role
+  int suffix_warp_items;           // != 0: a suffix CTA's four warps each take one (split, kv head, sequence) item
+  int n_suffix_items;              // suffix_splits * Hkv * B
   float* ws_acc;
   float* ws_ml;
   int* counters;                   // [B * Hq] arrival counters, zero before and after the launch; null: separate combine
@@ -66,7 +68,10 @@ struct CascadeParams {
 // tile appends the new token's rotated k and its v, exactly as paged_attn_tma_kernel<.., FUSED> does.
 constexpr int kMaxMergeSplits = 256;  // as attn_combine_kernel
 
-template <typename T, int D, int STAGES, int NT, bool SUFFIX, bool FUSED, bool ROUND>
+// WARPITEM (suffix role only): the calling WARP owns the whole work item — it walks every block of the run itself and
+// files the partial on its own, so a CTA carries four items and nothing is merged across warps (short runs: the
+// per-CTA fixed cost, not the data, is what a launch of many short items pays for).
+template <typename T, int D, int STAGES, int NT, bool SUFFIX, bool FUSED, bool ROUND, bool WARPITEM = false>
 __device__ __forceinline__ void cascade_role(const CUtensorMap& k_map, const CUtensorMap& v_map, const CascadeParams& p,
                                              int split, int kvh, int zi) {
   using S = Smem<D, STAGES>;
@@ -83,8 +88,11 @@ __device__ __forceinline__ void cascade_role(const CUtensorMap& k_map, const CUt
   float* ws_ml = p.ws_ml;
   const int splits_total = p.prefix_splits + p.suffix_splits;
   const int qgroup = zi;
+  static_assert(!WARPITEM || SUFFIX, "one warp per item is a suffix-role variant");
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int quad = lane >> 2, tq = lane & 3;
+  constexpr int WSTRIDE = WARPITEM ? 1 : kWarps;  // distance between the blocks one warp takes
+  const int wofs = WARPITEM ? 0 : warp;           // its first block within the run
 
   extern __shared__ unsigned char smem_raw[];
   unsigned char* smem = reinterpret_cast<unsigned char*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
@@ -112,15 +120,15 @@ __device__ __forceinline__ void cascade_role(const CUtensorMap& k_map, const CUt
     table_row = p.block_tables;  // the prefix entries are the same in every row
   }
   const int n_cta = max(0, blk_end - blk_begin);
-  const int n_mine = n_cta > warp ? (n_cta - warp + kWarps - 1) / kWarps : 0;
-  const int32_t* table = table_row + blk_begin + warp;
+  const int n_mine = n_cta > wofs ? (n_cta - wofs + WSTRIDE - 1) / WSTRIDE : 0;
+  const int32_t* table = table_row + blk_begin + wofs;
 
   int win_base = 0;
-  int32_t win_slot = (lane < n_mine) ? table[lane * kWarps] : 0;
+  int32_t win_slot = (lane < n_mine) ? table[lane * WSTRIDE] : 0;
   auto issue = [&](int j) {
     if (j - win_base >= 32) {
       win_base += 32;
-      win_slot = (win_base + lane < n_mine) ? table[(win_base + lane) * kWarps] : 0;
+      win_slot = (win_base + lane < n_mine) ? table[(win_base + lane) * WSTRIDE] : 0;
     }
     const int32_t slot = __shfl_sync(0xffffffffu, win_slot, j - win_base);
     if (lane == 0) {
@@ -181,7 +189,7 @@ __device__ __forceinline__ void cascade_role(const CUtensorMap& k_map, const CUt
   FusedAppend<T> fa{};
   if constexpr (SUFFIX) {
     const int last_blk = (ctx + kTok - 1) / kTok - 1;
-    owns_last = ctx > 0 && last_blk >= blk_begin && last_blk < blk_end && ((last_blk - blk_begin) % kWarps) == warp;
+    owns_last = ctx > 0 && last_blk >= blk_begin && last_blk < blk_end && ((last_blk - blk_begin) % WSTRIDE) == wofs;
   }
   if constexpr (FUSED && SUFFIX) {
     const int last_blk = (ctx + kTok - 1) / kTok - 1;
@@ -245,7 +253,7 @@ __device__ __forceinline__ void cascade_role(const CUtensorMap& k_map, const CUt
     float corr[NT][2];
     uint32_t pb[NT][2];
     bool rescale = false;
-    const int tok0 = (blk_begin + warp + i * kWarps) * kTok + quad;
+    const int tok0 = (blk_begin + wofs + i * WSTRIDE) * kTok + quad;
     const bool ok_lo = !SUFFIX || tok0 < ctx, ok_hi = !SUFFIX || tok0 + 8 < ctx;
 #pragma unroll
     for (int nt = 0; nt < NT; ++nt) {
@@ -307,6 +315,36 @@ __device__ __forceinline__ void cascade_role(const CUtensorMap& k_map, const CUt
       l_run[nt][c] += __shfl_xor_sync(0xffffffffu, l_run[nt][c], 8);
       l_run[nt][c] += __shfl_xor_sync(0xffffffffu, l_run[nt][c], 16);
     }
+  if constexpr (WARPITEM) {
+    // The warp's own ring is idle now (every tile it asked for has been consumed): the partial is staged there, so
+    // that lanes can write whole rows, and filed by this warp alone — no block-wide barrier anywhere on this path.
+    __syncwarp();
+    float* o_w = reinterpret_cast<float*>(smem + warp * STAGES * S::kStageBytes);  // [COLS][D]
+    float* m_w = o_w + COLS * D;                                                   // [COLS]
+    float* l_w = m_w + COLS;                                                       // [COLS]
+#pragma unroll
+    for (int mt = 0; mt < MTILES; ++mt)
+#pragma unroll
+      for (int e = 0; e < 4; ++e) o_w[(2 * tq + (e & 1)) * D + 16 * mt + quad + ((e >> 1) << 3)] = o[mt][0][e];
+    if (quad == 0) {
+#pragma unroll
+      for (int c = 0; c < 2; ++c) {
+        m_w[2 * tq + c] = m_run[0][c];
+        l_w[2 * tq + c] = l_run[0][c];
+      }
+    }
+    __syncwarp();
+    for (int idx = lane; idx < G * D; idx += 32) {
+      const int c = idx / D, d = idx - c * D;
+      const int64_t pidx = (static_cast<int64_t>(zi) * Hq + kvh * G + c) * splits_total + p.prefix_splits + split;
+      ws_acc[pidx * D + d] = o_w[c * D + d];
+      if (d == 0) {
+        ws_ml[pidx * 2 + 0] = m_w[c] * 0.6931471805599453f;  // natural-log domain, as attn_combine_kernel expects
+        ws_ml[pidx * 2 + 1] = l_w[c];
+      }
+    }
+    return;
+  }
   __syncthreads();
   float* o_s = reinterpret_cast<float*>(smem);   // [W][COLS][D]
   float* m_s = o_s + kWarps * COLS * D;          // [W][COLS]
@@ -451,6 +489,14 @@ paged_attn_cascade_kernel(const __grid_constant__ CUtensorMap k_map, const __gri
     cascade_role<T, D, STAGES, NT, false, FUSED, ROUND>(k_map, v_map, p, split, rest % p.Hkv, rest / p.Hkv);
   } else {
     const int j = id - p.n_prefix_ctas;
+    if (p.suffix_warp_items) {  // short runs: one item per warp
+      const int item = j * kWarps + (threadIdx.x >> 5);
+      if (item >= p.n_suffix_items) return;
+      const int split = item % p.suffix_splits;
+      const int rest = item / p.suffix_splits;
+      cascade_role<T, D, STAGES, 1, true, FUSED, ROUND, true>(k_map, v_map, p, split, rest % p.Hkv, rest / p.Hkv);
+      return;
+    }
     const int split = j % p.suffix_splits;
     const int rest = j / p.suffix_splits;
     cascade_role<T, D, STAGES, 1, true, FUSED, ROUND>(k_map, v_map, p, split, rest % p.Hkv, rest / p.Hkv);
@@ -461,6 +507,14 @@ inline int ceil_div(int a, int b) { return (a + b - 1) / b; }
 
 constexpr int kPrefixNT = 2;       // 16 query rows ((sequence, head) pairs) per prefix CTA
 constexpr int kPrefixStages = 3;   // ring depth at 2 CTAs per SM (2 stages x 3 CTAs measured the same: 63.2 vs 63.5 us on config 5)
+
+bool warp_items_allowed() {  // B200_PREFIX_WARP_ITEMS=0 keeps one CTA per suffix item (for A/B measurements)
+  static const bool v = [] {
+    const char* e = getenv("B200_PREFIX_WARP_ITEMS");
+    return !(e && atoi(e) == 0);
+  }();
+  return v;
+}
 
 int separate_combine() {  // -1: library's choice, 0 / 1: forced by B200_PREFIX_SEPARATE_COMBINE
   static const int v = [] {
@@ -516,7 +570,14 @@ int launch_cascade_impl(const AttnArgs& a, int dtype, int prefix_blocks, int pre
     p.k_pool = const_cast<void*>(a.k_pool);
     p.v_pool = const_cast<void*>(a.v_pool);
   }
-  const int grid = p.n_prefix_ctas + suffix_splits * a.Hkv * a.B;
+  // Short runs after the prefix (<= 32 blocks per piece) in a launch of many items: one item per WARP, four per CTA —
+  // the fixed cost of a CTA (barriers, table read, first TMA round trip, cross-warp merge, partial write) is paid a
+  // quarter as often.  Needs the combine launch (no block-wide barrier on that path, hence no arrival counting).
+  p.n_suffix_items = suffix_splits * a.Hkv * a.B;
+  p.suffix_warp_items = warp_items_allowed() && counters == nullptr && p.n_suffix_items > 2 * kNumSMs &&
+                        p.suffix_bps <= 32;
+  const int suffix_ctas = p.suffix_warp_items ? ceil_div(p.n_suffix_items, kWarps) : p.n_suffix_items;
+  const int grid = p.n_prefix_ctas + suffix_ctas;
   kern<<<grid, kWarps * 32, S::kTotal, stream>>>(km, vm, p);
   return check_launch("b200_paged_decode_attn_prefix(cascade)");
 }

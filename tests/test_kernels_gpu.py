@@ -380,6 +380,10 @@ PREFIX_CASES = [
     (5, 64, 8, 128, 33, [0, 0, 10, 200, 47]),                 # 70B shape: group 8, 40 rows = 2.5 q-groups
     (4, 8, 2, 64, 20, [128, 129, 1, 77]),                     # head_dim 64
     (2, 8, 8, 64, 3, [9, 40]),                                # MHA (group 1)
+    # many short runs (> 296 suffix items of <= 32 blocks): the suffix role hands one item to each WARP
+    (48, 32, 8, 128, 20, [(53 * i) % 301 for i in range(48)]),   # tails 0..300 tokens, incl. empty ones and full blocks
+    (40, 8, 8, 64, 5, [1 + (29 * i) % 500 for i in range(40)]),  # head_dim 64, MHA
+    (38, 64, 8, 128, 9, [16 * (i % 7) + (i % 3) for i in range(38)]),  # group 8; 304 items, the last CTA partly filled
 ]
 
 
@@ -619,6 +623,8 @@ def test_fused_rope_append_attention_equals_the_separate_kernels(dtype, B, Hq, H
     (4, 32, 8, 128, 640, [33, 1, 16, 250]),      # 8B shape; a tail of one token, an exact block, ragged
     (3, 8, 2, 64, 160, [17, 160, 5]),            # config-1 shape
     (8, 64, 8, 128, 2048, [100 + 37 * i for i in range(8)]),  # 70B shape, group 8
+    (40, 32, 8, 128, 320, [1 + (37 * i) % 290 for i in range(40)]),  # 320 short suffix items: one per warp
+    (39, 64, 8, 128, 64, [1 + (16 * i) % 97 for i in range(39)]),    # 312 items, group 8, tails ending on block edges
 ])
 def test_fused_rope_append_cascade_equals_the_separate_kernels(dtype, B, Hq, Hkv, D, prefix, tails):
     bs = 16

@@ -48,7 +48,7 @@ def main():
         Hkv = rng.choice([1, 2, 4, 8])
         G = rng.choice([1, 2, 4, 8])
         Hq = Hkv * G
-        B = rng.choice([1, 2, 3, 5, 8, 17])
+        B = rng.choice([1, 2, 3, 5, 8, 17, 40])  # 40 x Hkv 8 = 320 suffix items: the one-item-per-warp role
         bs = 16
         use_prefix = B > 1 and rng.random() < 0.5
         prefix_blocks = rng.choice([1, 3, 16, 40]) if use_prefix else 0
