@@ -111,25 +111,42 @@ using namespace tma;
 
 namespace {
 
-template <typename T, int D, int STAGES, bool FUSED>
+// WARPITEM: launches of many SHORT items (a large batch at a short context).  Each warp of a CTA takes a whole
+// (partition, kv head, sequence) item — grid.x = ceil(items / 4), every block of the item walked by that one warp,
+// result filed by that warp — so the per-CTA fixed cost (barrier set-up, table read, first TMA round trip, the
+// cross-warp merge through shared memory) is paid once for four items and no block-wide barrier is taken at all.
+template <typename T, int D, int STAGES, bool FUSED, bool WARPITEM = false>
 __global__ void __launch_bounds__(kWarps * 32, (STAGES <= 3 ? 2 : 1))
 paged_attn_tma_kernel(const __grid_constant__ CUtensorMap k_map, const __grid_constant__ CUtensorMap v_map,
                       T* __restrict__ out, const T* __restrict__ q, int64_t q_row_stride,
                       const int32_t* __restrict__ block_tables, int table_stride,
                       const int32_t* __restrict__ context_lens, int Hq, int Hkv, int G, float scale,
                       int blocks_per_split, int num_splits, float* __restrict__ ws_acc, float* __restrict__ ws_ml,
-                      int round_scores, const FusedAppend<T> fa) {
+                      int round_scores, const FusedAppend<T> fa, int n_items) {
   using S = Smem<D, STAGES>;
   constexpr int KSTEPS = D / 16;   // mma k-steps over head_dim for S^T
   constexpr int MTILES = D / 16;   // mma m-tiles over head_dim for O^T
   constexpr int BOXES = D / 64;    // TMA boxes per tile
 
-  const int split = blockIdx.x, kvh = blockIdx.y, b = blockIdx.z;
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int quad = lane >> 2, tq = lane & 3;
+  constexpr int WSTRIDE = WARPITEM ? 1 : kWarps;  // distance between the blocks one warp takes
+  const int wofs = WARPITEM ? 0 : warp;           // its first block within the CTA's (or its own) run
+  int split, kvh, b;
+  if constexpr (WARPITEM) {
+    const int item = blockIdx.x * kWarps + warp;
+    split = item % num_splits;
+    kvh = (item / num_splits) % Hkv;
+    b = item / (num_splits * Hkv);
+  } else {
+    split = blockIdx.x, kvh = blockIdx.y, b = blockIdx.z;
+  }
   // split-K: the combine grid is a programmatic dependent of this one (attn_combine) and may be scheduled as soon as
   // every CTA here has started; a no-op when nothing depends on this launch
   asm volatile("griddepcontrol.launch_dependents;");
+  if constexpr (WARPITEM) {
+    if (blockIdx.x * kWarps + warp >= n_items) return;  // the last CTA may carry fewer than four items
+  }
 
   extern __shared__ unsigned char smem_raw[];
   unsigned char* smem = reinterpret_cast<unsigned char*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
@@ -150,17 +167,17 @@ paged_attn_tma_kernel(const __grid_constant__ CUtensorMap k_map, const __grid_co
   const int blk_begin = min(n_blocks, split * blocks_per_split);
   const int blk_end = (split == num_splits - 1) ? n_blocks : min(n_blocks, (split + 1) * blocks_per_split);
   const int n_cta = blk_end - blk_begin;
-  const int n_mine = n_cta > warp ? (n_cta - warp + kWarps - 1) / kWarps : 0;  // tiles warp, warp+4, ...
-  const int32_t* table = block_tables + static_cast<int64_t>(b) * table_stride + blk_begin + warp;
+  const int n_mine = n_cta > wofs ? (n_cta - wofs + WSTRIDE - 1) / WSTRIDE : 0;  // tiles warp, warp+4, ... (or all)
+  const int32_t* table = block_tables + static_cast<int64_t>(b) * table_stride + blk_begin + wofs;
 
   // Block-table window: lane L holds the pool slot of this warp's tile (win * 32 + L).
   int win_base = 0;
-  int32_t win_slot = (lane < n_mine) ? table[lane * kWarps] : 0;
+  int32_t win_slot = (lane < n_mine) ? table[lane * WSTRIDE] : 0;
 
   auto issue = [&](int j) {  // all lanes call; lane 0 issues tile j of this warp into stage j % STAGES
     if (j - win_base >= 32) {
       win_base += 32;
-      win_slot = (win_base + lane < n_mine) ? table[(win_base + lane) * kWarps] : 0;
+      win_slot = (win_base + lane < n_mine) ? table[(win_base + lane) * WSTRIDE] : 0;
     }
     const int32_t slot = __shfl_sync(0xffffffffu, win_slot, j - win_base);
     if (lane == 0) {
@@ -204,7 +221,7 @@ paged_attn_tma_kernel(const __grid_constant__ CUtensorMap k_map, const __grid_co
   }
   // the warp that owns the sequence's last KV tile (the one the new token lands in) does the append
   const int last_blk = n_blocks - 1;
-  const bool owns_last = ctx > 0 && last_blk >= blk_begin && last_blk < blk_end && ((last_blk - blk_begin) % kWarps) == warp;
+  const bool owns_last = ctx > 0 && last_blk >= blk_begin && last_blk < blk_end && ((last_blk - blk_begin) % WSTRIDE) == wofs;
   const bool append_here = FUSED && owns_last;
   // The new token's k / v / cos / sin rows and its pool slot are fetched NOW, while the first KV tiles are in
   // flight, so that the patch of the last tile (end of this warp's loop) does not wait on global memory.
@@ -253,7 +270,7 @@ paged_attn_tma_kernel(const __grid_constant__ CUtensorMap k_map, const __grid_co
     }
 
     // online softmax.  s[0], s[1]: token `quad`; s[2], s[3]: token `quad + 8`; columns g = 2 tq, 2 tq + 1
-    const int tok0 = (blk_begin + warp + i * kWarps) * kTok + quad;
+    const int tok0 = (blk_begin + wofs + i * WSTRIDE) * kTok + quad;
     const bool ok_lo = tok0 < ctx, ok_hi = tok0 + 8 < ctx;
     float x[4];
 #pragma unroll
@@ -319,6 +336,42 @@ paged_attn_tma_kernel(const __grid_constant__ CUtensorMap k_map, const __grid_co
     l_run[c] += __shfl_xor_sync(0xffffffffu, l_run[c], 8);
     l_run[c] += __shfl_xor_sync(0xffffffffu, l_run[c], 16);
   }
+  if constexpr (WARPITEM) {
+    // this warp's ring is idle (every tile it asked for has been consumed): stage the result there so that lanes
+    // write whole rows, and file it without any block-wide barrier
+    __syncwarp();
+    float* o_w = reinterpret_cast<float*>(smem + warp * STAGES * S::kStageBytes);  // [8][D]
+    float* m_w = o_w + 8 * D;                                                      // [8]
+    float* l_w = m_w + 8;                                                          // [8]
+#pragma unroll
+    for (int mt = 0; mt < MTILES; ++mt)
+#pragma unroll
+      for (int e = 0; e < 4; ++e) o_w[(2 * tq + (e & 1)) * D + 16 * mt + quad + ((e >> 1) << 3)] = o[mt][e];
+    if (quad == 0) {
+#pragma unroll
+      for (int c = 0; c < 2; ++c) {
+        m_w[2 * tq + c] = m_run[c];
+        l_w[2 * tq + c] = l_run[c];
+      }
+    }
+    __syncwarp();
+    for (int idx = lane; idx < G * D; idx += 32) {
+      const int g = idx / D, d = idx - g * D;
+      const float acc = o_w[g * D + d], L = l_w[g];
+      const int hq = kvh * G + g;
+      if (num_splits == 1) {
+        out[(static_cast<int64_t>(b) * Hq + hq) * D + d] = Cvt<T>::from_f32(L > 0.f ? acc / L : 0.f);
+      } else {
+        const int64_t pidx = (static_cast<int64_t>(b) * Hq + hq) * num_splits + split;
+        ws_acc[pidx * D + d] = acc;
+        if (d == 0) {
+          ws_ml[pidx * 2 + 0] = m_w[g] * 0.6931471805599453f;  // natural-log domain, as attn_combine_kernel expects
+          ws_ml[pidx * 2 + 1] = L;
+        }
+      }
+    }
+    return;
+  }
   __syncthreads();
   float* o_s = reinterpret_cast<float*>(smem);        // [W][8][D]
   float* m_s = o_s + kWarps * 8 * D;                  // [W][8]
@@ -368,7 +421,7 @@ paged_attn_tma_kernel(const __grid_constant__ CUtensorMap k_map, const __grid_co
   }
 }
 
-template <typename T, int D, int STAGES, bool FUSED>
+template <typename T, int D, int STAGES, bool FUSED, bool WARPITEM = false>
 int launch_tma(const AttnArgs& a, int dtype, cudaStream_t stream) {
   using S = Smem<D, STAGES>;
   const uint64_t rows = static_cast<uint64_t>(a.max_blocks) * a.Hkv * kTok;
@@ -377,7 +430,7 @@ int launch_tma(const AttnArgs& a, int dtype, cudaStream_t stream) {
   if (rc) return rc;
   rc = get_tensor_map(a.v_pool, rows, D, dtype, &vm);
   if (rc) return rc;
-  auto kern = paged_attn_tma_kernel<T, D, STAGES, FUSED>;
+  auto kern = paged_attn_tma_kernel<T, D, STAGES, FUSED, WARPITEM>;
   FusedAppend<T> fa{};
   if (FUSED) {
     fa.k_new = static_cast<const T*>(a.k_new);
@@ -391,11 +444,12 @@ int launch_tma(const AttnArgs& a, int dtype, cudaStream_t stream) {
   }
   cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, S::kTotal);
   if (e != cudaSuccess) return fail(static_cast<int>(e), "cudaFuncSetAttribute: %s", cudaGetErrorString(e));
-  dim3 grid(a.num_splits, a.Hkv, a.B);
+  const int n_items = a.num_splits * a.Hkv * a.B;
+  const dim3 grid = WARPITEM ? dim3((n_items + kWarps - 1) / kWarps) : dim3(a.num_splits, a.Hkv, a.B);
   kern<<<grid, kWarps * 32, S::kTotal, stream>>>(km, vm, static_cast<T*>(a.out), static_cast<const T*>(a.q),
                                                   a.q_row_stride, a.block_tables, a.table_stride, a.context_lens, a.Hq,
                                                   a.Hkv, a.Hq / a.Hkv, a.scale, a.blocks_per_split, a.num_splits,
-                                                  a.ws_acc, a.ws_ml, a.round_scores, fa);
+                                                  a.ws_acc, a.ws_ml, a.round_scores, fa, n_items);
   return check_launch("b200_paged_decode_attn(tma)");
 }
 
@@ -412,12 +466,13 @@ bool attn_tma_supported(const AttnArgs& a, int dtype) {
   return tensor_maps_available();
 }
 
-template <int STAGES, bool FUSED>
+template <int STAGES, bool FUSED, bool WARPITEM = false>
 int attn_tma_stages(const AttnArgs& a, int dtype, cudaStream_t s) {
   if (dtype == B200_DTYPE_BF16)
-    return a.D == 128 ? launch_tma<__nv_bfloat16, 128, STAGES, FUSED>(a, dtype, s)
-                      : launch_tma<__nv_bfloat16, 64, STAGES, FUSED>(a, dtype, s);
-  return a.D == 128 ? launch_tma<__half, 128, STAGES, FUSED>(a, dtype, s) : launch_tma<__half, 64, STAGES, FUSED>(a, dtype, s);
+    return a.D == 128 ? launch_tma<__nv_bfloat16, 128, STAGES, FUSED, WARPITEM>(a, dtype, s)
+                      : launch_tma<__nv_bfloat16, 64, STAGES, FUSED, WARPITEM>(a, dtype, s);
+  return a.D == 128 ? launch_tma<__half, 128, STAGES, FUSED, WARPITEM>(a, dtype, s)
+                    : launch_tma<__half, 64, STAGES, FUSED, WARPITEM>(a, dtype, s);
 }
 
 // Ring depth: 3 stages x 2 CTAs per SM when the grid has at least two CTAs for every SM; 6 stages x 1 CTA per SM
@@ -428,8 +483,15 @@ int attn_tma(const AttnArgs& a, int dtype, cudaStream_t s) {
     const char* e = getenv("B200_ATTN_STAGES");
     return e ? atoi(e) : 0;
   }();
+  static const bool warp_items = [] {  // B200_ATTN_WARP_ITEMS=0: always one CTA per item (A/B measurements)
+    const char* e = getenv("B200_ATTN_WARP_ITEMS");
+    return !(e && atoi(e) == 0);
+  }();
   const long ctas = static_cast<long>(a.num_splits) * a.Hkv * a.B;
   const int stages = forced ? forced : (ctas >= 2L * kNumSMs ? 3 : 6);
+  // many short items (more than two per SM, at most 32 blocks = 512 tokens each): one item per warp, see the kernel
+  if (warp_items && !forced && ctas > 2L * kNumSMs && a.blocks_per_split <= 32)
+    return a.k_new != nullptr ? attn_tma_stages<3, true, true>(a, dtype, s) : attn_tma_stages<3, false, true>(a, dtype, s);
   if (a.k_new != nullptr)  // fused RoPE + append + attention (3-stage ring only)
     return attn_tma_stages<3, true>(a, dtype, s);
   return stages >= 6 ? attn_tma_stages<6, false>(a, dtype, s) : attn_tma_stages<3, false>(a, dtype, s);

@@ -183,6 +183,10 @@ CASES = [
     (2, 4, 4, 32, 8, [5, 64]),                           # MHA, small block
     (1, 16, 1, 128, 16, [333]),                          # MQA, group 16
     (3, 8, 2, 64, 16, [0, 16, 15]),                      # empty sequence
+    # many short items (> 296 of <= 512 tokens): one (partition, kv head, sequence) item per WARP
+    (40, 32, 8, 128, 16, [(61 * i) % 513 for i in range(40)]),     # 320 items, contexts 0..512 incl. block edges
+    (38, 64, 8, 128, 16, [1 + (97 * i) % 300 for i in range(38)]),  # group 8; 304 items: the last CTA partly filled
+    (80, 8, 4, 64, 16, [1 + (13 * i) % 200 for i in range(80)]),    # head_dim 64, group 2
 ]
 
 
@@ -593,6 +597,8 @@ def test_attention_random_configurations_against_oracle():
     (3, 64, 8, 128, [4096, 33, 1000], 3),                    # 70B shape, split-K
     (4, 8, 2, 64, [128, 129, 1, 77], 2),                     # head_dim 64
     (2, 12, 4, 128, [50, 310], 0),                           # group 3
+    (40, 32, 8, 128, [1 + (61 * i) % 512 for i in range(40)], 1),   # 320 short items: one per warp
+    (75, 32, 4, 128, [1 + (16 * i) % 241 for i in range(75)], 2),   # 600 items with split-K, contexts on block edges
 ])
 def test_fused_rope_append_attention_equals_the_separate_kernels(dtype, B, Hq, Hkv, D, ctx, splits):
     bs = 16
